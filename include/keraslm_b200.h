@@ -1,0 +1,146 @@
+/*
+ * keraslm_b200.h -- C ABI of libkeraslm_b200.so: the sm_100a device side of the
+ * ocrd_keraslm LSTM rating path.
+ *
+ * The reference (OCR-D/ocrd_keraslm) has no FFI of its own for this path: everything
+ * below `ocrd_keraslm.lib.Rater` is Keras 2.3 / TensorFlow 1.15 calls.  Every entry
+ * point here therefore cites the reference *call site* it replaces
+ * (file:line in /root/reference/ocrd_keraslm/lib/rating.py unless noted).
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative KLM_E* code otherwise;
+ *     klm_last_error() gives the message of the last failure on the calling thread.
+ *   - no exceptions, no torch types: plain pointers and sizes.
+ *   - `mem` says where the caller's index/score buffers live: KLM_MEM_HOST (the
+ *     library stages them through its own device scratch, H2D/D2H on the model's
+ *     stream, and returns after the results are in the host buffer) or
+ *     KLM_MEM_DEVICE (pointers are device pointers on the model's device; the call
+ *     only enqueues work on the model's stream).
+ *   - a model handle is not re-entrant (one Rater <-> one device <-> one stream,
+ *     like the reference: wrapper/rate.py:65 `max_workers = 1`).
+ *   - LSTM states live in a device-resident pool of `slots`; one slot holds
+ *     [depth][2][width] float32 = h1,c1,h2,c2,... (order of rating.py:137-142,622-629).
+ */
+#ifndef KERASLM_B200_H
+#define KERASLM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KLM_MAX_CTX    4
+#define KLM_MAX_DEPTH  8
+
+#define KLM_OK          0
+#define KLM_EINVAL     -1   /* bad argument (shape, index out of range, NULL) */
+#define KLM_ECUDA      -2   /* CUDA runtime failure, message has the CUDA error string */
+#define KLM_ENOMEM     -3
+#define KLM_ESTATE     -4   /* slot out of range / pool not allocated */
+
+#define KLM_MEM_HOST    0
+#define KLM_MEM_DEVICE  1
+
+typedef struct klm_model klm_model;
+
+/* Shape of the network that Rater.configure builds (rating.py:61-179). */
+typedef struct klm_config {
+    int32_t width;                  /* LSTM units per layer = char embedding dim (:103-106) */
+    int32_t depth;                  /* number of LSTM layers (:126) */
+    int32_t voc_size;               /* rows of the char embedding = output classes (:104,:163) */
+    int32_t n_ctx;                  /* number of context variables (reference: 1, :110-114) */
+    int32_t ctx_rows[KLM_MAX_CTX];  /* rows of each context embedding (reference: 200) */
+    int32_t ctx_dim[KLM_MAX_CTX];   /* columns of each context embedding (reference: 10) */
+} klm_config;
+
+/*
+ * Replaces Rater.configure + Rater.load_weights (rating.py:61-179, :966-974): uploads the
+ * float32 weights (host pointers, Keras layouts) and prepares the device-resident
+ * forms.  `weights` holds 1 + n_ctx + 3*depth pointers in this order:
+ *   E [voc_size, width], C_1 [ctx_rows, ctx_dim] ... C_nctx,
+ *   then per layer l: kernel [D_l, 4*width], recurrent_kernel [width, 4*width], bias [4*width]
+ *   (gate order i|f|c|o; D_1 = width + sum ctx_dim, D_l>1 = width).
+ */
+int klm_create(const klm_config *cfg, const float *const *weights, int device, klm_model **out);
+int klm_destroy(klm_model *m);
+
+/* Message of the last failure on this thread ("" if none). */
+const char *klm_last_error(void);
+
+/* Run subsequent work on this CUDA stream (a cudaStream_t; NULL = the library's own stream). */
+int klm_set_stream(klm_model *m, void *cuda_stream);
+/* Block until everything enqueued on the model's stream has finished. */
+int klm_sync(klm_model *m);
+
+/*
+ * State pool.  Replaces the Keras backend variables of the stateful LSTM layers
+ * (rating.py:90-92,127-145) and the numpy state lists that Rater.predict passes
+ * around (:622-638).  New slots are zero (= model.reset_states(), :475,:555).
+ */
+int klm_state_pool_resize(klm_model *m, int32_t n_slots);
+int klm_state_reset(klm_model *m, const int32_t *slots, int32_t n);                      /* host ints */
+int klm_state_copy(klm_model *m, const int32_t *src, const int32_t *dst, int32_t n);     /* host ints */
+int klm_state_to_host(klm_model *m, const int32_t *slots, int32_t n, float *out);        /* [n][2*depth][width] */
+int klm_state_from_host(klm_model *m, const int32_t *slots, int32_t n, const float *in);
+/* L2 distances |state_a[k] - state_b[k]| for the first `n_arrays` arrays of the h1,c1,h2,..
+ * list (rating.py:887-916 compares range(depth) of them); out [n][n_arrays] host floats. */
+int klm_state_l2_distance(klm_model *m, const int32_t *a, const int32_t *b, int32_t n,
+                          int32_t n_arrays, float *out);
+
+/*
+ * Teacher-forced rating of n_streams independent character streams in ONE launch.
+ * Replaces model.predict_generator over the windows of Rater._gen_data (rating.py:516,
+ * :1005-1102) plus the target pick of Rater.rate (:520-528), and the per-character
+ * predict_on_batch loop of Rater.rate2 (:555-575).
+ *
+ *   slots    [n]      host ints: state slot of each stream; state is read at the start and
+ *                     written back at the end (stateful carry, no reset: :493-529)
+ *   offsets  [n+1]    stream s owns positions offsets[s] .. offsets[s+1]-1 of chars/targets/out
+ *   chars    [total]  input character index per position (0 = unmapped / padding, :1133-1135)
+ *   targets  [total]  index whose score is wanted at that position (next character, :522-526)
+ *   n_real   [n]      positions >= n_real[s] are window padding: the context index is 0 there
+ *                     (:1141-1143); NULL = all positions real
+ *   ctx      [n][n_ctx] context indices per stream (time-constant, :1142)
+ *   out_logp [total]  natural-log probability of targets[] at each position (float32)
+ * offsets is int64, the others int32; all five live where `mem` says.
+ */
+int klm_rate(klm_model *m, int32_t n_streams, const int32_t *slots, const int64_t *offsets,
+             const int32_t *chars, const int32_t *targets, const int32_t *n_real,
+             const int32_t *ctx, float *out_logp, int mem);
+
+/*
+ * One timestep for n hypotheses with explicit state passing.  Replaces
+ * model.predict_on_batch in Rater.predict (rating.py:631) incl. the vstack/slicing
+ * of states around it (:625-638).
+ *
+ *   chars     [n]        input character index per hypothesis
+ *   ctx       [n][n_ctx] context indices
+ *   slots_in  [n]        host ints; -1 = zero state (None in the reference, :625-627)
+ *   slots_out [n]        host ints; distinct; where the new state goes (may equal slots_in[i])
+ *   targets   [n] or NULL
+ *   out       targets != NULL: [n] natural-log probability of targets[i]
+ *             targets == NULL: [n][voc_size] full softmax rows (what predict returns, :632)
+ * chars, ctx, targets, out live where `mem` says.
+ */
+int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx,
+             const int32_t *slots_in, const int32_t *slots_out, const int32_t *targets,
+             float *out, int mem);
+
+/* Introspection for bench.py / tests. */
+typedef struct klm_info {
+    int32_t sm_count;
+    int32_t grid;               /* CTAs of the persistent kernel */
+    int32_t weights_in_smem;    /* 1 if every CTA keeps its weight slice in shared memory */
+    int32_t smem_bytes;         /* dynamic shared memory per CTA */
+    int64_t kernel_launches;    /* kernels of this library launched so far on this model */
+    double  last_kernel_ms;     /* device time of the last klm_rate/klm_step main kernel (CUDA events) */
+    int32_t max_streams;        /* largest n one launch takes; larger calls are split */
+    int32_t reserved;
+} klm_info;
+int klm_get_info(klm_model *m, klm_info *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KERASLM_B200_H */

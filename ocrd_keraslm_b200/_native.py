@@ -1,0 +1,226 @@
+"""ctypes binding of libkeraslm_b200.so (include/keraslm_b200.h) and its in-tree build.
+
+There is no CPU fallback: if the library cannot be loaded or no CUDA device is present the
+product raises, it never routes through another implementation.
+"""
+import ctypes
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, 'csrc')
+LIB_PATH = os.path.join(HERE, 'libkeraslm_b200.so')
+SOURCES = ['klm_api.cu', 'klm_seq_fma.cu']
+NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
+              '-shared', '-Xcompiler', '-fPIC']
+
+KLM_MAX_CTX = 4
+MEM_HOST, MEM_DEVICE = 0, 1
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _sources():
+    out = [os.path.join(CSRC, s) for s in SOURCES]
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(('.cuh', '.h'))]
+    hdrs.append(os.path.join(os.path.dirname(HERE), 'include', 'keraslm_b200.h'))
+    return out, hdrs
+
+
+def needs_build():
+    if not os.path.exists(LIB_PATH):
+        return True
+    srcs, hdrs = _sources()
+    t = os.path.getmtime(LIB_PATH)
+    return any(os.path.getmtime(f) > t for f in srcs + hdrs)
+
+
+def build(force=False, verbose=False):
+    """Compile the CUDA sources for sm_100a into ocrd_keraslm_b200/libkeraslm_b200.so (in-tree)."""
+    if not force and not needs_build():
+        return LIB_PATH
+    nvcc = os.environ.get('NVCC') or '/usr/local/cuda/bin/nvcc'
+    if not os.path.exists(nvcc):
+        nvcc = 'nvcc'
+    srcs, _ = _sources()
+    cmd = [nvcc] + NVCC_FLAGS + ['-o', LIB_PATH] + srcs
+    if verbose:
+        print(' '.join(cmd), file=sys.stderr)
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, universal_newlines=True)
+    if res.returncode != 0:
+        raise NativeError('nvcc failed:\n' + res.stdout)
+    return LIB_PATH
+
+
+class KlmConfig(ctypes.Structure):
+    _fields_ = [('width', ctypes.c_int32), ('depth', ctypes.c_int32), ('voc_size', ctypes.c_int32),
+                ('n_ctx', ctypes.c_int32), ('ctx_rows', ctypes.c_int32 * KLM_MAX_CTX),
+                ('ctx_dim', ctypes.c_int32 * KLM_MAX_CTX)]
+
+
+class KlmInfo(ctypes.Structure):
+    _fields_ = [('sm_count', ctypes.c_int32), ('grid', ctypes.c_int32), ('weights_in_smem', ctypes.c_int32),
+                ('smem_bytes', ctypes.c_int32), ('kernel_launches', ctypes.c_int64),
+                ('last_kernel_ms', ctypes.c_double), ('max_streams', ctypes.c_int32), ('reserved', ctypes.c_int32)]
+
+
+# every symbol include/keraslm_b200.h declares: (name, restype, argtypes)
+_P = ctypes.c_void_p
+_I = ctypes.c_int32
+SYMBOLS = [
+    ('klm_create', ctypes.c_int, [ctypes.POINTER(KlmConfig), ctypes.POINTER(_P), ctypes.c_int, ctypes.POINTER(_P)]),
+    ('klm_destroy', ctypes.c_int, [_P]),
+    ('klm_last_error', ctypes.c_char_p, []),
+    ('klm_set_stream', ctypes.c_int, [_P, _P]),
+    ('klm_sync', ctypes.c_int, [_P]),
+    ('klm_state_pool_resize', ctypes.c_int, [_P, _I]),
+    ('klm_state_reset', ctypes.c_int, [_P, _P, _I]),
+    ('klm_state_copy', ctypes.c_int, [_P, _P, _P, _I]),
+    ('klm_state_to_host', ctypes.c_int, [_P, _P, _I, _P]),
+    ('klm_state_from_host', ctypes.c_int, [_P, _P, _I, _P]),
+    ('klm_state_l2_distance', ctypes.c_int, [_P, _P, _P, _I, _I, _P]),
+    ('klm_rate', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
+    ('klm_step', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
+    ('klm_get_info', ctypes.c_int, [_P, ctypes.POINTER(KlmInfo)]),
+]
+
+_lib = None
+
+
+def load():
+    """dlopen the library (building it first if the sources are newer) and bind all symbols."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if needs_build():
+        build()
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, res, args in SYMBOLS:
+        fn = getattr(lib, name)          # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    """Host numpy array / int address / None -> void pointer value."""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        assert a.flags['C_CONTIGUOUS']
+        return a.ctypes.data
+    return int(a)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+class Model(object):
+    """Owner of one klm_model handle."""
+
+    def __init__(self, width, depth, voc_size, ctx_shapes, weights, device=0):
+        lib = load()
+        cfg = KlmConfig()
+        cfg.width, cfg.depth, cfg.voc_size, cfg.n_ctx = width, depth, voc_size, len(ctx_shapes)
+        if len(ctx_shapes) > KLM_MAX_CTX:
+            raise ValueError('at most %d context variables are supported' % KLM_MAX_CTX)
+        for k, (rows, dim) in enumerate(ctx_shapes):
+            cfg.ctx_rows[k], cfg.ctx_dim[k] = rows, dim
+        self._keep = [np.ascontiguousarray(w, dtype=np.float32) for w in weights]
+        assert len(self._keep) == 1 + len(ctx_shapes) + 3 * depth
+        arr = (_P * len(self._keep))(*[w.ctypes.data for w in self._keep])
+        handle = _P()
+        self._lib = lib
+        self._h = None
+        self.check(lib.klm_create(ctypes.byref(cfg), arr, device, ctypes.byref(handle)))
+        self._h = handle
+        self._keep = None
+        self.width, self.depth, self.voc_size, self.n_ctx = width, depth, voc_size, len(ctx_shapes)
+        self.device = device
+        self.n_slots = 0
+
+    def check(self, rc):
+        if rc != 0:
+            msg = self._lib.klm_last_error().decode('utf-8', 'replace')
+            if rc == -1:
+                raise ValueError(msg)
+            raise NativeError('libkeraslm_b200 error %d: %s' % (rc, msg))
+
+    def close(self):
+        if self._h is not None:
+            self._lib.klm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream):
+        self.check(self._lib.klm_set_stream(self._h, _P(cuda_stream) if cuda_stream else None))
+
+    def sync(self):
+        self.check(self._lib.klm_sync(self._h))
+
+    def info(self):
+        inf = KlmInfo()
+        self.check(self._lib.klm_get_info(self._h, ctypes.byref(inf)))
+        return dict((f, getattr(inf, f)) for f, _ in KlmInfo._fields_)
+
+    # ---- state pool ----
+    def pool_resize(self, n):
+        if n > self.n_slots:
+            self.check(self._lib.klm_state_pool_resize(self._h, n))
+            self.n_slots = n
+
+    def state_reset(self, slots):
+        s = _i32(slots)
+        self.check(self._lib.klm_state_reset(self._h, _ptr(s), len(s)))
+
+    def state_copy(self, src, dst):
+        a, b = _i32(src), _i32(dst)
+        assert len(a) == len(b)
+        self.check(self._lib.klm_state_copy(self._h, _ptr(a), _ptr(b), len(a)))
+
+    def state_to_host(self, slots):
+        s = _i32(slots)
+        out = np.empty((len(s), 2 * self.depth, self.width), dtype=np.float32)
+        self.check(self._lib.klm_state_to_host(self._h, _ptr(s), len(s), _ptr(out)))
+        return out
+
+    def state_from_host(self, slots, values):
+        s = _i32(slots)
+        v = np.ascontiguousarray(values, dtype=np.float32).reshape(len(s), 2 * self.depth, self.width)
+        self.check(self._lib.klm_state_from_host(self._h, _ptr(s), len(s), _ptr(v)))
+
+    def state_l2_distance(self, a, b, n_arrays):
+        a, b = _i32(a), _i32(b)
+        out = np.empty((len(a), n_arrays), dtype=np.float32)
+        self.check(self._lib.klm_state_l2_distance(self._h, _ptr(a), _ptr(b), len(a), n_arrays, _ptr(out)))
+        return out
+
+    # ---- the path ----
+    def rate(self, slots, offsets, chars, targets, n_real, ctx, out, mem=MEM_HOST):
+        """See klm_rate.  chars/targets/out: numpy arrays (MEM_HOST) or device addresses (MEM_DEVICE)."""
+        slots = _i32(slots)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        n_real = None if n_real is None else _i32(n_real)
+        ctx = None if ctx is None else _i32(ctx)
+        self.check(self._lib.klm_rate(self._h, len(slots), _ptr(slots), _ptr(offsets), _ptr(chars), _ptr(targets),
+                                      _ptr(n_real), _ptr(ctx), _ptr(out), mem))
+
+    def step(self, chars, ctx, slots_in, slots_out, targets, out, mem=MEM_HOST):
+        chars = _i32(chars)
+        ctx = None if ctx is None else _i32(ctx)
+        si, so = _i32(slots_in), _i32(slots_out)
+        targets = None if targets is None else _i32(targets)
+        self.check(self._lib.klm_step(self._h, len(chars), _ptr(chars), _ptr(ctx), _ptr(si), _ptr(so), _ptr(targets),
+                                      _ptr(out), mem))

@@ -1,0 +1,665 @@
+// Host side of libkeraslm_b200.so: the C ABI declared in include/keraslm_b200.h.
+// Model preparation (weight packing, pre-contracted embedding tables), launch planning,
+// the device state pool and the two entry points of the rating path (klm_rate, klm_step).
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "klm_common.cuh"
+
+cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cudaStream_t stream);
+
+// ------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CK(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess)                                                                \
+            return fail(KLM_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),    \
+                        __FILE__, __LINE__);                                                  \
+    } while (0)
+
+extern "C" const char *klm_last_error(void) { return g_err.c_str(); }
+
+// ------------------------------------------------------------------------------------------
+struct KlmPlan {
+    std::vector<KlmRole> roles;
+    KlmRole *d_roles = nullptr;
+    int grid = 0;
+    int wsmem = 0;
+    int stage_floats = 0;
+    size_t smem = 0;
+    int max_streams = 0;
+};
+
+#define KLM_RING 4
+struct klm_model {
+    int device = 0;
+    klm_config cfg{};
+    int W = 0, D = 0, V = 0, V4 = 0, Nc = 0;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    // device-resident model
+    float4 *P = nullptr, *Q[KLM_MAX_CTX] = {}, *Wl[KLM_MAX_DEPTH] = {}, *bias[KLM_MAX_DEPTH] = {}, *Ep = nullptr;
+    // plans
+    KlmPlan plan_k, plan_b;
+    // scratch
+    float *hbuf = nullptr, *logits = nullptr;
+    unsigned int *barrier = nullptr;
+    int bp_cap = 0;
+    // state pool
+    float *state = nullptr;
+    int n_slots = 0;
+    // per-launch small arrays (pinned ring + device copy)
+    char *h_ring[KLM_RING] = {}, *d_ring[KLM_RING] = {};
+    cudaEvent_t ring_ev[KLM_RING] = {};
+    size_t ring_bytes = 0;
+    int ring_pos = 0;
+    // staging for KLM_MEM_HOST position arrays
+    int *d_chars = nullptr, *d_targets = nullptr;
+    float *d_out = nullptr;
+    size_t cap_pos = 0, cap_out = 0;
+    // stats
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    long long launches = 0;
+};
+
+// ------------------------------------------------------------------------------------------
+// One-time table construction: P = E.K1[:W] + b1 and Q_k = C_k.K1[W+off_k:...], accumulated in
+// double so that the tables are correctly rounded float32 values of the exact contraction.
+__global__ void klm_prep_table(const float *__restrict__ A /*[rows][kdim]*/, const float *__restrict__ Kmat /*[.][4W]*/,
+                               const float *__restrict__ b /*[4W] or null*/, int rows, int kdim, int krow0, int W,
+                               float4 *__restrict__ out /*[rows][W]*/) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)rows * W) return;
+    const int u = (int)(idx % W), r = (int)(idx / W);
+    double acc[4] = {0, 0, 0, 0};
+    for (int k = 0; k < kdim; ++k) {
+        const double a = A[(size_t)r * kdim + k];
+        const float *kr = Kmat + (size_t)(krow0 + k) * 4 * W;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) acc[g] += a * (double)kr[g * W + u];
+    }
+    if (b) for (int g = 0; g < 4; ++g) acc[g] += (double)b[g * W + u];
+    out[idx] = make_float4((float)acc[0], (float)acc[1], (float)acc[2], (float)acc[3]);
+}
+
+__global__ void klm_state_zero(float *state, const int *slots, int n, int stride) {
+    const int s = blockIdx.x;
+    if (s >= n) return;
+    float *dst = state + (size_t)slots[s] * stride;
+    for (int i = threadIdx.x; i < stride; i += blockDim.x) dst[i] = 0.f;
+}
+__global__ void klm_state_move(float *state, const int *src, const int *dst, int n, int stride) {
+    const int s = blockIdx.x;
+    if (s >= n || src[s] == dst[s]) return;
+    const float *a = state + (size_t)src[s] * stride;
+    float *d = state + (size_t)dst[s] * stride;
+    for (int i = threadIdx.x; i < stride; i += blockDim.x) d[i] = a[i];
+}
+__global__ void klm_state_gather(const float *state, const int *slots, int n, int stride, float *out, int to_pool) {
+    const int s = blockIdx.x;
+    if (s >= n) return;
+    float *pool = const_cast<float *>(state) + (size_t)slots[s] * stride;
+    float *lin = out + (size_t)s * stride;
+    for (int i = threadIdx.x; i < stride; i += blockDim.x) {
+        if (to_pool) pool[i] = lin[i]; else lin[i] = pool[i];
+    }
+}
+__global__ void klm_state_dist(const float *state, const int *a, const int *b, int n, int n_arrays, int W, int stride,
+                               float *out) {
+    const int s = blockIdx.x / n_arrays, k = blockIdx.x % n_arrays;
+    if (s >= n) return;
+    const float *x = state + (size_t)a[s] * stride + (size_t)k * W;
+    const float *y = state + (size_t)b[s] * stride + (size_t)k * W;
+    float acc = 0.f;
+    for (int i = threadIdx.x; i < W; i += blockDim.x) { const float d = x[i] - y[i]; acc = fmaf(d, d, acc); }
+    __shared__ float red[32];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int i = 0; i < (int)(blockDim.x + 31) / 32; ++i) t += red[i];
+        out[s * n_arrays + k] = sqrtf(t);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Launch plan: which CTA owns which slice of which stage (see klm_seq_fma.cu).
+static int make_plan(klm_model *m, bool kpar, KlmPlan *pl) {
+    const int W = m->W, D = m->D;
+    struct Seg { int kind, layer, items, K, n; };
+    std::vector<Seg> segs;
+    for (int l = 0; l < D; ++l) segs.push_back({KLM_ROLE_LSTM, l, W, l ? 2 * W : W, 1});
+    segs.push_back({KLM_ROLE_PROJ, 0, m->V4 / 4, W, 1});
+    const int avail = m->sm_count - 1;                       // one CTA for the LSE stage
+    if (avail < (int)segs.size()) return fail(KLM_EINVAL, "device has too few SMs (%d)", m->sm_count);
+    pl->stage_floats = kpar ? std::max(8192, KLM_MODEK_MAXB * 2 * W) : 8192;
+    const size_t stage_bytes = (size_t)pl->stage_floats * 4;
+    if (stage_bytes + 1024 > m->smem_optin) return fail(KLM_EINVAL, "width %d too large for shared staging", W);
+    const size_t budget = m->smem_optin - stage_bytes;
+    double total_cost = 0; size_t total_bytes = 0; int total_items = 0;
+    for (auto &s : segs) { total_cost += (double)s.items * s.K; total_bytes += (size_t)s.items * s.K * 16; total_items += s.items; }
+    int n_target = avail;
+    if (kpar) {
+        const int by_smem = (int)((total_bytes + budget - 1) / budget) + (int)segs.size();
+        const int by_warp = (total_items + KLM_WARPS - 1) / KLM_WARPS;
+        n_target = std::min(avail, std::max(std::max(by_smem, by_warp), (int)segs.size()));
+    }
+    for (;;) {
+        for (auto &s : segs) s.n = 1;
+        int used = (int)segs.size();
+        while (used < n_target) {                            // greedy: relieve the most loaded stage
+            int best = -1; double load = -1;
+            for (int i = 0; i < (int)segs.size(); ++i) {
+                if (segs[i].n >= segs[i].items) continue;
+                const double ld = std::ceil((double)segs[i].items / segs[i].n) * segs[i].K;
+                if (ld > load) { load = ld; best = i; }
+            }
+            if (best < 0) break;
+            segs[best].n++; used++;
+        }
+        bool fits = true;
+        for (auto &s : segs) {
+            const int per = (s.items + s.n - 1) / s.n;
+            if ((size_t)per * s.K * 16 > budget) fits = false;
+        }
+        if (fits) { pl->wsmem = 1; break; }
+        if (n_target < avail) { n_target++; continue; }
+        pl->wsmem = 0; break;
+    }
+    pl->roles.clear();
+    int per_max = 1; size_t wbytes_max = 0;
+    for (auto &s : segs) {
+        const int per = (s.items + s.n - 1) / s.n;
+        for (int first = 0; first < s.items; first += per) {
+            KlmRole r = {s.kind, s.layer, first, std::min(per, s.items - first)};
+            pl->roles.push_back(r);
+        }
+        per_max = std::max(per_max, per);
+        wbytes_max = std::max(wbytes_max, (size_t)per * s.K * 16);
+    }
+    pl->roles.push_back({KLM_ROLE_LSE, 0, 0, 0});
+    pl->grid = (int)pl->roles.size();
+    pl->smem = stage_bytes + (pl->wsmem ? wbytes_max : 0);
+    if (kpar) {
+        if (per_max > KLM_WARPS * KLM_MAX_UNITS_K) return fail(KLM_EINVAL, "model too large for the K-parallel plan");
+        pl->max_streams = KLM_MODEK_MAXB;
+    } else {
+        const int nsg = (KLM_WARPS * KLM_MAX_ITEMS) / per_max;
+        if (nsg < 1) return fail(KLM_EINVAL, "model too large for the stream-parallel plan");
+        pl->max_streams = std::min(256, 32 * nsg);
+    }
+    CK(cudaMalloc(&pl->d_roles, pl->roles.size() * sizeof(KlmRole)));
+    CK(cudaMemcpy(pl->d_roles, pl->roles.data(), pl->roles.size() * sizeof(KlmRole), cudaMemcpyHostToDevice));
+    return KLM_OK;
+}
+
+template <typename T> static int upload(T **dst, const std::vector<T> &src) {
+    CK(cudaMalloc(dst, src.size() * sizeof(T)));
+    CK(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return KLM_OK;
+}
+
+extern "C" int klm_destroy(klm_model *m) {
+    if (!m) return KLM_OK;
+    cudaSetDevice(m->device);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    cudaFree(m->P); cudaFree(m->Ep);
+    for (int i = 0; i < KLM_MAX_CTX; ++i) cudaFree(m->Q[i]);
+    for (int i = 0; i < KLM_MAX_DEPTH; ++i) { cudaFree(m->Wl[i]); cudaFree(m->bias[i]); }
+    cudaFree(m->plan_k.d_roles); cudaFree(m->plan_b.d_roles);
+    cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
+    for (int i = 0; i < KLM_RING; ++i) {
+        if (m->h_ring[i]) cudaFreeHost(m->h_ring[i]);
+        cudaFree(m->d_ring[i]);
+        if (m->ring_ev[i]) cudaEventDestroy(m->ring_ev[i]);
+    }
+    cudaFree(m->d_chars); cudaFree(m->d_targets); cudaFree(m->d_out);
+    if (m->ev0) cudaEventDestroy(m->ev0);
+    if (m->ev1) cudaEventDestroy(m->ev1);
+    if (m->own_stream) cudaStreamDestroy(m->own_stream);
+    delete m;
+    return KLM_OK;
+}
+
+extern "C" int klm_create(const klm_config *cfg, const float *const *weights, int device, klm_model **out) {
+    if (!cfg || !weights || !out) return fail(KLM_EINVAL, "klm_create: NULL argument");
+    if (cfg->width < 4 || cfg->width % 4 || cfg->depth < 1 || cfg->depth > KLM_MAX_DEPTH || cfg->voc_size < 2 ||
+        cfg->n_ctx < 0 || cfg->n_ctx > KLM_MAX_CTX)
+        return fail(KLM_EINVAL, "klm_create: unsupported shape width=%d depth=%d voc=%d n_ctx=%d (width must be a "
+                    "multiple of 4, depth <= %d, n_ctx <= %d)", cfg->width, cfg->depth, cfg->voc_size, cfg->n_ctx,
+                    KLM_MAX_DEPTH, KLM_MAX_CTX);
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(KLM_EINVAL, "klm_create: no CUDA device %d (have %d)", device, ndev);
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(KLM_EINVAL, "klm_create: device %d is sm_%d%d; this library is built for sm_100a only",
+                                     device, prop.major, prop.minor);
+    klm_model *m = new klm_model();
+    m->device = device; m->cfg = *cfg;
+    const int W = m->W = cfg->width, D = m->D = cfg->depth, V = m->V = cfg->voc_size, Nc = m->Nc = cfg->n_ctx;
+    m->V4 = (V + 3) / 4 * 4;
+    m->sm_count = prop.multiProcessorCount;
+    m->smem_optin = prop.sharedMemPerBlockOptin;
+    int rc = KLM_OK;
+#define TRY(x) do { rc = (x); if (rc != KLM_OK) { klm_destroy(m); return rc; } } while (0)
+#define TRYC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { rc = fail(KLM_ECUDA, "%s failed: %s", #call, \
+                        cudaGetErrorString(e_)); klm_destroy(m); return rc; } } while (0)
+    TRYC(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
+    m->stream = m->own_stream;
+    TRYC(cudaEventCreate(&m->ev0)); TRYC(cudaEventCreate(&m->ev1));
+
+    int ctx_total = 0;
+    for (int k = 0; k < Nc; ++k) {
+        if (cfg->ctx_rows[k] < 1 || cfg->ctx_dim[k] < 1) { klm_destroy(m); return fail(KLM_EINVAL, "bad context table %d", k); }
+        ctx_total += cfg->ctx_dim[k];
+    }
+    const float *E = weights[0];
+    const float *const *C = weights + 1;
+    const float *const *L = weights + 1 + Nc;              // K_l, R_l, b_l triples
+    const int D1 = W + ctx_total;
+
+    // ---- raw uploads needed by the table kernels ----
+    float *dE = nullptr, *dK1 = nullptr, *db1 = nullptr;
+    TRYC(cudaMalloc(&dE, (size_t)V * W * 4));  TRYC(cudaMemcpy(dE, E, (size_t)V * W * 4, cudaMemcpyHostToDevice));
+    TRYC(cudaMalloc(&dK1, (size_t)D1 * 4 * W * 4)); TRYC(cudaMemcpy(dK1, L[0], (size_t)D1 * 4 * W * 4, cudaMemcpyHostToDevice));
+    TRYC(cudaMalloc(&db1, (size_t)4 * W * 4)); TRYC(cudaMemcpy(db1, L[2], (size_t)4 * W * 4, cudaMemcpyHostToDevice));
+    TRYC(cudaMalloc(&m->P, (size_t)V * W * 16));
+    {
+        const long long n = (long long)V * W;
+        klm_prep_table<<<(unsigned)((n + 255) / 256), 256, 0, m->stream>>>(dE, dK1, db1, V, W, 0, W, m->P);
+        m->launches++;
+    }
+    int off = W;
+    for (int k = 0; k < Nc; ++k) {
+        float *dC = nullptr;
+        const size_t nb = (size_t)cfg->ctx_rows[k] * cfg->ctx_dim[k] * 4;
+        TRYC(cudaMalloc(&dC, nb)); TRYC(cudaMemcpy(dC, C[k], nb, cudaMemcpyHostToDevice));
+        TRYC(cudaMalloc(&m->Q[k], (size_t)cfg->ctx_rows[k] * W * 16));
+        const long long n = (long long)cfg->ctx_rows[k] * W;
+        klm_prep_table<<<(unsigned)((n + 255) / 256), 256, 0, m->stream>>>(dC, dK1, nullptr, cfg->ctx_rows[k],
+                                                                            cfg->ctx_dim[k], off, W, m->Q[k]);
+        m->launches++;
+        TRYC(cudaStreamSynchronize(m->stream));
+        cudaFree(dC);
+        off += cfg->ctx_dim[k];
+    }
+    TRYC(cudaStreamSynchronize(m->stream));
+    cudaFree(dE); cudaFree(dK1); cudaFree(db1);
+
+    // ---- packed recurrent / input weights: Wl[l][u][k] = (w_i, w_f, w_g, w_o) ----
+    for (int l = 0; l < D; ++l) {
+        const float *Kl = L[3 * l], *Rl = L[3 * l + 1], *bl = L[3 * l + 2];
+        const int Kdim = l ? 2 * W : W;
+        std::vector<float4> pk((size_t)W * Kdim);
+        for (int u = 0; u < W; ++u)
+            for (int k = 0; k < Kdim; ++k) {
+                const float *row = (l && k < W) ? Kl + (size_t)k * 4 * W : Rl + (size_t)(l ? k - W : k) * 4 * W;
+                pk[(size_t)u * Kdim + k] = make_float4(row[u], row[W + u], row[2 * W + u], row[3 * W + u]);
+            }
+        TRY(upload(&m->Wl[l], pk));
+        std::vector<float4> bb(W);
+        for (int u = 0; u < W; ++u) bb[u] = make_float4(bl[u], bl[W + u], bl[2 * W + u], bl[3 * W + u]);
+        TRY(upload(&m->bias[l], bb));
+    }
+    {
+        std::vector<float4> pe((size_t)(m->V4 / 4) * W);
+        for (int g = 0; g < m->V4 / 4; ++g)
+            for (int k = 0; k < W; ++k) {
+                float v[4];
+                for (int j = 0; j < 4; ++j) v[j] = (4 * g + j < V) ? E[(size_t)(4 * g + j) * W + k] : 0.f;
+                pe[(size_t)g * W + k] = make_float4(v[0], v[1], v[2], v[3]);
+            }
+        TRY(upload(&m->Ep, pe));
+    }
+    TRY(make_plan(m, true, &m->plan_k));
+    TRY(make_plan(m, false, &m->plan_b));
+
+    m->bp_cap = std::max(32, m->plan_b.max_streams);
+    TRYC(cudaMalloc(&m->hbuf, (size_t)D * 2 * W * m->bp_cap * 4));
+    TRYC(cudaMemset(m->hbuf, 0, (size_t)D * 2 * W * m->bp_cap * 4));
+    TRYC(cudaMalloc(&m->logits, (size_t)2 * m->V4 * m->bp_cap * 4));
+    TRYC(cudaMemset(m->logits, 0, (size_t)2 * m->V4 * m->bp_cap * 4));
+    TRYC(cudaMalloc(&m->barrier, 256));
+    m->ring_bytes = (size_t)m->bp_cap * (4 * 4 + 8 + 4 * KLM_MAX_CTX) + 64;
+    m->ring_bytes = std::max(m->ring_bytes, (size_t)1 << 16);
+    for (int i = 0; i < KLM_RING; ++i) {
+        TRYC(cudaMallocHost(&m->h_ring[i], m->ring_bytes));
+        TRYC(cudaMalloc(&m->d_ring[i], m->ring_bytes));
+        TRYC(cudaEventCreateWithFlags(&m->ring_ev[i], cudaEventDisableTiming));
+    }
+    *out = m;
+    return KLM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+extern "C" int klm_set_stream(klm_model *m, void *s) {
+    if (!m) return fail(KLM_EINVAL, "NULL model");
+    m->stream = s ? (cudaStream_t)s : m->own_stream;
+    return KLM_OK;
+}
+extern "C" int klm_sync(klm_model *m) {
+    if (!m) return fail(KLM_EINVAL, "NULL model");
+    CK(cudaSetDevice(m->device));
+    CK(cudaStreamSynchronize(m->stream));
+    return KLM_OK;
+}
+
+// Small per-call arrays travel through a ring of pinned buffers: one H2D copy per call.
+struct RingSlot { char *h, *d; int idx; size_t used; };
+static int ring_acquire(klm_model *m, RingSlot *rs, size_t need) {
+    if (need > m->ring_bytes) return fail(KLM_EINVAL, "per-call arrays too large (%zu bytes)", need);
+    rs->idx = m->ring_pos; m->ring_pos = (m->ring_pos + 1) % KLM_RING;
+    CK(cudaEventSynchronize(m->ring_ev[rs->idx]));
+    rs->h = m->h_ring[rs->idx]; rs->d = m->d_ring[rs->idx]; rs->used = 0;
+    return KLM_OK;
+}
+template <typename T> static T *ring_put(RingSlot *rs, const T *src, size_t n, T **dev) {
+    rs->used = (rs->used + 15) & ~(size_t)15;
+    T *h = reinterpret_cast<T *>(rs->h + rs->used);
+    if (src) memcpy(h, src, n * sizeof(T));
+    *dev = reinterpret_cast<T *>(rs->d + rs->used);
+    rs->used += n * sizeof(T);
+    return h;
+}
+static int ring_commit(klm_model *m, RingSlot *rs) {
+    CK(cudaMemcpyAsync(rs->d, rs->h, rs->used, cudaMemcpyHostToDevice, m->stream));
+    CK(cudaEventRecord(m->ring_ev[rs->idx], m->stream));
+    return KLM_OK;
+}
+
+static int check_slots(klm_model *m, const int32_t *slots, int n, bool allow_none, const char *what) {
+    if (!slots) return fail(KLM_EINVAL, "%s: NULL slot array", what);
+    for (int i = 0; i < n; ++i)
+        if (slots[i] >= m->n_slots || slots[i] < (allow_none ? -1 : 0))
+            return fail(KLM_ESTATE, "%s: slot %d out of range (pool has %d)", what, slots[i], m->n_slots);
+    return KLM_OK;
+}
+
+extern "C" int klm_state_pool_resize(klm_model *m, int32_t n_slots) {
+    if (!m || n_slots < 0) return fail(KLM_EINVAL, "klm_state_pool_resize: bad argument");
+    CK(cudaSetDevice(m->device));
+    if (n_slots <= m->n_slots) return KLM_OK;                // never shrinks: handles stay valid
+    const size_t stride = (size_t)m->D * 2 * m->W * 4;
+    float *ns = nullptr;
+    CK(cudaMalloc(&ns, stride * n_slots));
+    CK(cudaStreamSynchronize(m->stream));
+    CK(cudaMemset(ns, 0, stride * n_slots));
+    if (m->state) { CK(cudaMemcpy(ns, m->state, stride * m->n_slots, cudaMemcpyDeviceToDevice)); cudaFree(m->state); }
+    m->state = ns; m->n_slots = n_slots;
+    return KLM_OK;
+}
+
+extern "C" int klm_state_reset(klm_model *m, const int32_t *slots, int32_t n) {
+    if (!m) return fail(KLM_EINVAL, "NULL model");
+    if (n <= 0) return KLM_OK;
+    CK(cudaSetDevice(m->device));
+    int rc = check_slots(m, slots, n, false, "klm_state_reset"); if (rc) return rc;
+    const int stride = m->D * 2 * m->W;
+    for (int i0 = 0; i0 < n; i0 += 4096) {
+        const int nb = std::min(4096, n - i0);
+        RingSlot rs; rc = ring_acquire(m, &rs, (size_t)nb * 4 + 64); if (rc) return rc;
+        int *d; ring_put(&rs, slots + i0, nb, &d);
+        rc = ring_commit(m, &rs); if (rc) return rc;
+        klm_state_zero<<<nb, 256, 0, m->stream>>>(m->state, d, nb, stride);
+        m->launches++;
+    }
+    CK(cudaGetLastError());
+    return KLM_OK;
+}
+
+extern "C" int klm_state_copy(klm_model *m, const int32_t *src, const int32_t *dst, int32_t n) {
+    if (!m) return fail(KLM_EINVAL, "NULL model");
+    if (n <= 0) return KLM_OK;
+    CK(cudaSetDevice(m->device));
+    int rc = check_slots(m, src, n, false, "klm_state_copy"); if (rc) return rc;
+    rc = check_slots(m, dst, n, false, "klm_state_copy"); if (rc) return rc;
+    const int stride = m->D * 2 * m->W;
+    for (int i0 = 0; i0 < n; i0 += 4096) {
+        const int nb = std::min(4096, n - i0);
+        RingSlot rs; rc = ring_acquire(m, &rs, (size_t)nb * 8 + 64); if (rc) return rc;
+        int *ds, *dd; ring_put(&rs, src + i0, nb, &ds); ring_put(&rs, dst + i0, nb, &dd);
+        rc = ring_commit(m, &rs); if (rc) return rc;
+        klm_state_move<<<nb, 256, 0, m->stream>>>(m->state, ds, dd, nb, stride);
+        m->launches++;
+    }
+    CK(cudaGetLastError());
+    return KLM_OK;
+}
+
+static int state_xfer(klm_model *m, const int32_t *slots, int n, float *host, int to_pool) {
+    if (!m || !host) return fail(KLM_EINVAL, "state transfer: NULL argument");
+    if (n <= 0) return KLM_OK;
+    CK(cudaSetDevice(m->device));
+    int rc = check_slots(m, slots, n, false, "state transfer"); if (rc) return rc;
+    const int stride = m->D * 2 * m->W;
+    float *lin = nullptr;
+    CK(cudaMalloc(&lin, (size_t)n * stride * 4));
+    int *dsl = nullptr;
+    CK(cudaMalloc(&dsl, (size_t)n * 4));
+    CK(cudaMemcpyAsync(dsl, slots, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    if (to_pool) CK(cudaMemcpyAsync(lin, host, (size_t)n * stride * 4, cudaMemcpyHostToDevice, m->stream));
+    klm_state_gather<<<n, 256, 0, m->stream>>>(m->state, dsl, n, stride, lin, to_pool);
+    m->launches++;
+    if (!to_pool) CK(cudaMemcpyAsync(host, lin, (size_t)n * stride * 4, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    cudaFree(lin); cudaFree(dsl);
+    return KLM_OK;
+}
+extern "C" int klm_state_to_host(klm_model *m, const int32_t *slots, int32_t n, float *out) {
+    return state_xfer(m, slots, n, out, 0);
+}
+extern "C" int klm_state_from_host(klm_model *m, const int32_t *slots, int32_t n, const float *in) {
+    return state_xfer(m, slots, n, const_cast<float *>(in), 1);
+}
+
+extern "C" int klm_state_l2_distance(klm_model *m, const int32_t *a, const int32_t *b, int32_t n, int32_t n_arrays,
+                                     float *out) {
+    if (!m || !out) return fail(KLM_EINVAL, "klm_state_l2_distance: NULL argument");
+    if (n <= 0) return KLM_OK;
+    if (n_arrays < 1 || n_arrays > 2 * m->D) return fail(KLM_EINVAL, "klm_state_l2_distance: n_arrays %d", n_arrays);
+    CK(cudaSetDevice(m->device));
+    int rc = check_slots(m, a, n, false, "klm_state_l2_distance"); if (rc) return rc;
+    rc = check_slots(m, b, n, false, "klm_state_l2_distance"); if (rc) return rc;
+    int *da = nullptr; float *dout = nullptr;
+    CK(cudaMalloc(&da, (size_t)n * 8)); CK(cudaMalloc(&dout, (size_t)n * n_arrays * 4));
+    CK(cudaMemcpyAsync(da, a, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    CK(cudaMemcpyAsync(da + n, b, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    klm_state_dist<<<n * n_arrays, 128, 0, m->stream>>>(m->state, da, da + n, n, n_arrays, m->W, m->D * 2 * m->W, dout);
+    m->launches++;
+    CK(cudaMemcpyAsync(out, dout, (size_t)n * n_arrays * 4, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    cudaFree(da); cudaFree(dout);
+    return KLM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// One cooperative launch over nb streams (nb <= plan.max_streams).  offsets0 are relative to
+// d_chars / d_targets / d_out.
+static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_t *slots_out, const int64_t *offsets0,
+                     const int32_t *n_real, const int32_t *ctx, const int *d_chars, const int *d_targets, float *d_out,
+                     int full_rows) {
+    KlmPlan &pl = (nb <= KLM_MODEK_MAXB) ? m->plan_k : m->plan_b;
+    if (nb > pl.max_streams) return fail(KLM_EINVAL, "internal: batch of %d streams exceeds plan (%d)", nb, pl.max_streams);
+    long long tmax = 0;
+    for (int s = 0; s < nb; ++s) {
+        const long long len = offsets0[s + 1] - offsets0[s];
+        if (len < 0 || len > 0x7fffffff) return fail(KLM_EINVAL, "bad offsets at stream %d", s);
+        tmax = std::max(tmax, len);
+    }
+    if (tmax == 0) return KLM_OK;
+    RingSlot rs;
+    int rc = ring_acquire(m, &rs, (size_t)nb * (4 * 3 + 4 * m->Nc) + (nb + 1) * 8 + 128);
+    if (rc) return rc;
+    KlmSeqParams p;
+    memset(&p, 0, sizeof p);
+    int *d_si, *d_so, *d_nr = nullptr, *d_cx;
+    long long *d_off;
+    ring_put(&rs, slots_in, nb, &d_si);
+    ring_put(&rs, slots_out, nb, &d_so);
+    ring_put(&rs, reinterpret_cast<const long long *>(offsets0), nb + 1, &d_off);
+    if (n_real) ring_put(&rs, n_real, nb, &d_nr);
+    int *hcx = ring_put<int>(&rs, nullptr, (size_t)nb * std::max(1, m->Nc), &d_cx);
+    for (int i = 0; i < nb * m->Nc; ++i) hcx[i] = ctx ? ctx[i] : 0;
+    rc = ring_commit(m, &rs); if (rc) return rc;
+
+    p.W = m->W; p.D = m->D; p.V = m->V; p.V4 = m->V4; p.Nc = m->Nc;
+    p.B = nb; p.Bp = (nb <= KLM_MODEK_MAXB) ? nb : (nb + 31) / 32 * 32; p.T_max = (int)tmax;
+    for (int k = 0; k < m->Nc; ++k) { p.ctx_rows[k] = m->cfg.ctx_rows[k]; p.Q[k] = m->Q[k]; }
+    p.P = m->P; p.Ep = m->Ep;
+    for (int l = 0; l < m->D; ++l) { p.Wl[l] = m->Wl[l]; p.bias[l] = m->bias[l]; }
+    p.state = m->state; p.slots_in = d_si; p.slots_out = d_so; p.offsets = d_off;
+    p.chars = d_chars; p.targets = d_targets; p.n_real = d_nr; p.ctx = d_cx;
+    p.out = d_out; p.full_rows = full_rows;
+    p.hbuf = m->hbuf; p.logits = m->logits; p.barrier = m->barrier;
+    p.roles = pl.d_roles; p.wsmem = pl.wsmem; p.stage_floats = pl.stage_floats;
+    CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
+    CK(klm_launch_seq_fma(p, pl.grid, pl.smem, m->stream));
+    m->launches++;
+    return KLM_OK;
+}
+
+static int ensure_pos_cap(klm_model *m, size_t npos, size_t nout) {
+    if (npos > m->cap_pos) {
+        CK(cudaStreamSynchronize(m->stream));
+        cudaFree(m->d_chars); cudaFree(m->d_targets); m->d_chars = m->d_targets = nullptr; m->cap_pos = 0;
+        const size_t cap = npos + npos / 4 + 1024;
+        CK(cudaMalloc(&m->d_chars, cap * 4)); CK(cudaMalloc(&m->d_targets, cap * 4));
+        m->cap_pos = cap;
+    }
+    if (nout > m->cap_out) {
+        CK(cudaStreamSynchronize(m->stream));
+        cudaFree(m->d_out); m->d_out = nullptr; m->cap_out = 0;
+        const size_t cap = nout + nout / 4 + 1024;
+        CK(cudaMalloc(&m->d_out, cap * 4));
+        m->cap_out = cap;
+    }
+    return KLM_OK;
+}
+
+extern "C" int klm_rate(klm_model *m, int32_t n, const int32_t *slots, const int64_t *offsets, const int32_t *chars,
+                        const int32_t *targets, const int32_t *n_real, const int32_t *ctx, float *out_logp, int mem) {
+    if (!m) return fail(KLM_EINVAL, "NULL model");
+    if (n <= 0) return KLM_OK;
+    if (!offsets || !chars || !targets || !out_logp) return fail(KLM_EINVAL, "klm_rate: NULL argument");
+    if (m->Nc > 0 && !ctx) return fail(KLM_EINVAL, "klm_rate: model has %d context variables but ctx is NULL", m->Nc);
+    CK(cudaSetDevice(m->device));
+    int rc = check_slots(m, slots, n, false, "klm_rate"); if (rc) return rc;
+    const long long total = offsets[n] - offsets[0];
+    if (total < 0) return fail(KLM_EINVAL, "klm_rate: offsets not increasing");
+    if (total == 0) return KLM_OK;
+    for (int k = 0; k < m->Nc; ++k)
+        for (int s = 0; s < n; ++s)
+            if (ctx[s * m->Nc + k] < 0 || ctx[s * m->Nc + k] >= m->cfg.ctx_rows[k])
+                return fail(KLM_EINVAL, "klm_rate: context %d of stream %d is %d, table has %d rows", k, s,
+                            ctx[s * m->Nc + k], m->cfg.ctx_rows[k]);
+    const int *dc, *dt; float *dout;
+    const long long base = offsets[0];
+    if (mem == KLM_MEM_HOST) {
+        rc = ensure_pos_cap(m, (size_t)total, (size_t)total); if (rc) return rc;
+        CK(cudaMemcpyAsync(m->d_chars, chars + base, (size_t)total * 4, cudaMemcpyHostToDevice, m->stream));
+        CK(cudaMemcpyAsync(m->d_targets, targets + base, (size_t)total * 4, cudaMemcpyHostToDevice, m->stream));
+        dc = m->d_chars; dt = m->d_targets; dout = m->d_out;
+    } else {
+        dc = chars + base; dt = targets + base; dout = out_logp + base;
+    }
+    CK(cudaEventRecord(m->ev0, m->stream));
+    const int bmax = (n <= KLM_MODEK_MAXB) ? KLM_MODEK_MAXB : m->plan_b.max_streams;
+    std::vector<int64_t> off0;
+    for (int s0 = 0; s0 < n; s0 += bmax) {
+        const int nb = std::min(bmax, n - s0);
+        off0.resize(nb + 1);
+        for (int i = 0; i <= nb; ++i) off0[i] = offsets[s0 + i] - base;
+        rc = run_batch(m, nb, slots + s0, slots + s0, off0.data(), n_real ? n_real + s0 : nullptr,
+                       ctx ? ctx + (size_t)s0 * m->Nc : nullptr, dc, dt, dout, 0);
+        if (rc) return rc;
+    }
+    CK(cudaEventRecord(m->ev1, m->stream));
+    m->timed = true;
+    if (mem == KLM_MEM_HOST) {
+        CK(cudaMemcpyAsync(out_logp + base, m->d_out, (size_t)total * 4, cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaStreamSynchronize(m->stream));
+    }
+    return KLM_OK;
+}
+
+extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx, const int32_t *slots_in,
+                        const int32_t *slots_out, const int32_t *targets, float *out, int mem) {
+    if (!m) return fail(KLM_EINVAL, "NULL model");
+    if (n <= 0) return KLM_OK;
+    if (!chars || !out) return fail(KLM_EINVAL, "klm_step: NULL argument");
+    if (m->Nc > 0 && !ctx) return fail(KLM_EINVAL, "klm_step: model has %d context variables but ctx is NULL", m->Nc);
+    CK(cudaSetDevice(m->device));
+    int rc = check_slots(m, slots_in, n, true, "klm_step"); if (rc) return rc;
+    rc = check_slots(m, slots_out, n, false, "klm_step"); if (rc) return rc;
+    for (int k = 0; k < m->Nc; ++k)
+        for (int s = 0; s < n; ++s)
+            if (ctx[s * m->Nc + k] < 0 || ctx[s * m->Nc + k] >= m->cfg.ctx_rows[k])
+                return fail(KLM_EINVAL, "klm_step: context %d of hypothesis %d is %d, table has %d rows", k, s,
+                            ctx[s * m->Nc + k], m->cfg.ctx_rows[k]);
+    const int full = targets ? 0 : 1;
+    const size_t nout = full ? (size_t)n * m->V : (size_t)n;
+    rc = ensure_pos_cap(m, (size_t)n, mem == KLM_MEM_HOST ? nout : 0); if (rc) return rc;
+    // chars/targets are per-hypothesis host arrays: they ride along as position arrays of length n
+    CK(cudaMemcpyAsync(m->d_chars, chars, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    if (targets) CK(cudaMemcpyAsync(m->d_targets, targets, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    float *dout = (mem == KLM_MEM_HOST) ? m->d_out : out;
+    CK(cudaEventRecord(m->ev0, m->stream));
+    const int bmax = (n <= KLM_MODEK_MAXB) ? KLM_MODEK_MAXB : m->plan_b.max_streams;
+    std::vector<int64_t> off0;
+    for (int s0 = 0; s0 < n; s0 += bmax) {
+        const int nb = std::min(bmax, n - s0);
+        off0.resize(nb + 1);
+        for (int i = 0; i <= nb; ++i) off0[i] = s0 + i;
+        rc = run_batch(m, nb, slots_in + s0, slots_out + s0, off0.data(), nullptr, ctx ? ctx + (size_t)s0 * m->Nc : nullptr,
+                       m->d_chars, targets ? m->d_targets : nullptr, dout, full);
+        if (rc) return rc;
+    }
+    CK(cudaEventRecord(m->ev1, m->stream));
+    m->timed = true;
+    if (mem == KLM_MEM_HOST) {
+        CK(cudaMemcpyAsync(out, m->d_out, nout * 4, cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaStreamSynchronize(m->stream));
+    }
+    return KLM_OK;
+}
+
+extern "C" int klm_get_info(klm_model *m, klm_info *out) {
+    if (!m || !out) return fail(KLM_EINVAL, "klm_get_info: NULL argument");
+    memset(out, 0, sizeof *out);
+    out->sm_count = m->sm_count;
+    out->grid = m->plan_b.grid;
+    out->weights_in_smem = m->plan_b.wsmem;
+    out->smem_bytes = (int32_t)m->plan_b.smem;
+    out->kernel_launches = m->launches;
+    out->max_streams = m->plan_b.max_streams;
+    if (m->timed) {
+        CK(cudaSetDevice(m->device));
+        CK(cudaEventSynchronize(m->ev1));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, m->ev0, m->ev1));
+        out->last_kernel_ms = ms;
+    }
+    return KLM_OK;
+}

@@ -1,0 +1,360 @@
+// Persistent stacked-LSTM sequence kernel, FP32 FMA path (small numbers of streams / hypotheses,
+// and the general fallback shape for any model that the tensor-core path does not take).
+//
+// ONE cooperative launch streams whole character sequences: fused embedding gather (as a lookup
+// into the pre-contracted tables P/Q), depth x LSTM, tied output projection, log-softmax and
+// target pick.  Replaces the per-window Session.run of Rater.rate (rating.py:516), the
+// per-character one of Rater.rate2 (:566) and the per-step one of Rater.predict (:631).
+//
+// Decomposition: every CTA owns a fixed slice of one stage for the whole launch --
+//   LSTM layer l : `count` units (= 4 gate columns each), weights resident in shared memory
+//   PROJ         : `count` groups of 4 vocabulary rows of E
+//   LSE          : one CTA, log-sum-exp over the logits and the target pick / full softmax rows
+// and the stages run as a wavefront over "ticks": at tick k layer l works on position k-l,
+// PROJ on k-D, LSE on k-D-1.  Hidden vectors travel through L2 in hbuf[l][parity][unit][stream];
+// one grid-wide barrier per tick.  Cell states never leave the registers of their owner thread.
+#include "klm_common.cuh"
+
+__device__ __forceinline__ float klm_sigmoid(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int *p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Grid-wide barrier on a monotonically increasing counter (kernel is launched cooperatively,
+// so all CTAs are co-resident).
+__device__ __forceinline__ void grid_barrier(unsigned int *ctr, unsigned int target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(ctr, 1u);
+        while (ld_acquire_u32(ctr) < target) { }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ void fma4(float4 &a, const float4 w, const float h) {
+    a.x = fmaf(w.x, h, a.x); a.y = fmaf(w.y, h, a.y); a.z = fmaf(w.z, h, a.z); a.w = fmaf(w.w, h, a.w);
+}
+__device__ __forceinline__ void add4(float4 &a, const float4 b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+
+// Pre-activation of layer-1 inputs: gather of the pre-contracted embedding rows
+// (fused char + context embedding gather/concat + input contraction; rating.py:103-115,125).
+__device__ __forceinline__ float4 gather_input(const KlmSeqParams &p, int b, long long pos, int t, int u) {
+    int x = __ldg(p.chars + pos);
+    x = min(max(x, 0), p.V - 1);
+    float4 pre = __ldg(p.P + (size_t)x * p.W + u);
+    const bool real = p.n_real ? (t < __ldg(p.n_real + b)) : true;
+    for (int k = 0; k < p.Nc; ++k) {
+        int z = real ? __ldg(p.ctx + b * p.Nc + k) : 0;       // padding: context 0 (:1141-1143)
+        z = min(max(z, 0), p.ctx_rows[k] - 1);
+        add4(pre, __ldg(p.Q[k] + (size_t)z * p.W + u));
+    }
+    return pre;
+}
+
+// LSTM cell update (Keras LSTMCell, gate order i|f|c|o, exact sigmoid; rating.py:133-134).
+__device__ __forceinline__ void lstm_cell(const float4 a, float &c, float &h) {
+    const float i = klm_sigmoid(a.x), f = klm_sigmoid(a.y), g = tanhf(a.z), o = klm_sigmoid(a.w);
+    c = fmaf(f, c, i * g);
+    h = o * tanhf(c);
+}
+
+// ---------------------------------------------------------------------------------------------
+// LSE stage: one warp per stream, lanes over the vocabulary.
+__device__ __forceinline__ void lse_stage(const KlmSeqParams &p, int tick) {
+    const int t = tick - p.D - 1;
+    if (t < 0) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float *lg = p.logits + (size_t)(tick & 1) * p.V4 * p.Bp;
+    for (int b = warp; b < p.B; b += KLM_WARPS) {
+        const long long o0 = p.offsets[b];
+        const int len = (int)(p.offsets[b + 1] - o0);
+        if (t >= len) continue;
+        float m = -INFINITY;
+        for (int v = lane; v < p.V; v += 32) m = fmaxf(m, __ldcg(lg + (size_t)v * p.Bp + b));
+        for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
+        float sum = 0.f;
+        for (int v = lane; v < p.V; v += 32) sum += expf(__ldcg(lg + (size_t)v * p.Bp + b) - m);
+        for (int s = 16; s > 0; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
+        if (p.full_rows) {
+            float *row = p.out + (size_t)(o0 + t) * p.V;
+            const float inv = 1.0f / sum;
+            for (int v = lane; v < p.V; v += 32) row[v] = expf(__ldcg(lg + (size_t)v * p.Bp + b) - m) * inv;
+        } else if (lane == 0) {
+            int tg = __ldg(p.targets + o0 + t);
+            tg = min(max(tg, 0), p.V - 1);
+            p.out[o0 + t] = (__ldcg(lg + (size_t)tg * p.Bp + b) - m) - logf(sum);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Stream-parallel mode (B > 8): lane = stream, each thread walks K sequentially; the hidden vectors
+// are staged [k][stream] so that the weight read is a broadcast and the h read is conflict-free.
+__global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_streams(const KlmSeqParams p) {
+    extern __shared__ float4 smem4[];
+    const KlmRole role = p.roles[blockIdx.x];
+    const int W = p.W, B = p.B, Bp = p.Bp;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int l = role.layer;
+    const bool is_lstm = role.kind == KLM_ROLE_LSTM, is_proj = role.kind == KLM_ROLE_PROJ;
+    const int K = (is_lstm && l > 0) ? 2 * W : W;
+    const int nsg = Bp / 32;
+    const int nitems = role.count * nsg;
+
+    const float4 *wptr = nullptr;
+    float *stage = reinterpret_cast<float *>(smem4);
+    if (is_lstm || is_proj) {
+        wptr = (is_lstm ? p.Wl[l] : p.Ep) + (size_t)role.first * K;
+        if (p.wsmem) {
+            const int n4 = role.count * K;
+            for (int i = threadIdx.x; i < n4; i += KLM_THREADS) smem4[i] = __ldg(wptr + i);
+            wptr = smem4;
+            stage = reinterpret_cast<float *>(smem4 + n4);
+        }
+    }
+    const int KC = p.stage_floats / Bp;
+
+    float c_reg[KLM_MAX_ITEMS], h_reg[KLM_MAX_ITEMS];
+    // ---- init: load the carried state of own units, publish h into parity 0 ----
+#pragma unroll
+    for (int j = 0; j < KLM_MAX_ITEMS; ++j) {
+        c_reg[j] = 0.f; h_reg[j] = 0.f;
+        const int it = warp + j * KLM_WARPS;
+        if (is_lstm && it < nitems) {
+            const int u = role.first + it / nsg, b = (it % nsg) * 32 + lane;
+            if (b < B) {
+                const int slot = p.slots_in[b];
+                if (slot >= 0) {
+                    const float *st = p.state + ((size_t)slot * p.D + l) * 2 * W;
+                    h_reg[j] = st[u]; c_reg[j] = st[W + u];
+                }
+                p.hbuf[((size_t)(l * 2 + 0) * W + u) * Bp + b] = h_reg[j];
+            }
+        }
+    }
+    unsigned int bar = 0;
+    grid_barrier(p.barrier, (++bar) * gridDim.x);
+
+    const int nticks = p.T_max + p.D + 1;
+    for (int tick = 0; tick < nticks; ++tick) {
+        const int par = tick & 1;
+        if (is_lstm || is_proj) {
+            float4 acc[KLM_MAX_ITEMS];
+#pragma unroll
+            for (int j = 0; j < KLM_MAX_ITEMS; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int nsrc = (is_lstm && l > 0) ? 2 : 1;
+            for (int src = 0; src < nsrc; ++src) {
+                int hl;                                      // which layer's hidden vector
+                if (is_proj) hl = p.D - 1; else if (l == 0) hl = 0; else hl = (src == 0) ? l - 1 : l;
+                const float *hsrc = p.hbuf + (size_t)(hl * 2 + par) * W * Bp;
+                for (int k0 = 0; k0 < W; k0 += KC) {
+                    const int kc = min(KC, W - k0);
+                    __syncthreads();
+                    const float4 *g4 = reinterpret_cast<const float4 *>(hsrc + (size_t)k0 * Bp);
+                    float4 *s4 = reinterpret_cast<float4 *>(stage);
+                    for (int i = threadIdx.x; i < kc * Bp / 4; i += KLM_THREADS) s4[i] = __ldcg(g4 + i);
+                    __syncthreads();
+#pragma unroll
+                    for (int j = 0; j < KLM_MAX_ITEMS; ++j) {
+                        const int it = warp + j * KLM_WARPS;
+                        if (it < nitems) {
+                            const float4 *wrow = wptr + (size_t)(it / nsg) * K + src * W + k0;
+                            const float *hcol = stage + (it % nsg) * 32 + lane;
+                            float4 a = acc[j];
+#pragma unroll 8
+                            for (int k = 0; k < kc; ++k) fma4(a, wrow[k], hcol[k * Bp]);
+                            acc[j] = a;
+                        }
+                    }
+                }
+            }
+            // ---- epilogue ----
+#pragma unroll
+            for (int j = 0; j < KLM_MAX_ITEMS; ++j) {
+                const int it = warp + j * KLM_WARPS;
+                if (it < nitems) {
+                    const int ui = role.first + it / nsg, b = (it % nsg) * 32 + lane;
+                    if (b < B) {
+                        if (is_lstm) {
+                            const int t = tick - l;
+                            const long long o0 = p.offsets[b];
+                            const int len = (int)(p.offsets[b + 1] - o0);
+                            if (t >= 0 && t < len) {
+                                float4 a = acc[j];
+                                if (l == 0) add4(a, gather_input(p, b, o0 + t, t, ui));
+                                else add4(a, __ldg(p.bias[l] + ui));
+                                lstm_cell(a, c_reg[j], h_reg[j]);
+                            }
+                            p.hbuf[((size_t)(l * 2 + (par ^ 1)) * W + ui) * Bp + b] = h_reg[j];
+                        } else {
+                            float *lg = p.logits + ((size_t)(par ^ 1) * p.V4 + 4 * ui) * Bp + b;
+                            lg[0] = acc[j].x; lg[Bp] = acc[j].y; lg[2 * Bp] = acc[j].z; lg[3 * Bp] = acc[j].w;
+                        }
+                    }
+                }
+            }
+        } else if (role.kind == KLM_ROLE_LSE) {
+            lse_stage(p, tick);
+        }
+        grid_barrier(p.barrier, (++bar) * gridDim.x);
+    }
+
+    // ---- write the final state back ----
+    if (is_lstm) {
+#pragma unroll
+        for (int j = 0; j < KLM_MAX_ITEMS; ++j) {
+            const int it = warp + j * KLM_WARPS;
+            if (it < nitems) {
+                const int u = role.first + it / nsg, b = (it % nsg) * 32 + lane;
+                if (b < B) {
+                    float *st = p.state + ((size_t)p.slots_out[b] * p.D + l) * 2 * W;
+                    st[u] = h_reg[j]; st[W + u] = c_reg[j];
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K-parallel mode (B <= 8: single documents, tiny beams): lanes split the contraction index,
+// partial sums are combined with warp shuffles; the whole input vector of a tick is staged once.
+template <int BT>
+__global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_kpar(const KlmSeqParams p) {
+    extern __shared__ float4 smem4[];
+    const KlmRole role = p.roles[blockIdx.x];
+    const int W = p.W, B = p.B, Bp = p.Bp;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int l = role.layer;
+    const bool is_lstm = role.kind == KLM_ROLE_LSTM, is_proj = role.kind == KLM_ROLE_PROJ;
+    const int K = (is_lstm && l > 0) ? 2 * W : W;
+
+    const float4 *wptr = nullptr;
+    float *stage = reinterpret_cast<float *>(smem4);
+    if (is_lstm || is_proj) {
+        wptr = (is_lstm ? p.Wl[l] : p.Ep) + (size_t)role.first * K;
+        if (p.wsmem) {
+            const int n4 = role.count * K;
+            for (int i = threadIdx.x; i < n4; i += KLM_THREADS) smem4[i] = __ldg(wptr + i);
+            wptr = smem4;
+            stage = reinterpret_cast<float *>(smem4 + n4);
+        }
+    }
+
+    // lane b (< B) of the warp that owns unit j keeps that stream's cell/hidden value
+    float c_reg[KLM_MAX_UNITS_K], h_reg[KLM_MAX_UNITS_K];
+#pragma unroll
+    for (int j = 0; j < KLM_MAX_UNITS_K; ++j) {
+        c_reg[j] = 0.f; h_reg[j] = 0.f;
+        const int ui = warp + j * KLM_WARPS;
+        if (is_lstm && ui < role.count && lane < B) {
+            const int u = role.first + ui, b = lane;
+            const int slot = p.slots_in[b];
+            if (slot >= 0) {
+                const float *st = p.state + ((size_t)slot * p.D + l) * 2 * W;
+                h_reg[j] = st[u]; c_reg[j] = st[W + u];
+            }
+            p.hbuf[((size_t)(l * 2 + 0) * W + u) * Bp + b] = h_reg[j];
+        }
+    }
+    unsigned int bar = 0;
+    grid_barrier(p.barrier, (++bar) * gridDim.x);
+
+    const int nticks = p.T_max + p.D + 1;
+    for (int tick = 0; tick < nticks; ++tick) {
+        const int par = tick & 1;
+        if (is_lstm || is_proj) {
+            // ---- stage the input vector(s): stage[b][K] <- hbuf[hl][par][k][b] ----
+            const int nsrc = (is_lstm && l > 0) ? 2 : 1;
+            for (int src = 0; src < nsrc; ++src) {
+                int hl;
+                if (is_proj) hl = p.D - 1; else if (l == 0) hl = 0; else hl = (src == 0) ? l - 1 : l;
+                const float *hsrc = p.hbuf + (size_t)(hl * 2 + par) * W * Bp;
+                for (int i = threadIdx.x; i < W * B; i += KLM_THREADS) {
+                    const int k = i / B, b = i - k * B;
+                    stage[b * K + src * W + k] = __ldcg(hsrc + (size_t)k * Bp + b);
+                }
+            }
+            __syncthreads();
+#pragma unroll
+            for (int j = 0; j < KLM_MAX_UNITS_K; ++j) {
+                const int ui = warp + j * KLM_WARPS;
+                if (ui < role.count) {
+                    float4 acc[BT];
+#pragma unroll
+                    for (int bb = 0; bb < BT; ++bb) acc[bb] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float4 *wrow = wptr + (size_t)ui * K;
+                    for (int k = lane; k < K; k += 32) {
+                        const float4 w = wrow[k];
+#pragma unroll
+                        for (int bb = 0; bb < BT; ++bb)
+                            if (bb < B) fma4(acc[bb], w, stage[bb * K + k]);
+                    }
+                    float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int bb = 0; bb < BT; ++bb) {
+#pragma unroll
+                        for (int s = 16; s > 0; s >>= 1) {
+                            acc[bb].x += __shfl_xor_sync(0xffffffffu, acc[bb].x, s);
+                            acc[bb].y += __shfl_xor_sync(0xffffffffu, acc[bb].y, s);
+                            acc[bb].z += __shfl_xor_sync(0xffffffffu, acc[bb].z, s);
+                            acc[bb].w += __shfl_xor_sync(0xffffffffu, acc[bb].w, s);
+                        }
+                        if (lane == bb) mine = acc[bb];
+                    }
+                    if (lane < B) {
+                        const int u = role.first + ui, b = lane;
+                        if (is_lstm) {
+                            const int t = tick - l;
+                            const long long o0 = p.offsets[b];
+                            const int len = (int)(p.offsets[b + 1] - o0);
+                            if (t >= 0 && t < len) {
+                                if (l == 0) add4(mine, gather_input(p, b, o0 + t, t, u));
+                                else add4(mine, __ldg(p.bias[l] + u));
+                                lstm_cell(mine, c_reg[j], h_reg[j]);
+                            }
+                            p.hbuf[((size_t)(l * 2 + (par ^ 1)) * W + u) * Bp + b] = h_reg[j];
+                        } else {
+                            float *lg = p.logits + ((size_t)(par ^ 1) * p.V4 + 4 * u) * Bp + b;
+                            lg[0] = mine.x; lg[Bp] = mine.y; lg[2 * Bp] = mine.z; lg[3 * Bp] = mine.w;
+                        }
+                    }
+                }
+            }
+        } else if (role.kind == KLM_ROLE_LSE) {
+            lse_stage(p, tick);
+        }
+        grid_barrier(p.barrier, (++bar) * gridDim.x);
+    }
+
+    if (is_lstm) {
+#pragma unroll
+        for (int j = 0; j < KLM_MAX_UNITS_K; ++j) {
+            const int ui = warp + j * KLM_WARPS;
+            if (ui < role.count && lane < B) {
+                const int u = role.first + ui;
+                float *st = p.state + ((size_t)p.slots_out[lane] * p.D + l) * 2 * W;
+                st[u] = h_reg[j]; st[W + u] = c_reg[j];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Launch helper used by klm_api.cu
+cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cudaStream_t stream) {
+    void *args[] = { const_cast<KlmSeqParams *>(&p) };
+    const void *fn;
+    if (p.B > KLM_MODEK_MAXB) fn = (const void *)klm_seq_fma_streams;
+    else if (p.B > 4) fn = (const void *)klm_seq_fma_kpar<8>;
+    else if (p.B > 2) fn = (const void *)klm_seq_fma_kpar<4>;
+    else if (p.B > 1) fn = (const void *)klm_seq_fma_kpar<2>;
+    else fn = (const void *)klm_seq_fma_kpar<1>;
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(KLM_THREADS), args, smem, stream);
+}

@@ -1,0 +1,244 @@
+"""Parity of the CUDA path (through the C ABI, via the product ``Rater``) against
+
+  * the golden vectors produced by the reference's own rating.py (tests/golden/), and
+  * the CPU oracle on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): per-character log-probabilities within 1e-3 nats,
+hidden/cell states within 1e-4 relative, identical beam-search paths.
+"""
+import io
+import logging
+import math
+
+import numpy as np
+import pytest
+
+from oracle import lstm_numpy as ln
+from oracle.rater_oracle import OracleRater
+from ocrd_keraslm_b200 import synth
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+LOGP_TOL = 1e-3       # nats
+STATE_TOL = 1e-4      # relative (max |diff| / max |ref|)
+
+quiet = logging.getLogger('gpu-test')
+quiet.setLevel(logging.CRITICAL)
+
+
+def product(wd, maparr, length, stateful=True, incremental=False):
+    from ocrd_keraslm_b200.lib import Rater
+    return Rater.from_weights(wd, maparr, length, stateful=stateful, incremental=incremental, logger=quiet)
+
+
+def assert_logp_close(got, ref, tol=LOGP_TOL):
+    got = np.log(np.maximum(np.asarray(got, dtype=np.float64), 1e-300))
+    ref = np.log(np.maximum(np.asarray(ref, dtype=np.float64), 1e-300))
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() <= tol, np.abs(got - ref).max()
+
+
+def assert_state_close(got, ref, tol=STATE_TOL):
+    got, ref = np.asarray(got, np.float64), np.asarray(ref, np.float64)
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() <= tol * max(np.abs(ref).max(), 1e-30), np.abs(got - ref).max()
+
+
+# ------------------------------------------------------------------ golden vectors (small model)
+def test_rate_golden_windows_padding_state_carry():
+    j, _ = util.golden()
+    g = j['rate_small']
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, g['length'])
+    for case in g['cases']:                 # successive calls, no reset in between
+        probs = r.rate(case['text'], case['context'])
+        assert len(probs) == len(case['text']) and probs[0] == 1.0
+        assert_logp_close(probs, case['probs'])
+
+
+def test_rate_degenerate_lengths():
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, 8)
+    assert r.rate('') == []
+    assert r.rate('a') == [1.0]
+
+
+def test_rate2_golden():
+    j, _ = util.golden()
+    g = j['rate2_small']
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, g['length'])
+    for case in g['cases']:
+        res, ppl = r.rate2(case['text'], case['context'])
+        assert [c for c, _ in res] == [c for c, _ in case['result']]
+        assert_logp_close([p for _, p in res], [p for _, p in case['result']])
+        assert ppl == pytest.approx(case['perplexity'], rel=2e-3)
+
+
+def test_predict_golden_probs_and_states():
+    j, a = util.golden()
+    g = j['predict_small']
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, 8, stateful=False, incremental=True)
+    s_in = [None] * 5
+    p1, s1 = r.predict(list(g['cands1']), s_in, g['ctx1'])
+    assert all(s is not None for s in s_in)             # mutated in place like the reference
+    assert_logp_close(np.stack(p1), a['predict_small/probs1'])
+    assert_state_close(np.stack([np.concatenate(list(s), 0) for s in s1]), a['predict_small/states1'])
+    st = [s1[k] if k >= 0 else None for k in g['perm2']]
+    p2, s2 = r.predict(list(g['cands2']), st, g['ctx2'])
+    assert_logp_close(np.stack(p2), a['predict_small/probs2'])
+    assert_state_close(np.stack([np.concatenate(list(s), 0) for s in s2]), a['predict_small/states2'])
+    assert len(s2[0]) == 4 and s2[0][0].shape == (1, 16)
+    np.testing.assert_allclose(np.stack(p2).sum(axis=1), 1.0, rtol=1e-5)
+
+
+def test_predict_accepts_host_state_lists():
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, 8, stateful=False, incremental=True)
+    p1, s1 = r.predict(['a', 'b'], [None, None], [3])
+    as_lists = [[np.array(x) for x in s] for s in s1]
+    pa, _ = r.predict(['c', 'd'], list(s1), [3])
+    pb, _ = r.predict(['c', 'd'], as_lists, [3])
+    np.testing.assert_array_equal(np.stack(pa), np.stack(pb))
+
+
+def test_generate_golden():
+    j, _ = util.golden()
+    g = j['generate_small']
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, 8, stateful=False, incremental=True)
+    assert r.generate(g['prefix'], g['length'], context=g['context'], variants=g['variants']) == g['result']
+
+
+def test_test_perplexity_golden():
+    j, _ = util.golden()
+    g = j['test_small']
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, g['length'])
+    files = []
+    for name, content in g['files']:
+        f = io.StringIO(content)
+        f.name = name
+        files.append(f)
+    assert r.test(files) == pytest.approx(g['perplexity'], rel=1e-3)
+
+
+@pytest.mark.parametrize('idx', range(4))
+def test_rate_best_golden_paths(idx):
+    j, _ = util.golden()
+    g = j['rate_best_small'][idx]
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, 8, stateful=False, incremental=True)
+    r.batch_size = g['batch_size']
+    tb = None
+    for page in g['pages']:
+        graph = util.lattice_from_json(page['edges'])
+        path, entropy, tb = r.rate_best(graph, page['start'], page['end'], start_traceback=tb, context=g['context'],
+                                        lm_weight=g['lm_weight'], beam_width=g['beam_width'],
+                                        beam_clustering_dist=g['dist'])
+        got = util.path_to_json(path)
+        assert [p[:3] for p in got] == [p[:3] for p in page['path']]
+        np.testing.assert_allclose([p[3] for p in got], [p[3] for p in page['path']], rtol=2e-3)
+        assert entropy == pytest.approx(page['entropy'], rel=2e-3, abs=2e-3)
+        assert [n.value for n in tb[0]] == [v for _, v, _ in page['traceback']]
+        np.testing.assert_allclose([n.cum_cost for n in tb[0]], [c for c, _, _ in page['traceback']], rtol=2e-3, atol=2e-3)
+    path, entropy, _ = r.next_path(tb[0], ([], tb[1]))
+    assert [p[:3] for p in util.path_to_json(path)] == [p[:3] for p in g['flush']['path']]
+
+
+# ------------------------------------------------------------------ seeded models vs reference-run goldens
+def test_cfg1_model_against_reference_run():
+    j, a = util.golden()
+    g = j['cfg1']
+    wd = synth.weights(g['seed_weights'], width=128, depth=2, voc_size=256, style='trained')
+    r = product(wd, synth.vocabulary(), g['length'])
+    text = synth.text(g['seed_text'], g['size'])
+    pa = r.rate(text[:g['split']], g['context'])
+    pb = r.rate(text[g['split']:], g['context'])
+    assert_logp_close(pa, a['cfg1/probs_a'])
+    assert_logp_close(pb, a['cfg1/probs_b'])
+
+
+def test_cfg4_three_context_variables():
+    j, a = util.golden()
+    g = j['cfg4']
+    wd = synth.weights(g['seed_weights'], width=32, depth=3, voc_size=256, contexts=((200, 16),) * 3, style='trained')
+    r = product(wd, synth.vocabulary(), g['length'])
+    for d, doc in enumerate(g['docs']):
+        r.reset_states()
+        probs = r.rate(synth.text(doc['seed_text'], doc['size']), doc['context'])
+        assert_logp_close(probs, a['cfg4/probs_%d' % d])
+    # the same documents as one mixed-context batch
+    texts = [synth.text(doc['seed_text'], doc['size']) for doc in g['docs']]
+    many = r.rate_many(texts, [doc['context'] for doc in g['docs']])
+    for d in range(len(texts)):
+        ref = np.array(a['cfg4/probs_%d' % d])
+        assert_logp_close(many[d], ref[:len(many[d])])
+
+
+def test_context_out_of_range_raises():
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, 8)
+    with pytest.raises(ValueError):
+        r.rate('abc', [200])
+
+
+# ------------------------------------------------------------------ against the oracle on the same seeded inputs
+def oracle_for(wd, maparr, length):
+    return OracleRater(util.to_model(wd), synth.mapping_from_array(maparr), length, logger=quiet)
+
+
+@pytest.mark.parametrize('width,depth,n_docs', [(64, 2, 3), (64, 2, 20), (128, 3, 70), (512, 3, 64)])
+def test_rate_many_matches_oracle(width, depth, n_docs):
+    """K-parallel (<= 8 streams) and stream-parallel kernels, ragged lengths, incl. BASELINE config 2's shape."""
+    wd = synth.weights(11 + width, width=width, depth=depth, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 32)
+    rng = np.random.default_rng(width + n_docs)
+    sizes = rng.integers(2, 60 if width < 512 else 24, n_docs)
+    sizes[0] = 1
+    texts = [synth.text(1000 + i, int(s)) for i, s in enumerate(sizes)]
+    ctxs = [[int(rng.integers(0, 200))] for _ in texts]
+    got = r.rate_many(texts, ctxs)
+    o = oracle_for(wd, maparr, 32)
+    for i, (t, c) in enumerate(zip(texts, ctxs)):
+        ref, _ = o.rate2(t, c)
+        assert_logp_close(got[i], [p for _, p in ref])
+
+
+def test_states_after_rate_match_oracle():
+    wd = synth.weights(3, width=128, depth=3, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 16)
+    o = oracle_for(wd, maparr, 16)
+    text = synth.text(77, 100)               # (T-1) % L != 0: padded tail advances the state
+    assert_logp_close(r.rate(text, [5]), o.rate(text, [5]))
+    got = r._native.state_to_host([0])[0]
+    ref = np.concatenate([s for s in o.states], axis=0)
+    assert_state_close(got, ref)
+
+
+def test_long_document_drift_and_chunking():
+    """Size-independent properties at BASELINE config 1's size: rate == rate2 from a zero state, and rating
+    a document in window-aligned pieces (state carry) equals rating it at once."""
+    wd = synth.weights(8, width=128, depth=2, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    L = 256
+    r = product(wd, maparr, L)
+    text = synth.text(20261104 + 1000, 100000)
+    r.reset_states()
+    whole = np.array(r.rate(text, [179]))
+    two, ppl = r.rate2(text, [179])
+    np.testing.assert_array_equal(whole, np.array([p for _, p in two], dtype=np.float32))
+    r.reset_states()
+    cut = 40 * L + 1                          # first piece consumes exactly 40 full windows
+    a = r.rate(text[:cut], [179])
+    b = r.rate(text[cut - 1:], [179])         # overlap by one char: b[0] is the dummy 1.0
+    np.testing.assert_allclose(np.array(a + b[1:]), whole, rtol=1e-6)
+    # oracle on a prefix (the oracle finishes 3000 chars in seconds)
+    o = oracle_for(wd, maparr, L)
+    ref = o.rate(text[:3000], [179])
+    assert_logp_close(whole[:2999], ref[:2999])
+    assert ppl > 1.0 and math.isfinite(ppl)
