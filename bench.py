@@ -1,0 +1,471 @@
+#!/usr/bin/env python
+"""Benchmark of the stateful rating path (BASELINE.json metric: chars/sec rated).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload cfg2|cfg1|cfg4|cfg5] [--docs D] [--chars C]
+
+One "step" = one pass of the hot path over one batch of synthetic documents: every document
+is rated from a zero state, all documents of the batch advancing concurrently in the
+persistent kernel (cfg2: 64 documents x 100 000 characters, width 512, depth 3, length 512).
+
+Our arm prints ONE JSON line with
+  value        chars/s, inputs resident in HBM when the timed region starts (C ABI, KLM_MEM_DEVICE),
+               CUDA events on the launching stream, L2 flushed between timed steps, max over ranks
+  e2e          the same metric through the public API (`Rater.rate_many` on Python strings):
+               tokenisation, pinned host buffers, H2D, kernel, D2H inside the timed region
+  roofline     the persistent sequence kernel against the measured tensor peak (MEASURED_PEAKS.json)
+  cpu_baseline the CPU oracle (oracle/, a port: the reference's Keras CPU path cannot be installed
+               here) timed on the host cores on a bounded sample (rank 0, N=1 only)
+`--impl reference` times that CPU arm alone, on the same config, with every host core.
+Multi-GPU (torchrun): documents are independent, every rank rates its own batch, no data-path
+collective; NCCL only carries the timing reduction and a checksum.
+"""
+import argparse
+import json
+import logging
+import math
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from ocrd_keraslm_b200 import synth  # noqa: E402
+
+WORKLOADS = {
+    #        width depth length contexts            docs   chars   what
+    'cfg1': (128, 2, 256, ((200, 10),), 1, 100000, 'stateful rating width=128 depth=2 length=256, 1 document x 100000 chars'),
+    'cfg2': (512, 3, 512, ((200, 10),), 64, 100000, 'stateful rating width=512 depth=3 length=512, 64 documents x 100000 chars'),
+    'cfg4': (512, 3, 512, ((200, 16),) * 3, 64, 100000, 'context-conditioned (3 context variables, dim 16) width=512 depth=3, 64 documents x 100000 chars'),
+    'cfg5': (1024, 3, 512, ((200, 10),), 10000, 70, 'page-sharded rating width=1024 depth=3, 10000 lines of 20..120 chars'),
+}
+CFG_INDEX = {'cfg1': 1, 'cfg2': 2, 'cfg4': 4, 'cfg5': 5}
+FALLBACK_PEAKS = {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0}
+
+quiet = logging.getLogger('bench')
+quiet.setLevel(logging.CRITICAL)
+
+
+def flops_per_char(width, depth, contexts, voc_size=256):
+    """F = sum_l 2*4W*(D_l+W) + 2*V*W."""
+    d1 = width + sum(d for _, d in contexts)
+    return sum(2 * 4 * width * ((d1 if l == 0 else width) + width) for l in range(depth)) + 2 * voc_size * width
+
+
+def make_docs(workload, n_docs, n_chars, first_doc):
+    """Seeded synthetic documents and their context rows."""
+    width, depth, length, contexts, _, _, _ = WORKLOADS[workload]
+    cfg = CFG_INDEX[workload]
+    texts, ctxs = [], []
+    for d in range(first_doc, first_doc + n_docs):
+        seed = 20261104 + 1000 * cfg + d
+        rng = np.random.default_rng(seed)
+        size = n_chars if workload != 'cfg5' else int(rng.integers(20, 121))
+        texts.append(synth.text(seed, size))
+        if len(contexts) == 1:
+            ctxs.append([179])
+        else:
+            row = [int(x) for x in rng.integers(0, 200, len(contexts))]
+            if rng.random() < 0.1:
+                row = [0] * len(contexts)
+            ctxs.append(row)
+    return texts, ctxs
+
+
+def model_weights(workload):
+    width, depth, length, contexts, _, _, _ = WORKLOADS[workload]
+    return synth.weights(7 + CFG_INDEX[workload], width=width, depth=depth, voc_size=256, contexts=contexts, style='keras')
+
+
+def peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        with open(path) as f:
+            p = json.load(f)
+        return p, 'measured (MEASURED_PEAKS.json)'
+    except Exception:
+        return dict(FALLBACK_PEAKS), 'fallback (B200_PROFILING.md)'
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+_CPU = {}
+
+
+def _cpu_worker(job):
+    """Rate one sample document with the oracle, reference call structure (one model call per window,
+    batch 1: rating.py:516), single BLAS thread; documents run in parallel across processes."""
+    from threadpoolctl import threadpool_limits
+    from oracle.rater_oracle import OracleRater
+    doc, n_chars = job
+    with threadpool_limits(limits=1):
+        o = OracleRater(_CPU['model'], _CPU['mapping'], _CPU['length'], logger=quiet)
+        t0 = time.perf_counter()
+        probs = o.rate(_CPU['texts'][doc][:n_chars], _CPU['ctxs'][doc])
+        dt = time.perf_counter() - t0
+    return len(probs), dt, float(np.log(np.maximum(np.asarray(probs[1:], dtype=np.float64), 1e-300)).sum())
+
+
+class CpuArm(object):
+    """The oracle port on the host cores: one process per core, one document each."""
+
+    def __init__(self, workload, procs=None):
+        import multiprocessing as mp
+        from tests import util
+        width, depth, length, contexts, _, _, _ = WORKLOADS[workload]
+        self.procs = procs or len(os.sched_getaffinity(0))
+        wd = model_weights(workload)
+        _CPU['model'] = util.to_model(wd)
+        _CPU['mapping'] = synth.mapping_from_array(synth.vocabulary())
+        _CPU['length'] = length
+        self.workload = workload
+        self.pool = None
+        self.mp = mp.get_context('fork')
+
+    def prepare(self, n_chars):
+        texts, ctxs = make_docs(self.workload, self.procs, max(n_chars, 2), 0)
+        _CPU['texts'], _CPU['ctxs'] = texts, ctxs
+        self.pool = self.mp.Pool(self.procs)          # fork AFTER the globals are in place
+
+    def step(self, n_chars):
+        t0 = time.perf_counter()
+        res = self.pool.map(_cpu_worker, [(d, n_chars) for d in range(self.procs)], chunksize=1)
+        dt = time.perf_counter() - t0
+        return sum(r[0] for r in res), dt
+
+    def close(self):
+        if self.pool is not None:
+            self.pool.close()
+            self.pool.join()
+            self.pool = None
+
+
+def cpu_sample_chars(workload):
+    """Characters per process and step: sized for ~5-8 s of CPU work per step."""
+    width, depth = WORKLOADS[workload][0], WORKLOADS[workload][1]
+    per_char = 2.0e-3 * (width / 512.0) ** 2 * (depth / 3.0)      # measured ~1.6 ms/char at W512 D3 on one core
+    if workload == 'cfg5':
+        return 120
+    return int(min(WORKLOADS[workload][5], max(513, 6.0 / per_char)))
+
+
+def run_reference(args):
+    """`--impl reference`: the CPU arm alone (rank 0 only)."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    wl = args.workload
+    arm = CpuArm(wl)
+    n_chars = cpu_sample_chars(wl)
+    arm.prepare(n_chars)
+    for _ in range(args.warmup):
+        arm.step(min(n_chars, 257))                   # warm-up: page in BLAS, fork pool, short sample
+    total_chars, total_t = 0, 0.0
+    for _ in range(args.steps):
+        c, dt = arm.step(n_chars)
+        total_chars += c
+        total_t += dt
+    arm.close()
+    value = total_chars / total_t
+    line = base_line(args, value, 1000.0 * total_t / max(args.steps, 1))
+    sample = '%d processes x 1 document x %d chars per step (of %s)' % (arm.procs, n_chars, WORKLOADS[wl][6])
+    line.update({
+        'impl': 'reference',
+        'dtype': 'f32',
+        'cpu_baseline': {'value': value, 'unit': 'chars/s', 'cores': arm.procs, 'kind': 'port', 'sample': sample,
+                         'note': 'reference Keras/TF CPU path is not installable here (no keras/tensorflow/h5py wheels, '
+                                 'no network): oracle/ port of its algorithm with the reference call structure '
+                                 '(batch 1, one model call per window), documents spread over all host cores'},
+        'e2e': {'value': value, 'unit': 'chars/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    })
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock and clock-event reasons of one GPU every 100 ms while the timed region runs."""
+
+    def __init__(self, device_index):
+        threading.Thread.__init__(self, daemon=True)
+        self.stop_ev = threading.Event()
+        self.sm = []
+        self.reasons = set()
+        self.sm_max = None
+        self.power = []
+        self.err = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+            idx = device_index
+            if vis:
+                ids = [v.strip() for v in vis.split(',') if v.strip()]
+                if device_index < len(ids) and ids[device_index].isdigit():
+                    idx = int(ids[device_index])
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:                         # noqa: BLE001
+            self.nv = None
+            self.err = repr(e)
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksEventReasonHwSlowdown: 'hw_slowdown',
+            nv.nvmlClocksEventReasonHwThermalSlowdown: 'hw_thermal_slowdown',
+            nv.nvmlClocksEventReasonSwThermalSlowdown: 'sw_thermal_slowdown',
+            nv.nvmlClocksEventReasonSwPowerCap: 'sw_power_cap',
+            nv.nvmlClocksEventReasonHwPowerBrakeSlowdown: 'hw_power_brake_slowdown',
+            nv.nvmlClocksEventReasonApplicationsClocksSetting: 'applications_clocks_setting',
+        }
+        while not self.stop_ev.is_set():
+            try:
+                self.sm.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+            except Exception as e:                     # noqa: BLE001
+                self.err = repr(e)
+                break
+            self.stop_ev.wait(0.1)
+
+    def finish(self):
+        self.stop_ev.set()
+        self.join(timeout=2.0)
+        out = {'sm_mhz': float(np.median(self.sm)) if self.sm else None, 'sm_max_mhz': self.sm_max,
+               'reasons': sorted(self.reasons), 'samples': len(self.sm)}
+        if self.power:
+            out['power_w_max'] = round(max(self.power), 1)
+        if self.err:
+            out['error'] = self.err
+        return out
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def base_line(args, value, ms_per_step):
+    width, depth, length, contexts, docs, chars, what = WORKLOADS[args.workload]
+    docs = args.docs or docs
+    chars = args.chars or chars
+    return {
+        'metric': 'chars/sec rated (stateful LSTM LM)',
+        'value': value,
+        'unit': 'chars/s',
+        'n_gpus': args.gpus,
+        'steps': args.steps,
+        'warmup': args.warmup,
+        'ms_per_step': ms_per_step,
+        'higher_is_better': True,
+        'scaling': 'weak',
+        'vs_baseline': None,
+        'dtype': 'f32',
+        'data': 'synthetic (seeded Zipf-like text, random-init Keras-default weights; SURVEY.md 8d)',
+        'config': {'workload': '%s: %s' % (args.workload, what), 'width': width, 'depth': depth, 'length': length,
+                   'voc_size': 256, 'n_ctx': len(contexts), 'ctx_dim': contexts[0][1],
+                   'docs_per_gpu': docs, 'chars_per_doc': chars if args.workload != 'cfg5' else 'U{20..120}',
+                   'flops_per_char': flops_per_char(width, depth, contexts),
+                   'l2': 'flushed (512 MiB write) between timed steps'},
+    }
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from ocrd_keraslm_b200 import _native
+    from ocrd_keraslm_b200.lib import Rater
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit('bench.py --gpus %d must be launched with torchrun (one rank per GPU)' % args.gpus)
+        args.gpus = world
+    # ---- CPU baseline beside it (rank 0, N=1 only); runs first, before CUDA is initialised (it forks) ----
+    cpu_line = None
+    if world == 1 and not args.no_cpu:
+        arm = CpuArm(args.workload)
+        n_chars = cpu_sample_chars(args.workload)
+        arm.prepare(n_chars)
+        arm.step(min(n_chars, 129))
+        c, dt = arm.step(n_chars)
+        arm.close()
+        cpu_line = {
+            'value': c / dt, 'unit': 'chars/s', 'cores': arm.procs, 'kind': 'port',
+            'sample': '%d processes x 1 document x %d chars (of %s), %.1f s' % (arm.procs, n_chars,
+                                                                               WORKLOADS[args.workload][6], dt)}
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU arm)')
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+
+    wl = args.workload
+    width, depth, length, contexts, docs, chars, what = WORKLOADS[wl]
+    docs = args.docs or docs
+    chars = args.chars or chars
+    F = flops_per_char(width, depth, contexts)
+
+    wd = model_weights(wl)
+    rater = Rater.from_weights(wd, synth.vocabulary(), length, logger=quiet, device=local)
+    native = rater._native
+    texts, ctxs = make_docs(wl, docs, chars, rank * docs)
+
+    # ---- device-resident form of the batch (tokenised once, outside the timed region) ----
+    lens = np.array([max(len(t) - 1, 0) for t in texts], dtype=np.int64)
+    order = np.argsort(-lens, kind='stable')
+    offsets = np.zeros(docs + 1, dtype=np.int64)
+    offsets[1:] = np.cumsum(lens[order])
+    total = int(offsets[-1])
+    h_chars = np.empty(total, dtype=np.int32)
+    h_targets = np.empty(total, dtype=np.int32)
+    for j, i in enumerate(order):
+        idx, _ = rater._indices(texts[i])
+        h_chars[offsets[j]:offsets[j + 1]] = idx[:-1]
+        h_targets[offsets[j]:offsets[j + 1]] = idx[1:]
+    ctx_rows = np.array([ctxs[i] for i in order], dtype=np.int32)
+    d_chars = torch.from_numpy(h_chars).cuda()
+    d_targets = torch.from_numpy(h_targets).cuda()
+    d_out = torch.empty(total, dtype=torch.float32, device='cuda')
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device='cuda')
+    stream = torch.cuda.current_stream()
+    native.set_stream(stream.cuda_stream)
+    slots = rater._pool.acquire(docs)
+    chars_per_step = int(lens.sum())                 # characters scored (the first of each document is free)
+
+    def device_step():
+        native.state_reset(slots)
+        native.rate(slots, offsets, d_chars.data_ptr(), d_targets.data_ptr(), None, ctx_rows, d_out.data_ptr(),
+                    mem=_native.MEM_DEVICE)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(args.warmup):
+        device_step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    launches0 = native.info()['kernel_launches']
+    barrier()
+    torch.cuda.synchronize()
+    sampler.start()
+    step_ms, kernel_ms = [], []
+    wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()                                # untimed: evict the batch from L2
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        device_step()
+        e1.record(stream)
+        e1.synchronize()
+        step_ms.append(e0.elapsed_time(e1))
+        kernel_ms.append(native.info()['last_kernel_ms'])
+    torch.cuda.synchronize()
+    barrier()
+    wall = time.perf_counter() - wall0
+    clocks = sampler.finish()
+    launches = native.info()['kernel_launches'] - launches0
+    checksum = float(d_out.double().sum().item())
+
+    total_ms = float(sum(step_ms))
+    if world > 1:
+        t = torch.tensor([total_ms], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+        cs = torch.tensor([checksum, float(launches)], dtype=torch.float64, device='cuda')
+        dist.all_reduce(cs, op=dist.ReduceOp.SUM)
+        checksum, launches = float(cs[0].item()), int(cs[1].item())
+    value = world * chars_per_step * args.steps / (total_ms / 1000.0)
+
+    # ---- end to end through the public API: strings in, probabilities out ----
+    for _ in range(min(args.warmup, 2)):
+        rater.rate_many(texts, ctxs)
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res = rater.rate_many(texts, ctxs)
+    native.sync()
+    e2e_t = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_t], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_t = float(t.item())
+    e2e_value = world * chars_per_step * args.steps / e2e_t
+    e2e_checksum = float(sum(np.log(np.maximum(r[1:].astype(np.float64), 1e-300)).sum() for r in res))
+    h2d = 2 * 4 * total + docs * (4 * 2 + 8 + 4 * len(contexts))
+    d2h = 4 * total
+
+    # ---- roofline of the dominant kernel (the persistent sequence kernel; one launch per step) ----
+    pk, pk_src = peaks()
+    info = native.info()
+    k_ms = float(np.mean(kernel_ms))
+    achieved = chars_per_step * F / (k_ms / 1000.0) / 1e12
+    peak = float(pk.get('bf16_tflops_sustained', FALLBACK_PEAKS['bf16_tflops_sustained']))
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
+            tj = json.load(f)
+        if tj.get(wl, {}).get('dram_bytes_per_char') is not None:
+            traffic = tj[wl]['dram_bytes_per_char'] * chars_per_step
+    except Exception:
+        pass
+    roofline = {
+        'bound': 'tensor', 'kernel': info.get('kernel_name', 'klm_seq'), 'achieved': achieved, 'peak': peak,
+        'unit': 'TFLOP/s', 'frac': achieved / peak, 'traffic': traffic, 'peak_source': pk_src + ', bf16 sustained',
+        'kernel_ms': k_ms, 'algorithmic_flops_per_launch': chars_per_step * F,
+        'algorithmic_hbm_bytes_per_launch': 8 * chars_per_step,
+        'hbm_frac': (8 * chars_per_step / (k_ms / 1000.0) / 1e9) / float(pk.get('hbm_gbs', FALLBACK_PEAKS['hbm_gbs'])),
+        'grid': info['grid'], 'smem_bytes': info['smem_bytes'], 'weights_in_smem': info['weights_in_smem'],
+    }
+
+    line = base_line(args, value, total_ms / args.steps)
+    line.update({
+        'e2e': {'value': e2e_value, 'unit': 'chars/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+                'api': 'Rater.rate_many(texts, contexts) -> klm_rate(KLM_MEM_HOST)', 'ms_per_step': 1000 * e2e_t / args.steps},
+        'gpu_launches': launches,
+        'clocks': clocks,
+        'roofline': roofline,
+        'checksum_logp': checksum,
+        'e2e_checksum_logp': e2e_checksum,
+        'wall_s_timed_region': wall,
+    })
+
+    if cpu_line is not None:
+        line['cpu_baseline'] = cpu_line
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=3)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--workload', default='cfg2', choices=sorted(WORKLOADS))
+    ap.add_argument('--docs', type=int, default=0, help='documents per GPU (default: the workload\'s)')
+    ap.add_argument('--chars', type=int, default=0, help='characters per document (default: the workload\'s)')
+    ap.add_argument('--no-cpu', action='store_true', help='skip the CPU baseline leg')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

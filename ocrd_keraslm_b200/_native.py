@@ -118,6 +118,13 @@ def _ptr(a):
     return int(a)
 
 
+def pinned_empty(n, dtype):
+    """Page-locked host array (through torch, which is only the buffer carrier here)."""
+    import torch
+    tdt = {np.dtype(np.int32): torch.int32, np.dtype(np.float32): torch.float32}[np.dtype(dtype)]
+    return torch.empty(int(n), dtype=tdt, pin_memory=True).numpy()
+
+
 def _i32(a):
     return np.ascontiguousarray(a, dtype=np.int32)
 

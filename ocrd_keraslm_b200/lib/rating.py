@@ -208,6 +208,7 @@ class Rater(object):
         self._lut = None
         self._lut_src = None
         self._pending_weights = None
+        self._pin = None
 
     # ------------------------------------------------------------------ lifecycle
     def load_config(self, filename):
@@ -454,8 +455,7 @@ class Rater(object):
         offsets = np.zeros(n + 1, dtype=np.int64)
         offsets[1:] = np.cumsum(lens[order])
         total = int(offsets[-1])
-        chars = np.empty(total, dtype=np.int32)
-        targets = np.empty(total, dtype=np.int32)
+        chars, targets, logp = self._pinned(total)
         for j, i in enumerate(order):
             if lens[i] == 0:
                 continue
@@ -464,7 +464,6 @@ class Rater(object):
                 self.logger.error('unmapped character "%s" at input position %d', norm[i][t], int(t))
             chars[offsets[j]:offsets[j + 1]] = idx[:-1]
             targets[offsets[j]:offsets[j + 1]] = idx[1:]
-        logp = np.empty(total, dtype=np.float32)
         if total:
             slots = self._pool.acquire(n)
             try:
@@ -481,6 +480,14 @@ class Rater(object):
             else:
                 out[i] = np.concatenate([np.ones(min(len(norm[i]), 1), np.float32), np.exp(seg)])
         return out
+
+    def _pinned(self, total):
+        """Page-locked index/score buffers for a batch of `total` positions (grow-only, reused)."""
+        if self._pin is None or len(self._pin[0]) < total:
+            cap = total + total // 8 + 1024
+            self._pin = (_native.pinned_empty(cap, np.int32), _native.pinned_empty(cap, np.int32),
+                         _native.pinned_empty(cap, np.float32))
+        return tuple(a[:total] for a in self._pin)
 
     def test(self, test_data):
         """Perplexity over text files (reference :462-491, :977-1002).
