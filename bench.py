@@ -337,7 +337,8 @@ def run_ours(args):
     d_targets = torch.from_numpy(h_targets).cuda()
     d_out = torch.empty(total, dtype=torch.float32, device='cuda')
     flush = torch.empty(512 << 20, dtype=torch.uint8, device='cuda')
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()              # a real (non-NULL) stream: NULL would mean "the library's own"
+    torch.cuda.set_stream(stream)
     native.set_stream(stream.cuda_stream)
     slots = rater._pool.acquire(docs)
     chars_per_step = int(lens.sum())                 # characters scored (the first of each document is free)
