@@ -136,9 +136,16 @@ typedef struct klm_info {
     int64_t kernel_launches;    /* kernels of this library launched so far on this model */
     double  last_kernel_ms;     /* device time of the last klm_rate/klm_step main kernel (CUDA events) */
     int32_t max_streams;        /* largest n one launch takes; larger calls are split */
-    int32_t reserved;
+    int32_t tc_enabled;         /* 1 if the tcgen05 sequence kernel serves 9..64 streams for this model */
+    int32_t tc_grid;            /* CTAs of the tcgen05 kernel */
+    int32_t tc_smem_bytes;      /* dynamic shared memory per CTA of the tcgen05 kernel */
+    int64_t tc_launches;        /* launches of the tcgen05 kernel so far */
 } klm_info;
 int klm_get_info(klm_model *m, klm_info *out);
+
+/* Self-test of the tcgen05 / TMEM / bulk-copy building blocks: D[128 x N] = A[128 x K] . B[N x K]^T for
+ * fp16 operand images in the kernel's shared-memory layout ([K/8][rows][8] halves); host pointers. */
+int klm_selftest_umma(int device, int32_t N, int32_t K, const uint16_t *A_img, const uint16_t *B_img, float *D);
 
 #ifdef __cplusplus
 }

@@ -13,7 +13,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB_PATH = os.path.join(HERE, 'libkeraslm_b200.so')
-SOURCES = ['klm_api.cu', 'klm_seq_fma.cu']
+SOURCES = ['klm_api.cu', 'klm_seq_fma.cu', 'klm_seq_tc.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-shared', '-Xcompiler', '-fPIC']
 
@@ -66,7 +66,8 @@ class KlmConfig(ctypes.Structure):
 class KlmInfo(ctypes.Structure):
     _fields_ = [('sm_count', ctypes.c_int32), ('grid', ctypes.c_int32), ('weights_in_smem', ctypes.c_int32),
                 ('smem_bytes', ctypes.c_int32), ('kernel_launches', ctypes.c_int64),
-                ('last_kernel_ms', ctypes.c_double), ('max_streams', ctypes.c_int32), ('reserved', ctypes.c_int32)]
+                ('last_kernel_ms', ctypes.c_double), ('max_streams', ctypes.c_int32), ('tc_enabled', ctypes.c_int32),
+                ('tc_grid', ctypes.c_int32), ('tc_smem_bytes', ctypes.c_int32), ('tc_launches', ctypes.c_int64)]
 
 
 # every symbol include/keraslm_b200.h declares: (name, restype, argtypes)
@@ -87,6 +88,7 @@ SYMBOLS = [
     ('klm_rate', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
     ('klm_step', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
     ('klm_get_info', ctypes.c_int, [_P, ctypes.POINTER(KlmInfo)]),
+    ('klm_selftest_umma', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
 ]
 
 _lib = None
@@ -127,6 +129,27 @@ def pinned_empty(n, dtype):
 
 def _i32(a):
     return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def operand_image(mat):
+    """fp16 [rows, K] -> the kernels' shared-memory operand layout [K/8][rows][8] (as uint16)."""
+    rows, K = mat.shape
+    assert K % 8 == 0
+    return np.ascontiguousarray(mat.astype(np.float16).reshape(rows, K // 8, 8).transpose(1, 0, 2)).view(np.uint16)
+
+
+def selftest_umma(A, B, device=0):
+    """D = A . B^T on the tensor cores through the library's self-test kernel; A [128, K], B [N, K] (fp16 values)."""
+    lib = load()
+    A = np.asarray(A, dtype=np.float16)
+    B = np.asarray(B, dtype=np.float16)
+    assert A.shape[0] == 128 and A.shape[1] == B.shape[1]
+    D = np.empty((128, B.shape[0]), dtype=np.float32)
+    ai, bi = operand_image(A), operand_image(B)
+    rc = lib.klm_selftest_umma(device, B.shape[0], A.shape[1], ai.ctypes.data, bi.ctypes.data, D.ctypes.data)
+    if rc != 0:
+        raise NativeError('klm_selftest_umma: %s' % lib.klm_last_error().decode())
+    return D
 
 
 class Model(object):

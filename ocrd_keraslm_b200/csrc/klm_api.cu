@@ -12,6 +12,8 @@
 #include "klm_common.cuh"
 
 cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cudaStream_t stream);
+cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
+cudaError_t klm_launch_umma_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
 
 // ------------------------------------------------------------------------------------------
 static thread_local std::string g_err;
@@ -47,6 +49,19 @@ struct KlmPlan {
     int max_streams = 0;
 };
 
+// Plan of the tensor-core sequence kernel (klm_seq_tc.cu): one role per CTA + the B images.
+struct KlmTcPlan {
+    bool ok = false;
+    std::vector<KlmTcRole> roles;
+    KlmTcRole *d_roles = nullptr;
+    unsigned char *d_wimg = nullptr;
+    int grid = 0, stages = 0, Vp = 0;
+    size_t smem = 0;
+    __half *hx = nullptr;
+    float *Z = nullptr, *logits = nullptr;
+    int *err = nullptr;
+};
+
 #define KLM_RING 4
 struct klm_model {
     int device = 0;
@@ -59,6 +74,7 @@ struct klm_model {
     float4 *P = nullptr, *Q[KLM_MAX_CTX] = {}, *Wl[KLM_MAX_DEPTH] = {}, *bias[KLM_MAX_DEPTH] = {}, *Ep = nullptr;
     // plans
     KlmPlan plan_k, plan_b;
+    KlmTcPlan tc;
     // scratch
     float *hbuf = nullptr, *logits = nullptr;
     unsigned int *barrier = nullptr;
@@ -78,7 +94,7 @@ struct klm_model {
     // stats
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
-    long long launches = 0;
+    long long launches = 0, tc_launches = 0;
 };
 
 // ------------------------------------------------------------------------------------------
@@ -213,6 +229,106 @@ static int make_plan(klm_model *m, bool kpar, KlmPlan *pl) {
     return KLM_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// Tensor-core plan: distributes the columns of R_l (REC), K_l (IN, l >= 1) and the rows of E (PROJ)
+// over the SMs in pairs of units (8 columns), builds each CTA's fp16 hi/lo B image in the shared
+// memory operand layout [W/8][2N][8], and allocates the exchange buffers.  Not eligible (ok stays
+// false, the FMA kernels take over) if W is not a multiple of 64, a weight overflows fp16, or the
+// images do not fit the shared memory of the device.
+static int make_tc_plan(klm_model *m, const float *E, const float *const *L) {
+    KlmTcPlan &pl = m->tc;
+    const int W = m->W, D = m->D, V = m->V;
+    if (getenv("KLM_DISABLE_TC")) return KLM_OK;
+    if (W % KLM_TC_KC != 0 || W < KLM_TC_KC) return KLM_OK;
+    const int nchunks = W / KLM_TC_KC;
+    pl.stages = std::min(3, nchunks);
+    pl.Vp = (V + 7) / 8 * 8;
+    const size_t fixed = (size_t)pl.stages * KLM_TC_CHUNK_BYTES + KLM_TC_XCHG_BYTES + 128;
+    if (fixed + 32 * (size_t)W > m->smem_optin) return KLM_OK;
+    const int pairs_max = (int)std::min<size_t>(KLM_TC_MAX_PAIRS, (m->smem_optin - fixed) / (32 * (size_t)W));
+    if (pairs_max < 1) return KLM_OK;
+
+    struct Ty { int kind, layer, src, sigma, pairs, n; const float *mat; };
+    std::vector<Ty> tys;
+    for (int l = 0; l < D; ++l) {
+        if (l > 0) tys.push_back({KLM_TC_IN, l, l - 1, 2 * l - 1, W / 2, 0, L[3 * l]});
+        tys.push_back({KLM_TC_REC, l, l, 2 * l, W / 2, 0, L[3 * l + 1]});
+    }
+    tys.push_back({KLM_TC_PROJ, 0, D - 1, 2 * D - 1, pl.Vp / 8, 0, E});
+    const int n_lse = 1;
+    int used = n_lse;
+    for (auto &t : tys) { t.n = (t.pairs + pairs_max - 1) / pairs_max; used += t.n; }
+    if (used > m->sm_count) return KLM_OK;
+    while (used < m->sm_count) {                      // spare SMs go to the stage with the widest slices
+        int best = -1; double load = 0;
+        for (int i = 0; i < (int)tys.size(); ++i) {
+            if (tys[i].n >= tys[i].pairs) continue;
+            const double ld = std::ceil((double)tys[i].pairs / tys[i].n);
+            if (ld > load) { load = ld; best = i; }
+        }
+        if (best < 0 || load <= 1) break;
+        tys[best].n++; used++;
+    }
+    // fp16 range check
+    {
+        float mx = 0.f;
+        for (auto &t : tys) {
+            const size_t cnt = t.kind == KLM_TC_PROJ ? (size_t)V * W : (size_t)W * 4 * W;
+            for (size_t i = 0; i < cnt; ++i) mx = std::max(mx, std::fabs(t.mat[i]));
+        }
+        if (!(mx < 60000.f)) return KLM_OK;
+    }
+    std::vector<__half> img;
+    int max_pairs = 0;
+    for (auto &t : tys) {
+        const int base = t.pairs / t.n, rem = t.pairs % t.n;
+        int first = 0;
+        for (int c = 0; c < t.n; ++c) {
+            const int np = base + (c < rem ? 1 : 0);
+            const int N = 8 * np;
+            KlmTcRole r = {t.kind, t.layer, t.src, t.sigma, first, np, (long long)(img.size() * sizeof(__half))};
+            pl.roles.push_back(r);
+            const size_t o = img.size();
+            img.resize(o + (size_t)W * 2 * N);
+            for (int j = 0; j < N; ++j) {
+                for (int k = 0; k < W; ++k) {
+                    float val;
+                    if (t.kind == KLM_TC_PROJ) {
+                        const int v = 8 * first + j;
+                        val = v < V ? t.mat[(size_t)v * W + k] : 0.f;
+                    } else {
+                        const int u = 2 * first + j / 4, g = j % 4;
+                        val = t.mat[(size_t)k * 4 * W + g * W + u];
+                    }
+                    const __half hi = __float2half_rn(val);
+                    const __half lo = __float2half_rn(val - __half2float(hi));
+                    img[o + ((size_t)(k / 8) * 2 * N + j) * 8 + (k % 8)] = hi;
+                    img[o + ((size_t)(k / 8) * 2 * N + N + j) * 8 + (k % 8)] = lo;
+                }
+            }
+            first += np;
+            max_pairs = std::max(max_pairs, np);
+        }
+    }
+    for (int i = 0; i < n_lse; ++i) pl.roles.push_back({KLM_TC_LSE, 0, 0, 2 * D, i, n_lse, 0});
+    pl.grid = (int)pl.roles.size();
+    pl.smem = fixed + (size_t)32 * W * max_pairs;
+    CK(cudaMalloc(&pl.d_roles, pl.roles.size() * sizeof(KlmTcRole)));
+    CK(cudaMemcpy(pl.d_roles, pl.roles.data(), pl.roles.size() * sizeof(KlmTcRole), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&pl.d_wimg, img.size() * sizeof(__half)));
+    CK(cudaMemcpy(pl.d_wimg, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    const size_t hx_bytes = (size_t)D * 2 * W * 128 * sizeof(__half);
+    const size_t z_bytes = (size_t)D * 2 * 64 * 4 * W * sizeof(float);
+    const size_t lg_bytes = (size_t)2 * 64 * pl.Vp * sizeof(float);
+    CK(cudaMalloc(&pl.hx, hx_bytes)); CK(cudaMemset(pl.hx, 0, hx_bytes));
+    CK(cudaMalloc(&pl.Z, z_bytes)); CK(cudaMemset(pl.Z, 0, z_bytes));
+    CK(cudaMalloc(&pl.logits, lg_bytes)); CK(cudaMemset(pl.logits, 0, lg_bytes));
+    CK(cudaMalloc(&pl.err, 256)); CK(cudaMemset(pl.err, 0, 256));
+    // the kernel is launched cooperatively: all CTAs must be co-resident
+    pl.ok = true;
+    return KLM_OK;
+}
+
 template <typename T> static int upload(T **dst, const std::vector<T> &src) {
     CK(cudaMalloc(dst, src.size() * sizeof(T)));
     CK(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
@@ -227,6 +343,8 @@ extern "C" int klm_destroy(klm_model *m) {
     for (int i = 0; i < KLM_MAX_CTX; ++i) cudaFree(m->Q[i]);
     for (int i = 0; i < KLM_MAX_DEPTH; ++i) { cudaFree(m->Wl[i]); cudaFree(m->bias[i]); }
     cudaFree(m->plan_k.d_roles); cudaFree(m->plan_b.d_roles);
+    cudaFree(m->tc.d_roles); cudaFree(m->tc.d_wimg); cudaFree(m->tc.hx); cudaFree(m->tc.Z); cudaFree(m->tc.logits);
+    cudaFree(m->tc.err);
     cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
     for (int i = 0; i < KLM_RING; ++i) {
         if (m->h_ring[i]) cudaFreeHost(m->h_ring[i]);
@@ -335,6 +453,7 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
     }
     TRY(make_plan(m, true, &m->plan_k));
     TRY(make_plan(m, false, &m->plan_b));
+    TRY(make_tc_plan(m, E, L));
 
     m->bp_cap = std::max(32, m->plan_b.max_streams);
     TRYC(cudaMalloc(&m->hbuf, (size_t)D * 2 * W * m->bp_cap * 4));
@@ -354,6 +473,8 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
 }
 
 // ------------------------------------------------------------------------------------------
+static int check_device_error(klm_model *m);
+
 extern "C" int klm_set_stream(klm_model *m, void *s) {
     if (!m) return fail(KLM_EINVAL, "NULL model");
     m->stream = s ? (cudaStream_t)s : m->own_stream;
@@ -363,7 +484,7 @@ extern "C" int klm_sync(klm_model *m) {
     if (!m) return fail(KLM_EINVAL, "NULL model");
     CK(cudaSetDevice(m->device));
     CK(cudaStreamSynchronize(m->stream));
-    return KLM_OK;
+    return check_device_error(m);
 }
 
 // Small per-call arrays travel through a ring of pinned buffers: one H2D copy per call.
@@ -512,6 +633,36 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     RingSlot rs;
     int rc = ring_acquire(m, &rs, (size_t)nb * (4 * 3 + 4 * m->Nc) + (nb + 1) * 8 + 128);
     if (rc) return rc;
+    if (m->tc.ok && nb > KLM_MODEK_MAXB && nb <= KLM_TC_STREAMS) {
+        if ((double)(tmax + 2 * m->D + 2) * m->tc.grid >= 4.0e9)
+            return fail(KLM_EINVAL, "stream of %lld positions is too long for one launch", tmax);
+        KlmTcParams q;
+        memset(&q, 0, sizeof q);
+        int *d_si, *d_so, *d_nr = nullptr, *d_cx;
+        long long *d_off;
+        ring_put(&rs, slots_in, nb, &d_si);
+        ring_put(&rs, slots_out, nb, &d_so);
+        ring_put(&rs, reinterpret_cast<const long long *>(offsets0), nb + 1, &d_off);
+        if (n_real) ring_put(&rs, n_real, nb, &d_nr);
+        int *hcx = ring_put<int>(&rs, nullptr, (size_t)nb * std::max(1, m->Nc), &d_cx);
+        for (int i = 0; i < nb * m->Nc; ++i) hcx[i] = ctx ? ctx[i] : 0;
+        rc = ring_commit(m, &rs); if (rc) return rc;
+        q.W = m->W; q.D = m->D; q.V = m->V; q.Vp = m->tc.Vp; q.Nc = m->Nc;
+        q.B = nb; q.T_max = (int)tmax; q.stages = m->tc.stages;
+        for (int k = 0; k < m->Nc; ++k) { q.ctx_rows[k] = m->cfg.ctx_rows[k]; q.Q[k] = m->Q[k]; }
+        q.P = m->P;
+        for (int l = 0; l < m->D; ++l) q.bias[l] = m->bias[l];
+        q.wimg = m->tc.d_wimg; q.roles = m->tc.d_roles;
+        q.hx = m->tc.hx; q.Z = m->tc.Z; q.logits = m->tc.logits;
+        q.state = m->state; q.slots_in = d_si; q.slots_out = d_so; q.offsets = d_off;
+        q.chars = d_chars; q.targets = d_targets; q.n_real = d_nr; q.ctx = d_cx;
+        q.out = d_out; q.full_rows = full_rows;
+        q.barrier = m->barrier; q.err = m->tc.err;
+        CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
+        CK(klm_launch_seq_tc(q, m->tc.grid, m->tc.smem, m->stream));
+        m->launches++; m->tc_launches++;
+        return KLM_OK;
+    }
     KlmSeqParams p;
     memset(&p, 0, sizeof p);
     int *d_si, *d_so, *d_nr = nullptr, *d_cx;
@@ -537,6 +688,22 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
     CK(klm_launch_seq_fma(p, pl.grid, pl.smem, m->stream));
     m->launches++;
+    return KLM_OK;
+}
+
+// Largest number of streams one launch takes for a call of n streams.
+static int batch_max(klm_model *m, int n) {
+    if (n <= KLM_MODEK_MAXB) return KLM_MODEK_MAXB;
+    if (m->tc.ok) return KLM_TC_STREAMS;
+    return m->plan_b.max_streams;
+}
+
+// Device-side watchdog of the tensor-core kernel: a wait that timed out leaves a code in tc.err.
+static int check_device_error(klm_model *m) {
+    if (!m->tc.ok || m->tc_launches == 0) return KLM_OK;
+    int code = 0;
+    CK(cudaMemcpy(&code, m->tc.err, sizeof code, cudaMemcpyDeviceToHost));
+    if (code != 0) return fail(KLM_ECUDA, "klm_seq_tc: device-side wait timed out (code %d)", code);
     return KLM_OK;
 }
 
@@ -585,7 +752,7 @@ extern "C" int klm_rate(klm_model *m, int32_t n, const int32_t *slots, const int
         dc = chars + base; dt = targets + base; dout = out_logp + base;
     }
     CK(cudaEventRecord(m->ev0, m->stream));
-    const int bmax = (n <= KLM_MODEK_MAXB) ? KLM_MODEK_MAXB : m->plan_b.max_streams;
+    const int bmax = batch_max(m, n);
     std::vector<int64_t> off0;
     for (int s0 = 0; s0 < n; s0 += bmax) {
         const int nb = std::min(bmax, n - s0);
@@ -600,6 +767,7 @@ extern "C" int klm_rate(klm_model *m, int32_t n, const int32_t *slots, const int
     if (mem == KLM_MEM_HOST) {
         CK(cudaMemcpyAsync(out_logp + base, m->d_out, (size_t)total * 4, cudaMemcpyDeviceToHost, m->stream));
         CK(cudaStreamSynchronize(m->stream));
+        return check_device_error(m);
     }
     return KLM_OK;
 }
@@ -626,7 +794,7 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
     if (targets) CK(cudaMemcpyAsync(m->d_targets, targets, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
     float *dout = (mem == KLM_MEM_HOST) ? m->d_out : out;
     CK(cudaEventRecord(m->ev0, m->stream));
-    const int bmax = (n <= KLM_MODEK_MAXB) ? KLM_MODEK_MAXB : m->plan_b.max_streams;
+    const int bmax = batch_max(m, n);
     std::vector<int64_t> off0;
     for (int s0 = 0; s0 < n; s0 += bmax) {
         const int nb = std::min(bmax, n - s0);
@@ -641,6 +809,7 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
     if (mem == KLM_MEM_HOST) {
         CK(cudaMemcpyAsync(out, m->d_out, nout * 4, cudaMemcpyDeviceToHost, m->stream));
         CK(cudaStreamSynchronize(m->stream));
+        return check_device_error(m);
     }
     return KLM_OK;
 }
@@ -653,7 +822,11 @@ extern "C" int klm_get_info(klm_model *m, klm_info *out) {
     out->weights_in_smem = m->plan_b.wsmem;
     out->smem_bytes = (int32_t)m->plan_b.smem;
     out->kernel_launches = m->launches;
-    out->max_streams = m->plan_b.max_streams;
+    out->max_streams = m->tc.ok ? KLM_TC_STREAMS : m->plan_b.max_streams;
+    out->tc_enabled = m->tc.ok ? 1 : 0;
+    out->tc_grid = m->tc.grid;
+    out->tc_smem_bytes = (int32_t)m->tc.smem;
+    out->tc_launches = m->tc_launches;
     if (m->timed) {
         CK(cudaSetDevice(m->device));
         CK(cudaEventSynchronize(m->ev1));
@@ -661,5 +834,29 @@ extern "C" int klm_get_info(klm_model *m, klm_info *out) {
         CK(cudaEventElapsedTime(&ms, m->ev0, m->ev1));
         out->last_kernel_ms = ms;
     }
+    return KLM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Self-test of the tcgen05 / TMEM / bulk-copy building blocks (tests/): D[128 x N] = A . B^T for fp16
+// operand images in the kernel's shared-memory layout ([K/8][rows][8] halves).  Host pointers.
+extern "C" int klm_selftest_umma(int device, int32_t N, int32_t K, const uint16_t *A_img, const uint16_t *B_img, float *D) {
+    if (!A_img || !B_img || !D) return fail(KLM_EINVAL, "klm_selftest_umma: NULL argument");
+    if (N < 16 || N > 256 || N % 16 || K < 16 || K % 16 || (size_t)K * (128 + N) * 2 > 200 * 1024)
+        return fail(KLM_EINVAL, "klm_selftest_umma: unsupported shape N=%d K=%d", N, K);
+    CK(cudaSetDevice(device));
+    __half *dA = nullptr, *dB = nullptr; float *dD = nullptr; int *derr = nullptr;
+    CK(cudaMalloc(&dA, (size_t)K * 128 * 2)); CK(cudaMalloc(&dB, (size_t)K * N * 2));
+    CK(cudaMalloc(&dD, (size_t)128 * N * 4)); CK(cudaMalloc(&derr, 4));
+    CK(cudaMemcpy(dA, A_img, (size_t)K * 128 * 2, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dB, B_img, (size_t)K * N * 2, cudaMemcpyHostToDevice));
+    CK(cudaMemset(dD, 0, (size_t)128 * N * 4)); CK(cudaMemset(derr, 0, 4));
+    CK(klm_launch_umma_selftest(dA, dB, dD, N, K, derr, 0));
+    CK(cudaDeviceSynchronize());
+    int code = 0;
+    CK(cudaMemcpy(&code, derr, 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(D, dD, (size_t)128 * N * 4, cudaMemcpyDeviceToHost));
+    cudaFree(dA); cudaFree(dB); cudaFree(dD); cudaFree(derr);
+    if (code) return fail(KLM_ECUDA, "klm_selftest_umma: device-side wait timed out (code %d)", code);
     return KLM_OK;
 }

@@ -16,6 +16,7 @@
 //   bias[l][W] float4     l > 1 (layer 1's bias is folded into P)
 //   Ep [V4/4][W] float4   output projection: four vocabulary rows of E per "unit"
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/keraslm_b200.h"
@@ -63,4 +64,52 @@ struct KlmSeqParams {
     const KlmRole *roles;         // [grid]
     int wsmem;                    // weights slice cached in shared memory
     int stage_floats;             // floats of staging area
+};
+
+// ---------------------------------------------------------------------------------------------
+// Tensor-core sequence kernel (klm_seq_tc.cu)
+#define KLM_TC_THREADS      192
+#define KLM_TC_STREAMS      64                     // accumulator rows 0..63 = hi part, 64..127 = lo part
+#define KLM_TC_KC           64                     // k per ring chunk
+#define KLM_TC_CHUNK_BYTES  (KLM_TC_KC / 8 * 128 * 16)
+#define KLM_TC_OWN          5                      // pairs of units finished by one epilogue thread
+#define KLM_TC_MAX_PAIRS    (2 * KLM_TC_OWN)       // N <= 80 columns per CTA
+#define KLM_TC_XCHG_BYTES   (KLM_TC_OWN * 8 * 64 * 4)
+#define KLM_TC_TMEM_COLS    256
+
+#define KLM_TC_REC  0
+#define KLM_TC_IN   1
+#define KLM_TC_PROJ 2
+#define KLM_TC_LSE  3
+
+struct KlmTcRole {
+    int kind;          // KLM_TC_*
+    int layer;         // LSTM layer (REC, IN)
+    int src_layer;     // whose hidden vector is the A operand
+    int sigma;         // wavefront stage: works on position tick - sigma
+    int first_pair;    // first pair of units (REC/IN), first group of 8 vocabulary rows (PROJ), LSE index (LSE)
+    int npairs;        // pairs owned (N = 8 * npairs columns); number of LSE CTAs (LSE)
+    long long wofs;    // byte offset of the CTA's B image in wimg
+};
+
+struct KlmTcParams {
+    int W, D, V, Vp, Nc;
+    int B, T_max, stages;
+    int ctx_rows[KLM_MAX_CTX];
+    const float4 *P;
+    const float4 *Q[KLM_MAX_CTX];
+    const float4 *bias[KLM_MAX_DEPTH];
+    const unsigned char *wimg;
+    const KlmTcRole *roles;
+    __half *hx;                   // [D][2][W/8][128][8]
+    float *Z;                     // [D][2][64][4W]  (unit-interleaved gate columns)
+    float *logits;                // [2][64][Vp]
+    float *state;
+    const int *slots_in, *slots_out;
+    const long long *offsets;
+    const int *chars, *targets, *n_real, *ctx;
+    float *out;
+    int full_rows;
+    unsigned int *barrier;
+    int *err;                     // device-side watchdog: non-zero = a wait timed out (code says which)
 };

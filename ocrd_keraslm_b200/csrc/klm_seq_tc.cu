@@ -1,0 +1,508 @@
+// Persistent stacked-LSTM sequence kernel on the 5th-generation tensor cores (tcgen05 + TMEM),
+// for 9..64 concurrent streams / hypotheses.
+//
+// Replaces the per-window Session.run of Rater.rate (rating.py:516) and the per-step one of
+// Rater.predict (:631) when many streams advance together (rate_many, beams).
+//
+// Every CTA owns, for the whole launch, N <= 80 columns of ONE weight matrix, resident in shared
+// memory as an fp16 hi/lo split in the tcgen05 operand layout ("B image", [W/8][2N][8] halves,
+// rows 0..N-1 = hi, N..2N-1 = lo):
+//   REC l : recurrent kernel R_l of LSTM layer l          (gate columns unit-interleaved i,f,c,o)
+//   IN  l : input kernel K_l of layer l >= 1               (layer 1's input is the table P, no GEMM)
+//   PROJ  : rows of the char embedding E (tied output projection)
+//   LSE   : no weights; log-sum-exp over the logits, target pick / full softmax rows
+// Per tick a GEMM CTA computes D[128 x 2N] = A[128 x W] . B[2N x W]^T where A is one layer's
+// hidden vector for all 64 streams, rows 0..63 the fp16 hi part and rows 64..127 the lo part,
+// fetched from the exchange buffer `hx` with bulk async copies through an mbarrier ring.
+// pre-activation = D[s][j] + D[s][N+j] + D[64+s][j]   (hi.hi + hi.lo + lo.hi; lo.lo is dropped)
+//
+// Wavefront over ticks, stage sigma works on position t = tick - sigma:
+//   REC l: sigma = 2l, IN l: 2l-1, PROJ: 2D-1, LSE: 2D.   IN l writes Z_l[t] (+ bias), REC l adds it
+// one tick later, so each CTA needs exactly one hidden vector per tick.  One grid-wide barrier per
+// tick (release/acquire counter); everything handed over is double-buffered by tick parity.
+//
+// Warp roles in a GEMM CTA (192 threads): warp 0 lane 0 = producer (grid barrier wait + bulk
+// copies), warp 1 lane 0 = MMA issuer, warps 2..5 = epilogue (TMEM -> registers, hi/lo halves
+// exchanged through shared memory, LSTM cell in registers, hand-over stores).
+#include "klm_common.cuh"
+#include "klm_tc.cuh"
+
+#define TC_SPIN_LIMIT (1u << 24)
+
+__device__ __forceinline__ bool tc_spin_fail(unsigned &n, const KlmTcParams &p, int code) {
+    if ((++n & 0x3FFu) == 0) {
+        if (*(volatile int *)p.err != 0) return true;
+        if (n > TC_SPIN_LIMIT) { atomicCAS(p.err, 0, code); return true; }
+    }
+    return false;
+}
+__device__ __forceinline__ bool tc_wait_grid(const KlmTcParams &p, unsigned target, int code) {
+    unsigned n = 0;
+    while (tc::ld_acquire(p.barrier) < target)
+        if (tc_spin_fail(n, p, code)) return false;
+    return true;
+}
+__device__ __forceinline__ bool tc_wait_mbar(uint32_t bar, uint32_t parity, const KlmTcParams &p, int code) {
+    unsigned n = 0;
+    while (!tc::mbar_try_wait(bar, parity))
+        if (tc_spin_fail(n, p, code)) return false;
+    return true;
+}
+__device__ __forceinline__ void tc_bar_epi() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// exp via ex2.approx (2 ulp), reciprocal via rcp.approx: absolute error of the gates ~1e-7
+__device__ __forceinline__ float tc_exp(float x) { return exp2f(x * 1.4426950408889634f); }
+__device__ __forceinline__ float tc_clamp(float x) { return fminf(fmaxf(x, -30.f), 30.f); }
+
+// LSTM cell (Keras LSTMCell, gate order i|f|c|o, exact logistic; rating.py:133-134), 8 MUFU ops:
+//   i*g = (1 - e^-2g) / ((1 + e^-i)(1 + e^-2g)),  f = 1/(1 + e^-f),  h = o*tanh(c) likewise
+__device__ __forceinline__ void tc_cell(float ai, float af, float ag, float ao, float &c, float &h) {
+    const float ei = tc_exp(-tc_clamp(ai)), ef = tc_exp(-tc_clamp(af)), eg = tc_exp(-2.f * tc_clamp(ag)),
+                eo = tc_exp(-tc_clamp(ao));
+    const float ig = __fdividef(1.f - eg, (1.f + ei) * (1.f + eg));
+    const float f = __fdividef(1.f, 1.f + ef);
+    c = fmaf(f, c, ig);
+    const float ec = tc_exp(-2.f * tc_clamp(c));
+    h = __fdividef(1.f - ec, (1.f + eo) * (1.f + ec));
+}
+
+__device__ __forceinline__ void tc_split(float v, __half &hi, __half &lo) {
+    hi = __float2half_rn(v);
+    lo = __float2half_rn(v - __half2float(hi));
+}
+
+// ---------------------------------------------------------------------------------------------
+__device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const unsigned G = gridDim.x;
+    const int nticks = p.T_max + 2 * p.D;
+    const int nwarps = KLM_TC_THREADS / 32;
+    __shared__ int ok_s;
+    if (tid == 0) tc::red_release_add(p.barrier, 1u);
+    for (int tick = 0; tick < nticks; ++tick) {
+        if (tid == 0) ok_s = tc_wait_grid(p, (unsigned)(tick + 1) * G, 10) ? 1 : 0;
+        __syncthreads();
+        if (!ok_s) return;
+        const int t = tick - role.sigma;
+        if (t >= 0) {
+            for (int s = role.first_pair * nwarps + warp; s < p.B; s += role.npairs * nwarps) {
+                const long long o0 = p.offsets[s];
+                const int len = (int)(p.offsets[s + 1] - o0);
+                if (t >= len) continue;
+                const float *row = p.logits + ((size_t)(tick & 1) * 64 + s) * p.Vp;
+                float m = -INFINITY;
+                for (int v = lane; v < p.V; v += 32) m = fmaxf(m, __ldcg(row + v));
+                for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+                float sum = 0.f;
+                for (int v = lane; v < p.V; v += 32) sum += expf(__ldcg(row + v) - m);
+                for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                if (p.full_rows) {
+                    float *dst = p.out + (size_t)(o0 + t) * p.V;
+                    const float inv = 1.0f / sum;
+                    for (int v = lane; v < p.V; v += 32) dst[v] = expf(__ldcg(row + v) - m) * inv;
+                } else if (lane == 0) {
+                    int tg = __ldg(p.targets + o0 + t);
+                    tg = min(max(tg, 0), p.V - 1);
+                    p.out[o0 + t] = (__ldcg(row + tg) - m) - logf(sum);
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) tc::red_release_add(p.barrier, 1u);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const KlmTcRole role = p.roles[blockIdx.x];
+    if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role); return; }
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int W = p.W, S = p.stages;
+    const unsigned G = gridDim.x;
+    const int nticks = p.T_max + 2 * p.D;
+    const int NP = role.npairs, N = 8 * NP;
+    const int nchunks = W / KLM_TC_KC;
+
+    // ---- shared memory carve-up ----
+    unsigned char *ring = smem;                                          // S x 16 KB: A operand chunks
+    float *xchg = reinterpret_cast<float *>(smem + (size_t)S * KLM_TC_CHUNK_BYTES);       // 10 KB
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)S * KLM_TC_CHUNK_BYTES + KLM_TC_XCHG_BYTES);
+    unsigned char *wsm = smem + (size_t)S * KLM_TC_CHUNK_BYTES + KLM_TC_XCHG_BYTES + 128; // B image
+    const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + 4);
+    const uint32_t bar_tfull = tc::smem_u32(bars + 8), bar_tempty = tc::smem_u32(bars + 9);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 10);
+
+    if (warp == 0) {
+        tc::tmem_alloc(tc::smem_u32(tmem_slot), KLM_TC_TMEM_COLS);
+        tc::tmem_relinquish();
+    }
+    if (tid == 32) {
+        for (int i = 0; i < S; ++i) { tc::mbar_init(bar_full + 8 * i, 1); tc::mbar_init(bar_empty + 8 * i, 1); }
+        tc::mbar_init(bar_tfull, 1);
+        tc::mbar_init(bar_tempty, 128);
+        tc::fence_mbar_init();
+    }
+    {   // B image: global -> shared, once per launch
+        const uint4 *src = reinterpret_cast<const uint4 *>(p.wimg + role.wofs);
+        uint4 *dst = reinterpret_cast<uint4 *>(wsm);
+        const int n16 = (W / 8) * 2 * N;
+        for (int i = tid; i < n16; i += KLM_TC_THREADS) dst[i] = __ldg(src + i);
+        tc::fence_proxy_async();                     // generic writes -> visible to the MMA's operand reads
+    }
+
+    // ---- epilogue thread identity ----
+    const int q = warp & 3;                          // TMEM lane quarter this warp may read
+    const int row = 32 * q + lane;                   // accumulator row: 0..63 hi part, 64..127 lo part
+    const int half = row >> 6, s = row & 63;
+    const int Ph = (NP + 1) / 2;                     // pairs [0,Ph) are finished by the hi half, the rest by the lo half
+    const int own_first = half ? Ph : 0, nown = half ? NP - Ph : Ph;
+    const bool is_epi = warp >= 2;
+    const bool is_rec = role.kind == KLM_TC_REC;
+    const int l = role.layer;
+
+    float c_reg[KLM_TC_OWN][2], h_reg[KLM_TC_OWN][2];
+    long long o0 = 0;
+    int len = 0;
+    if (is_epi) {
+        if (s < p.B) { o0 = p.offsets[s]; len = (int)(p.offsets[s + 1] - o0); }
+#pragma unroll
+        for (int i = 0; i < KLM_TC_OWN; ++i) {
+            c_reg[i][0] = c_reg[i][1] = h_reg[i][0] = h_reg[i][1] = 0.f;
+            if (is_rec && i < nown) {
+                const int u = 2 * (role.first_pair + own_first + i);
+                if (s < p.B) {
+                    const int slot = p.slots_in[s];
+                    if (slot >= 0) {
+                        const float *st = p.state + ((size_t)slot * p.D + l) * 2 * W;
+                        h_reg[i][0] = st[u]; h_reg[i][1] = st[u + 1];
+                        c_reg[i][0] = st[W + u]; c_reg[i][1] = st[W + u + 1];
+                    }
+                }
+                // publish the carried hidden state for tick 0 (parity 0)
+                __half hi0, lo0, hi1, lo1;
+                tc_split(h_reg[i][0], hi0, lo0); tc_split(h_reg[i][1], hi1, lo1);
+                __half *dst = p.hx + ((size_t)(l * 2 + 0) * (W / 8) + u / 8) * (128 * 8) + (u & 7);
+                *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
+                *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
+            }
+        }
+        tc::fence_proxy_async();                     // generic global writes -> later bulk (async proxy) reads
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (tid == 0) tc::red_release_add(p.barrier, 1u);
+
+    if (warp == 0) {
+        // =============================== producer ===============================
+        if (lane == 0) {
+            uint32_t it = 0;
+            bool ok = true;
+            for (int tick = 0; tick < nticks && ok; ++tick) {
+                if (!tc_wait_grid(p, (unsigned)(tick + 1) * G, 1)) break;
+                tc::fence_proxy_async();
+                const unsigned char *src = reinterpret_cast<const unsigned char *>(
+                    p.hx + (size_t)(role.src_layer * 2 + (tick & 1)) * W * 128);
+                for (int c = 0; c < nchunks; ++c, ++it) {
+                    const uint32_t st = it % S, ph = (it / S) & 1;
+                    if (!tc_wait_mbar(bar_empty + 8 * st, ph ^ 1, p, 2)) { ok = false; break; }
+                    tc::mbar_arrive_expect_tx(bar_full + 8 * st, KLM_TC_CHUNK_BYTES);
+                    tc::bulk_g2s(tc::smem_u32(ring + (size_t)st * KLM_TC_CHUNK_BYTES), src + (size_t)c * KLM_TC_CHUNK_BYTES,
+                                 KLM_TC_CHUNK_BYTES, bar_full + 8 * st);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // =============================== MMA issuer ===============================
+        if (lane == 0) {
+            const uint32_t idesc = tc::idesc_f16(128, 2 * N);
+            const uint32_t lbo_a = 128 * 16, lbo_b = 2 * N * 16;
+            const uint32_t ring_a = tc::smem_u32(ring), w_a = tc::smem_u32(wsm);
+            uint32_t it = 0;
+            bool ok = true;
+            for (int tick = 0; tick < nticks && ok; ++tick) {
+                if (!tc_wait_mbar(bar_tempty, (tick & 1) ^ 1, p, 3)) break;
+                tc::tc_fence_after();
+                for (int c = 0; c < nchunks; ++c, ++it) {
+                    const uint32_t st = it % S, ph = (it / S) & 1;
+                    if (!tc_wait_mbar(bar_full + 8 * st, ph, p, 4)) { ok = false; break; }
+                    tc::tc_fence_after();
+#pragma unroll
+                    for (int kk = 0; kk < KLM_TC_KC / 16; ++kk) {
+                        const uint64_t ad = tc::smem_desc(ring_a + st * KLM_TC_CHUNK_BYTES + kk * 2 * lbo_a, lbo_a, 128);
+                        const uint64_t bd = tc::smem_desc(w_a + (uint32_t)(c * (KLM_TC_KC / 8) + kk * 2) * lbo_b, lbo_b, 128);
+                        tc::mma_f16(tmem_base, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+                    }
+                    tc::mma_commit(bar_empty + 8 * st);       // ring slot free once these MMAs have read it
+                }
+                if (ok) tc::mma_commit(bar_tfull);            // accumulators of this tick complete
+            }
+        }
+    } else {
+        // =============================== epilogue ===============================
+        const uint32_t trow = tmem_base + ((uint32_t)(32 * q) << 16);
+        float4 bias4[KLM_TC_OWN][2];
+        if (role.kind == KLM_TC_IN) {
+#pragma unroll
+            for (int i = 0; i < KLM_TC_OWN; ++i)
+                if (i < nown) {
+                    const int u = 2 * (role.first_pair + own_first + i);
+                    bias4[i][0] = __ldg(p.bias[l] + u); bias4[i][1] = __ldg(p.bias[l] + u + 1);
+                }
+        }
+        for (int tick = 0; tick < nticks; ++tick) {
+            int ok = 1;
+            if (lane == 0) ok = tc_wait_grid(p, (unsigned)(tick + 1) * G, 5) ? 1 : 0;
+            ok = __shfl_sync(0xffffffffu, ok, 0);
+            __syncwarp();
+            if (!ok) break;
+            const int t = tick - role.sigma;
+            const bool active = s < p.B && t >= 0 && t < len;
+            const int par_in = tick & 1, par_out = (tick + 1) & 1;
+
+            // ---- addends, fetched while the MMAs run ----
+            float4 add4[KLM_TC_OWN][2];
+            if (is_rec && active) {
+                if (l == 0) {
+                    // fused char + context embedding gather / concat / input contraction (rating.py:103-115,125)
+                    int x = __ldg(p.chars + o0 + t);
+                    x = min(max(x, 0), p.V - 1);
+                    const bool real = p.n_real ? (t < __ldg(p.n_real + s)) : true;
+                    int z[KLM_MAX_CTX];
+                    for (int k = 0; k < p.Nc; ++k) {
+                        z[k] = real ? __ldg(p.ctx + s * p.Nc + k) : 0;       // padding: context 0 (:1141-1143)
+                        z[k] = min(max(z[k], 0), p.ctx_rows[k] - 1);
+                    }
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                        if (i < nown) {
+                            const int u = 2 * (role.first_pair + own_first + i);
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                float4 a = __ldg(p.P + (size_t)x * W + u + e);
+                                for (int k = 0; k < p.Nc; ++k) {
+                                    const float4 b = __ldg(p.Q[k] + (size_t)z[k] * W + u + e);
+                                    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+                                }
+                                add4[i][e] = a;
+                            }
+                        }
+                } else {
+                    const float4 *zrow = reinterpret_cast<const float4 *>(p.Z + ((size_t)(l * 2 + par_in) * 64 + s) * 4 * W);
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                        if (i < nown) {
+                            const int u = 2 * (role.first_pair + own_first + i);
+                            add4[i][0] = __ldcg(zrow + u); add4[i][1] = __ldcg(zrow + u + 1);
+                        }
+                }
+            }
+
+            // ---- accumulators ----
+            ok = tc_wait_mbar(bar_tfull, tick & 1, p, 6) ? 1 : 0;
+            ok = __all_sync(0xffffffffu, ok);
+            if (!ok) break;
+            tc::tc_fence_after();
+            float acc[KLM_TC_OWN][8];
+#pragma unroll
+            for (int i = 0; i < KLM_TC_OWN; ++i)
+                if (i < nown) {
+                    const int pr = own_first + i;
+                    tc::tmem_ld8(trow + 8 * pr, acc[i]);
+                    if (half == 0) {
+                        float b[8];
+                        tc::tmem_ld8(trow + N + 8 * pr, b);
+                        tc::tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc[i][j] += b[j];
+                    } else {
+                        tc::tmem_ld_wait();
+                    }
+                }
+            // round 1: the lo half hands its part of pairs [0,Ph) to the hi half
+            if (half == 1) {
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (i < Ph) {
+                        float v[8];
+                        tc::tmem_ld8(trow + 8 * i, v);
+                        tc::tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) xchg[(i * 8 + j) * 64 + s] = v[j];
+                    }
+            }
+            tc_bar_epi();
+            if (half == 0) {
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (i < nown) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc[i][j] += xchg[(i * 8 + j) * 64 + s];
+                    }
+            }
+            tc_bar_epi();
+            // round 2: the hi half hands its part of pairs [Ph,NP) to the lo half
+            if (half == 0) {
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (Ph + i < NP) {
+                        float a[8], b[8];
+                        tc::tmem_ld8(trow + 8 * (Ph + i), a);
+                        tc::tmem_ld8(trow + N + 8 * (Ph + i), b);
+                        tc::tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) xchg[(i * 8 + j) * 64 + s] = a[j] + b[j];
+                    }
+            }
+            tc::tc_fence_before();
+            tc::mbar_arrive(bar_tempty);                      // this thread is done reading TMEM
+            tc_bar_epi();
+            if (half == 1) {
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (i < nown) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc[i][j] += xchg[(i * 8 + j) * 64 + s];
+                    }
+            }
+
+            // ---- finish and hand over ----
+            if (is_rec) {
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (i < nown) {
+                        const int u = 2 * (role.first_pair + own_first + i);
+                        if (active) {
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const float4 a = add4[i][e];
+                                tc_cell(acc[i][4 * e] + a.x, acc[i][4 * e + 1] + a.y, acc[i][4 * e + 2] + a.z,
+                                        acc[i][4 * e + 3] + a.w, c_reg[i][e], h_reg[i][e]);
+                            }
+                        }
+                        __half hi0, lo0, hi1, lo1;
+                        tc_split(h_reg[i][0], hi0, lo0); tc_split(h_reg[i][1], hi1, lo1);
+                        __half *dst = p.hx + ((size_t)(l * 2 + par_out) * (W / 8) + u / 8) * (128 * 8) + (u & 7);
+                        *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
+                        *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
+                    }
+                tc::fence_proxy_async();
+            } else if (role.kind == KLM_TC_IN) {
+                float4 *zrow = reinterpret_cast<float4 *>(p.Z + ((size_t)(l * 2 + par_out) * 64 + s) * 4 * W);
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (i < nown) {
+                        const int u = 2 * (role.first_pair + own_first + i);
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const float4 b = bias4[i][e];
+                            __stcg(zrow + u + e, make_float4(acc[i][4 * e] + b.x, acc[i][4 * e + 1] + b.y,
+                                                             acc[i][4 * e + 2] + b.z, acc[i][4 * e + 3] + b.w));
+                        }
+                    }
+            } else {   // PROJ: logits of vocabulary rows 8*(first_pair + pair) ..
+                float4 *lrow = reinterpret_cast<float4 *>(p.logits + ((size_t)par_out * 64 + s) * p.Vp);
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (i < nown) {
+                        const int g8 = role.first_pair + own_first + i;
+                        __stcg(lrow + 2 * g8, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
+                        __stcg(lrow + 2 * g8 + 1, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
+                    }
+            }
+            tc_bar_epi();
+            if (tid == 64) tc::red_release_add(p.barrier, 1u);
+        }
+        // ---- write the final state back ----
+        if (is_rec && s < p.B) {
+            float *st = p.state + ((size_t)p.slots_out[s] * p.D + l) * 2 * W;
+#pragma unroll
+            for (int i = 0; i < KLM_TC_OWN; ++i)
+                if (i < nown) {
+                    const int u = 2 * (role.first_pair + own_first + i);
+                    st[u] = h_reg[i][0]; st[u + 1] = h_reg[i][1];
+                    st[W + u] = c_reg[i][0]; st[W + u + 1] = c_reg[i][1];
+                }
+        }
+    }
+
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        __syncwarp();
+        tc::tmem_dealloc(tmem_base, KLM_TC_TMEM_COLS);
+    }
+}
+
+cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream) {
+    void *args[] = { const_cast<KlmTcParams *>(&p) };
+    cudaError_t e = cudaFuncSetAttribute((const void *)klm_seq_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaLaunchCooperativeKernel((const void *)klm_seq_tc, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Self-test of the tcgen05 building blocks: D[128 x N] = A[128 x K] . B[N x K]^T for fp16 operand
+// images in the layout above (A through bulk async copies, B through generic stores).
+__global__ void __launch_bounds__(128, 1) klm_umma_selftest(const __half *A, const __half *B, float *Dout, int N, int K,
+                                                             int *err) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t a_bytes = (uint32_t)K * 128 * 2, b_bytes = (uint32_t)K * N * 2;
+    unsigned char *sa = smem, *sb = smem + a_bytes;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + a_bytes + b_bytes);
+    const uint32_t bar_full = tc::smem_u32(bars), bar_done = tc::smem_u32(bars + 1);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
+    if (warp == 0) { tc::tmem_alloc(tc::smem_u32(tmem_slot), 256); tc::tmem_relinquish(); }
+    if (tid == 32) { tc::mbar_init(bar_full, 1); tc::mbar_init(bar_done, 1); tc::fence_mbar_init(); }
+    for (uint32_t i = tid; i < b_bytes / 16; i += 128) reinterpret_cast<uint4 *>(sb)[i] = reinterpret_cast<const uint4 *>(B)[i];
+    tc::fence_proxy_async();
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (tid == 0) {
+        tc::mbar_arrive_expect_tx(bar_full, a_bytes);
+        for (uint32_t off = 0; off < a_bytes; off += 16384)
+            tc::bulk_g2s(tc::smem_u32(sa + off), reinterpret_cast<const unsigned char *>(A) + off, min(16384u, a_bytes - off), bar_full);
+    }
+    if (tid == 32) {
+        unsigned n = 0;
+        while (!tc::mbar_try_wait(bar_full, 0)) if (++n > (1u << 22)) { atomicExch(err, 1); break; }
+        tc::tc_fence_after();
+        const uint32_t idesc = tc::idesc_f16(128, N);
+        const uint32_t lbo_a = 128 * 16, lbo_b = N * 16;
+        for (int k = 0; k < K / 16; ++k)
+            tc::mma_f16(tmem_base, tc::smem_desc(tc::smem_u32(sa) + k * 2 * lbo_a, lbo_a, 128),
+                        tc::smem_desc(tc::smem_u32(sb) + k * 2 * lbo_b, lbo_b, 128), idesc, k != 0 ? 1u : 0u);
+        tc::mma_commit(bar_done);
+    }
+    __syncwarp();
+    {
+        unsigned n = 0;
+        while (!tc::mbar_try_wait(bar_done, 0)) if (++n > (1u << 22)) { atomicExch(err, 2); break; }
+    }
+    __syncwarp();
+    tc::tc_fence_after();
+    const uint32_t trow = tmem_base + ((uint32_t)(32 * warp) << 16);
+    for (int c = 0; c < N; c += 8) {
+        float v[8];
+        tc::tmem_ld8(trow + c, v);
+        tc::tmem_ld_wait();
+        for (int j = 0; j < 8; ++j) Dout[(size_t)(32 * warp + lane) * N + c + j] = v[j];
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { __syncwarp(); tc::tmem_dealloc(tmem_base, 256); }
+}
+
+cudaError_t klm_launch_umma_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream) {
+    const size_t smem = (size_t)K * 128 * 2 + (size_t)K * N * 2 + 64;
+    cudaError_t e = cudaFuncSetAttribute((const void *)klm_umma_selftest, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    klm_umma_selftest<<<1, 128, smem, stream>>>(A, B, D, N, K, err);
+    return cudaGetLastError();
+}

@@ -1,0 +1,120 @@
+"""The tcgen05 sequence kernel (csrc/klm_seq_tc.cu): building-block self-test and parity with the
+oracle for 9..64 concurrent streams (same tolerances as test_gpu_parity.py)."""
+import logging
+
+import numpy as np
+import pytest
+
+from oracle.rater_oracle import OracleRater
+from ocrd_keraslm_b200 import synth
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+quiet = logging.getLogger('gpu-test-tc')
+quiet.setLevel(logging.CRITICAL)
+
+
+def product(wd, maparr, length, stateful=True, incremental=False):
+    from ocrd_keraslm_b200.lib import Rater
+    return Rater.from_weights(wd, maparr, length, stateful=stateful, incremental=incremental, logger=quiet)
+
+
+def logp_err(got, ref):
+    got = np.log(np.maximum(np.asarray(got, dtype=np.float64), 1e-300))
+    ref = np.log(np.maximum(np.asarray(ref, dtype=np.float64), 1e-300))
+    assert got.shape == ref.shape
+    return np.abs(got - ref).max()
+
+
+@pytest.mark.parametrize('N,K', [(16, 16), (64, 64), (160, 128), (144, 256), (256, 64)])
+def test_umma_selftest_matches_numpy(N, K):
+    """tcgen05.mma with the no-swizzle K-major descriptors, bulk async copy and tcgen05.ld: exact for
+    small-integer fp16 operands, fp32-accurate for random ones."""
+    from ocrd_keraslm_b200 import _native
+    rng = np.random.default_rng(N * 1000 + K)
+    A = rng.integers(-4, 5, (128, K)).astype(np.float16)
+    B = rng.integers(-4, 5, (N, K)).astype(np.float16)
+    D = _native.selftest_umma(A, B)
+    np.testing.assert_array_equal(D, A.astype(np.float32) @ B.astype(np.float32).T)
+    A = rng.standard_normal((128, K)).astype(np.float16)
+    B = rng.standard_normal((N, K)).astype(np.float16)
+    D = _native.selftest_umma(A, B)
+    ref = A.astype(np.float64) @ B.astype(np.float64).T
+    assert np.abs(D - ref).max() <= 1e-4 * max(1.0, np.abs(ref).max())
+
+
+@pytest.mark.parametrize('width,depth,n_docs,nctx', [(64, 1, 9, 1), (128, 2, 33, 1), (256, 3, 64, 3), (512, 3, 40, 1)])
+def test_tc_rate_many_matches_oracle(width, depth, n_docs, nctx):
+    wd = synth.weights(31 + width, width=width, depth=depth, voc_size=256, contexts=((200, 10),) * nctx, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 32)
+    info = r._native.info()
+    assert info['tc_enabled'] == 1
+    rng = np.random.default_rng(width + n_docs)
+    sizes = rng.integers(2, 40 if width < 512 else 20, n_docs)
+    sizes[1] = 1
+    texts = [synth.text(3000 + i, int(s)) for i, s in enumerate(sizes)]
+    ctxs = [[int(x) for x in rng.integers(0, 200, nctx)] for _ in texts]
+    got = r.rate_many(texts, ctxs)
+    assert r._native.info()['tc_launches'] >= 1
+    o = OracleRater(util.to_model(wd), synth.mapping_from_array(maparr), 32, logger=quiet)
+    worst = 0.0
+    for i, (t, c) in enumerate(zip(texts, ctxs)):
+        ref, _ = o.rate2(t, c)
+        worst = max(worst, logp_err(got[i], [p for _, p in ref]))
+    assert worst <= 1e-3, worst
+
+
+def test_tc_states_and_carry_match_oracle():
+    """Hidden and cell states after a launch (1e-4 relative) and a second launch continuing from them."""
+    width, depth, n = 128, 2, 12
+    wd = synth.weights(5, width=width, depth=depth, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 16)
+    nat = r._native
+    texts = [synth.text(500 + i, 30 + i) for i in range(n)]
+    slots = r._pool.acquire(n)
+    nat.state_reset(slots)
+    oracles = [OracleRater(util.to_model(wd), synth.mapping_from_array(maparr), 16, logger=quiet) for _ in range(n)]
+    for piece in (slice(0, 17), slice(16, None)):          # second piece continues from the carried state
+        idx = [r._indices(t[piece])[0] for t in texts]
+        lens = np.array([len(i) - 1 for i in idx])
+        offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+        chars = np.concatenate([i[:-1] for i in idx]).astype(np.int32)
+        targets = np.concatenate([i[1:] for i in idx]).astype(np.int32)
+        logp = np.empty(len(chars), dtype=np.float32)
+        nat.rate(slots, offsets, chars, targets, None, [[7]] * n, logp)
+        for k in range(n):
+            # oracle: same steps without reset / padding
+            o = oracles[k]
+            from oracle import lstm_numpy as ln
+            x = idx[k][:-1][None, :].astype(np.int64)
+            z = [np.full_like(x, 7)]
+            out, o.states = ln.run_sequence(o.w, x, z, o.states, want='target', targets=idx[k][1:][None, :].astype(np.int64))
+            seg = logp[offsets[k]:offsets[k + 1]]
+            assert np.abs(seg - np.log(out[0].astype(np.float64))).max() <= 1e-3
+        got = nat.state_to_host(slots)
+        for k in range(n):
+            ref = np.concatenate([s_ for s_ in oracles[k].states], axis=0)
+            assert np.abs(got[k] - ref).max() <= 1e-4 * np.abs(ref).max()
+
+
+def test_tc_step_full_rows_match_fma():
+    """klm_step through the tensor-core kernel (n = 40 hypotheses, full softmax rows) against the
+    FMA K-parallel kernel (n <= 8) on the same inputs."""
+    wd = synth.weights(77, width=128, depth=2, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 8, stateful=False, incremental=True)
+    cands = [chr(97 + i % 26) for i in range(40)]
+    p1, s1 = r.predict(list(cands), [None] * 40, [3])
+    p2, s2 = r.predict(list(cands), list(s1), [3])
+    for lo in range(0, 40, 8):
+        q1, t1 = r.predict(cands[lo:lo + 8], [None] * 8, [3])
+        q2, t2 = r.predict(cands[lo:lo + 8], list(t1), [3])
+        assert logp_err(np.stack(p1[lo:lo + 8]), np.stack(q1)) <= 1e-3
+        assert logp_err(np.stack(p2[lo:lo + 8]), np.stack(q2)) <= 1e-3
+        a = np.stack([np.concatenate(list(s), 0) for s in s2[lo:lo + 8]])
+        b = np.stack([np.concatenate(list(s), 0) for s in t2])
+        assert np.abs(a - b).max() <= 1e-4 * np.abs(b).max()
+    np.testing.assert_allclose(np.stack(p2).sum(axis=1), 1.0, rtol=1e-5)
