@@ -417,17 +417,20 @@ def run_ours(args):
     try:
         with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
             tj = json.load(f)
-        if tj.get(wl, {}).get('dram_bytes_per_char') is not None:
-            traffic = tj[wl]['dram_bytes_per_char'] * chars_per_step
+        if tj.get(wl, {}).get('dram_bytes_per_launch_measured') is not None:
+            fixed = tj[wl]['dram_bytes_per_launch_measured'] - 8 * tj[wl]['positions_in_measured_launch']
+            traffic = fixed + 8 * chars_per_step          # measured one-time part + the per-position streams
     except Exception:
         pass
     roofline = {
-        'bound': 'tensor', 'kernel': info.get('kernel_name', 'klm_seq'), 'achieved': achieved, 'peak': peak,
+        'bound': 'tensor', 'kernel': 'klm_seq_tc' if info.get('tc_launches', 0) > 0 else 'klm_seq_fma', 'achieved': achieved, 'peak': peak,
         'unit': 'TFLOP/s', 'frac': achieved / peak, 'traffic': traffic, 'peak_source': pk_src + ', bf16 sustained',
         'kernel_ms': k_ms, 'algorithmic_flops_per_launch': chars_per_step * F,
         'algorithmic_hbm_bytes_per_launch': 8 * chars_per_step,
         'hbm_frac': (8 * chars_per_step / (k_ms / 1000.0) / 1e9) / float(pk.get('hbm_gbs', FALLBACK_PEAKS['hbm_gbs'])),
-        'grid': info['grid'], 'smem_bytes': info['smem_bytes'], 'weights_in_smem': info['weights_in_smem'],
+        'grid': info['tc_grid'] if info.get('tc_launches', 0) > 0 else info['grid'],
+        'smem_bytes': info['tc_smem_bytes'] if info.get('tc_launches', 0) > 0 else info['smem_bytes'],
+        'weights_in_smem': 1 if info.get('tc_launches', 0) > 0 else info['weights_in_smem'],
     }
 
     line = base_line(args, value, total_ms / args.steps)

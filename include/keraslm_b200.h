@@ -147,6 +147,12 @@ int klm_get_info(klm_model *m, klm_info *out);
  * fp16 operand images in the kernel's shared-memory layout ([K/8][rows][8] halves); host pointers. */
 int klm_selftest_umma(int device, int32_t N, int32_t K, const uint16_t *A_img, const uint16_t *B_img, float *D);
 
+/* Debug timeline of the tcgen05 kernel.  out == NULL: arm tracing of 16 ticks from `first_tick` for the
+ * following launches; out != NULL: copy [tc_grid][16][8] SM-clock samples (events: 0 tick start, 1 copies
+ * issued, 2 first / 3 last operand chunk landed, 4 accumulators complete, 5 TMEM drained, 6 hand-over stored,
+ * 7 barrier arrive) and, if roles_out != NULL, [tc_grid][4] ints (kind, layer, pairs, stage). */
+int klm_tc_trace(klm_model *m, int32_t first_tick, uint64_t *out, int32_t *roles_out);
+
 #ifdef __cplusplus
 }
 #endif

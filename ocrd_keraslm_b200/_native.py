@@ -89,6 +89,7 @@ SYMBOLS = [
     ('klm_step', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
     ('klm_get_info', ctypes.c_int, [_P, ctypes.POINTER(KlmInfo)]),
     ('klm_selftest_umma', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
+    ('klm_tc_trace', ctypes.c_int, [_P, _I, _P, _P]),
 ]
 
 _lib = None
@@ -204,6 +205,16 @@ class Model(object):
         inf = KlmInfo()
         self.check(self._lib.klm_get_info(self._h, ctypes.byref(inf)))
         return dict((f, getattr(inf, f)) for f, _ in KlmInfo._fields_)
+
+    def tc_trace_arm(self, first_tick):
+        self.check(self._lib.klm_tc_trace(self._h, first_tick, None, None))
+
+    def tc_trace_read(self):
+        grid = self.info()['tc_grid']
+        out = np.zeros((grid, 16, 8), dtype=np.uint64)
+        roles = np.zeros((grid, 4), dtype=np.int32)
+        self.check(self._lib.klm_tc_trace(self._h, 0, _ptr(out), _ptr(roles)))
+        return out, roles
 
     # ---- state pool ----
     def pool_resize(self, n):

@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -60,6 +61,9 @@ struct KlmTcPlan {
     __half *hx = nullptr;
     float *Z = nullptr, *logits = nullptr;
     int *err = nullptr;
+    int ingest_bulk = 0;
+    unsigned long long *trace = nullptr;
+    int trace_t0 = 0;
 };
 
 #define KLM_RING 4
@@ -241,13 +245,14 @@ static int make_tc_plan(klm_model *m, const float *E, const float *const *L) {
     if (getenv("KLM_DISABLE_TC")) return KLM_OK;
     if (W % KLM_TC_KC != 0 || W < KLM_TC_KC) return KLM_OK;
     const int nchunks = W / KLM_TC_KC;
-    pl.stages = std::min(3, nchunks);
+    pl.stages = std::min(4, nchunks);
     pl.Vp = (V + 7) / 8 * 8;
-    const size_t fixed = (size_t)pl.stages * KLM_TC_CHUNK_BYTES + KLM_TC_XCHG_BYTES + 128;
+    const size_t fixed = KLM_TC_FIXED_BYTES((size_t)pl.stages);
     if (fixed + 32 * (size_t)W > m->smem_optin) return KLM_OK;
     const int pairs_max = (int)std::min<size_t>(KLM_TC_MAX_PAIRS, (m->smem_optin - fixed) / (32 * (size_t)W));
     if (pairs_max < 1) return KLM_OK;
 
+    const int sm_avail = getenv("KLM_TC_MAX_CTAS") ? std::min(m->sm_count, atoi(getenv("KLM_TC_MAX_CTAS"))) : m->sm_count;
     struct Ty { int kind, layer, src, sigma, pairs, n; const float *mat; };
     std::vector<Ty> tys;
     for (int l = 0; l < D; ++l) {
@@ -255,11 +260,12 @@ static int make_tc_plan(klm_model *m, const float *E, const float *const *L) {
         tys.push_back({KLM_TC_REC, l, l, 2 * l, W / 2, 0, L[3 * l + 1]});
     }
     tys.push_back({KLM_TC_PROJ, 0, D - 1, 2 * D - 1, pl.Vp / 8, 0, E});
-    const int n_lse = 1;
-    int used = n_lse;
+    int n_lse = 1, used = 0;
     for (auto &t : tys) { t.n = (t.pairs + pairs_max - 1) / pairs_max; used += t.n; }
-    if (used > m->sm_count) return KLM_OK;
-    while (used < m->sm_count) {                      // spare SMs go to the stage with the widest slices
+    if (used + n_lse > sm_avail) return KLM_OK;
+    n_lse = std::max(1, std::min(4, sm_avail - used));      // the LSE stage must not be the slowest one
+    used += n_lse;
+    while (used < sm_avail) {                      // spare SMs go to the stage with the widest slices
         int best = -1; double load = 0;
         for (int i = 0; i < (int)tys.size(); ++i) {
             if (tys[i].n >= tys[i].pairs) continue;
@@ -317,6 +323,7 @@ static int make_tc_plan(klm_model *m, const float *E, const float *const *L) {
     CK(cudaMemcpy(pl.d_roles, pl.roles.data(), pl.roles.size() * sizeof(KlmTcRole), cudaMemcpyHostToDevice));
     CK(cudaMalloc(&pl.d_wimg, img.size() * sizeof(__half)));
     CK(cudaMemcpy(pl.d_wimg, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    pl.ingest_bulk = getenv("KLM_TC_INGEST_BULK") ? atoi(getenv("KLM_TC_INGEST_BULK")) : 1;
     const size_t hx_bytes = (size_t)D * 2 * W * 128 * sizeof(__half);
     const size_t z_bytes = (size_t)D * 2 * 64 * 4 * W * sizeof(float);
     const size_t lg_bytes = (size_t)2 * 64 * pl.Vp * sizeof(float);
@@ -344,7 +351,7 @@ extern "C" int klm_destroy(klm_model *m) {
     for (int i = 0; i < KLM_MAX_DEPTH; ++i) { cudaFree(m->Wl[i]); cudaFree(m->bias[i]); }
     cudaFree(m->plan_k.d_roles); cudaFree(m->plan_b.d_roles);
     cudaFree(m->tc.d_roles); cudaFree(m->tc.d_wimg); cudaFree(m->tc.hx); cudaFree(m->tc.Z); cudaFree(m->tc.logits);
-    cudaFree(m->tc.err);
+    cudaFree(m->tc.err); cudaFree(m->tc.trace);
     cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
     for (int i = 0; i < KLM_RING; ++i) {
         if (m->h_ring[i]) cudaFreeHost(m->h_ring[i]);
@@ -654,10 +661,12 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         for (int l = 0; l < m->D; ++l) q.bias[l] = m->bias[l];
         q.wimg = m->tc.d_wimg; q.roles = m->tc.d_roles;
         q.hx = m->tc.hx; q.Z = m->tc.Z; q.logits = m->tc.logits;
+        q.ingest_bulk = m->tc.ingest_bulk;
         q.state = m->state; q.slots_in = d_si; q.slots_out = d_so; q.offsets = d_off;
         q.chars = d_chars; q.targets = d_targets; q.n_real = d_nr; q.ctx = d_cx;
         q.out = d_out; q.full_rows = full_rows;
         q.barrier = m->barrier; q.err = m->tc.err;
+        q.trace = m->tc.trace; q.trace_t0 = m->tc.trace_t0;
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         CK(klm_launch_seq_tc(q, m->tc.grid, m->tc.smem, m->stream));
         m->launches++; m->tc_launches++;
@@ -858,5 +867,30 @@ extern "C" int klm_selftest_umma(int device, int32_t N, int32_t K, const uint16_
     CK(cudaMemcpy(D, dD, (size_t)128 * N * 4, cudaMemcpyDeviceToHost));
     cudaFree(dA); cudaFree(dB); cudaFree(dD); cudaFree(derr);
     if (code) return fail(KLM_ECUDA, "klm_selftest_umma: device-side wait timed out (code %d)", code);
+    return KLM_OK;
+}
+
+// Debug timeline of the tensor-core kernel.  out == NULL: arm tracing of KLM_TC_TRACE_TICKS ticks from
+// `first_tick` for subsequent launches.  out != NULL: copy the [grid][ticks][8] SM-clock samples and the
+// role table ([grid][4] ints: kind, layer, npairs, sigma) to host.
+extern "C" int klm_tc_trace(klm_model *m, int32_t first_tick, uint64_t *out, int32_t *roles_out) {
+    if (!m) return fail(KLM_EINVAL, "NULL model");
+    if (!m->tc.ok) return fail(KLM_EINVAL, "klm_tc_trace: the tensor-core plan is not enabled for this model");
+    CK(cudaSetDevice(m->device));
+    const size_t n = (size_t)m->tc.grid * KLM_TC_TRACE_TICKS * 8;
+    if (!out) {
+        if (!m->tc.trace) CK(cudaMalloc(&m->tc.trace, n * 8));
+        CK(cudaMemset(m->tc.trace, 0, n * 8));
+        m->tc.trace_t0 = first_tick;
+        return KLM_OK;
+    }
+    if (!m->tc.trace) return fail(KLM_EINVAL, "klm_tc_trace: not armed");
+    CK(cudaStreamSynchronize(m->stream));
+    CK(cudaMemcpy(out, m->tc.trace, n * 8, cudaMemcpyDeviceToHost));
+    if (roles_out)
+        for (int i = 0; i < m->tc.grid; ++i) {
+            roles_out[4 * i] = m->tc.roles[i].kind; roles_out[4 * i + 1] = m->tc.roles[i].layer;
+            roles_out[4 * i + 2] = m->tc.roles[i].npairs; roles_out[4 * i + 3] = m->tc.roles[i].sigma;
+        }
     return KLM_OK;
 }

@@ -68,14 +68,18 @@ struct KlmSeqParams {
 
 // ---------------------------------------------------------------------------------------------
 // Tensor-core sequence kernel (klm_seq_tc.cu)
-#define KLM_TC_THREADS      192
+#define KLM_TC_THREADS      320                    // producer warp, MMA warp, 8 epilogue warps
 #define KLM_TC_STREAMS      64                     // accumulator rows 0..63 = hi part, 64..127 = lo part
 #define KLM_TC_KC           64                     // k per ring chunk
 #define KLM_TC_CHUNK_BYTES  (KLM_TC_KC / 8 * 128 * 16)
-#define KLM_TC_OWN          5                      // pairs of units finished by one epilogue thread
-#define KLM_TC_MAX_PAIRS    (2 * KLM_TC_OWN)       // N <= 80 columns per CTA
-#define KLM_TC_XCHG_BYTES   (KLM_TC_OWN * 8 * 64 * 4)
+#define KLM_TC_OWN          3                      // pairs of units finished by one epilogue thread
+#define KLM_TC_MAX_PAIRS    10                     // N <= 80 columns per CTA
+#define KLM_TC_XCHG_BYTES   (2 * (KLM_TC_MAX_PAIRS / 2) * 8 * 64 * 4)
+// shared memory before the B image: ring of S chunks (the hand-over buffer aliases it when it fits), barriers
+#define KLM_TC_XCHG_OFS     0
+#define KLM_TC_FIXED_BYTES(S) ((((S) * KLM_TC_CHUNK_BYTES > KLM_TC_XCHG_BYTES) ? (S) * KLM_TC_CHUNK_BYTES : KLM_TC_XCHG_BYTES) + 128)
 #define KLM_TC_TMEM_COLS    256
+#define KLM_TC_TRACE_TICKS  16
 
 #define KLM_TC_REC  0
 #define KLM_TC_IN   1
@@ -102,6 +106,7 @@ struct KlmTcParams {
     const unsigned char *wimg;
     const KlmTcRole *roles;
     __half *hx;                   // [D][2][W/8][128][8]
+    int ingest_bulk;              // 0: the epilogue warps copy the A operand (ld.global.cg / st.shared); 1: cp.async.bulk
     float *Z;                     // [D][2][64][4W]  (unit-interleaved gate columns)
     float *logits;                // [2][64][Vp]
     float *state;
@@ -112,4 +117,6 @@ struct KlmTcParams {
     int full_rows;
     unsigned int *barrier;
     int *err;                     // device-side watchdog: non-zero = a wait timed out (code says which)
+    unsigned long long *trace;    // optional [grid][KLM_TC_TRACE_TICKS][8] SM-clock timeline (klm_tc_trace)
+    int trace_t0;
 };

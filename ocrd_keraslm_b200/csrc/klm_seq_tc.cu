@@ -48,7 +48,15 @@ __device__ __forceinline__ bool tc_wait_mbar(uint32_t bar, uint32_t parity, cons
         if (tc_spin_fail(n, p, code)) return false;
     return true;
 }
-__device__ __forceinline__ void tc_bar_epi() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// optional timeline instrumentation (klm_tc_trace): SM clock of key events for KLM_TC_TRACE_TICKS ticks
+__device__ __forceinline__ void tc_trace(const KlmTcParams &p, int tick, int ev) {
+    if (p.trace) {
+        const int k = tick - p.trace_t0;
+        if (k >= 0 && k < KLM_TC_TRACE_TICKS)
+            p.trace[((size_t)blockIdx.x * KLM_TC_TRACE_TICKS + k) * 8 + ev] = (unsigned long long)clock64();
+    }
+}
+__device__ __forceinline__ void tc_bar_epi() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // exp via ex2.approx (2 ulp), reciprocal via rcp.approx: absolute error of the gates ~1e-7
 __device__ __forceinline__ float tc_exp(float x) { return exp2f(x * 1.4426950408889634f); }
@@ -90,12 +98,30 @@ __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
                 const int len = (int)(p.offsets[s + 1] - o0);
                 if (t >= len) continue;
                 const float *row = p.logits + ((size_t)(tick & 1) * 64 + s) * p.Vp;
-                float m = -INFINITY;
-                for (int v = lane; v < p.V; v += 32) m = fmaxf(m, __ldcg(row + v));
-                for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-                float sum = 0.f;
-                for (int v = lane; v < p.V; v += 32) sum += expf(__ldcg(row + v) - m);
+                // one pass: running maximum and rescaled sum per lane, then combined across the warp
+                float m = -INFINITY, sum = 0.f;
+                for (int v0 = 0; v0 < p.V; v0 += 256) {
+                    float x[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int v = v0 + 32 * j + lane;
+                        x[j] = v < p.V ? __ldcg(row + v) : -INFINITY;
+                    }
+                    float mx = m;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) mx = fmaxf(mx, x[j]);
+                    if (mx > -INFINITY) {
+                        float acc = sum * __expf(m - mx);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc += __expf(x[j] - mx);
+                        sum = acc; m = mx;
+                    }
+                }
+                float mw = m;
+                for (int o = 16; o > 0; o >>= 1) mw = fmaxf(mw, __shfl_xor_sync(0xffffffffu, mw, o));
+                sum = (m > -INFINITY) ? sum * __expf(m - mw) : 0.f;
                 for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                m = mw;
                 if (p.full_rows) {
                     float *dst = p.out + (size_t)(o0 + t) * p.V;
                     const float inv = 1.0f / sum;
@@ -127,21 +153,24 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
 
     // ---- shared memory carve-up ----
     unsigned char *ring = smem;                                          // S x 16 KB: A operand chunks
-    float *xchg = reinterpret_cast<float *>(smem + (size_t)S * KLM_TC_CHUNK_BYTES);       // 10 KB
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)S * KLM_TC_CHUNK_BYTES + KLM_TC_XCHG_BYTES);
-    unsigned char *wsm = smem + (size_t)S * KLM_TC_CHUNK_BYTES + KLM_TC_XCHG_BYTES + 128; // B image
+    float *xchg = reinterpret_cast<float *>(smem + KLM_TC_XCHG_OFS);    // 20 KB hi<->lo hand-over; aliases the ring when
+                                                                         // S >= 2 (the ring is idle while the epilogue runs)
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + KLM_TC_FIXED_BYTES(S) - 128);
+    unsigned char *wsm = smem + KLM_TC_FIXED_BYTES(S);                   // B image
     const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + 4);
     const uint32_t bar_tfull = tc::smem_u32(bars + 8), bar_tempty = tc::smem_u32(bars + 9);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 10);
+    const uint32_t bar_go = tc::smem_u32(bars + 10);       // producer -> epilogue: grid barrier of this tick passed
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 11);
 
     if (warp == 0) {
         tc::tmem_alloc(tc::smem_u32(tmem_slot), KLM_TC_TMEM_COLS);
         tc::tmem_relinquish();
     }
     if (tid == 32) {
-        for (int i = 0; i < S; ++i) { tc::mbar_init(bar_full + 8 * i, 1); tc::mbar_init(bar_empty + 8 * i, 1); }
+        for (int i = 0; i < S; ++i) { tc::mbar_init(bar_full + 8 * i, p.ingest_bulk ? 1 : 256); tc::mbar_init(bar_empty + 8 * i, 1); }
         tc::mbar_init(bar_tfull, 1);
-        tc::mbar_init(bar_tempty, 128);
+        tc::mbar_init(bar_tempty, 256);
+        tc::mbar_init(bar_go, 1);
         tc::fence_mbar_init();
     }
     {   // B image: global -> shared, once per launch
@@ -156,8 +185,12 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
     const int q = warp & 3;                          // TMEM lane quarter this warp may read
     const int row = 32 * q + lane;                   // accumulator row: 0..63 hi part, 64..127 lo part
     const int half = row >> 6, s = row & 63;
-    const int Ph = (NP + 1) / 2;                     // pairs [0,Ph) are finished by the hi half, the rest by the lo half
-    const int own_first = half ? Ph : 0, nown = half ? NP - Ph : Ph;
+    const int ch = (warp - 2) >> 2;                  // two warps share a lane quarter and split its pairs
+    const int Ph = (NP + 1) / 2;                     // pairs [0,Ph) are finished by hi-row threads, the rest by lo-row threads
+    const int my_first = half ? Ph : 0, my_n = half ? NP - Ph : Ph;          // this half's pairs
+    const int oth_first = half ? 0 : Ph, oth_n = half ? Ph : NP - Ph;        // the other half's pairs
+    const int own_first = my_first + (ch ? (my_n + 1) / 2 : 0), nown = ch ? my_n - (my_n + 1) / 2 : (my_n + 1) / 2;
+    const int send_first = oth_first + (ch ? (oth_n + 1) / 2 : 0), nsend = ch ? oth_n - (oth_n + 1) / 2 : (oth_n + 1) / 2;
     const bool is_epi = warp >= 2;
     const bool is_rec = role.kind == KLM_TC_REC;
     const int l = role.layer;
@@ -188,7 +221,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                 *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
             }
         }
-        tc::fence_proxy_async();                     // generic global writes -> later bulk (async proxy) reads
+        if (p.ingest_bulk) tc::fence_proxy_async(); // generic global writes -> later bulk (async proxy) reads
     }
     tc::tc_fence_before();
     __syncthreads();
@@ -203,15 +236,23 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
             bool ok = true;
             for (int tick = 0; tick < nticks && ok; ++tick) {
                 if (!tc_wait_grid(p, (unsigned)(tick + 1) * G, 1)) break;
-                tc::fence_proxy_async();
-                const unsigned char *src = reinterpret_cast<const unsigned char *>(
-                    p.hx + (size_t)(role.src_layer * 2 + (tick & 1)) * W * 128);
-                for (int c = 0; c < nchunks; ++c, ++it) {
-                    const uint32_t st = it % S, ph = (it / S) & 1;
-                    if (!tc_wait_mbar(bar_empty + 8 * st, ph ^ 1, p, 2)) { ok = false; break; }
-                    tc::mbar_arrive_expect_tx(bar_full + 8 * st, KLM_TC_CHUNK_BYTES);
-                    tc::bulk_g2s(tc::smem_u32(ring + (size_t)st * KLM_TC_CHUNK_BYTES), src + (size_t)c * KLM_TC_CHUNK_BYTES,
-                                 KLM_TC_CHUNK_BYTES, bar_full + 8 * st);
+                tc::mbar_arrive(bar_go);
+                tc_trace(p, tick, 0);
+                if (p.ingest_bulk) {
+                    // operand fetch by the bulk-copy engine (measured: ~25 B/clk per SM + ~90 clk per copy,
+                    // slower than the load/store path below; kept selectable for comparison)
+                    tc::fence_proxy_async();             // generic global writes of other CTAs -> async-proxy reads
+                    const unsigned char *src = reinterpret_cast<const unsigned char *>(
+                        p.hx + (size_t)(role.src_layer * 2 + (tick & 1)) * W * 128);
+                    for (int c0 = 0; c0 < nchunks; ++c0, ++it) {
+                        const int c = (c0 + (int)blockIdx.x) % nchunks;    // spread the CTAs over the chunks
+                        const uint32_t st = it % S, ph = (it / S) & 1;
+                        if (!tc_wait_mbar(bar_empty + 8 * st, ph ^ 1, p, 2)) { ok = false; break; }
+                        tc::mbar_arrive_expect_tx(bar_full + 8 * st, KLM_TC_CHUNK_BYTES);
+                        tc::bulk_g2s(tc::smem_u32(ring + (size_t)st * KLM_TC_CHUNK_BYTES), src + (size_t)c * KLM_TC_CHUNK_BYTES,
+                                     KLM_TC_CHUNK_BYTES, bar_full + 8 * st);
+                        if (c0 == 0) tc_trace(p, tick, 1);
+                    }
                 }
             }
         }
@@ -226,15 +267,17 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
             for (int tick = 0; tick < nticks && ok; ++tick) {
                 if (!tc_wait_mbar(bar_tempty, (tick & 1) ^ 1, p, 3)) break;
                 tc::tc_fence_after();
-                for (int c = 0; c < nchunks; ++c, ++it) {
+                for (int c0 = 0; c0 < nchunks; ++c0, ++it) {
+                    const int c = (c0 + (int)blockIdx.x) % nchunks;
                     const uint32_t st = it % S, ph = (it / S) & 1;
                     if (!tc_wait_mbar(bar_full + 8 * st, ph, p, 4)) { ok = false; break; }
+                    tc_trace(p, tick, c0 == 0 ? 2 : 3);
                     tc::tc_fence_after();
 #pragma unroll
                     for (int kk = 0; kk < KLM_TC_KC / 16; ++kk) {
                         const uint64_t ad = tc::smem_desc(ring_a + st * KLM_TC_CHUNK_BYTES + kk * 2 * lbo_a, lbo_a, 128);
                         const uint64_t bd = tc::smem_desc(w_a + (uint32_t)(c * (KLM_TC_KC / 8) + kk * 2) * lbo_b, lbo_b, 128);
-                        tc::mma_f16(tmem_base, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+                        tc::mma_f16(tmem_base, ad, bd, idesc, (c0 | kk) != 0 ? 1u : 0u);
                     }
                     tc::mma_commit(bar_empty + 8 * st);       // ring slot free once these MMAs have read it
                 }
@@ -253,11 +296,12 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                     bias4[i][0] = __ldg(p.bias[l] + u); bias4[i][1] = __ldg(p.bias[l] + u + 1);
                 }
         }
+        uint32_t lit = 0;                                 // ring position of the load/store ingest
         for (int tick = 0; tick < nticks; ++tick) {
-            int ok = 1;
-            if (lane == 0) ok = tc_wait_grid(p, (unsigned)(tick + 1) * G, 5) ? 1 : 0;
-            ok = __shfl_sync(0xffffffffu, ok, 0);
-            __syncwarp();
+            // the producer thread polls the grid barrier; its mbarrier arrive (release.cta) hands the
+            // acquired view of the other CTAs' writes (Z, logits) on to the epilogue threads
+            int ok = tc_wait_mbar(bar_go, tick & 1, p, 5) ? 1 : 0;
+            ok = __all_sync(0xffffffffu, ok);
             if (!ok) break;
             const int t = tick - role.sigma;
             const bool active = s < p.B && t >= 0 && t < len;
@@ -265,6 +309,8 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
 
             // ---- addends, fetched while the MMAs run ----
             float4 add4[KLM_TC_OWN][2];
+#pragma unroll
+            for (int i = 0; i < KLM_TC_OWN; ++i) add4[i][0] = add4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (is_rec && active) {
                 if (l == 0) {
                     // fused char + context embedding gather / concat / input contraction (rating.py:103-115,125)
@@ -301,12 +347,55 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                 }
             }
 
+            // ---- A operand of this tick: the hidden vector, global (L2) -> ring, by the epilogue warps ----
+            if (!p.ingest_bulk) {
+                const uint4 *src = reinterpret_cast<const uint4 *>(p.hx + (size_t)(role.src_layer * 2 + par_in) * W * 128);
+                const int et = tid - 64;                                   // 0..255; a chunk is 4 x 256 uint4
+                uint4 ba[4], bb[4], bc[4];
+                bool okl = true;
+#define TC_LOAD(c0_, buf_)                                                                      \
+                {                                                                               \
+                    const uint4 *sp_ = src + (size_t)(((c0_) + (int)blockIdx.x) % nchunks) * 1024 + et; \
+                    _Pragma("unroll") for (int j = 0; j < 4; ++j) buf_[j] = __ldcg(sp_ + 256 * j); \
+                }
+#define TC_STORE(c0_, buf_)                                                                     \
+                {                                                                               \
+                    const uint32_t st_ = lit % S, ph_ = (lit / S) & 1;                          \
+                    okl = okl && tc_wait_mbar(bar_empty + 8 * st_, ph_ ^ 1, p, 2);              \
+                    uint4 *dp_ = reinterpret_cast<uint4 *>(ring + (size_t)st_ * KLM_TC_CHUNK_BYTES) + et; \
+                    _Pragma("unroll") for (int j = 0; j < 4; ++j) dp_[256 * j] = buf_[j];       \
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                \
+                    tc::mbar_arrive(bar_full + 8 * st_);                                        \
+                    if ((c0_) == 0 && tid == 64) tc_trace(p, tick, 1);                          \
+                    ++lit;                                                                      \
+                }
+                TC_LOAD(0, ba);
+                if (nchunks > 1) TC_LOAD(1, bb);
+                for (int c0 = 0; c0 < nchunks; c0 += 3) {
+                    if (c0 + 2 < nchunks) TC_LOAD(c0 + 2, bc);
+                    TC_STORE(c0, ba);
+                    if (c0 + 3 < nchunks) TC_LOAD(c0 + 3, ba);
+                    if (c0 + 1 < nchunks) TC_STORE(c0 + 1, bb);
+                    if (c0 + 4 < nchunks) TC_LOAD(c0 + 4, bb);
+                    if (c0 + 2 < nchunks) TC_STORE(c0 + 2, bc);
+                }
+#undef TC_LOAD
+#undef TC_STORE
+                if (!__all_sync(0xffffffffu, okl ? 1 : 0)) break;
+            }
+
             // ---- accumulators ----
             ok = tc_wait_mbar(bar_tfull, tick & 1, p, 6) ? 1 : 0;
             ok = __all_sync(0xffffffffu, ok);
             if (!ok) break;
+            if (tid == 64) tc_trace(p, tick, 4);
             tc::tc_fence_after();
             float acc[KLM_TC_OWN][8];
+#pragma unroll
+            for (int i = 0; i < KLM_TC_OWN; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+            // own pairs: this row's part (hi rows: hi.hi + hi.lo columns; lo rows: lo.hi columns)
 #pragma unroll
             for (int i = 0; i < KLM_TC_OWN; ++i)
                 if (i < nown) {
@@ -322,74 +411,86 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                         tc::tmem_ld_wait();
                     }
                 }
-            // round 1: the lo half hands its part of pairs [0,Ph) to the hi half
-            if (half == 1) {
+            // the other half's pairs: hand this row's part over through shared memory (both directions at once)
+            {
+                float *xs = xchg + (half ? 0 : KLM_TC_MAX_PAIRS / 2 * 8 * 64);
 #pragma unroll
                 for (int i = 0; i < KLM_TC_OWN; ++i)
-                    if (i < Ph) {
+                    if (i < nsend) {
+                        const int pr = send_first + i, xi = pr - oth_first;
                         float v[8];
-                        tc::tmem_ld8(trow + 8 * i, v);
-                        tc::tmem_ld_wait();
+                        tc::tmem_ld8(trow + 8 * pr, v);
+                        if (half == 0) {
+                            float b[8];
+                            tc::tmem_ld8(trow + N + 8 * pr, b);
+                            tc::tmem_ld_wait();
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) xchg[(i * 8 + j) * 64 + s] = v[j];
-                    }
-            }
-            tc_bar_epi();
-            if (half == 0) {
+                            for (int j = 0; j < 8; ++j) v[j] += b[j];
+                        } else {
+                            tc::tmem_ld_wait();
+                        }
 #pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
-                    if (i < nown) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) acc[i][j] += xchg[(i * 8 + j) * 64 + s];
-                    }
-            }
-            tc_bar_epi();
-            // round 2: the hi half hands its part of pairs [Ph,NP) to the lo half
-            if (half == 0) {
-#pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
-                    if (Ph + i < NP) {
-                        float a[8], b[8];
-                        tc::tmem_ld8(trow + 8 * (Ph + i), a);
-                        tc::tmem_ld8(trow + N + 8 * (Ph + i), b);
-                        tc::tmem_ld_wait();
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) xchg[(i * 8 + j) * 64 + s] = a[j] + b[j];
+                        for (int j = 0; j < 8; ++j) xs[(xi * 8 + j) * 64 + s] = v[j];
                     }
             }
             tc::tc_fence_before();
             tc::mbar_arrive(bar_tempty);                      // this thread is done reading TMEM
             tc_bar_epi();
-            if (half == 1) {
+            {
+                const float *xr = xchg + (half ? KLM_TC_MAX_PAIRS / 2 * 8 * 64 : 0);
 #pragma unroll
                 for (int i = 0; i < KLM_TC_OWN; ++i)
                     if (i < nown) {
+                        const int xi = own_first + i - my_first;
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) acc[i][j] += xchg[(i * 8 + j) * 64 + s];
+                        for (int j = 0; j < 8; ++j) acc[i][j] += xr[(xi * 8 + j) * 64 + s];
                     }
+                // the hand-over buffer aliases the ring: order these generic accesses before the next bulk copies
+                if (p.ingest_bulk) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             }
 
             // ---- finish and hand over ----
+            if (tid == 64) tc_trace(p, tick, 5);
             if (is_rec) {
+                // LSTM cell for all owned units, staged so that the MUFU chains of different units overlap
+                float e1[KLM_TC_OWN][2], e2[KLM_TC_OWN][2], e3[KLM_TC_OWN][2], e4[KLM_TC_OWN][2];
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float4 a = add4[i][e];
+                        e1[i][e] = tc_exp(-tc_clamp(acc[i][4 * e] + a.x));
+                        e2[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 1] + a.y));
+                        e3[i][e] = tc_exp(-2.f * tc_clamp(acc[i][4 * e + 2] + a.z));
+                        e4[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 3] + a.w));
+                    }
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float ig = __fdividef(1.f - e3[i][e], (1.f + e1[i][e]) * (1.f + e3[i][e]));
+                        const float f = __fdividef(1.f, 1.f + e2[i][e]);
+                        e1[i][e] = fmaf(f, c_reg[i][e], ig);                       // new cell state
+                        e2[i][e] = tc_exp(-2.f * tc_clamp(e1[i][e]));
+                    }
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float hn = __fdividef(1.f - e2[i][e], (1.f + e4[i][e]) * (1.f + e2[i][e]));
+                        if (active) { c_reg[i][e] = e1[i][e]; h_reg[i][e] = hn; }
+                    }
 #pragma unroll
                 for (int i = 0; i < KLM_TC_OWN; ++i)
                     if (i < nown) {
                         const int u = 2 * (role.first_pair + own_first + i);
-                        if (active) {
-#pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                const float4 a = add4[i][e];
-                                tc_cell(acc[i][4 * e] + a.x, acc[i][4 * e + 1] + a.y, acc[i][4 * e + 2] + a.z,
-                                        acc[i][4 * e + 3] + a.w, c_reg[i][e], h_reg[i][e]);
-                            }
-                        }
                         __half hi0, lo0, hi1, lo1;
                         tc_split(h_reg[i][0], hi0, lo0); tc_split(h_reg[i][1], hi1, lo1);
                         __half *dst = p.hx + ((size_t)(l * 2 + par_out) * (W / 8) + u / 8) * (128 * 8) + (u & 7);
                         *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
                         *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
                     }
-                tc::fence_proxy_async();
+                if (p.ingest_bulk) tc::fence_proxy_async();
             } else if (role.kind == KLM_TC_IN) {
                 float4 *zrow = reinterpret_cast<float4 *>(p.Z + ((size_t)(l * 2 + par_out) * 64 + s) * 4 * W);
 #pragma unroll
@@ -413,8 +514,9 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                         __stcg(lrow + 2 * g8 + 1, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
                     }
             }
+            if (tid == 64) tc_trace(p, tick, 6);
             tc_bar_epi();
-            if (tid == 64) tc::red_release_add(p.barrier, 1u);
+            if (tid == 64) { tc::red_release_add(p.barrier, 1u); tc_trace(p, tick, 7); }
         }
         // ---- write the final state back ----
         if (is_rec && s < p.B) {

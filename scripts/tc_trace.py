@@ -1,0 +1,41 @@
+"""Timeline of the tcgen05 sequence kernel: per role, mean SM-clock offsets of the per-tick events.
+usage: tc_trace.py [cfg2|W,D] [T]"""
+import os, sys, logging
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench
+from ocrd_keraslm_b200 import synth, _native
+from ocrd_keraslm_b200.lib import Rater
+
+wl = sys.argv[1] if len(sys.argv) > 1 else 'cfg2'
+T = int(sys.argv[2]) if len(sys.argv) > 2 else 3000
+log = logging.getLogger('t'); log.setLevel(logging.CRITICAL)
+if wl in bench.WORKLOADS:
+    width, depth, length, contexts, docs, chars, what = bench.WORKLOADS[wl]
+    wd = bench.model_weights(wl)
+else:
+    width, depth = [int(x) for x in wl.split(',')]
+    length = 512
+    wd = synth.weights(3, width=width, depth=depth, style='keras')
+r = Rater.from_weights(wd, synth.vocabulary(), length, logger=log)
+texts = [synth.text(100 + i, T) for i in range(64)]
+ctxs = [[179]] * 64 if len(r.context_shapes) == 1 else [[1] * len(r.context_shapes)] * 64
+r.rate_many(texts, ctxs)
+r._native.tc_trace_arm(1000)
+r.rate_many(texts, ctxs)
+tr, roles = r._native.tc_trace_read()
+info = r._native.info()
+print('grid', info['tc_grid'], 'last kernel ms', info['last_kernel_ms'], 'per tick us', 1e3 * info['last_kernel_ms'] / (T + 2 * depth))
+names = {0: 'REC', 1: 'IN', 2: 'PROJ', 3: 'LSE'}
+tr = tr.astype(np.int64)
+ev = ['start', 'issue0', 'chunk0', 'chunkN', 'mma_done', 'drained', 'stored', 'arrive']
+for kind in (0, 1, 2):
+    for layer in range(depth):
+        sel = [i for i in range(len(roles)) if roles[i, 0] == kind and roles[i, 1] == layer]
+        if not sel:
+            continue
+        x = tr[sel][:, 2:14, :]                   # [cta][tick][ev]
+        period = (x[:, 1:, 0] - x[:, :-1, 0]).mean()
+        rel = (x - x[:, :, :1]).mean(axis=(0, 1))
+        print('%s l%d n=%d pairs=%s period %.0f clk | ' % (names[kind], layer, len(sel), sorted(set(int(v) for v in roles[sel, 2])), period) +
+              ' '.join('%s %+.0f' % (e, v) for e, v in zip(ev, rel)))
