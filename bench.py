@@ -41,10 +41,11 @@ WORKLOADS = {
     #        width depth length contexts            docs   chars   what
     'cfg1': (128, 2, 256, ((200, 10),), 1, 100000, 'stateful rating width=128 depth=2 length=256, 1 document x 100000 chars'),
     'cfg2': (512, 3, 512, ((200, 10),), 64, 100000, 'stateful rating width=512 depth=3 length=512, 64 documents x 100000 chars'),
+    'cfg3': (512, 3, 512, ((200, 10),), 4, 200, 'rate_best beam search, beam=100, 5 alternatives/word, pages of 200 words chained by traceback, width=512 depth=3'),
     'cfg4': (512, 3, 512, ((200, 16),) * 3, 64, 100000, 'context-conditioned (3 context variables, dim 16) width=512 depth=3, 64 documents x 100000 chars'),
     'cfg5': (1024, 3, 512, ((200, 10),), 10000, 70, 'page-sharded rating width=1024 depth=3, 10000 lines of 20..120 chars'),
 }
-CFG_INDEX = {'cfg1': 1, 'cfg2': 2, 'cfg4': 4, 'cfg5': 5}
+CFG_INDEX = {'cfg1': 1, 'cfg2': 2, 'cfg3': 3, 'cfg4': 4, 'cfg5': 5}
 FALLBACK_PEAKS = {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0}
 
 quiet = logging.getLogger('bench')
@@ -183,6 +184,81 @@ def run_reference(args):
         'e2e': {'value': value, 'unit': 'chars/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     })
+    print(json.dumps(line))
+
+
+
+# ------------------------------------------------------------------------------------------ beam search (cfg3)
+def beam_pages(rater, n_pages, n_words, first_page=0):
+    """rate_best over `n_pages` synthetic lattices chained through the traceback (wrapper/rate.py:186-290)."""
+    tb = None
+    chosen = []
+    for pg in range(first_page, first_page + n_pages):
+        graph, start, end = synth.lattice(20261104 + 3000 + pg, n_words=n_words, n_alts=5)
+        path, entropy, tb = rater.rate_best(graph, start, end, start_traceback=tb, context=[179], lm_weight=0.5,
+                                            beam_width=100, beam_clustering_dist=0)
+        chosen.append([alt.Unicode for _, alt, _ in path])
+    path, entropy, _ = rater.next_path(tb[0], ([], tb[1]))
+    chosen.append([alt.Unicode for _, alt, _ in path])
+    return chosen
+
+
+def run_beam(args):
+    """`--workload cfg3`: beam steps/sec of rate_best (one step = one batched advance of all live hypotheses
+    by one character).  Our arm: Rater.rate_best with the device step kernel; reference arm: the oracle port."""
+    width, depth, length, contexts, pages, words, what = WORKLOADS['cfg3']
+    pages = args.docs or pages
+    words = args.chars or words
+    wd = model_weights('cfg2')                      # cfg3 uses the model of cfg2 (SURVEY 8d)
+    if args.impl == 'reference':
+        if int(os.environ.get('RANK', '0')) != 0:
+            return
+        from tests import util
+        from oracle.rater_oracle import OracleRater
+        o = OracleRater(util.to_model(wd), synth.mapping_from_array(synth.vocabulary()), length, logger=quiet)
+        words_cpu = min(words, 12)
+        beam_pages(o, 1, 4)
+        t0 = time.perf_counter()
+        c0 = o.device_calls
+        for _ in range(args.steps):
+            beam_pages(o, 1, words_cpu)
+        dt = time.perf_counter() - t0
+        steps = o.device_calls - c0
+        line = base_line(args, steps / dt, 1000.0 * dt / args.steps)
+        line.update({'metric': 'beam steps/sec (rate_best)', 'unit': 'steps/s', 'impl': 'reference', 'gpu_launches': 0,
+                     'cpu_baseline': {'value': steps / dt, 'unit': 'steps/s', 'cores': len(os.sched_getaffinity(0)), 'kind': 'port',
+                                      'sample': '%d page(s) of %d words per step, numpy BLAS threads' % (1, words_cpu)},
+                     'e2e': {'value': steps / dt, 'unit': 'steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}})
+        print(json.dumps(line))
+        return
+    import torch
+    from ocrd_keraslm_b200.lib import Rater
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    r = Rater.from_weights(wd, synth.vocabulary(), length, stateful=False, incremental=True, logger=quiet, device=local)
+    for _ in range(min(args.warmup, 2)):
+        beam_pages(r, 1, 10)
+    r._native.sync()
+    l0 = r._native.info()['kernel_launches']
+    s0, h0 = r.device_steps, r.hypothesis_steps
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        beam_pages(r, pages, words)
+    r._native.sync()
+    dt = time.perf_counter() - t0
+    steps, hyps = r.device_steps - s0, r.hypothesis_steps - h0
+    line = base_line(args, steps / dt, 1000.0 * dt / args.steps)
+    F = flops_per_char(width, depth, contexts)
+    pk, pk_src = peaks()
+    line.update({'metric': 'beam steps/sec (rate_best)', 'unit': 'steps/s',
+                 'hypothesis_steps_per_s': hyps / dt, 'mean_hypotheses_per_step': hyps / max(steps, 1),
+                 'gpu_launches': r._native.info()['kernel_launches'] - l0,
+                 'e2e': {'value': steps / dt, 'unit': 'steps/s', 'h2d_bytes_per_step': int(12 * hyps / args.steps),
+                         'd2h_bytes_per_step': int(4 * hyps / args.steps), 'api': 'Rater.rate_best(graph, ...)'},
+                 'roofline': {'bound': 'tensor', 'kernel': 'klm_seq_tc (one tick per klm_step)', 'achieved': hyps / dt * F / 1e12,
+                              'peak': float(pk.get('bf16_tflops', 1590.0)), 'unit': 'TFLOP/s',
+                              'frac': hyps / dt * F / 1e12 / float(pk.get('bf16_tflops', 1590.0)), 'traffic': None,
+                              'note': 'wall-clock of the whole search incl. the host-side beam logic, not kernel time'}})
     print(json.dumps(line))
 
 
@@ -465,7 +541,9 @@ def main():
     ap.add_argument('--no-cpu', action='store_true', help='skip the CPU baseline leg')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
-    if args.impl == 'reference':
+    if args.workload == 'cfg3':
+        run_beam(args)
+    elif args.impl == 'reference':
         run_reference(args)
     else:
         run_ours(args)

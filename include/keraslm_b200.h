@@ -127,6 +127,30 @@ int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx,
              const int32_t *slots_in, const int32_t *slots_out, const int32_t *targets,
              float *out, int mem);
 
+/*
+ * One lattice edge of the beam search.  Replaces the per-edge loop of Rater.rate_best (rating.py:789-852):
+ * candidates = incoming hypotheses x alternatives, character-synchronous batched steps (klm_step with
+ * targets), worst-first pops, projected-cost ordering with bisect.insort_left semantics, the +15 bit
+ * cardinality break (:816), the +2.5 bit threshold (:847) and the truncation (:851).  Not covered (the caller
+ * keeps the reference control flow for these): beam_clustering_dist != 0, an out-node that already has a beam.
+ *
+ *   hyp_slot/hyp_last_char/hyp_cum_cost [n_hyp]  state slot (-1 = zeros), index of the last character and
+ *                                                cumulative cost of every hypothesis of the incoming beam
+ *   alt_offsets [n_alt+1], alt_chars             character indices of the alternatives, alt_conf [n_alt]
+ *   ctx [n_ctx]                                  context indices; lm_weight, batch_size as in the reference
+ *   scratch_slots [n_scratch]                    free state slots the search may use (>= n_hyp*n_alt + batch_size)
+ *   out_* [max_out]                              the first max_out finished candidates in beam order: hypothesis
+ *                                                index, alternative index, cumulative cost, state slot (one of
+ *                                                scratch_slots, or -2 = the incoming hypothesis' own state)
+ * All pointers are host pointers; the call returns when the edge is finished.
+ */
+int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slot, const int32_t *hyp_last_char,
+                  const double *hyp_cum_cost, int32_t n_alt, const int32_t *alt_offsets, const int32_t *alt_chars,
+                  const double *alt_conf, const int32_t *ctx, double lm_weight, int32_t batch_size,
+                  int32_t n_scratch, const int32_t *scratch_slots, int32_t max_out, int32_t *out_hyp,
+                  int32_t *out_alt, double *out_cum_cost, int32_t *out_slot, int32_t *n_out, int64_t *n_steps,
+                  int64_t *n_hyp_steps);
+
 /* Introspection for bench.py / tests. */
 typedef struct klm_info {
     int32_t sm_count;

@@ -90,6 +90,8 @@ SYMBOLS = [
     ('klm_get_info', ctypes.c_int, [_P, ctypes.POINTER(KlmInfo)]),
     ('klm_selftest_umma', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
     ('klm_tc_trace', ctypes.c_int, [_P, _I, _P, _P]),
+    ('klm_beam_edge', ctypes.c_int, [_P, _I, _P, _P, _P, _I, _P, _P, _P, _P, ctypes.c_double, _I, _I, _P, _I,
+                                     _P, _P, _P, _P, _P, _P, _P]),
 ]
 
 _lib = None
@@ -205,6 +207,27 @@ class Model(object):
         inf = KlmInfo()
         self.check(self._lib.klm_get_info(self._h, ctypes.byref(inf)))
         return dict((f, getattr(inf, f)) for f, _ in KlmInfo._fields_)
+
+    def beam_edge(self, hyp_slot, hyp_last_char, hyp_cum_cost, alt_offsets, alt_chars, alt_conf, ctx, lm_weight,
+                  batch_size, scratch_slots, max_out):
+        """See klm_beam_edge.  Returns (hyp, alt, cum_cost, slot) arrays of the finished candidates in beam order
+        and (device steps, hypothesis steps)."""
+        hs, hl = _i32(hyp_slot), _i32(hyp_last_char)
+        hc = np.ascontiguousarray(hyp_cum_cost, dtype=np.float64)
+        ao, ac = _i32(alt_offsets), _i32(alt_chars)
+        af = np.ascontiguousarray(alt_conf, dtype=np.float64)
+        cx = None if ctx is None or len(ctx) == 0 else _i32(ctx)
+        sc = _i32(scratch_slots)
+        oh, oa = np.empty(max_out, np.int32), np.empty(max_out, np.int32)
+        oc, os_ = np.empty(max_out, np.float64), np.empty(max_out, np.int32)
+        n_out = ctypes.c_int32(0)
+        st, hst = ctypes.c_int64(0), ctypes.c_int64(0)
+        self.check(self._lib.klm_beam_edge(self._h, len(hs), _ptr(hs), _ptr(hl), _ptr(hc), len(af), _ptr(ao), _ptr(ac),
+                                           _ptr(af), _ptr(cx), float(lm_weight), int(batch_size), len(sc), _ptr(sc),
+                                           int(max_out), _ptr(oh), _ptr(oa), _ptr(oc), _ptr(os_), ctypes.byref(n_out),
+                                           ctypes.byref(st), ctypes.byref(hst)))
+        k = n_out.value
+        return oh[:k], oa[:k], oc[:k], os_[:k], st.value, hst.value
 
     def tc_trace_arm(self, first_tick):
         self.check(self._lib.klm_tc_trace(self._h, first_tick, None, None))

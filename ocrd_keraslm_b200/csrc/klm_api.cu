@@ -894,3 +894,118 @@ extern "C" int klm_tc_trace(klm_model *m, int32_t first_tick, uint64_t *out, int
         }
     return KLM_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// One lattice edge of the beam search, natively: replaces the inner loop of Rater.rate_best
+// (rating.py:789-852) for one edge -- candidate = (incoming hypothesis, alternative), character-
+// synchronous batched steps, worst-first pops, projected-cost ordering with Python's
+// bisect.insort_left (replicated comparison by comparison, including its behaviour on the not yet
+// sorted initial list), the +15 bit cardinality break, the +2.5 bit threshold and the truncation of
+// the waiting list.  Clustering (beam_clustering_dist) and joins into an already populated node are
+// left to the host-language path.
+namespace {
+struct BeamCand { int hyp, alt, len, alt_len, slot; bool own; double cum, conf_cost; };
+struct BeamLists {
+    std::vector<BeamCand> c;
+    double pro(int i) const { return c[i].cum + 0.5 * (double)(c[i].alt_len - c[i].len); }
+    void insort_left(std::vector<int> &a, int x) const {       // bisect.insort_left with Node.__lt__ (:1300-1318)
+        size_t lo = 0, hi = a.size();
+        const double px = pro(x);
+        while (lo < hi) {
+            const size_t mid = (lo + hi) / 2;
+            if (pro(a[mid]) < px) lo = mid + 1; else hi = mid;
+        }
+        a.insert(a.begin() + lo, x);
+    }
+};
+}  // namespace
+
+extern "C" int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slot, const int32_t *hyp_last_char,
+                             const double *hyp_cum_cost, int32_t n_alt, const int32_t *alt_offsets,
+                             const int32_t *alt_chars, const double *alt_conf, const int32_t *ctx, double lm_weight,
+                             int32_t batch_size, int32_t n_scratch, const int32_t *scratch_slots, int32_t max_out,
+                             int32_t *out_hyp, int32_t *out_alt, double *out_cum_cost, int32_t *out_slot, int32_t *n_out,
+                             int64_t *n_steps, int64_t *n_hyp_steps) {
+    if (!m || !hyp_slot || !hyp_last_char || !hyp_cum_cost || !alt_offsets || !alt_chars || !alt_conf || !scratch_slots ||
+        !out_hyp || !out_alt || !out_cum_cost || !out_slot || !n_out)
+        return fail(KLM_EINVAL, "klm_beam_edge: NULL argument");
+    if (n_hyp < 0 || n_alt < 1 || batch_size < 1 || max_out < 0) return fail(KLM_EINVAL, "klm_beam_edge: bad sizes");
+    *n_out = 0;
+    if (n_steps) *n_steps = 0;
+    if (n_hyp_steps) *n_hyp_steps = 0;
+    BeamLists L;
+    std::vector<int> waiting, done, batch, free_slots(scratch_slots, scratch_slots + n_scratch);
+    const double log2d = std::log(2.0);
+    int max_len = 0;
+    for (int a = 0; a < n_alt; ++a) max_len = std::max(max_len, alt_offsets[a + 1] - alt_offsets[a]);
+    for (int h = 0; h < n_hyp; ++h)
+        for (int a = 0; a < n_alt; ++a) {                        // beam-major, not re-sorted (:789-795)
+            BeamCand c;
+            c.hyp = h; c.alt = a; c.len = 0; c.alt_len = alt_offsets[a + 1] - alt_offsets[a];
+            c.slot = hyp_slot[h]; c.own = false; c.cum = hyp_cum_cost[h];
+            c.conf_cost = -(std::log(std::max(alt_conf[a], 1e-99)) / log2d) * (1.0 - lm_weight);
+            waiting.push_back((int)L.c.size());
+            L.c.push_back(c);
+        }
+    auto release = [&](int i) { if (L.c[i].own) { free_slots.push_back(L.c[i].slot); L.c[i].own = false; } };
+    const int rounds = 3 * max_len;                              // :797
+    std::vector<int32_t> feed, want, s_in, s_out, cx;
+    std::vector<float> logp;
+    for (int r = 0; r < rounds; ++r) {
+        batch.clear();
+        while (!waiting.empty()) {                               // most expensive first (:800-810)
+            const int i = waiting.back();
+            waiting.pop_back();
+            if (L.c[i].len == L.c[i].alt_len) L.insort_left(done, i);
+            else L.insort_left(batch, i);
+            if ((int)batch.size() >= batch_size) break;
+        }
+        if (batch.empty()) break;
+        if (!done.empty() && L.c[batch[0]].cum >= L.c[done[0]].cum + 15.0) {   // :816-818
+            for (int i : batch) release(i);
+            for (int i : waiting) release(i);
+            batch.clear(); waiting.clear();
+            break;
+        }
+        const int n = (int)batch.size();
+        if ((int)free_slots.size() < n) return fail(KLM_ESTATE, "klm_beam_edge: out of scratch state slots");
+        feed.resize(n); want.resize(n); s_in.resize(n); s_out.resize(n); logp.resize(n);
+        cx.resize((size_t)n * std::max(1, m->Nc));
+        for (int k = 0; k < n; ++k) {
+            const BeamCand &c = L.c[batch[k]];
+            feed[k] = c.len ? alt_chars[alt_offsets[c.alt] + c.len - 1] : hyp_last_char[c.hyp];   // :821-824
+            want[k] = alt_chars[alt_offsets[c.alt] + c.len];
+            s_in[k] = c.slot;
+            s_out[k] = free_slots.back(); free_slots.pop_back();
+            for (int j = 0; j < m->Nc; ++j) cx[(size_t)k * m->Nc + j] = ctx ? ctx[j] : 0;
+        }
+        int rc = klm_step(m, n, feed.data(), m->Nc ? cx.data() : nullptr, s_in.data(), s_out.data(), want.data(), logp.data(),
+                          KLM_MEM_HOST);
+        if (rc) return rc;
+        if (n_steps) ++*n_steps;
+        if (n_hyp_steps) *n_hyp_steps += n;
+        for (int k = 0; k < n; ++k) {                            // ascending projected cost (:827-849)
+            const int i = batch[k];
+            BeamCand &c = L.c[i];
+            const float prob = expf(logp[k]);                    // float32, like the softmax output it replaces
+            c.cum += -(std::log(std::max((double)prob, 1e-99)) / log2d) * lm_weight + c.conf_cost;
+            c.len += 1;
+            release(i);
+            c.slot = s_out[k]; c.own = true;
+            if (!waiting.empty() && c.cum >= L.c[waiting[0]].cum + 2.5) { release(i); continue; }   // :847-848
+            L.insort_left(waiting, i);
+        }
+        const size_t keep = (size_t)rounds * batch_size;         // :851
+        if (waiting.size() > keep) {
+            for (size_t k = keep; k < waiting.size(); ++k) release(waiting[k]);
+            waiting.resize(keep);
+        }
+    }
+    const int no = std::min<int>(max_out, (int)done.size());
+    for (int k = 0; k < no; ++k) {
+        const BeamCand &c = L.c[done[k]];
+        out_hyp[k] = c.hyp; out_alt[k] = c.alt; out_cum_cost[k] = c.cum; out_slot[k] = c.own ? c.slot : -2;   // -2: the parent's state
+    }
+    *n_out = no;
+    return KLM_OK;
+}

@@ -209,6 +209,9 @@ class Rater(object):
         self._lut_src = None
         self._pending_weights = None
         self._pin = None
+        self.native_beam = True            # rate_best: run whole lattice edges through klm_beam_edge where possible
+        self.device_steps = 0              # klm_step calls / hypotheses advanced so far (bench.py: beam steps/sec)
+        self.hypothesis_steps = 0
 
     # ------------------------------------------------------------------ lifecycle
     def load_config(self, filename):
@@ -556,6 +559,8 @@ class Rater(object):
         else:
             out = np.empty(n, dtype=np.float32)
         self._native.step(indices, ctx, slots_in, out_slots, targets, out)
+        self.device_steps += 1
+        self.hypothesis_steps += n
         del temps
         return out, new_states
 
@@ -648,6 +653,10 @@ class Rater(object):
             element, alternatives = edge['element'], edge['alternatives']
             in_attrs, out_attrs = graph.nodes[in_node], graph.nodes[out_node]
             assert 'traceback' in in_attrs, "graph not topologically connected at node %s" % str(in_node)
+            if self.native_beam and not beam_clustering_dist and 'traceback' not in out_attrs:
+                out_attrs['traceback'] = self._beam_edge_native(in_attrs['traceback'], element, alternatives, context,
+                                                                lm_weight, beam_width)
+                continue
             done = out_attrs['traceback'] if 'traceback' in out_attrs else []
             waiting = [Node(parent=hyp, state=hyp.state, value="", cost=0.0, extras=(element, alt))
                        for hyp in in_attrs['traceback'] for alt in alternatives]
@@ -702,6 +711,56 @@ class Rater(object):
         assert out_node == end_node, 'graph must have a path from start_node to end_node'
         assert out_attrs is not None and 'traceback' in out_attrs, 'graph has no traceback at end_node'
         return self.next_path(out_attrs['traceback'], start_traceback)
+
+    def _beam_edge_native(self, beam, element, alternatives, context, lm_weight, beam_width):
+        """One lattice edge through ``klm_beam_edge``: the reference's per-edge loop (:789-852) run natively.
+
+        Only the finished candidates that make it into the beam become ``Node`` objects; their states stay in
+        the device pool.  Unmapped characters are reported once per alternative up front.
+        """
+        c_i = self.mapping[0]
+        n_hyp, n_alt = len(beam), len(alternatives)
+        offsets = np.zeros(n_alt + 1, dtype=np.int32)
+        chars = []
+        for a, alt in enumerate(alternatives):
+            seen = []
+            for ch in alt.Unicode:
+                if ch not in c_i and ch not in seen:
+                    self.logger.error('unmapped character "%s" at input alternative %d of element %s',
+                                      ch, alt.index or 0, element.id if element else "space")
+                    seen.append(ch)
+                chars.append(c_i.get(ch, 0))
+            offsets[a + 1] = len(chars)
+        if n_hyp == 0:
+            return []
+        slots, temps = self._slots_for([hyp.state for hyp in beam])
+        last = np.fromiter((c_i.get(hyp.value[-1], 0) for hyp in beam), dtype=np.int32, count=n_hyp)
+        cum = np.fromiter((hyp.cum_cost for hyp in beam), dtype=np.float64, count=n_hyp)
+        conf = np.fromiter((alt.conf for alt in alternatives), dtype=np.float64, count=n_alt)
+        scratch = self._pool.acquire(n_hyp * n_alt + self.batch_size)
+        try:
+            oh, oa, oc, osl, steps, hsteps = self._native.beam_edge(
+                slots, last, cum, offsets, np.asarray(chars, dtype=np.int32), conf, context, lm_weight, self.batch_size,
+                scratch, beam_width)
+        except Exception:
+            for sl in scratch:
+                self._pool.release(sl)
+            raise
+        self.device_steps += steps
+        self.hypothesis_steps += hsteps
+        kept = set(int(x) for x in osl if x >= 0)
+        for sl in scratch:
+            if sl not in kept:
+                self._pool.release(sl)
+        del temps
+        out = []
+        for h, a, cost, sl in zip(oh, oa, oc, osl):
+            hyp, alt = beam[int(h)], alternatives[int(a)]
+            state = DeviceState(self._pool, int(sl)) if sl >= 0 else hyp.state
+            node = Node(parent=hyp, state=state, value=alt.Unicode, cost=0.0, extras=(element, alt))
+            node.cum_cost = float(cost)
+            out.append(node)
+        return out
 
     def next_path(self, beam, traceback):
         """Decide the previous graph's path from the current beam and cut histories there (reference :862-885)."""

@@ -242,3 +242,34 @@ def test_long_document_drift_and_chunking():
     ref = o.rate(text[:3000], [179])
     assert_logp_close(whole[:2999], ref[:2999])
     assert ppl > 1.0 and math.isfinite(ppl)
+
+
+# ------------------------------------------------------------------ native beam edge (klm_beam_edge) vs the host-language loop
+@pytest.mark.parametrize('width,beam_width,batch_size', [(64, 10, 128), (128, 100, 128), (128, 7, 16)])
+def test_rate_best_native_edge_equals_python_loop(width, beam_width, batch_size):
+    wd = synth.weights(21, width=width, depth=2, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    results = []
+    for native in (True, False):
+        r = product(wd, maparr, 8, stateful=False, incremental=True)
+        r.native_beam = native
+        r.batch_size = batch_size
+        tb = None
+        pages = []
+        for pg in range(2):
+            graph, start, end = synth.lattice(900 + pg, n_words=12, n_alts=5)
+            path, entropy, tb = r.rate_best(graph, start, end, start_traceback=tb, context=[42], lm_weight=0.5,
+                                            beam_width=beam_width, beam_clustering_dist=0)
+            pages.append(([(el.id if el else None, alt.Unicode, alt.index) for el, alt, _ in path],
+                          [s for _, _, s in path], entropy, [n.value for n in tb[0]], [n.cum_cost for n in tb[0]]))
+        path, entropy, _ = r.next_path(tb[0], ([], tb[1]))
+        pages.append(([(el.id if el else None, alt.Unicode, alt.index) for el, alt, _ in path], [s for _, _, s in path],
+                      entropy, [], []))
+        results.append((pages, r.device_steps, r.hypothesis_steps))
+    (pa, sa, ha), (pb, sb, hb) = results
+    assert (sa, ha) == (sb, hb)                      # same number of device steps and hypotheses advanced
+    for x, y in zip(pa, pb):
+        assert x[0] == y[0] and x[3] == y[3]
+        np.testing.assert_allclose(x[1], y[1], rtol=1e-6)
+        np.testing.assert_allclose(x[4], y[4], rtol=1e-6, atol=1e-6)
+        assert x[2] == pytest.approx(y[2], rel=1e-6, abs=1e-6)
