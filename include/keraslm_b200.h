@@ -171,6 +171,10 @@ int klm_get_info(klm_model *m, klm_info *out);
  * fp16 operand images in the kernel's shared-memory layout ([K/8][rows][8] halves); host pointers. */
 int klm_selftest_umma(int device, int32_t N, int32_t K, const uint16_t *A_img, const uint16_t *B_img, float *D);
 
+/* Self-test of the CTA-pair MMA (cta_group::2, M = 128 over two CTAs): A_img = the two [K/8][64][8] row halves,
+ * B_img = the two [K/8][N/2][8] row halves; D = raw TMEM dump [2 CTAs][128 lanes][N/2 columns]; host pointers. */
+int klm_selftest_umma2(int device, int32_t N, int32_t K, const uint16_t *A_img, const uint16_t *B_img, float *D);
+
 /* Debug timeline of the tcgen05 kernel.  out == NULL: arm tracing of 16 ticks from `first_tick` for the
  * following launches; out != NULL: copy [tc_grid][16][8] SM-clock samples (events: 0 tick start, 1 copies
  * issued, 2 first / 3 last operand chunk landed, 4 accumulators complete, 5 TMEM drained, 6 hand-over stored,

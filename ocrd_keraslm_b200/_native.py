@@ -89,6 +89,7 @@ SYMBOLS = [
     ('klm_step', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
     ('klm_get_info', ctypes.c_int, [_P, ctypes.POINTER(KlmInfo)]),
     ('klm_selftest_umma', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
+    ('klm_selftest_umma2', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
     ('klm_tc_trace', ctypes.c_int, [_P, _I, _P, _P]),
     ('klm_beam_edge', ctypes.c_int, [_P, _I, _P, _P, _P, _I, _P, _P, _P, _P, ctypes.c_double, _I, _I, _P, _I,
                                      _P, _P, _P, _P, _P, _P, _P]),
@@ -153,6 +154,28 @@ def selftest_umma(A, B, device=0):
     if rc != 0:
         raise NativeError('klm_selftest_umma: %s' % lib.klm_last_error().decode())
     return D
+
+
+def selftest_umma2_raw(A, B, device=0):
+    """CTA-pair MMA (cta_group::2): A [128, K], B [N, K]; returns the raw TMEM dump [2][128 lanes][N/2 columns]."""
+    lib = load()
+    A = np.asarray(A, dtype=np.float16)
+    B = np.asarray(B, dtype=np.float16)
+    N, K = B.shape
+    ai = np.concatenate([operand_image(A[:64]).ravel(), operand_image(A[64:]).ravel()])
+    bi = np.concatenate([operand_image(B[:N // 2]).ravel(), operand_image(B[N // 2:]).ravel()])
+    D = np.empty((2, 128, N // 2), dtype=np.float32)
+    rc = lib.klm_selftest_umma2(device, N, K, ai.ctypes.data, bi.ctypes.data, D.ctypes.data)
+    if rc != 0:
+        raise NativeError('klm_selftest_umma2: %s' % lib.klm_last_error().decode())
+    return D
+
+
+def selftest_umma2(A, B, device=0):
+    """D = A . B^T through the CTA-pair MMA, reassembled from the 2x2 accumulator layout:
+    CTA r holds rows 64r..64r+63; lanes 0..63 carry columns [0, N/2), lanes 64..127 columns [N/2, N)."""
+    raw = selftest_umma2_raw(A, B, device)
+    return np.concatenate([np.concatenate([raw[r, :64], raw[r, 64:]], axis=1) for r in range(2)], axis=0)
 
 
 class Model(object):

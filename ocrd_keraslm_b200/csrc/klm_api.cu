@@ -14,6 +14,7 @@
 
 cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
+cudaError_t klm_launch_umma2_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
 cudaError_t klm_launch_umma_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
 
 // ------------------------------------------------------------------------------------------
@@ -1007,5 +1008,28 @@ extern "C" int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slo
         out_hyp[k] = c.hyp; out_alt[k] = c.alt; out_cum_cost[k] = c.cum; out_slot[k] = c.own ? c.slot : -2;   // -2: the parent's state
     }
     *n_out = no;
+    return KLM_OK;
+}
+
+// Self-test of the CTA-pair MMA (cta_group::2): A_img = two [K/8][64][8] halves (rows 0..63, 64..127), B_img = two
+// [K/8][N/2][8] halves; D receives the raw TMEM dump [2 CTAs][128 lanes][N/2 columns].  Host pointers.
+extern "C" int klm_selftest_umma2(int device, int32_t N, int32_t K, const uint16_t *A_img, const uint16_t *B_img, float *D) {
+    if (!A_img || !B_img || !D) return fail(KLM_EINVAL, "klm_selftest_umma2: NULL argument");
+    if (N < 32 || N > 256 || N % 32 || K < 16 || K % 16 || (size_t)K * (64 + N / 2) * 2 > 200 * 1024)
+        return fail(KLM_EINVAL, "klm_selftest_umma2: unsupported shape N=%d K=%d", N, K);
+    CK(cudaSetDevice(device));
+    __half *dA = nullptr, *dB = nullptr; float *dD = nullptr; int *derr = nullptr;
+    CK(cudaMalloc(&dA, (size_t)K * 128 * 2)); CK(cudaMalloc(&dB, (size_t)K * N * 2));
+    CK(cudaMalloc(&dD, (size_t)2 * 128 * (N / 2) * 4)); CK(cudaMalloc(&derr, 4));
+    CK(cudaMemcpy(dA, A_img, (size_t)K * 128 * 2, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dB, B_img, (size_t)K * N * 2, cudaMemcpyHostToDevice));
+    CK(cudaMemset(dD, 0, (size_t)2 * 128 * (N / 2) * 4)); CK(cudaMemset(derr, 0, 4));
+    CK(klm_launch_umma2_selftest(dA, dB, dD, N, K, derr, 0));
+    CK(cudaDeviceSynchronize());
+    int code = 0;
+    CK(cudaMemcpy(&code, derr, 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(D, dD, (size_t)2 * 128 * (N / 2) * 4, cudaMemcpyDeviceToHost));
+    cudaFree(dA); cudaFree(dB); cudaFree(dD); cudaFree(derr);
+    if (code) return fail(KLM_ECUDA, "klm_selftest_umma2: device-side wait timed out (code %d)", code);
     return KLM_OK;
 }

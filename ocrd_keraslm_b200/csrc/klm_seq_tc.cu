@@ -608,3 +608,65 @@ cudaError_t klm_launch_umma_selftest(const __half *A, const __half *B, float *D,
     klm_umma_selftest<<<1, 128, smem, stream>>>(A, B, D, N, K, err);
     return cudaGetLastError();
 }
+
+// ---------------------------------------------------------------------------------------------
+// Self-test of the CTA-pair MMA (cta_group::2, M = 128 over two CTAs): CTA r holds rows 64r..64r+63 of A
+// ([K/8][64][8] halves) and rows (N/2)r.. of B ([K/8][N/2][8]); every CTA dumps its TMEM (128 lanes x N/2
+// columns) so that the host can check the accumulator layout.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
+klm_umma2_selftest(const __half *A, const __half *B, float *Dout, int N, int K, int *err) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const uint32_t a_bytes = (uint32_t)K * 64 * 2, b_bytes = (uint32_t)K * (N / 2) * 2;
+    unsigned char *sa = smem, *sb = smem + a_bytes;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + a_bytes + b_bytes);
+    const uint32_t bar_done = tc::smem_u32(bars);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
+    if (warp == 0) { tc::tmem_alloc2(tc::smem_u32(tmem_slot), 256); tc::tmem_relinquish2(); }
+    if (tid == 32) { tc::mbar_init(bar_done, 1); tc::fence_mbar_init(); }
+    const uint4 *ga = reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned char *>(A) + (size_t)rank * a_bytes);
+    const uint4 *gb = reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned char *>(B) + (size_t)rank * b_bytes);
+    for (uint32_t i = tid; i < a_bytes / 16; i += 128) reinterpret_cast<uint4 *>(sa)[i] = ga[i];
+    for (uint32_t i = tid; i < b_bytes / 16; i += 128) reinterpret_cast<uint4 *>(sb)[i] = gb[i];
+    tc::fence_proxy_async();
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::cluster_sync();                                  // both CTAs: operands in place, TMEM allocated, barriers ready
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (rank == 0 && tid == 32) {
+        const uint32_t idesc = tc::idesc_f16(128, N);
+        const uint32_t lbo_a = 64 * 16, lbo_b = (N / 2) * 16;
+        for (int k = 0; k < K / 16; ++k)
+            tc::mma2_f16(tmem_base, tc::smem_desc(tc::smem_u32(sa) + k * 2 * lbo_a, lbo_a, 128),
+                         tc::smem_desc(tc::smem_u32(sb) + k * 2 * lbo_b, lbo_b, 128), idesc, k != 0 ? 1u : 0u);
+        tc::mma2_commit(bar_done, 3);
+    }
+    __syncwarp();
+    {
+        unsigned n = 0;
+        while (!tc::mbar_try_wait(bar_done, 0)) if (++n > (1u << 22)) { atomicExch(err, 2 + (int)rank); break; }
+    }
+    __syncwarp();
+    tc::tc_fence_after();
+    const uint32_t trow = tmem_base + ((uint32_t)(32 * warp) << 16);
+    for (int c = 0; c < N / 2; c += 8) {
+        float v[8];
+        tc::tmem_ld8(trow + c, v);
+        tc::tmem_ld_wait();
+        for (int j = 0; j < 8; ++j) Dout[((size_t)rank * 128 + 32 * warp + lane) * (N / 2) + c + j] = v[j];
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::cluster_sync();
+    if (warp == 0) { __syncwarp(); tc::tmem_dealloc2(tmem_base, 256); }
+}
+
+cudaError_t klm_launch_umma2_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream) {
+    const size_t smem = (size_t)K * 64 * 2 + (size_t)K * (N / 2) * 2 + 64;
+    cudaError_t e = cudaFuncSetAttribute((const void *)klm_umma2_selftest, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    klm_umma2_selftest<<<2, 128, smem, stream>>>(A, B, D, N, K, err);
+    return cudaGetLastError();
+}
