@@ -14,6 +14,7 @@
 
 cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
+cudaError_t klm_launch_seq_tc2(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_umma2_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
 cudaError_t klm_launch_umma_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
 
@@ -62,7 +63,7 @@ struct KlmTcPlan {
     __half *hx = nullptr;
     float *Z = nullptr, *logits = nullptr;
     int *err = nullptr;
-    int ingest_bulk = 0;
+    int ingest_bulk = 0, kc = KLM_TC_KC, ring_bytes = 0;
     unsigned long long *trace = nullptr;
     int trace_t0 = 0;
 };
@@ -79,7 +80,7 @@ struct klm_model {
     float4 *P = nullptr, *Q[KLM_MAX_CTX] = {}, *Wl[KLM_MAX_DEPTH] = {}, *bias[KLM_MAX_DEPTH] = {}, *Ep = nullptr;
     // plans
     KlmPlan plan_k, plan_b;
-    KlmTcPlan tc;
+    KlmTcPlan tc, tc2;                 // single-CTA MMA plan, CTA-pair (cta_group::2) plan
     // scratch
     float *hbuf = nullptr, *logits = nullptr;
     unsigned int *barrier = nullptr;
@@ -240,15 +241,21 @@ static int make_plan(klm_model *m, bool kpar, KlmPlan *pl) {
 // memory operand layout [W/8][2N][8], and allocates the exchange buffers.  Not eligible (ok stays
 // false, the FMA kernels take over) if W is not a multiple of 64, a weight overflows fp16, or the
 // images do not fit the shared memory of the device.
-static int make_tc_plan(klm_model *m, const float *E, const float *const *L) {
-    KlmTcPlan &pl = m->tc;
+// pair = true plans the CTA-pair kernel (klm_seq_tc2.cu): even CTA counts per stage, the two CTAs of a cluster
+// get B images padded to the same number of pairs.
+static int make_tc_plan(klm_model *m, const float *E, const float *const *L, bool pair, KlmTcPlan &pl) {
     const int W = m->W, D = m->D, V = m->V;
     if (getenv("KLM_DISABLE_TC")) return KLM_OK;
+    // measured on cfg2: the pair kernel is slower (9.5 vs 8.0 us per tick) -- with only 64 accumulator rows per CTA the
+    // tensor cores run at half rate -- so it is opt-in; it pays for >= 128 streams per launch (not implemented yet)
+    if (pair && !getenv("KLM_ENABLE_TC2")) return KLM_OK;
     if (W % KLM_TC_KC != 0 || W < KLM_TC_KC) return KLM_OK;
-    const int nchunks = W / KLM_TC_KC;
+    pl.kc = (pair && W % 128 == 0) ? 128 : KLM_TC_KC;
+    const int nchunks = W / pl.kc;
     pl.stages = std::min(4, nchunks);
     pl.Vp = (V + 7) / 8 * 8;
-    const size_t fixed = KLM_TC_FIXED_BYTES((size_t)pl.stages);
+    pl.ring_bytes = std::max(pl.stages * pl.kc * 128, KLM_TC_XCHG_BYTES);
+    const size_t fixed = pair ? (size_t)pl.ring_bytes + 256 : KLM_TC_FIXED_BYTES((size_t)pl.stages);
     if (fixed + 32 * (size_t)W > m->smem_optin) return KLM_OK;
     const int pairs_max = (int)std::min<size_t>(KLM_TC_MAX_PAIRS, (m->smem_optin - fixed) / (32 * (size_t)W));
     if (pairs_max < 1) return KLM_OK;
@@ -261,20 +268,21 @@ static int make_tc_plan(klm_model *m, const float *E, const float *const *L) {
         tys.push_back({KLM_TC_REC, l, l, 2 * l, W / 2, 0, L[3 * l + 1]});
     }
     tys.push_back({KLM_TC_PROJ, 0, D - 1, 2 * D - 1, pl.Vp / 8, 0, E});
-    int n_lse = 1, used = 0;
-    for (auto &t : tys) { t.n = (t.pairs + pairs_max - 1) / pairs_max; used += t.n; }
+    const int q = pair ? 2 : 1;                              // CTAs come in clusters of q
+    int n_lse = q, used = 0;
+    for (auto &t : tys) { t.n = (t.pairs + pairs_max - 1) / pairs_max; t.n = (t.n + q - 1) / q * q; used += t.n; }
     if (used + n_lse > sm_avail) return KLM_OK;
-    n_lse = std::max(1, std::min(4, sm_avail - used));      // the LSE stage must not be the slowest one
+    n_lse = std::max(q, std::min(4, (sm_avail - used) / q * q));      // the LSE stage must not be the slowest one
     used += n_lse;
-    while (used < sm_avail) {                      // spare SMs go to the stage with the widest slices
+    while (used + q <= sm_avail) {                           // spare SMs go to the stage with the widest slices
         int best = -1; double load = 0;
         for (int i = 0; i < (int)tys.size(); ++i) {
-            if (tys[i].n >= tys[i].pairs) continue;
+            if (tys[i].n + q > tys[i].pairs) continue;
             const double ld = std::ceil((double)tys[i].pairs / tys[i].n);
             if (ld > load) { load = ld; best = i; }
         }
         if (best < 0 || load <= 1) break;
-        tys[best].n++; used++;
+        tys[best].n += q; used += q;
     }
     // fp16 range check
     {
@@ -292,12 +300,14 @@ static int make_tc_plan(klm_model *m, const float *E, const float *const *L) {
         int first = 0;
         for (int c = 0; c < t.n; ++c) {
             const int np = base + (c < rem ? 1 : 0);
-            const int N = 8 * np;
-            KlmTcRole r = {t.kind, t.layer, t.src, t.sigma, first, np, (long long)(img.size() * sizeof(__half))};
+            const int c2 = pair ? (c ^ 1) : c;               // the other CTA of the cluster
+            const int npm = std::max(np, base + (c2 < rem ? 1 : 0));
+            const int N = 8 * npm;                           // image rows: [0,N) hi, [N,2N) lo; rows >= 8*np are zero padding
+            KlmTcRole r = {t.kind, t.layer, t.src, t.sigma, first, np, (long long)(img.size() * sizeof(__half)), npm, 0};
             pl.roles.push_back(r);
             const size_t o = img.size();
-            img.resize(o + (size_t)W * 2 * N);
-            for (int j = 0; j < N; ++j) {
+            img.resize(o + (size_t)W * 2 * N, __float2half_rn(0.f));
+            for (int j = 0; j < 8 * np; ++j) {
                 for (int k = 0; k < W; ++k) {
                     float val;
                     if (t.kind == KLM_TC_PROJ) {
@@ -314,10 +324,10 @@ static int make_tc_plan(klm_model *m, const float *E, const float *const *L) {
                 }
             }
             first += np;
-            max_pairs = std::max(max_pairs, np);
+            max_pairs = std::max(max_pairs, npm);
         }
     }
-    for (int i = 0; i < n_lse; ++i) pl.roles.push_back({KLM_TC_LSE, 0, 0, 2 * D, i, n_lse, 0});
+    for (int i = 0; i < n_lse; ++i) pl.roles.push_back({KLM_TC_LSE, 0, 0, 2 * D, i, n_lse, 0, 0, 0});
     pl.grid = (int)pl.roles.size();
     pl.smem = fixed + (size_t)32 * W * max_pairs;
     CK(cudaMalloc(&pl.d_roles, pl.roles.size() * sizeof(KlmTcRole)));
@@ -353,6 +363,8 @@ extern "C" int klm_destroy(klm_model *m) {
     cudaFree(m->plan_k.d_roles); cudaFree(m->plan_b.d_roles);
     cudaFree(m->tc.d_roles); cudaFree(m->tc.d_wimg); cudaFree(m->tc.hx); cudaFree(m->tc.Z); cudaFree(m->tc.logits);
     cudaFree(m->tc.err); cudaFree(m->tc.trace);
+    cudaFree(m->tc2.d_roles); cudaFree(m->tc2.d_wimg); cudaFree(m->tc2.hx); cudaFree(m->tc2.Z); cudaFree(m->tc2.logits);
+    cudaFree(m->tc2.err); cudaFree(m->tc2.trace);
     cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
     for (int i = 0; i < KLM_RING; ++i) {
         if (m->h_ring[i]) cudaFreeHost(m->h_ring[i]);
@@ -461,7 +473,8 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
     }
     TRY(make_plan(m, true, &m->plan_k));
     TRY(make_plan(m, false, &m->plan_b));
-    TRY(make_tc_plan(m, E, L));
+    TRY(make_tc_plan(m, E, L, false, m->tc));
+    TRY(make_tc_plan(m, E, L, true, m->tc2));
 
     m->bp_cap = std::max(32, m->plan_b.max_streams);
     TRYC(cudaMalloc(&m->hbuf, (size_t)D * 2 * W * m->bp_cap * 4));
@@ -642,7 +655,8 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     int rc = ring_acquire(m, &rs, (size_t)nb * (4 * 3 + 4 * m->Nc) + (nb + 1) * 8 + 128);
     if (rc) return rc;
     if (m->tc.ok && nb > KLM_MODEK_MAXB && nb <= KLM_TC_STREAMS) {
-        if ((double)(tmax + 2 * m->D + 2) * m->tc.grid >= 4.0e9)
+        KlmTcPlan &tp = m->tc2.ok ? m->tc2 : m->tc;
+        if ((double)(tmax + 2 * m->D + 2) * tp.grid >= 4.0e9)
             return fail(KLM_EINVAL, "stream of %lld positions is too long for one launch", tmax);
         KlmTcParams q;
         memset(&q, 0, sizeof q);
@@ -655,21 +669,23 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         int *hcx = ring_put<int>(&rs, nullptr, (size_t)nb * std::max(1, m->Nc), &d_cx);
         for (int i = 0; i < nb * m->Nc; ++i) hcx[i] = ctx ? ctx[i] : 0;
         rc = ring_commit(m, &rs); if (rc) return rc;
-        q.W = m->W; q.D = m->D; q.V = m->V; q.Vp = m->tc.Vp; q.Nc = m->Nc;
-        q.B = nb; q.T_max = (int)tmax; q.stages = m->tc.stages;
+        q.W = m->W; q.D = m->D; q.V = m->V; q.Vp = tp.Vp; q.Nc = m->Nc;
+        q.B = nb; q.T_max = (int)tmax; q.stages = tp.stages;
         for (int k = 0; k < m->Nc; ++k) { q.ctx_rows[k] = m->cfg.ctx_rows[k]; q.Q[k] = m->Q[k]; }
         q.P = m->P;
         for (int l = 0; l < m->D; ++l) q.bias[l] = m->bias[l];
-        q.wimg = m->tc.d_wimg; q.roles = m->tc.d_roles;
-        q.hx = m->tc.hx; q.Z = m->tc.Z; q.logits = m->tc.logits;
-        q.ingest_bulk = m->tc.ingest_bulk;
+        q.wimg = tp.d_wimg; q.roles = tp.d_roles;
+        q.hx = tp.hx; q.Z = tp.Z; q.logits = tp.logits;
+        q.ingest_bulk = tp.ingest_bulk;
         q.state = m->state; q.slots_in = d_si; q.slots_out = d_so; q.offsets = d_off;
         q.chars = d_chars; q.targets = d_targets; q.n_real = d_nr; q.ctx = d_cx;
         q.out = d_out; q.full_rows = full_rows;
-        q.barrier = m->barrier; q.err = m->tc.err;
-        q.trace = m->tc.trace; q.trace_t0 = m->tc.trace_t0;
+        q.barrier = m->barrier; q.err = tp.err;
+        q.trace = tp.trace; q.trace_t0 = tp.trace_t0;
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
-        CK(klm_launch_seq_tc(q, m->tc.grid, m->tc.smem, m->stream));
+        q.kc = tp.kc; q.ring_bytes = tp.ring_bytes;
+        if (&tp == &m->tc2) CK(klm_launch_seq_tc2(q, tp.grid, tp.smem, m->stream));
+        else CK(klm_launch_seq_tc(q, tp.grid, tp.smem, m->stream));
         m->launches++; m->tc_launches++;
         return KLM_OK;
     }
@@ -713,6 +729,7 @@ static int check_device_error(klm_model *m) {
     if (!m->tc.ok || m->tc_launches == 0) return KLM_OK;
     int code = 0;
     CK(cudaMemcpy(&code, m->tc.err, sizeof code, cudaMemcpyDeviceToHost));
+    if (code == 0 && m->tc2.ok) CK(cudaMemcpy(&code, m->tc2.err, sizeof code, cudaMemcpyDeviceToHost));
     if (code != 0) return fail(KLM_ECUDA, "klm_seq_tc: device-side wait timed out (code %d)", code);
     return KLM_OK;
 }
@@ -834,8 +851,9 @@ extern "C" int klm_get_info(klm_model *m, klm_info *out) {
     out->kernel_launches = m->launches;
     out->max_streams = m->tc.ok ? KLM_TC_STREAMS : m->plan_b.max_streams;
     out->tc_enabled = m->tc.ok ? 1 : 0;
-    out->tc_grid = m->tc.grid;
-    out->tc_smem_bytes = (int32_t)m->tc.smem;
+    out->tc_enabled = m->tc2.ok ? 2 : out->tc_enabled;        // 2: the CTA-pair kernel (cta_group::2) is the one in use
+    out->tc_grid = m->tc2.ok ? m->tc2.grid : m->tc.grid;
+    out->tc_smem_bytes = (int32_t)(m->tc2.ok ? m->tc2.smem : m->tc.smem);
     out->tc_launches = m->tc_launches;
     if (m->timed) {
         CK(cudaSetDevice(m->device));
@@ -878,20 +896,21 @@ extern "C" int klm_tc_trace(klm_model *m, int32_t first_tick, uint64_t *out, int
     if (!m) return fail(KLM_EINVAL, "NULL model");
     if (!m->tc.ok) return fail(KLM_EINVAL, "klm_tc_trace: the tensor-core plan is not enabled for this model");
     CK(cudaSetDevice(m->device));
-    const size_t n = (size_t)m->tc.grid * KLM_TC_TRACE_TICKS * 8;
+    KlmTcPlan &tp = m->tc2.ok ? m->tc2 : m->tc;
+    const size_t n = (size_t)tp.grid * KLM_TC_TRACE_TICKS * 8;
     if (!out) {
-        if (!m->tc.trace) CK(cudaMalloc(&m->tc.trace, n * 8));
-        CK(cudaMemset(m->tc.trace, 0, n * 8));
-        m->tc.trace_t0 = first_tick;
+        if (!tp.trace) CK(cudaMalloc(&tp.trace, n * 8));
+        CK(cudaMemset(tp.trace, 0, n * 8));
+        tp.trace_t0 = first_tick;
         return KLM_OK;
     }
-    if (!m->tc.trace) return fail(KLM_EINVAL, "klm_tc_trace: not armed");
+    if (!tp.trace) return fail(KLM_EINVAL, "klm_tc_trace: not armed");
     CK(cudaStreamSynchronize(m->stream));
-    CK(cudaMemcpy(out, m->tc.trace, n * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(out, tp.trace, n * 8, cudaMemcpyDeviceToHost));
     if (roles_out)
-        for (int i = 0; i < m->tc.grid; ++i) {
-            roles_out[4 * i] = m->tc.roles[i].kind; roles_out[4 * i + 1] = m->tc.roles[i].layer;
-            roles_out[4 * i + 2] = m->tc.roles[i].npairs; roles_out[4 * i + 3] = m->tc.roles[i].sigma;
+        for (int i = 0; i < tp.grid; ++i) {
+            roles_out[4 * i] = tp.roles[i].kind; roles_out[4 * i + 1] = tp.roles[i].layer;
+            roles_out[4 * i + 2] = tp.roles[i].npairs; roles_out[4 * i + 3] = tp.roles[i].sigma;
         }
     return KLM_OK;
 }

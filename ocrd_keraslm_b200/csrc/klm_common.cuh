@@ -94,6 +94,8 @@ struct KlmTcRole {
     int first_pair;    // first pair of units (REC/IN), first group of 8 vocabulary rows (PROJ), LSE index (LSE)
     int npairs;        // pairs owned (N = 8 * npairs columns); number of LSE CTAs (LSE)
     long long wofs;    // byte offset of the CTA's B image in wimg
+    int npm;           // CTA-pair kernel: pairs the B image is padded to (the larger of the two CTAs of the cluster)
+    int pad_;
 };
 
 struct KlmTcParams {
@@ -106,6 +108,8 @@ struct KlmTcParams {
     const unsigned char *wimg;
     const KlmTcRole *roles;
     __half *hx;                   // [D][2][W/8][128][8]
+    int kc;                       // CTA-pair kernel: k per ring chunk (64 or 128)
+    int ring_bytes;               // CTA-pair kernel: bytes of the ring region (>= the hand-over buffer aliased on it)
     int ingest_bulk;              // 0: the epilogue warps copy the A operand (ld.global.cg / st.shared); 1: cp.async.bulk
     float *Z;                     // [D][2][64][4W]  (unit-interleaved gate columns)
     float *logits;                // [2][64][Vp]
