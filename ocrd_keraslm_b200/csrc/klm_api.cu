@@ -63,7 +63,8 @@ struct KlmTcPlan {
     __half *hx = nullptr;
     float *Z = nullptr, *logits = nullptr;
     int *err = nullptr;
-    int ingest_bulk = 0, kc = KLM_TC_KC, ring_bytes = 0;
+    int ingest_bulk = 0, kc = KLM_TC_KC, ring_bytes = 0;     // CTA-pair kernel
+    int pub = 0, n_lse = 0, consumer_fence = 1;              // single-CTA kernel
     unsigned long long *trace = nullptr;
     int trace_t0 = 0;
 };
@@ -236,6 +237,176 @@ static int make_plan(klm_model *m, bool kpar, KlmPlan *pl) {
 }
 
 // ------------------------------------------------------------------------------------------
+// Plan of the single-CTA tensor-core kernel (klm_seq_tc.cu).  Distributes the columns of R_l (REC), K_l (IN,
+// l >= 1) and the rows of E (PROJ) over the SMs in pairs of units (8 columns) and builds each CTA's fp16 hi/lo
+// B image in the shared-memory operand layout [W/8][2N][8].
+//   * REC slices are whole groups of 8 units (4 pairs) so that the new hidden vector leaves the CTA as whole
+//     2 KB blocks of the readers' operand layout (role.pub; see the kernel header).  If that does not fit the
+//     SM budget the slices fall back to single pairs with scattered publication (pub = 0).
+//   * every role gets the largest operand ring that fits beside its B image: (k per chunk, slots) from
+//     (64,4), (64,3), (32,4), (32,3), (32,2).
+//   * spare SMs go, one refinement at a time, to the stage with the heaviest per-CTA epilogue (REC counts 1.5x:
+//     it also runs the LSTM cell and sits on the recurrence).
+// Not eligible (ok stays false, the FMA kernels take over) if W is not a multiple of 64, a weight overflows
+// fp16, or the images do not fit the device.
+static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, KlmTcPlan &pl) {
+    const int W = m->W, D = m->D, V = m->V;
+    if (getenv("KLM_DISABLE_TC")) return KLM_OK;
+    if (W % 64 != 0 || W < 64) return KLM_OK;
+    pl.Vp = (V + 7) / 8 * 8;
+    static const int geoms[6][2] = {{128, 3}, {64, 4}, {64, 3}, {32, 4}, {32, 3}, {32, 2}};
+    const bool kc128 = !(getenv("KLM_TC_KC128") && atoi(getenv("KLM_TC_KC128")) == 0);
+    int g_last = 3;                           // the 8 KB chunk geometries only if nothing else fits (each chunk costs the
+                                              // producer and the MMA issuer ~400 clk of mbarrier round trips)
+    auto ring_bytes_of = [&](int g) {
+        const int stages = std::min(geoms[g][1], W / geoms[g][0]);
+        return std::max(stages * geoms[g][0] * 256, KLM_TC1_ALIAS_BYTES);
+    };
+    auto geom_for = [&](int np) {            // first (largest) geometry that fits beside an image of np pairs
+        for (int g = 0; g < g_last; ++g) {
+            if (W % geoms[g][0] != 0 || (geoms[g][0] == 128 && !kc128)) continue;
+            if ((size_t)ring_bytes_of(g) + 128 + (size_t)32 * W * np <= m->smem_optin) return g;
+        }
+        return -1;
+    };
+    int pmax = 0;
+    const int sm_avail = getenv("KLM_TC_MAX_CTAS") ? std::min(m->sm_count, atoi(getenv("KLM_TC_MAX_CTAS"))) : m->sm_count;
+    int pub_mode = getenv("KLM_TC_PUB") ? atoi(getenv("KLM_TC_PUB")) : 2;
+    if (pub_mode < 0 || pub_mode > 2) pub_mode = 2;
+
+    struct Ty { int kind, layer, src, sigma, items, gran, n; double weight; const float *mat; };
+    std::vector<Ty> tys;
+    bool planned = false;
+    // attempts: (aligned REC slices, 16/32 KB chunks), (aligned, any chunk size), (single pairs, ...), (single pairs, any)
+    for (int attempt = (pub_mode ? 0 : 2); attempt < 4 && !planned; ++attempt) {
+        const int gran = attempt < 2 ? 4 : 1;                // pairs per indivisible REC item
+        g_last = (attempt & 1) ? 6 : 3;
+        pmax = 0;
+        for (int np = 1; np <= KLM_TC1_MAX_PAIRS; ++np) if (geom_for(np) >= 0) pmax = np;
+        if (getenv("KLM_TC_PMAX")) pmax = std::min(pmax, atoi(getenv("KLM_TC_PMAX")));
+        if (gran > pmax) continue;
+        tys.clear();
+        for (int l = 0; l < D; ++l) {
+            if (l > 0) tys.push_back({KLM_TC_IN, l, l - 1, 2 * l - 1, W / 2, 1, 0, 1.0, L[3 * l]});
+            tys.push_back({KLM_TC_REC, l, l, 2 * l, W / 2 / gran, gran, 0, 1.5, L[3 * l + 1]});
+        }
+        tys.push_back({KLM_TC_PROJ, 0, D - 1, 2 * D - 1, pl.Vp / 8, 1, 0, 1.0, E});
+        int used = 0;
+        for (auto &t : tys) { const int cap = pmax / t.gran; t.n = (t.items + cap - 1) / cap; used += t.n; }
+        if (used + 1 > sm_avail) continue;
+        const int lse_want = getenv("KLM_TC_NLSE") ? std::max(1, atoi(getenv("KLM_TC_NLSE"))) : 2;
+        int n_lse = std::max(1, std::min(lse_want, sm_avail - used));
+        used += n_lse;
+        auto load = [](const Ty &t, int n) { return (t.items + n - 1) / n * t.gran; };      // pairs of the largest slice
+        for (;;) {
+            // candidates in order of decreasing weighted load; take the first whose next refinement fits
+            std::vector<int> order(tys.size());
+            for (size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
+            std::sort(order.begin(), order.end(), [&](int a, int b) {
+                return load(tys[a], tys[a].n) * tys[a].weight > load(tys[b], tys[b].n) * tys[b].weight; });
+            bool done = true;
+            for (int i : order) {
+                Ty &t = tys[i];
+                const int cur = load(t, t.n);
+                if (cur <= t.gran) continue;
+                int n2 = t.n + 1;
+                while (n2 < t.items && load(t, n2) >= cur) ++n2;
+                if (load(t, n2) >= cur || used + (n2 - t.n) > sm_avail) continue;
+                used += n2 - t.n; t.n = n2; done = false;
+                break;
+            }
+            if (done) break;
+        }
+        pl.pub = attempt < 2 ? pub_mode : 0;
+        pl.n_lse = n_lse;
+        planned = true;
+    }
+    if (!planned) return KLM_OK;
+    // fp16 range check
+    {
+        float mx = 0.f;
+        for (auto &t : tys) {
+            const size_t cnt = t.kind == KLM_TC_PROJ ? (size_t)V * W : (size_t)W * 4 * W;
+            for (size_t i = 0; i < cnt; ++i) mx = std::max(mx, std::fabs(t.mat[i]));
+        }
+        if (!(mx < 60000.f)) return KLM_OK;
+    }
+    std::vector<__half> img;
+    size_t smem = 0;
+    for (auto &t : tys) {
+        const int base = t.items / t.n, rem = t.items % t.n;
+        int first = 0;
+        for (int c = 0; c < t.n; ++c) {
+            const int np = (base + (c < rem ? 1 : 0)) * t.gran;
+            const int N = 8 * np;                            // image rows: [0,N) hi, [N,2N) lo
+            const int g = geom_for(np);
+            KlmTcRole r;
+            memset(&r, 0, sizeof r);
+            r.kind = t.kind; r.layer = t.layer; r.src_layer = t.src; r.sigma = t.sigma;
+            r.first_pair = first; r.npairs = np; r.wofs = (long long)(img.size() * sizeof(__half)); r.npm = np;
+            r.kc = geoms[g][0]; r.stages = std::min(geoms[g][1], W / r.kc); r.ring_bytes = ring_bytes_of(g);
+            r.pub = t.kind == KLM_TC_REC ? pl.pub : 0;
+            pl.roles.push_back(r);
+            smem = std::max(smem, (size_t)r.ring_bytes + 128 + (size_t)32 * W * np);
+            const size_t o = img.size();
+            img.resize(o + (size_t)W * 2 * N, __float2half_rn(0.f));
+            for (int j = 0; j < N; ++j) {
+                for (int k = 0; k < W; ++k) {
+                    float val;
+                    if (t.kind == KLM_TC_PROJ) {
+                        const int v = 8 * first + j;
+                        val = v < V ? t.mat[(size_t)v * W + k] : 0.f;
+                    } else {
+                        const int u = 2 * first + j / 4, gate = j % 4;
+                        val = t.mat[(size_t)k * 4 * W + gate * W + u];
+                    }
+                    const __half hi = __float2half_rn(val);
+                    const __half lo = __float2half_rn(val - __half2float(hi));
+                    img[o + ((size_t)(k / 8) * 2 * N + j) * 8 + (k % 8)] = hi;
+                    img[o + ((size_t)(k / 8) * 2 * N + N + j) * 8 + (k % 8)] = lo;
+                }
+            }
+            first += np;
+        }
+    }
+    for (int i = 0; i < pl.n_lse; ++i) {
+        KlmTcRole r;
+        memset(&r, 0, sizeof r);
+        r.kind = KLM_TC_LSE; r.sigma = 2 * D; r.first_pair = i; r.npairs = pl.n_lse;
+        pl.roles.push_back(r);
+    }
+    pl.grid = (int)pl.roles.size();
+    pl.smem = smem;
+    if (getenv("KLM_TC_PLAN_DEBUG")) {
+        static const char *kn[] = {"REC", "IN", "PROJ", "LSE"};
+        for (size_t i = 0; i < tys.size(); ++i)
+            fprintf(stderr, "klm tc plan: %s l%d: %d CTAs, largest slice %d pairs\n", kn[tys[i].kind], tys[i].layer, tys[i].n,
+                    (tys[i].items + tys[i].n - 1) / tys[i].n * tys[i].gran);
+        fprintf(stderr, "klm tc plan: LSE %d CTAs; grid %d, smem %zu, pub %d\n", pl.n_lse, pl.grid, pl.smem, pl.pub);
+        for (auto &r : pl.roles)
+            if (r.kind != KLM_TC_LSE && r.first_pair == 0)
+                fprintf(stderr, "klm tc plan:   %s l%d first CTA: %d pairs, ring %d x %d k (%d B)\n", kn[r.kind], r.layer, r.npairs,
+                        r.stages, r.kc, r.ring_bytes);
+    }
+    // the writers order their stores against the async proxy themselves (bulk stores, or fence.proxy.async before
+    // the release), so the readers need no proxy fence of their own; KLM_TC_CONSUMER_FENCE=1 adds one (~600 clk per tick)
+    pl.consumer_fence = getenv("KLM_TC_CONSUMER_FENCE") ? atoi(getenv("KLM_TC_CONSUMER_FENCE")) : 0;
+    CK(cudaMalloc(&pl.d_roles, pl.roles.size() * sizeof(KlmTcRole)));
+    CK(cudaMemcpy(pl.d_roles, pl.roles.data(), pl.roles.size() * sizeof(KlmTcRole), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&pl.d_wimg, img.size() * sizeof(__half)));
+    CK(cudaMemcpy(pl.d_wimg, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    const size_t hx_bytes = (size_t)D * 2 * W * 128 * sizeof(__half);
+    const size_t z_bytes = (size_t)D * 2 * 64 * 4 * W * sizeof(float);
+    const size_t lg_bytes = (size_t)2 * 64 * pl.Vp * sizeof(float);
+    CK(cudaMalloc(&pl.hx, hx_bytes)); CK(cudaMemset(pl.hx, 0, hx_bytes));
+    CK(cudaMalloc(&pl.Z, z_bytes)); CK(cudaMemset(pl.Z, 0, z_bytes));
+    CK(cudaMalloc(&pl.logits, lg_bytes)); CK(cudaMemset(pl.logits, 0, lg_bytes));
+    CK(cudaMalloc(&pl.err, 256)); CK(cudaMemset(pl.err, 0, 256));
+    pl.ok = true;                                            // launched cooperatively: all CTAs are co-resident
+    return KLM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // Tensor-core plan: distributes the columns of R_l (REC), K_l (IN, l >= 1) and the rows of E (PROJ)
 // over the SMs in pairs of units (8 columns), builds each CTA's fp16 hi/lo B image in the shared
 // memory operand layout [W/8][2N][8], and allocates the exchange buffers.  Not eligible (ok stays
@@ -303,7 +474,10 @@ static int make_tc_plan(klm_model *m, const float *E, const float *const *L, boo
             const int c2 = pair ? (c ^ 1) : c;               // the other CTA of the cluster
             const int npm = std::max(np, base + (c2 < rem ? 1 : 0));
             const int N = 8 * npm;                           // image rows: [0,N) hi, [N,2N) lo; rows >= 8*np are zero padding
-            KlmTcRole r = {t.kind, t.layer, t.src, t.sigma, first, np, (long long)(img.size() * sizeof(__half)), npm, 0};
+            KlmTcRole r;
+            memset(&r, 0, sizeof r);
+            r.kind = t.kind; r.layer = t.layer; r.src_layer = t.src; r.sigma = t.sigma;
+            r.first_pair = first; r.npairs = np; r.wofs = (long long)(img.size() * sizeof(__half)); r.npm = npm;
             pl.roles.push_back(r);
             const size_t o = img.size();
             img.resize(o + (size_t)W * 2 * N, __float2half_rn(0.f));
@@ -327,7 +501,12 @@ static int make_tc_plan(klm_model *m, const float *E, const float *const *L, boo
             max_pairs = std::max(max_pairs, npm);
         }
     }
-    for (int i = 0; i < n_lse; ++i) pl.roles.push_back({KLM_TC_LSE, 0, 0, 2 * D, i, n_lse, 0, 0, 0});
+    for (int i = 0; i < n_lse; ++i) {
+        KlmTcRole r;
+        memset(&r, 0, sizeof r);
+        r.kind = KLM_TC_LSE; r.sigma = 2 * D; r.first_pair = i; r.npairs = n_lse;
+        pl.roles.push_back(r);
+    }
     pl.grid = (int)pl.roles.size();
     pl.smem = fixed + (size_t)32 * W * max_pairs;
     CK(cudaMalloc(&pl.d_roles, pl.roles.size() * sizeof(KlmTcRole)));
@@ -473,7 +652,7 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
     }
     TRY(make_plan(m, true, &m->plan_k));
     TRY(make_plan(m, false, &m->plan_b));
-    TRY(make_tc_plan(m, E, L, false, m->tc));
+    TRY(make_tc1_plan(m, E, L, m->tc));
     TRY(make_tc_plan(m, E, L, true, m->tc2));
 
     m->bp_cap = std::max(32, m->plan_b.max_streams);
@@ -676,12 +855,14 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         for (int l = 0; l < m->D; ++l) q.bias[l] = m->bias[l];
         q.wimg = tp.d_wimg; q.roles = tp.d_roles;
         q.hx = tp.hx; q.Z = tp.Z; q.logits = tp.logits;
-        q.ingest_bulk = tp.ingest_bulk;
+        q.ingest_bulk = tp.ingest_bulk; q.consumer_fence = tp.consumer_fence;
         q.state = m->state; q.slots_in = d_si; q.slots_out = d_so; q.offsets = d_off;
         q.chars = d_chars; q.targets = d_targets; q.n_real = d_nr; q.ctx = d_cx;
         q.out = d_out; q.full_rows = full_rows;
         q.barrier = m->barrier; q.err = tp.err;
         q.trace = tp.trace; q.trace_t0 = tp.trace_t0;
+        q.trace_mode = getenv("KLM_TC_TRACE_MODE") ? atoi(getenv("KLM_TC_TRACE_MODE")) : 0;
+        q.debug_skip = getenv("KLM_TC_DEBUG_SKIP") ? atoi(getenv("KLM_TC_DEBUG_SKIP")) : 0;
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         q.kc = tp.kc; q.ring_bytes = tp.ring_bytes;
         if (&tp == &m->tc2) CK(klm_launch_seq_tc2(q, tp.grid, tp.smem, m->stream));

@@ -79,6 +79,14 @@ struct KlmSeqParams {
 #define KLM_TC_XCHG_OFS     0
 #define KLM_TC_FIXED_BYTES(S) ((((S) * KLM_TC_CHUNK_BYTES > KLM_TC_XCHG_BYTES) ? (S) * KLM_TC_CHUNK_BYTES : KLM_TC_XCHG_BYTES) + 128)
 #define KLM_TC_TMEM_COLS    256
+// single-CTA kernel (klm_seq_tc.cu): up to 12 pairs per CTA; the region in front of the B image holds the ring of
+// A-operand chunks and, aliased on it (the ring is idle while the epilogue runs), the hi<->lo hand-over buffer and
+// the staging area of the hidden-vector publication ([groups of 8 units][128 rows][8] halves)
+#define KLM_TC1_MAX_PAIRS   12
+#define KLM_TC1_XCHG_BYTES  (2 * (KLM_TC1_MAX_PAIRS / 2) * 8 * 64 * 4)
+#define KLM_TC1_PUB_OFS     KLM_TC1_XCHG_BYTES
+#define KLM_TC1_PUB_BYTES   (KLM_TC1_MAX_PAIRS / 4 * 2048)
+#define KLM_TC1_ALIAS_BYTES (KLM_TC1_PUB_OFS + KLM_TC1_PUB_BYTES)
 #define KLM_TC_TRACE_TICKS  16
 
 #define KLM_TC_REC  0
@@ -95,6 +103,12 @@ struct KlmTcRole {
     int npairs;        // pairs owned (N = 8 * npairs columns); number of LSE CTAs (LSE)
     long long wofs;    // byte offset of the CTA's B image in wimg
     int npm;           // CTA-pair kernel: pairs the B image is padded to (the larger of the two CTAs of the cluster)
+    // single-CTA kernel: geometry of this CTA's operand ring and how it publishes its hidden-vector slice
+    int kc;            // k per ring chunk (chunk = kc * 256 bytes)
+    int stages;        // ring slots
+    int ring_bytes;    // bytes in front of the barriers (>= stages * chunk and >= KLM_TC1_ALIAS_BYTES)
+    int pub;           // REC: 0 = scattered 4-byte stores, 1 = staged in shared memory + coalesced 16-byte stores,
+                       //      2 = staged + one bulk async store (1 and 2 need slices aligned to 8 units)
     int pad_;
 };
 
@@ -110,7 +124,8 @@ struct KlmTcParams {
     __half *hx;                   // [D][2][W/8][128][8]
     int kc;                       // CTA-pair kernel: k per ring chunk (64 or 128)
     int ring_bytes;               // CTA-pair kernel: bytes of the ring region (>= the hand-over buffer aliased on it)
-    int ingest_bulk;              // 0: the epilogue warps copy the A operand (ld.global.cg / st.shared); 1: cp.async.bulk
+    int ingest_bulk;              // CTA-pair kernel only (the single-CTA kernel always uses bulk copies)
+    int consumer_fence;           // single-CTA kernel: fence.proxy.async between the grid barrier and the bulk reads
     float *Z;                     // [D][2][64][4W]  (unit-interleaved gate columns)
     float *logits;                // [2][64][Vp]
     float *state;
@@ -123,4 +138,6 @@ struct KlmTcParams {
     int *err;                     // device-side watchdog: non-zero = a wait timed out (code says which)
     unsigned long long *trace;    // optional [grid][KLM_TC_TRACE_TICKS][8] SM-clock timeline (klm_tc_trace)
     int trace_t0;
+    int debug_skip;               // timing experiments only (results are wrong): bit 0 = no MMAs, bit 1 = no operand copies
+    int trace_mode;               // 0: phase events; 1: arrival of chunk c in event slot c; 2: issue of the copy of chunk c
 };

@@ -21,30 +21,161 @@
 // one tick later, so each CTA needs exactly one hidden vector per tick.  One grid-wide barrier per
 // tick (release/acquire counter); everything handed over is double-buffered by tick parity.
 //
-// Warp roles in a GEMM CTA (192 threads): warp 0 lane 0 = producer (grid barrier wait + bulk
-// copies), warp 1 lane 0 = MMA issuer, warps 2..5 = epilogue (TMEM -> registers, hi/lo halves
+// Warp roles in a GEMM CTA (320 threads): warp 0 lane 0 = producer (grid barrier wait + bulk
+// copies), warp 1 lane 0 = MMA issuer, warps 2..9 = epilogue (TMEM -> registers, hi/lo halves
 // exchanged through shared memory, LSTM cell in registers, hand-over stores).
+//
+// Publication of the hidden vector (role.pub): the readers' bulk copies run at ~46 B/clk per SM when
+// the lines were last written by full-sector stores but only ~28 B/clk (19 in this kernel) after
+// scattered 4-byte stores (scripts/ubench/fetch_paths.cu), so REC CTAs own slices aligned to 8 units
+// (one 16-byte row piece of the operand layout), stage the new hi/lo halves in shared memory and write
+// them out as whole 2 KB blocks (coalesced 16-byte stores or one bulk async store).
 #include "klm_tc_dev.cuh"
 
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParams p) {
+// Producer and MMA-issuer loops for compile-time ring geometries (KC k per chunk, NCH chunks per tick, S slots).
+// Both roles are ONE thread each, and a lone thread retires a dependent instruction only every ~5 clk; with
+// run-time ring arithmetic the per-chunk bookkeeping (~400 clk, measured with the MMAs and copies switched off,
+// KLM_TC_DEBUG_SKIP) cost more than the four MMAs of the chunk (~290 clk), and because the MMA queue is shallow
+// the two add up.  Here slot numbers, shared-memory offsets and the K loop are unrolled constants; the only
+// running state is the chunk rotation and one phase bit per slot.
+struct TcLoopCtx {
+    uint32_t ring_a, bar_full, bar_empty, bar_tfull, bar_tempty, bar_go, tmem_base, wsm_a;
+    int nticks, N, crot, src_layer, W;
+    unsigned G;
+};
+
+template <int KC, int NCH, int S, bool TRACE>
+__device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoopCtx &x) {
+    constexpr uint32_t CB = KC * 256;
+    // everything the loop needs sits in registers: the asm statements clobber memory, so anything left in the
+    // context struct or the kernel parameters would be re-loaded after each of them
+    const uint32_t ring_a = x.ring_a, bar_full = x.bar_full, bar_empty = x.bar_empty, bar_go = x.bar_go;
+    const int nticks = x.nticks, crot = x.crot;
+    const unsigned G = x.G;
+    const int trace_mode = p.trace_mode, skip = p.debug_skip, cfence = p.consumer_fence;
+    const unsigned char *hx0 = reinterpret_cast<const unsigned char *>(p.hx + (size_t)(x.src_layer * 2) * x.W * 128);
+    const size_t hx_par = (size_t)x.W * 128 * sizeof(__half);
+    uint32_t phbits = 0;                                   // bit st: uses of slot st so far, mod 2
+    const bool lane0 = (threadIdx.x & 31) == 0;
+    for (int tick = 0; tick < nticks; ++tick) {
+        // the whole warp runs this loop converged; lane 0 polls the grid barrier and issues
+        int okg = 1;
+        if (lane0) {
+            okg = tc_wait_grid(p, (unsigned)(tick + 1) * G, 1) ? 1 : 0;
+            if (okg) {
+                tc::mbar_arrive(bar_go);
+                if (TRACE && trace_mode == 0) tc_trace(p, tick, 0);
+                if (cfence) tc::fence_proxy_async();
+            }
+        }
+        if (!__shfl_sync(0xffffffffu, okg, 0)) return;
+        const unsigned char *src = hx0 + ((tick & 1) ? hx_par : 0);
+        int c = crot;
+#pragma unroll
+        for (int c0 = 0; c0 < NCH; ++c0) {
+            const int st = c0 % S;
+            int okw = tc_wait_mbar(bar_empty + 8 * st, ((phbits >> st) & 1u) ^ 1u, p, 2) ? 1 : 0;
+            if (!__all_sync(0xffffffffu, okw)) return;
+            if (tc::elect_one()) {
+                if (skip & 2) tc::mbar_arrive(bar_full + 8 * st);
+                else {
+                    tc::mbar_arrive_expect_tx(bar_full + 8 * st, CB);
+                    tc::bulk_g2s(ring_a + st * CB, src + (size_t)c * CB, CB, bar_full + 8 * st);
+                }
+                if (TRACE) {
+                    if (trace_mode == 2) tc_trace(p, tick, c0 & 7);
+                    else if (c0 == 0 && trace_mode == 0) tc_trace(p, tick, 1);
+                }
+            }
+            __syncwarp();
+            phbits ^= 1u << st;
+            c = (c + 1 == NCH) ? 0 : c + 1;
+        }
+    }
+}
+
+template <int KC, int NCH, int S, bool TRACE>
+__device__ __noinline__ void tc_mma_fixed(const KlmTcParams &p, const TcLoopCtx &x) {
+    constexpr uint32_t CB = KC * 256;
+    const uint32_t idesc = tc::idesc_f16(128, 2 * x.N);
+    const uint32_t lbo_a = 128 * 16, lbo_b = 2 * x.N * 16;
+    const uint64_t a_base = tc::smem_desc(x.ring_a, lbo_a, 128);
+    const uint64_t b_base = tc::smem_desc(x.wsm_a, lbo_b, 128);
+    constexpr uint32_t a_k16 = (2 * 128 * 16) >> 4;
+    const uint32_t b_k16 = (2 * lbo_b) >> 4, b_chunk = ((uint32_t)(KC / 8) * lbo_b) >> 4;
+    const uint32_t bar_full = x.bar_full, bar_empty = x.bar_empty, bar_tfull = x.bar_tfull, bar_tempty = x.bar_tempty;
+    const uint32_t tmem_base = x.tmem_base;
+    const int nticks = x.nticks, crot = x.crot;
+    const int trace_mode = p.trace_mode, skip = p.debug_skip;
+    uint32_t phbits = 0;
+    for (int tick = 0; tick < nticks; ++tick) {
+        // the whole warp runs this loop converged; the elected lane (always lane 0) issues
+        int okw = tc_wait_mbar(bar_tempty, (tick & 1) ^ 1, p, 3) ? 1 : 0;
+        if (!__all_sync(0xffffffffu, okw)) return;
+        tc::tc_fence_after();
+        int c = crot;
+#pragma unroll
+        for (int c0 = 0; c0 < NCH; ++c0) {
+            const int st = c0 % S;
+            okw = tc_wait_mbar(bar_full + 8 * st, (phbits >> st) & 1u, p, 4) ? 1 : 0;
+            if (!__all_sync(0xffffffffu, okw)) return;
+            const uint64_t ad = a_base + (uint32_t)(st * (CB >> 4));
+            const uint64_t bd = b_base + (uint32_t)c * b_chunk;
+            if (tc::elect_one()) {
+                if (TRACE) {
+                    if (trace_mode == 1) tc_trace(p, tick, c0 & 7);
+                    else if (trace_mode == 0 && (c0 == 0 || c0 == NCH - 1)) tc_trace(p, tick, c0 == 0 ? 2 : 3);
+                }
+                if (!(skip & 1)) {
+#pragma unroll
+                    for (int kk = 0; kk < KC / 16; ++kk)
+                        tc::mma_f16(tmem_base, ad + kk * a_k16, bd + kk * b_k16, idesc, (c0 | kk) != 0 ? 1u : 0u);
+                }
+                tc::mma_commit(bar_empty + 8 * st);       // ring slot free once these MMAs have read it
+                if (c0 == NCH - 1) tc::mma_commit(bar_tfull);   // accumulators of this tick complete
+            }
+            __syncwarp();
+            phbits ^= 1u << st;
+            c = (c + 1 == NCH) ? 0 : c + 1;
+        }
+    }
+}
+
+#define TC_FIXED_GEOMS(F) F(64, 8, 4) F(64, 8, 3) F(32, 16, 4) F(64, 4, 4) F(128, 4, 3) F(128, 4, 2)
+
+static __device__ __forceinline__ bool tc_run_fixed(bool producer, const KlmTcParams &p, const TcLoopCtx &x, int kc, int nch, int S) {
+#define TC_TRY(KC_, NCH_, S_)                                                                                   \
+    if (kc == KC_ && nch == NCH_ && S == S_) {                                                                  \
+        if (p.trace) { if (producer) tc_produce_fixed<KC_, NCH_, S_, true>(p, x); else tc_mma_fixed<KC_, NCH_, S_, true>(p, x); }   \
+        else { if (producer) tc_produce_fixed<KC_, NCH_, S_, false>(p, x); else tc_mma_fixed<KC_, NCH_, S_, false>(p, x); }         \
+        return true;                                                                                            \
+    }
+    TC_FIXED_GEOMS(TC_TRY)
+#undef TC_TRY
+    return false;
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const KlmTcRole role = p.roles[blockIdx.x];
     if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role); return; }
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int W = p.W, S = p.stages;
+    const int W = p.W, S = role.stages, kc = role.kc;
     const unsigned G = gridDim.x;
     const int nticks = p.T_max + 2 * p.D;
     const int NP = role.npairs, N = 8 * NP;
-    const int nchunks = W / KLM_TC_KC;
+    const int nchunks = W / kc;
+    const uint32_t chunk_bytes = (uint32_t)kc * 256u;
 
     // ---- shared memory carve-up ----
-    unsigned char *ring = smem;                                          // S x 16 KB: A operand chunks
-    float *xchg = reinterpret_cast<float *>(smem + KLM_TC_XCHG_OFS);    // 20 KB hi<->lo hand-over; aliases the ring when
-                                                                         // S >= 2 (the ring is idle while the epilogue runs)
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + KLM_TC_FIXED_BYTES(S) - 128);
-    unsigned char *wsm = smem + KLM_TC_FIXED_BYTES(S);                   // B image
+    unsigned char *ring = smem;                                          // S chunks of the A operand
+    float *xchg = reinterpret_cast<float *>(smem);                       // hi<->lo hand-over and ...
+    __half *pubbuf = reinterpret_cast<__half *>(smem + KLM_TC1_PUB_OFS); // ... publication staging alias the idle ring
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + role.ring_bytes);
+    unsigned char *wsm = smem + role.ring_bytes + 128;                   // B image
     const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + 4);
     const uint32_t bar_tfull = tc::smem_u32(bars + 8), bar_tempty = tc::smem_u32(bars + 9);
     const uint32_t bar_go = tc::smem_u32(bars + 10);       // producer -> epilogue: grid barrier of this tick passed
@@ -55,7 +186,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
         tc::tmem_relinquish();
     }
     if (tid == 32) {
-        for (int i = 0; i < S; ++i) { tc::mbar_init(bar_full + 8 * i, p.ingest_bulk ? 1 : 256); tc::mbar_init(bar_empty + 8 * i, 1); }
+        for (int i = 0; i < S; ++i) { tc::mbar_init(bar_full + 8 * i, 1); tc::mbar_init(bar_empty + 8 * i, 1); }
         tc::mbar_init(bar_tfull, 1);
         tc::mbar_init(bar_tempty, 256);
         tc::mbar_init(bar_go, 1);
@@ -109,65 +240,90 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                 *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
             }
         }
-        if (p.ingest_bulk) tc::fence_proxy_async(); // generic global writes -> later bulk (async proxy) reads
+        tc::fence_proxy_async();                    // generic global writes -> later bulk (async proxy) reads
     }
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     if (tid == 0) tc::red_release_add(p.barrier, 1u);
+    TcLoopCtx lx;
+    lx.ring_a = tc::smem_u32(ring); lx.bar_full = bar_full; lx.bar_empty = bar_empty; lx.bar_tfull = bar_tfull;
+    lx.bar_tempty = bar_tempty; lx.bar_go = bar_go; lx.tmem_base = tmem_base; lx.wsm_a = tc::smem_u32(wsm);
+    lx.nticks = nticks; lx.N = N; lx.crot = (int)(blockIdx.x % (unsigned)nchunks); lx.src_layer = role.src_layer; lx.W = W;
+    lx.G = G;
 
     if (warp == 0) {
         // =============================== producer ===============================
-        if (lane == 0) {
-            uint32_t it = 0;
+        // (one thread: everything in these loops is a dependent chain of ~5 clk per instruction, so the ring
+        //  position, phase and chunk index are running counters -- an integer division per chunk costs more
+        //  than the copy itself)
+        if (!tc_run_fixed(true, p, lx, kc, nchunks, S) && lane == 0) {
+            uint32_t st = 0, ph = 0, ring_ofs = 0;
+            const int crot = (int)(blockIdx.x % (unsigned)nchunks);    // spread the CTAs over the chunks
+            const uint32_t ring_a = tc::smem_u32(ring);
             bool ok = true;
             for (int tick = 0; tick < nticks && ok; ++tick) {
                 if (!tc_wait_grid(p, (unsigned)(tick + 1) * G, 1)) break;
                 tc::mbar_arrive(bar_go);
-                tc_trace(p, tick, 0);
-                if (p.ingest_bulk) {
-                    // operand fetch by the bulk-copy engine (measured: ~25 B/clk per SM + ~90 clk per copy,
-                    // slower than the load/store path below; kept selectable for comparison)
-                    tc::fence_proxy_async();             // generic global writes of other CTAs -> async-proxy reads
-                    const unsigned char *src = reinterpret_cast<const unsigned char *>(
-                        p.hx + (size_t)(role.src_layer * 2 + (tick & 1)) * W * 128);
-                    for (int c0 = 0; c0 < nchunks; ++c0, ++it) {
-                        const int c = (c0 + (int)blockIdx.x) % nchunks;    // spread the CTAs over the chunks
-                        const uint32_t st = it % S, ph = (it / S) & 1;
-                        if (!tc_wait_mbar(bar_empty + 8 * st, ph ^ 1, p, 2)) { ok = false; break; }
-                        tc::mbar_arrive_expect_tx(bar_full + 8 * st, KLM_TC_CHUNK_BYTES);
-                        tc::bulk_g2s(tc::smem_u32(ring + (size_t)st * KLM_TC_CHUNK_BYTES), src + (size_t)c * KLM_TC_CHUNK_BYTES,
-                                     KLM_TC_CHUNK_BYTES, bar_full + 8 * st);
-                        if (c0 == 0) tc_trace(p, tick, 1);
+                if (p.trace_mode == 0) tc_trace(p, tick, 0);
+                // operand fetch by the bulk-copy engine
+                if (p.consumer_fence) tc::fence_proxy_async();   // generic global writes of other CTAs -> async-proxy reads
+                const unsigned char *src = reinterpret_cast<const unsigned char *>(
+                    p.hx + (size_t)(role.src_layer * 2 + (tick & 1)) * W * 128);
+                int c = crot;
+                for (int c0 = 0; c0 < nchunks; ++c0) {
+                    if (!tc_wait_mbar(bar_empty + 8 * st, ph ^ 1, p, 2)) { ok = false; break; }
+                    if (p.debug_skip & 2) tc::mbar_arrive(bar_full + 8 * st);
+                    else {
+                        tc::mbar_arrive_expect_tx(bar_full + 8 * st, chunk_bytes);
+                        tc::bulk_g2s(ring_a + ring_ofs, src + (size_t)c * chunk_bytes, chunk_bytes, bar_full + 8 * st);
                     }
+                    if (p.trace_mode == 2) tc_trace(p, tick, c0 & 7);
+                    else if (c0 == 0 && p.trace_mode == 0) tc_trace(p, tick, 1);
+                    ring_ofs += chunk_bytes;
+                    if (++st == (uint32_t)S) { st = 0; ph ^= 1; ring_ofs = 0; }
+                    if (++c == nchunks) c = 0;
                 }
             }
         }
     } else if (warp == 1) {
         // =============================== MMA issuer ===============================
-        if (lane == 0) {
+        if (!tc_run_fixed(false, p, lx, kc, nchunks, S) && lane == 0) {
             const uint32_t idesc = tc::idesc_f16(128, 2 * N);
             const uint32_t lbo_a = 128 * 16, lbo_b = 2 * N * 16;
-            const uint32_t ring_a = tc::smem_u32(ring), w_a = tc::smem_u32(wsm);
-            uint32_t it = 0;
+            // descriptors differ only in the start address field (bits 0-13, 16-byte units): add offsets to a base
+            const uint64_t a_base = tc::smem_desc(tc::smem_u32(ring), lbo_a, 128);
+            const uint64_t b_base = tc::smem_desc(tc::smem_u32(wsm), lbo_b, 128);
+            const uint32_t a_chunk = chunk_bytes >> 4, a_k16 = (2 * lbo_a) >> 4;
+            const uint32_t b_chunk = ((uint32_t)(kc / 8) * lbo_b) >> 4, b_k16 = (2 * lbo_b) >> 4;
+            const int crot = (int)(blockIdx.x % (unsigned)nchunks);
+            const int nk32 = kc / 32;
+            uint32_t st = 0, ph = 0, a_ofs = 0;
             bool ok = true;
             for (int tick = 0; tick < nticks && ok; ++tick) {
                 if (!tc_wait_mbar(bar_tempty, (tick & 1) ^ 1, p, 3)) break;
                 tc::tc_fence_after();
-                for (int c0 = 0; c0 < nchunks; ++c0, ++it) {
-                    const int c = (c0 + (int)blockIdx.x) % nchunks;
-                    const uint32_t st = it % S, ph = (it / S) & 1;
+                int c = crot;
+                uint32_t b_ofs = (uint32_t)crot * b_chunk;
+                uint32_t acc = 0;
+                for (int c0 = 0; c0 < nchunks; ++c0) {
                     if (!tc_wait_mbar(bar_full + 8 * st, ph, p, 4)) { ok = false; break; }
-                    tc_trace(p, tick, c0 == 0 ? 2 : 3);
+                    if (p.trace_mode == 1) tc_trace(p, tick, c0 & 7);
+                    else if (p.trace_mode == 0) tc_trace(p, tick, c0 == 0 ? 2 : 3);
                     tc::tc_fence_after();
-#pragma unroll
-                    for (int kk = 0; kk < KLM_TC_KC / 16; ++kk) {
-                        const uint64_t ad = tc::smem_desc(ring_a + st * KLM_TC_CHUNK_BYTES + kk * 2 * lbo_a, lbo_a, 128);
-                        const uint64_t bd = tc::smem_desc(w_a + (uint32_t)(c * (KLM_TC_KC / 8) + kk * 2) * lbo_b, lbo_b, 128);
-                        tc::mma_f16(tmem_base, ad, bd, idesc, (c0 | kk) != 0 ? 1u : 0u);
+                    uint64_t ad = a_base + a_ofs, bd = b_base + b_ofs;
+#pragma unroll 1
+                    for (int k2 = 0; k2 < ((p.debug_skip & 1) ? 0 : nk32); ++k2) {
+                        tc::mma_f16(tmem_base, ad, bd, idesc, acc);
+                        tc::mma_f16(tmem_base, ad + a_k16, bd + b_k16, idesc, 1u);
+                        acc = 1u;
+                        ad += 2 * a_k16; bd += 2 * b_k16;
                     }
                     tc::mma_commit(bar_empty + 8 * st);       // ring slot free once these MMAs have read it
+                    a_ofs += a_chunk; b_ofs += b_chunk;
+                    if (++st == (uint32_t)S) { st = 0; ph ^= 1; a_ofs = 0; }
+                    if (++c == nchunks) { c = 0; b_ofs = 0; }
                 }
                 if (ok) tc::mma_commit(bar_tfull);            // accumulators of this tick complete
             }
@@ -184,7 +340,6 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                     bias4[i][0] = __ldg(p.bias[l] + u); bias4[i][1] = __ldg(p.bias[l] + u + 1);
                 }
         }
-        uint32_t lit = 0;                                 // ring position of the load/store ingest
         for (int tick = 0; tick < nticks; ++tick) {
             // the producer thread polls the grid barrier; its mbarrier arrive (release.cta) hands the
             // acquired view of the other CTAs' writes (Z, logits) on to the epilogue threads
@@ -235,48 +390,11 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                 }
             }
 
-            // ---- A operand of this tick: the hidden vector, global (L2) -> ring, by the epilogue warps ----
-            if (!p.ingest_bulk) {
-                const uint4 *src = reinterpret_cast<const uint4 *>(p.hx + (size_t)(role.src_layer * 2 + par_in) * W * 128);
-                const int et = tid - 64;                                   // 0..255; a chunk is 4 x 256 uint4
-                uint4 ba[4], bb[4], bc[4];
-                bool okl = true;
-#define TC_LOAD(c0_, buf_)                                                                      \
-                {                                                                               \
-                    const uint4 *sp_ = src + (size_t)(((c0_) + (int)blockIdx.x) % nchunks) * 1024 + et; \
-                    _Pragma("unroll") for (int j = 0; j < 4; ++j) buf_[j] = __ldcg(sp_ + 256 * j); \
-                }
-#define TC_STORE(c0_, buf_)                                                                     \
-                {                                                                               \
-                    const uint32_t st_ = lit % S, ph_ = (lit / S) & 1;                          \
-                    okl = okl && tc_wait_mbar(bar_empty + 8 * st_, ph_ ^ 1, p, 2);              \
-                    uint4 *dp_ = reinterpret_cast<uint4 *>(ring + (size_t)st_ * KLM_TC_CHUNK_BYTES) + et; \
-                    _Pragma("unroll") for (int j = 0; j < 4; ++j) dp_[256 * j] = buf_[j];       \
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                \
-                    tc::mbar_arrive(bar_full + 8 * st_);                                        \
-                    if ((c0_) == 0 && tid == 64) tc_trace(p, tick, 1);                          \
-                    ++lit;                                                                      \
-                }
-                TC_LOAD(0, ba);
-                if (nchunks > 1) TC_LOAD(1, bb);
-                for (int c0 = 0; c0 < nchunks; c0 += 3) {
-                    if (c0 + 2 < nchunks) TC_LOAD(c0 + 2, bc);
-                    TC_STORE(c0, ba);
-                    if (c0 + 3 < nchunks) TC_LOAD(c0 + 3, ba);
-                    if (c0 + 1 < nchunks) TC_STORE(c0 + 1, bb);
-                    if (c0 + 4 < nchunks) TC_LOAD(c0 + 4, bb);
-                    if (c0 + 2 < nchunks) TC_STORE(c0 + 2, bc);
-                }
-#undef TC_LOAD
-#undef TC_STORE
-                if (!__all_sync(0xffffffffu, okl ? 1 : 0)) break;
-            }
-
             // ---- accumulators ----
             ok = tc_wait_mbar(bar_tfull, tick & 1, p, 6) ? 1 : 0;
             ok = __all_sync(0xffffffffu, ok);
             if (!ok) break;
-            if (tid == 64) tc_trace(p, tick, 4);
+            if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 4);
             tc::tc_fence_after();
             float acc[KLM_TC_OWN][8];
 #pragma unroll
@@ -301,7 +419,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                 }
             // the other half's pairs: hand this row's part over through shared memory (both directions at once)
             {
-                float *xs = xchg + (half ? 0 : KLM_TC_MAX_PAIRS / 2 * 8 * 64);
+                float *xs = xchg + (half ? 0 : KLM_TC1_MAX_PAIRS / 2 * 8 * 64);
 #pragma unroll
                 for (int i = 0; i < KLM_TC_OWN; ++i)
                     if (i < nsend) {
@@ -325,7 +443,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
             tc::mbar_arrive(bar_tempty);                      // this thread is done reading TMEM
             tc_bar_epi();
             {
-                const float *xr = xchg + (half ? KLM_TC_MAX_PAIRS / 2 * 8 * 64 : 0);
+                const float *xr = xchg + (half ? KLM_TC1_MAX_PAIRS / 2 * 8 * 64 : 0);
 #pragma unroll
                 for (int i = 0; i < KLM_TC_OWN; ++i)
                     if (i < nown) {
@@ -334,11 +452,11 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                         for (int j = 0; j < 8; ++j) acc[i][j] += xr[(xi * 8 + j) * 64 + s];
                     }
                 // the hand-over buffer aliases the ring: order these generic accesses before the next bulk copies
-                if (p.ingest_bulk) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             }
 
             // ---- finish and hand over ----
-            if (tid == 64) tc_trace(p, tick, 5);
+            if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 5);
             if (is_rec) {
                 // LSTM cell for all owned units, staged so that the MUFU chains of different units overlap
                 float e1[KLM_TC_OWN][2], e2[KLM_TC_OWN][2], e3[KLM_TC_OWN][2], e4[KLM_TC_OWN][2];
@@ -368,17 +486,54 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                         const float hn = __fdividef(1.f - e2[i][e], (1.f + e4[i][e]) * (1.f + e2[i][e]));
                         if (active) { c_reg[i][e] = e1[i][e]; h_reg[i][e] = hn; }
                     }
+                // publish the new hidden vector as fp16 hi/lo in the operand layout of its readers
+                __half *hx_out = p.hx + ((size_t)(l * 2 + par_out) * (W / 8)) * (128 * 8);
+                if (role.pub) {
+                    // slice = whole groups of 8 units: stage [group][128 rows][8], then write whole 2 KB blocks
 #pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
-                    if (i < nown) {
-                        const int u = 2 * (role.first_pair + own_first + i);
-                        __half hi0, lo0, hi1, lo1;
-                        tc_split(h_reg[i][0], hi0, lo0); tc_split(h_reg[i][1], hi1, lo1);
-                        __half *dst = p.hx + ((size_t)(l * 2 + par_out) * (W / 8) + u / 8) * (128 * 8) + (u & 7);
-                        *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
-                        *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                        if (i < nown) {
+                            const int ul = 2 * (own_first + i);
+                            __half hi0, lo0, hi1, lo1;
+                            tc_split(h_reg[i][0], hi0, lo0); tc_split(h_reg[i][1], hi1, lo1);
+                            __half *dst = pubbuf + (ul / 8) * (128 * 8) + (ul & 7);
+                            *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
+                            *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
+                        }
+                    __half *gdst = hx_out + (size_t)(role.first_pair / 4) * (128 * 8);
+                    const int n16 = (NP / 4) * 128;                       // 16-byte pieces of the slice
+                    if (role.pub == 2) {
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // staging writes -> bulk store reads
+                        if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
+                        tc_bar_epi();
+                        if (tid == 64) {
+                            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                                         ::"l"(gdst), "r"(tc::smem_u32(pubbuf)), "r"((uint32_t)n16 * 16u) : "memory");
+                            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // writes complete (not just read)
+                            tc::red_release_add(p.barrier, 1u);
+                            if (p.trace_mode == 0) tc_trace(p, tick, 7);
+                        }
+                        continue;
                     }
-                if (p.ingest_bulk) tc::fence_proxy_async();
+                    tc_bar_epi();
+                    const uint4 *sp = reinterpret_cast<const uint4 *>(pubbuf);
+                    uint4 *gp = reinterpret_cast<uint4 *>(gdst);
+                    for (int i = tid - 64; i < n16; i += 256) __stcg(gp + i, sp[i]);
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // staging reads -> next bulk copies into the ring
+                } else {
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                        if (i < nown) {
+                            const int u = 2 * (role.first_pair + own_first + i);
+                            __half hi0, lo0, hi1, lo1;
+                            tc_split(h_reg[i][0], hi0, lo0); tc_split(h_reg[i][1], hi1, lo1);
+                            __half *dst = hx_out + (size_t)(u / 8) * (128 * 8) + (u & 7);
+                            *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
+                            *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
+                        }
+                }
+                tc::fence_proxy_async();             // generic global writes -> bulk (async proxy) reads of other CTAs
             } else if (role.kind == KLM_TC_IN) {
                 float4 *zrow = reinterpret_cast<float4 *>(p.Z + ((size_t)(l * 2 + par_out) * 64 + s) * 4 * W);
 #pragma unroll
@@ -402,9 +557,9 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const KlmTcParam
                         __stcg(lrow + 2 * g8 + 1, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
                     }
             }
-            if (tid == 64) tc_trace(p, tick, 6);
+            if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
             tc_bar_epi();
-            if (tid == 64) { tc::red_release_add(p.barrier, 1u); tc_trace(p, tick, 7); }
+            if (tid == 64) { tc::red_release_add(p.barrier, 1u); if (p.trace_mode == 0) tc_trace(p, tick, 7); }
         }
         // ---- write the final state back ----
         if (is_rec && s < p.B) {

@@ -18,7 +18,7 @@
 
 #define TC2_XS (KLM_TC_MAX_PAIRS / 2 * 8 * 32)          // floats of one hand-over direction of one slice
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc2(const KlmTcParams p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc2(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const KlmTcRole role = p.roles[blockIdx.x];
     if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role); return; }      // LSE CTAs form clusters of their own

@@ -38,6 +38,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 
+// true in exactly one lane (the lowest) of a converged warp; lets ptxas predicate the single-thread instructions
+// (tcgen05.mma / commit, bulk copies) directly instead of wrapping each one in a loop over the active lanes
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // ---- proxies ----
 // Orders generic-proxy accesses (ld/st) against async-proxy accesses (bulk copies, tcgen05.mma operand reads).
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }

@@ -57,61 +57,141 @@ __device__ __forceinline__ void tc_split(float v, __half &hi, __half &lo) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// LSE stage: log-sum-exp over the logits of every stream + pick of the target's logit (or the full softmax row).
+// A warp owns up to 32 streams (lane k keeps stream k's offsets); per tick it walks over (stream, 256-logit block)
+// pairs with the loads of the next block in flight while the current one is reduced, and the target index and
+// target logit of all its streams are fetched up front by one lane each -- per tick the stage costs about one L2
+// round trip plus ~150 clk per stream instead of three dependent round trips per stream.
 static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const unsigned G = gridDim.x;
     const int nticks = p.T_max + 2 * p.D;
     const int nwarps = KLM_TC_THREADS / 32;
+    const int V = p.V, Vp = p.Vp, B = p.B, sigma = role.sigma, full_rows = p.full_rows;
+    const float *logits = p.logits;
+    const int *targets = p.targets;
+    float *out = p.out;
     __shared__ int ok_s;
+    // my streams: first, first + stride, ...; lane k holds stream k's data
+    const int first = role.first_pair * nwarps + warp, stride = role.npairs * nwarps;
+    const int nmine = first < B ? (B - first + stride - 1) / stride : 0;           // <= 32 (B <= 64, stride >= 10)
+    const int s_lane = first + lane * stride;
+    long long o0_lane = 0;
+    int len_lane = 0;
+    if (lane < nmine) { o0_lane = p.offsets[s_lane]; len_lane = (int)(p.offsets[s_lane + 1] - o0_lane); }
+    const int nblk = (V + 255) / 256, total = nmine * nblk;
     if (tid == 0) tc::red_release_add(p.barrier, 1u);
     for (int tick = 0; tick < nticks; ++tick) {
         if (tid == 0) ok_s = tc_wait_grid(p, (unsigned)(tick + 1) * G, 10) ? 1 : 0;
         __syncthreads();
         if (!ok_s) return;
-        const int t = tick - role.sigma;
-        if (t >= 0) {
-            for (int s = role.first_pair * nwarps + warp; s < p.B; s += role.npairs * nwarps) {
-                const long long o0 = p.offsets[s];
-                const int len = (int)(p.offsets[s + 1] - o0);
-                if (t >= len) continue;
-                const float *row = p.logits + ((size_t)(tick & 1) * 64 + s) * p.Vp;
-                // one pass: running maximum and rescaled sum per lane, then combined across the warp
-                float m = -INFINITY, sum = 0.f;
-                for (int v0 = 0; v0 < p.V; v0 += 256) {
-                    float x[8];
+        if (p.trace && p.trace_mode == 0 && tid == 0) tc_trace(p, tick, 0);
+        const int t = tick - sigma;
+        if (t >= 0 && total > 0) {
+            const float *base = logits + (size_t)(tick & 1) * 64 * Vp;
+            // target logit of my streams, one lane per stream
+            const bool act_lane = lane < nmine && t < len_lane;
+            float tl_lane = 0.f;
+            if (act_lane && !full_rows) {
+                int tg = __ldg(targets + o0_lane + t);
+                tg = min(max(tg, 0), V - 1);
+                tl_lane = __ldcg(base + (size_t)s_lane * Vp + tg);
+            }
+            if (nblk == 1 && nmine <= 8) {
+                // common case (V <= 256, at most 8 streams per warp): all loads in flight at once
+                float x[8][8];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const int v = v0 + 32 * j + lane;
-                        x[j] = v < p.V ? __ldcg(row + v) : -INFINITY;
+                for (int k = 0; k < 8; ++k)
+                    if (k < nmine) {
+                        const float *row = base + (size_t)(first + k * stride) * Vp;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int v = 32 * j + lane;
+                            x[k][j] = v < V ? __ldcg(row + v) : -INFINITY;
+                        }
                     }
-                    float mx = m;
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) mx = fmaxf(mx, x[j]);
-                    if (mx > -INFINITY) {
-                        float acc = sum * __expf(m - mx);
+                for (int k = 0; k < 8; ++k)
+                    if (k < nmine) {
+                        float m = x[k][0];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) acc += __expf(x[j] - mx);
-                        sum = acc; m = mx;
+                        for (int j = 1; j < 8; ++j) m = fmaxf(m, x[k][j]);
+                        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+                        float sum = 0.f;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) sum += __expf(x[k][j] - m);
+                        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                        const int act = __shfl_sync(0xffffffffu, act_lane ? 1 : 0, k);
+                        if (full_rows) {
+                            const long long o0 = __shfl_sync(0xffffffffu, o0_lane, k);
+                            if (act) {
+                                float *dst = out + (size_t)(o0 + t) * V;
+                                const float inv = 1.0f / sum;
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) {
+                                    const int v = 32 * j + lane;
+                                    if (v < V) dst[v] = expf(x[k][j] - m) * inv;
+                                }
+                            }
+                        } else if (lane == k && act) {
+                            out[o0_lane + t] = (tl_lane - m) - logf(sum);
+                        }
                     }
+                goto lse_tick_done;
+            }
+            float cur[8], nxt[8];
+            auto load_blk = [&](int b, float (&x)[8]) {
+                const int k = b / nblk, v0 = (b - k * nblk) * 256;
+                const float *row = base + (size_t)(first + k * stride) * Vp;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int v = v0 + 32 * j + lane;
+                    x[j] = v < V ? __ldcg(row + v) : -INFINITY;
                 }
-                float mw = m;
-                for (int o = 16; o > 0; o >>= 1) mw = fmaxf(mw, __shfl_xor_sync(0xffffffffu, mw, o));
-                sum = (m > -INFINITY) ? sum * __expf(m - mw) : 0.f;
-                for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                m = mw;
-                if (p.full_rows) {
-                    float *dst = p.out + (size_t)(o0 + t) * p.V;
-                    const float inv = 1.0f / sum;
-                    for (int v = lane; v < p.V; v += 32) dst[v] = expf(__ldcg(row + v) - m) * inv;
-                } else if (lane == 0) {
-                    int tg = __ldg(p.targets + o0 + t);
-                    tg = min(max(tg, 0), p.V - 1);
-                    p.out[o0 + t] = (__ldcg(row + tg) - m) - logf(sum);
+            };
+            load_blk(0, cur);
+            float m = -INFINITY, sum = 0.f;
+            for (int b = 0; b < total; ++b) {
+                if (b + 1 < total) load_blk(b + 1, nxt);
+                const int k = b / nblk, blk = b - k * nblk;
+                float mx = m;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) mx = fmaxf(mx, cur[j]);
+                if (mx > -INFINITY) {
+                    float acc = sum * __expf(m - mx);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc += __expf(cur[j] - mx);
+                    sum = acc; m = mx;
                 }
+                if (blk == nblk - 1) {                      // stream k complete: combine across the warp
+                    float mw = m;
+                    for (int o = 16; o > 0; o >>= 1) mw = fmaxf(mw, __shfl_xor_sync(0xffffffffu, mw, o));
+                    sum = (m > -INFINITY) ? sum * __expf(m - mw) : 0.f;
+                    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                    const int act = __shfl_sync(0xffffffffu, act_lane ? 1 : 0, k);
+                    if (full_rows) {
+                        const long long o0 = __shfl_sync(0xffffffffu, o0_lane, k);
+                        if (act) {
+                            const float *row = base + (size_t)(first + k * stride) * Vp;
+                            float *dst = out + (size_t)(o0 + t) * V;
+                            const float inv = 1.0f / sum;
+                            for (int v = lane; v < V; v += 32) dst[v] = expf(__ldcg(row + v) - mw) * inv;
+                        }
+                    } else if (lane == k && act) {
+                        out[o0_lane + t] = (tl_lane - mw) - logf(sum);
+                    }
+                    m = -INFINITY; sum = 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) cur[j] = nxt[j];
             }
         }
+    lse_tick_done:
         __syncthreads();
-        if (tid == 0) tc::red_release_add(p.barrier, 1u);
+        if (tid == 0) {
+            tc::red_release_add(p.barrier, 1u);
+            if (p.trace && p.trace_mode == 0) tc_trace(p, tick, 7);
+        }
     }
 }
 

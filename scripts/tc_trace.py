@@ -29,7 +29,7 @@ print('grid', info['tc_grid'], 'last kernel ms', info['last_kernel_ms'], 'per ti
 names = {0: 'REC', 1: 'IN', 2: 'PROJ', 3: 'LSE'}
 tr = tr.astype(np.int64)
 ev = ['start', 'issue0', 'chunk0', 'chunkN', 'mma_done', 'drained', 'stored', 'arrive']
-for kind in (0, 1, 2):
+for kind in (0, 1, 2, 3):
     for layer in range(depth):
         sel = [i for i in range(len(roles)) if roles[i, 0] == kind and roles[i, 1] == layer]
         if not sel:
@@ -37,5 +37,10 @@ for kind in (0, 1, 2):
         x = tr[sel][:, 2:14, :]                   # [cta][tick][ev]
         period = (x[:, 1:, 0] - x[:, :-1, 0]).mean()
         rel = (x - x[:, :, :1]).mean(axis=(0, 1))
+        if kind == 3:
+            print('LSE n=%d period %.0f clk | start +0 arrive %+.0f (slowest CTA %+.0f)' % (
+                len(sel), period, rel[7], (x[:, :, 7] - x[:, :, 0]).mean(axis=1).max()))
+            break
         print('%s l%d n=%d pairs=%s period %.0f clk | ' % (names[kind], layer, len(sel), sorted(set(int(v) for v in roles[sel, 2])), period) +
-              ' '.join('%s %+.0f' % (e, v) for e, v in zip(ev, rel)))
+              ' '.join('%s %+.0f' % (e, v) for e, v in zip(ev, rel)) +
+              ' | slowest CTA arrive %+.0f' % (x[:, :, 7] - x[:, :, 0]).mean(axis=1).max())
