@@ -126,8 +126,8 @@ struct KlmTcParams {
     int ring_bytes;               // CTA-pair kernel: bytes of the ring region (>= the hand-over buffer aliased on it)
     int ingest_bulk;              // CTA-pair kernel only (the single-CTA kernel always uses bulk copies)
     int consumer_fence;           // single-CTA kernel: fence.proxy.async between the grid barrier and the bulk reads
-    float *Z;                     // [D][2][64][4W]  (unit-interleaved gate columns)
-    float *logits;                // [2][64][Vp]
+    float *Z;                     // pre-activations of the IN stages: klm_seq_tc [D][2][W][64] float4 (i,f,c,o), klm_seq_tc2 [D][2][64][4W]
+    float *logits;                // [2][Vp/4][64] float4
     float *state;
     const int *slots_in, *slots_out;
     const long long *offsets;

@@ -58,8 +58,18 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
     const size_t hx_par = (size_t)x.W * 128 * sizeof(__half);
     uint32_t phbits = 0;                                   // bit st: uses of slot st so far, mod 2
     const bool lane0 = (threadIdx.x & 31) == 0;
+    constexpr int NPRE = S < NCH ? S : NCH;
     for (int tick = 0; tick < nticks; ++tick) {
-        // the whole warp runs this loop converged; lane 0 polls the grid barrier and issues
+        // the whole warp runs this loop converged; lane 0 polls the grid barrier and issues.
+        // The first ring round is armed before the grid barrier (its slots are free since the previous tick's
+        // MMAs), so that after the barrier the copies go out back to back.
+#pragma unroll
+        for (int c0 = 0; c0 < NPRE; ++c0) {
+            int okw = tc_wait_mbar(bar_empty + 8 * c0, ((phbits >> c0) & 1u) ^ 1u, p, 2) ? 1 : 0;
+            if (!__all_sync(0xffffffffu, okw)) return;
+            if (tc::elect_one() && !(skip & 2)) tc::mbar_arrive_expect_tx(bar_full + 8 * c0, CB);
+            __syncwarp();
+        }
         int okg = 1;
         if (lane0) {
             okg = tc_wait_grid(p, (unsigned)(tick + 1) * G, 1) ? 1 : 0;
@@ -75,12 +85,14 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
 #pragma unroll
         for (int c0 = 0; c0 < NCH; ++c0) {
             const int st = c0 % S;
-            int okw = tc_wait_mbar(bar_empty + 8 * st, ((phbits >> st) & 1u) ^ 1u, p, 2) ? 1 : 0;
-            if (!__all_sync(0xffffffffu, okw)) return;
+            if (c0 >= NPRE) {
+                int okw = tc_wait_mbar(bar_empty + 8 * st, ((phbits >> st) & 1u) ^ 1u, p, 2) ? 1 : 0;
+                if (!__all_sync(0xffffffffu, okw)) return;
+            }
             if (tc::elect_one()) {
                 if (skip & 2) tc::mbar_arrive(bar_full + 8 * st);
                 else {
-                    tc::mbar_arrive_expect_tx(bar_full + 8 * st, CB);
+                    if (c0 >= NPRE) tc::mbar_arrive_expect_tx(bar_full + 8 * st, CB);
                     tc::bulk_g2s(ring_a + st * CB, src + (size_t)c * CB, CB, bar_full + 8 * st);
                 }
                 if (TRACE) {
@@ -160,7 +172,7 @@ static __device__ __forceinline__ bool tc_run_fixed(bool producer, const KlmTcPa
 __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const KlmTcRole role = p.roles[blockIdx.x];
-    if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role); return; }
+    if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int W = p.W, S = role.stages, kc = role.kc;
@@ -340,6 +352,32 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
                     bias4[i][0] = __ldg(p.bias[l] + u); bias4[i][1] = __ldg(p.bias[l] + u + 1);
                 }
         }
+        // REC layer 1: first character index, number of real (non-padding) positions, and the context part of the
+        // input contraction sum_k Q_k[z_k][u], which does not change over the ticks
+        int x_next = 0, nreal_s = 0x7fffffff;
+        float4 qsum[KLM_TC_OWN][2];
+#pragma unroll
+        for (int i = 0; i < KLM_TC_OWN; ++i) qsum[i][0] = qsum[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (is_rec && l == 0 && s < p.B) {
+            if (len > 0) x_next = __ldg(p.chars + o0);
+            if (p.n_real) nreal_s = __ldg(p.n_real + s);
+#pragma unroll
+            for (int k = 0; k < KLM_MAX_CTX; ++k)
+                if (k < p.Nc) {
+                    int z = __ldg(p.ctx + s * p.Nc + k);
+                    z = min(max(z, 0), p.ctx_rows[k] - 1);
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                        if (i < nown) {
+                            const int u = 2 * (role.first_pair + own_first + i);
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const float4 b = __ldg(p.Q[k] + (size_t)z * W + u + e);
+                                qsum[i][e].x += b.x; qsum[i][e].y += b.y; qsum[i][e].z += b.z; qsum[i][e].w += b.w;
+                            }
+                        }
+                }
+        }
         for (int tick = 0; tick < nticks; ++tick) {
             // the producer thread polls the grid barrier; its mbarrier arrive (release.cta) hands the
             // acquired view of the other CTAs' writes (Z, logits) on to the epilogue threads
@@ -357,14 +395,10 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
             if (is_rec && active) {
                 if (l == 0) {
                     // fused char + context embedding gather / concat / input contraction (rating.py:103-115,125)
-                    int x = __ldg(p.chars + o0 + t);
-                    x = min(max(x, 0), p.V - 1);
-                    const bool real = p.n_real ? (t < __ldg(p.n_real + s)) : true;
-                    int z[KLM_MAX_CTX];
-                    for (int k = 0; k < p.Nc; ++k) {
-                        z[k] = real ? __ldg(p.ctx + s * p.Nc + k) : 0;       // padding: context 0 (:1141-1143)
-                        z[k] = min(max(z[k], 0), p.ctx_rows[k] - 1);
-                    }
+                    // the character index was fetched a tick ahead, the context part is tick-invariant (qsum)
+                    int x = min(max(x_next, 0), p.V - 1);
+                    if (t + 1 < len) x_next = __ldg(p.chars + o0 + t + 1);
+                    const bool real = t < nreal_s;
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i)
                         if (i < nown) {
@@ -372,20 +406,29 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
 #pragma unroll
                             for (int e = 0; e < 2; ++e) {
                                 float4 a = __ldg(p.P + (size_t)x * W + u + e);
-                                for (int k = 0; k < p.Nc; ++k) {
-                                    const float4 b = __ldg(p.Q[k] + (size_t)z[k] * W + u + e);
+                                if (real) {
+                                    const float4 b = qsum[i][e];
                                     a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+                                } else {                     // padding position: context 0 (:1141-1143)
+#pragma unroll
+                                    for (int k = 0; k < KLM_MAX_CTX; ++k)
+                                        if (k < p.Nc) {
+                                            const float4 b = __ldg(p.Q[k] + u + e);
+                                            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+                                        }
                                 }
                                 add4[i][e] = a;
                             }
                         }
                 } else {
-                    const float4 *zrow = reinterpret_cast<const float4 *>(p.Z + ((size_t)(l * 2 + par_in) * 64 + s) * 4 * W);
+                    // Z is [layer][parity][unit][64 streams] float4: the lanes of a warp (consecutive streams) touch 512
+                    // contiguous bytes per unit, on the IN side (stores) as well as here
+                    const float4 *zrow = reinterpret_cast<const float4 *>(p.Z) + (size_t)(l * 2 + par_in) * W * 64 + s;
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i)
                         if (i < nown) {
                             const int u = 2 * (role.first_pair + own_first + i);
-                            add4[i][0] = __ldcg(zrow + u); add4[i][1] = __ldcg(zrow + u + 1);
+                            add4[i][0] = __ldcg(zrow + (size_t)u * 64); add4[i][1] = __ldcg(zrow + (size_t)(u + 1) * 64);
                         }
                 }
             }
@@ -535,7 +578,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
                 }
                 tc::fence_proxy_async();             // generic global writes -> bulk (async proxy) reads of other CTAs
             } else if (role.kind == KLM_TC_IN) {
-                float4 *zrow = reinterpret_cast<float4 *>(p.Z + ((size_t)(l * 2 + par_out) * 64 + s) * 4 * W);
+                float4 *zrow = reinterpret_cast<float4 *>(p.Z) + (size_t)(l * 2 + par_out) * W * 64 + s;
 #pragma unroll
                 for (int i = 0; i < KLM_TC_OWN; ++i)
                     if (i < nown) {
@@ -543,18 +586,19 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             const float4 b = bias4[i][e];
-                            __stcg(zrow + u + e, make_float4(acc[i][4 * e] + b.x, acc[i][4 * e + 1] + b.y,
+                            __stcg(zrow + (size_t)(u + e) * 64, make_float4(acc[i][4 * e] + b.x, acc[i][4 * e + 1] + b.y,
                                                              acc[i][4 * e + 2] + b.z, acc[i][4 * e + 3] + b.w));
                         }
                     }
             } else {   // PROJ: logits of vocabulary rows 8*(first_pair + pair) ..
-                float4 *lrow = reinterpret_cast<float4 *>(p.logits + ((size_t)par_out * 64 + s) * p.Vp);
+                // logits are [parity][Vp/4][64 streams] float4: coalesced over the streams of a warp (read by the LSE stage)
+                float4 *lrow = reinterpret_cast<float4 *>(p.logits) + (size_t)par_out * (p.Vp / 4) * 64 + s;
 #pragma unroll
                 for (int i = 0; i < KLM_TC_OWN; ++i)
                     if (i < nown) {
                         const int g8 = role.first_pair + own_first + i;
-                        __stcg(lrow + 2 * g8, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
-                        __stcg(lrow + 2 * g8 + 1, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
+                        __stcg(lrow + (size_t)(2 * g8) * 64, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
+                        __stcg(lrow + (size_t)(2 * g8 + 1) * 64, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
                     }
             }
             if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);

@@ -21,7 +21,7 @@
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc2(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const KlmTcRole role = p.roles[blockIdx.x];
-    if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role); return; }      // LSE CTAs form clusters of their own
+    if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }      // LSE CTAs form clusters of their own
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = tc::cluster_ctarank();
@@ -350,13 +350,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(KLM_TC_THREADS, 1) k
                         }
                     }
             } else {   // PROJ
-                float4 *lrow = reinterpret_cast<float4 *>(p.logits + ((size_t)par_out * 64 + s) * p.Vp);
+                // logits are [parity][Vp/4][64 streams] float4: coalesced over the streams of a warp (read by the LSE stage)
+                float4 *lrow = reinterpret_cast<float4 *>(p.logits) + (size_t)par_out * (p.Vp / 4) * 64 + s;
 #pragma unroll
                 for (int i = 0; i < KLM_TC_OWN; ++i)
                     if (i < nown) {
                         const int g8 = roleX.first_pair + own_first + i;
-                        __stcg(lrow + 2 * g8, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
-                        __stcg(lrow + 2 * g8 + 1, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
+                        __stcg(lrow + (size_t)(2 * g8) * 64, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
+                        __stcg(lrow + (size_t)(2 * g8 + 1) * 64, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
                     }
             }
             if (tid == 64) tc_trace(p, tick, 6);

@@ -58,28 +58,36 @@ __device__ __forceinline__ void tc_split(float v, __half &hi, __half &lo) {
 
 // ---------------------------------------------------------------------------------------------
 // LSE stage: log-sum-exp over the logits of every stream + pick of the target's logit (or the full softmax row).
-// A warp owns up to 32 streams (lane k keeps stream k's offsets); per tick it walks over (stream, 256-logit block)
-// pairs with the loads of the next block in flight while the current one is reduced, and the target index and
-// target logit of all its streams are fetched up front by one lane each -- per tick the stage costs about one L2
-// round trip plus ~150 clk per stream instead of three dependent round trips per stream.
-static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
+// The logits arrive as [parity][Vp/4][64 streams] float4 (the PROJ stores are coalesced over streams).  Lane = stream:
+// a warp covers 32 streams and one slice of the vocabulary, reads whole 512-byte rows and keeps a running
+// (max, rescaled sum) per lane; the slices of a stream group are combined through shared memory.  One CTA handles
+// all 64 streams in about two L2 round trips per tick.
+#define TC_LSE_WARPS (KLM_TC_THREADS / 32)
+static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role, unsigned char *dyn_smem) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const unsigned G = gridDim.x;
     const int nticks = p.T_max + 2 * p.D;
-    const int nwarps = KLM_TC_THREADS / 32;
-    const int V = p.V, Vp = p.Vp, B = p.B, sigma = role.sigma, full_rows = p.full_rows;
-    const float *logits = p.logits;
+    const int V = p.V, Vq = p.Vp / 4, V4 = (V + 3) / 4, B = p.B, sigma = role.sigma, full_rows = p.full_rows;
+    const float4 *logits4 = reinterpret_cast<const float4 *>(p.logits);
     const int *targets = p.targets;
     float *out = p.out;
     __shared__ int ok_s;
-    // my streams: first, first + stride, ...; lane k holds stream k's data
-    const int first = role.first_pair * nwarps + warp, stride = role.npairs * nwarps;
-    const int nmine = first < B ? (B - first + stride - 1) / stride : 0;           // <= 32 (B <= 64, stride >= 10)
-    const int s_lane = first + lane * stride;
-    long long o0_lane = 0;
-    int len_lane = 0;
-    if (lane < nmine) { o0_lane = p.offsets[s_lane]; len_lane = (int)(p.offsets[s_lane + 1] - o0_lane); }
-    const int nblk = (V + 255) / 256, total = nmine * nblk;
+    // partial (max, sum) per warp and lane: in the dynamic shared memory (an LSE CTA has no other use for it; static
+    // shared memory would push the GEMM CTAs' carve-up over the per-block limit)
+    float (*part_m)[32] = reinterpret_cast<float (*)[32]>(dyn_smem);
+    float (*part_s)[32] = reinterpret_cast<float (*)[32]>(dyn_smem + TC_LSE_WARPS * 32 * sizeof(float));
+    // stream groups of 32: this CTA takes groups first_pair, first_pair + npairs, ...; its warps are split evenly
+    // over (group, vocabulary slice)
+    const int ngroups = (B + 31) / 32;
+    const int gmine = role.first_pair < ngroups ? (ngroups - role.first_pair + role.npairs - 1) / role.npairs : 0;
+    const int nslices = gmine > 0 ? TC_LSE_WARPS / gmine : 1;
+    const int gl = warp / nslices, sl = warp - gl * nslices;              // local group, slice
+    const bool warp_on = gmine > 0 && gl < gmine;
+    const int s = warp_on ? 32 * (role.first_pair + gl * role.npairs) + lane : 0;
+    long long o0 = 0;
+    int len = 0;
+    if (warp_on && s < B) { o0 = p.offsets[s]; len = (int)(p.offsets[s + 1] - o0); }
+    const int v4_lo = (int)((long long)V4 * sl / nslices), v4_hi = (int)((long long)V4 * (sl + 1) / nslices);
     if (tid == 0) tc::red_release_add(p.barrier, 1u);
     for (int tick = 0; tick < nticks; ++tick) {
         if (tid == 0) ok_s = tc_wait_grid(p, (unsigned)(tick + 1) * G, 10) ? 1 : 0;
@@ -87,106 +95,70 @@ static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role) 
         if (!ok_s) return;
         if (p.trace && p.trace_mode == 0 && tid == 0) tc_trace(p, tick, 0);
         const int t = tick - sigma;
-        if (t >= 0 && total > 0) {
-            const float *base = logits + (size_t)(tick & 1) * 64 * Vp;
-            // target logit of my streams, one lane per stream
-            const bool act_lane = lane < nmine && t < len_lane;
-            float tl_lane = 0.f;
-            if (act_lane && !full_rows) {
-                int tg = __ldg(targets + o0_lane + t);
-                tg = min(max(tg, 0), V - 1);
-                tl_lane = __ldcg(base + (size_t)s_lane * Vp + tg);
-            }
-            if (nblk == 1 && nmine <= 8) {
-                // common case (V <= 256, at most 8 streams per warp): all loads in flight at once
-                float x[8][8];
+        const bool act = warp_on && s < B && t >= 0 && t < len;
+        const float4 *base = logits4 + (size_t)(tick & 1) * Vq * 64 + s;
+        float tl = 0.f;
+        if (act && sl == 0 && !full_rows) {
+            int tg = __ldg(targets + o0 + t);
+            tg = min(max(tg, 0), V - 1);
+            tl = __ldcg(reinterpret_cast<const float *>(base + (size_t)(tg >> 2) * 64) + (tg & 3));
+        }
+        float m = -INFINITY, sum = 0.f;
+        if (warp_on && t >= 0) {
+            for (int v0 = v4_lo; v0 < v4_hi; v0 += 8) {
+                float4 x[8];
 #pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    if (k < nmine) {
-                        const float *row = base + (size_t)(first + k * stride) * Vp;
+                for (int j = 0; j < 8; ++j)
+                    x[j] = (v0 + j < v4_hi) ? __ldcg(base + (size_t)(v0 + j) * 64) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+                if (4 * (v0 + 8) > V) {                      // mask the padding entries of the last float4
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int v = 32 * j + lane;
-                            x[k][j] = v < V ? __ldcg(row + v) : -INFINITY;
-                        }
+                    for (int j = 0; j < 8; ++j) {
+                        const int v = 4 * (v0 + j);
+                        if (v + 1 >= V) x[j].y = -INFINITY;
+                        if (v + 2 >= V) x[j].z = -INFINITY;
+                        if (v + 3 >= V) x[j].w = -INFINITY;
+                        if (v >= V) x[j].x = -INFINITY;
                     }
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    if (k < nmine) {
-                        float m = x[k][0];
-#pragma unroll
-                        for (int j = 1; j < 8; ++j) m = fmaxf(m, x[k][j]);
-                        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-                        float sum = 0.f;
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) sum += __expf(x[k][j] - m);
-                        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                        const int act = __shfl_sync(0xffffffffu, act_lane ? 1 : 0, k);
-                        if (full_rows) {
-                            const long long o0 = __shfl_sync(0xffffffffu, o0_lane, k);
-                            if (act) {
-                                float *dst = out + (size_t)(o0 + t) * V;
-                                const float inv = 1.0f / sum;
-#pragma unroll
-                                for (int j = 0; j < 8; ++j) {
-                                    const int v = 32 * j + lane;
-                                    if (v < V) dst[v] = expf(x[k][j] - m) * inv;
-                                }
-                            }
-                        } else if (lane == k && act) {
-                            out[o0_lane + t] = (tl_lane - m) - logf(sum);
-                        }
-                    }
-                goto lse_tick_done;
-            }
-            float cur[8], nxt[8];
-            auto load_blk = [&](int b, float (&x)[8]) {
-                const int k = b / nblk, v0 = (b - k * nblk) * 256;
-                const float *row = base + (size_t)(first + k * stride) * Vp;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int v = v0 + 32 * j + lane;
-                    x[j] = v < V ? __ldcg(row + v) : -INFINITY;
                 }
-            };
-            load_blk(0, cur);
-            float m = -INFINITY, sum = 0.f;
-            for (int b = 0; b < total; ++b) {
-                if (b + 1 < total) load_blk(b + 1, nxt);
-                const int k = b / nblk, blk = b - k * nblk;
                 float mx = m;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) mx = fmaxf(mx, cur[j]);
+                for (int j = 0; j < 8; ++j) mx = fmaxf(fmaxf(fmaxf(mx, x[j].x), fmaxf(x[j].y, x[j].z)), x[j].w);
                 if (mx > -INFINITY) {
                     float acc = sum * __expf(m - mx);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) acc += __expf(cur[j] - mx);
+                    for (int j = 0; j < 8; ++j)
+                        acc += __expf(x[j].x - mx) + __expf(x[j].y - mx) + __expf(x[j].z - mx) + __expf(x[j].w - mx);
                     sum = acc; m = mx;
                 }
-                if (blk == nblk - 1) {                      // stream k complete: combine across the warp
-                    float mw = m;
-                    for (int o = 16; o > 0; o >>= 1) mw = fmaxf(mw, __shfl_xor_sync(0xffffffffu, mw, o));
-                    sum = (m > -INFINITY) ? sum * __expf(m - mw) : 0.f;
-                    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                    const int act = __shfl_sync(0xffffffffu, act_lane ? 1 : 0, k);
-                    if (full_rows) {
-                        const long long o0 = __shfl_sync(0xffffffffu, o0_lane, k);
-                        if (act) {
-                            const float *row = base + (size_t)(first + k * stride) * Vp;
-                            float *dst = out + (size_t)(o0 + t) * V;
-                            const float inv = 1.0f / sum;
-                            for (int v = lane; v < V; v += 32) dst[v] = expf(__ldcg(row + v) - mw) * inv;
-                        }
-                    } else if (lane == k && act) {
-                        out[o0_lane + t] = (tl_lane - mw) - logf(sum);
-                    }
-                    m = -INFINITY; sum = 0.f;
-                }
-#pragma unroll
-                for (int j = 0; j < 8; ++j) cur[j] = nxt[j];
             }
         }
-    lse_tick_done:
+        part_m[warp][lane] = m; part_s[warp][lane] = sum;
+        __syncthreads();
+        // every warp of the group combines the slices (cheap), slice 0 writes the score
+        float M = -INFINITY, S = 0.f;
+        if (warp_on) {
+            for (int i = 0; i < nslices; ++i) M = fmaxf(M, part_m[gl * nslices + i][lane]);
+            for (int i = 0; i < nslices; ++i) {
+                const float mi = part_m[gl * nslices + i][lane];
+                if (mi > -INFINITY) S += part_s[gl * nslices + i][lane] * __expf(mi - M);
+            }
+        }
+        if (act) {
+            if (!full_rows) {
+                if (sl == 0) out[o0 + t] = (tl - M) - logf(S);
+            } else {
+                float *dst = out + (size_t)(o0 + t) * V;
+                const float inv = 1.0f / S;
+                for (int v4 = v4_lo; v4 < v4_hi; ++v4) {
+                    const float4 x = __ldcg(base + (size_t)v4 * 64);
+                    const int v = 4 * v4;
+                    dst[v] = expf(x.x - M) * inv;
+                    if (v + 1 < V) dst[v + 1] = expf(x.y - M) * inv;
+                    if (v + 2 < V) dst[v + 2] = expf(x.z - M) * inv;
+                    if (v + 3 < V) dst[v + 3] = expf(x.w - M) * inv;
+                }
+            }
+        }
         __syncthreads();
         if (tid == 0) {
             tc::red_release_add(p.barrier, 1u);
@@ -194,4 +166,3 @@ static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role) 
         }
     }
 }
-
