@@ -74,12 +74,15 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
         if (lane0) {
             okg = tc_wait_grid(p, (unsigned)(tick + 1) * G, 1) ? 1 : 0;
             if (okg) {
+                if (TRACE && trace_mode == 3) tc_trace(p, tick, 0);
                 tc::mbar_arrive(bar_go);
                 if (TRACE && trace_mode == 0) tc_trace(p, tick, 0);
+                if (TRACE && trace_mode == 3) tc_trace(p, tick, 1);
                 if (cfence) tc::fence_proxy_async();
             }
         }
         if (!__shfl_sync(0xffffffffu, okg, 0)) return;
+        if (TRACE && trace_mode == 3 && lane0) tc_trace(p, tick, 2);
         const unsigned char *src = hx0 + ((tick & 1) ? hx_par : 0);
         int c = crot;
 #pragma unroll
@@ -90,11 +93,13 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
                 if (!__all_sync(0xffffffffu, okw)) return;
             }
             if (tc::elect_one()) {
+                if (TRACE && trace_mode == 3 && c0 == 0) tc_trace(p, tick, 3);
                 if (skip & 2) tc::mbar_arrive(bar_full + 8 * st);
                 else {
                     if (c0 >= NPRE) tc::mbar_arrive_expect_tx(bar_full + 8 * st, CB);
                     tc::bulk_g2s(ring_a + st * CB, src + (size_t)c * CB, CB, bar_full + 8 * st);
                 }
+                if (TRACE && trace_mode == 3 && c0 < 4) tc_trace(p, tick, 4 + c0);
                 if (TRACE) {
                     if (trace_mode == 2) tc_trace(p, tick, c0 & 7);
                     else if (c0 == 0 && trace_mode == 0) tc_trace(p, tick, 1);
@@ -507,6 +512,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
                 for (int i = 0; i < KLM_TC_OWN; ++i)
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
+                        if (i >= nown) continue;             // (warp-uniform)
                         const float4 a = add4[i][e];
                         e1[i][e] = tc_exp(-tc_clamp(acc[i][4 * e] + a.x));
                         e2[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 1] + a.y));
@@ -517,6 +523,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
                 for (int i = 0; i < KLM_TC_OWN; ++i)
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
+                        if (i >= nown) continue;
                         const float ig = __fdividef(1.f - e3[i][e], (1.f + e1[i][e]) * (1.f + e3[i][e]));
                         const float f = __fdividef(1.f, 1.f + e2[i][e]);
                         e1[i][e] = fmaf(f, c_reg[i][e], ig);                       // new cell state
@@ -526,6 +533,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
                 for (int i = 0; i < KLM_TC_OWN; ++i)
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
+                        if (i >= nown) continue;
                         const float hn = __fdividef(1.f - e2[i][e], (1.f + e4[i][e]) * (1.f + e2[i][e]));
                         if (active) { c_reg[i][e] = e1[i][e]; h_reg[i][e] = hn; }
                     }

@@ -36,7 +36,13 @@ __device__ __forceinline__ void tc_trace(const KlmTcParams &p, int tick, int ev)
 __device__ __forceinline__ void tc_bar_epi() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // exp via ex2.approx (2 ulp), reciprocal via rcp.approx: absolute error of the gates ~1e-7
-__device__ __forceinline__ float tc_exp(float x) { return exp2f(x * 1.4426950408889634f); }
+// (ex2.approx.ftz directly: the argument is clamped to +-30 * log2(e), far from the denormal range that exp2f()
+//  guards with a compare and two predicated multiplies per call)
+__device__ __forceinline__ float tc_exp(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+    return y;
+}
 __device__ __forceinline__ float tc_clamp(float x) { return fminf(fmaxf(x, -30.f), 30.f); }
 
 // LSTM cell (Keras LSTMCell, gate order i|f|c|o, exact logistic; rating.py:133-134), 8 MUFU ops:
