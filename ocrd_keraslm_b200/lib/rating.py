@@ -345,8 +345,45 @@ class Rater(object):
     def train(self, *args, **kwargs):
         raise NotImplementedError('training is outside the B200 rating path; train with the reference and load the file')
 
-    def remove_from_mapping(self, *args, **kwargs):
-        raise NotImplementedError('vocabulary pruning is outside the B200 rating path')
+    def remove_from_mapping(self, char=None, idx=None):
+        """Remove one character from the vocabulary and the matching row of the (tied) embedding,
+        shifting all higher indices down by one (reference :416-460); the device model is rebuilt
+        from the pruned weights.  Returns False (after logging) if there is nothing to remove."""
+        assert self.status > 1
+        assert self.voc_size > 0
+        if not char and not idx:
+            return False
+        if char:
+            if char in self.mapping[0]:
+                idx = self.mapping[0][char]
+            else:
+                self.logger.error('unmapped character "%s" cannot be removed', char)
+                return False
+        else:
+            if idx in self.mapping[1]:
+                char = self.mapping[1][idx]
+            else:
+                self.logger.error('unmapped index "%d" cannot be removed', idx)
+                return False
+        embedding = np.asarray(self._host_weights['char_embedding'], dtype=np.float32)
+        norm = np.linalg.norm(embedding[idx, :])
+        self.logger.warning('pruning character "%s" [%d] with norm %f', char, idx, norm)
+        self.mapping[0].pop(char)
+        self.mapping[1].pop(idx)
+        for i in range(idx + 1, self.voc_size):
+            otherchar = self.mapping[1][i]
+            self.mapping[0][otherchar] -= 1
+            self.mapping[1][i - 1] = otherchar
+            self.mapping[1].pop(i)
+        self.voc_size -= 1
+        wd = dict(self._host_weights)
+        wd['char_embedding'] = np.delete(embedding, idx, 0)
+        self._lut = None                     # char -> index table cache is stale now
+        self._lut_src = None
+        self.configure()
+        self.set_weights(wd)
+        self.status = 2
+        return True
 
     # ------------------------------------------------------------------ vocabulary
     def _indices(self, text):

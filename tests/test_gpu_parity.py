@@ -273,3 +273,37 @@ def test_rate_best_native_edge_equals_python_loop(width, beam_width, batch_size)
         np.testing.assert_allclose(x[1], y[1], rtol=1e-6)
         np.testing.assert_allclose(x[4], y[4], rtol=1e-6, atol=1e-6)
         assert x[2] == pytest.approx(y[2], rel=1e-6, abs=1e-6)
+
+
+# ------------------------------------------------------------------ vocabulary pruning
+def test_remove_from_mapping_shifts_indices_and_rebuilds_model():
+    """prune-charset (reference :416-460): the character's embedding row disappears, higher indices move down
+    by one, and the rebuilt device model rates like the oracle on the pruned weights."""
+    wd, maparr, mapping = util.small_model()
+    r = product(wd, maparr, 8)
+    victim = sorted(mapping[0].items(), key=lambda kv: kv[1])[3][0]       # some character in the middle
+    vidx = mapping[0][victim]
+    voc0 = r.voc_size
+    assert r.remove_from_mapping(char='☃') is False                   # unmapped: logged, nothing changes
+    assert r.remove_from_mapping() is False
+    assert r.voc_size == voc0
+    assert r.remove_from_mapping(char=victim) is True
+    assert r.status == 2 and r.voc_size == voc0 - 1
+    assert victim not in r.mapping[0]
+    for c, i in mapping[0].items():
+        if c == victim:
+            continue
+        assert r.mapping[0][c] == (i - 1 if i > vidx else i)
+        assert r.mapping[1][r.mapping[0][c]] == c
+    assert sorted(r.mapping[1]) == list(range(1, voc0 - 1))
+    # oracle on the pruned weights and mapping
+    wd2 = dict(wd)
+    wd2['char_embedding'] = np.delete(np.asarray(wd['char_embedding']), vidx, 0)
+    c_i = dict((c, (i - 1 if i > vidx else i)) for c, i in mapping[0].items() if c != victim)
+    i_c = dict((i, c) for c, i in c_i.items())
+    o = OracleRater(util.to_model(wd2), (c_i, i_c), 8, logger=quiet)
+    text = ''.join(sorted(mapping[0], key=mapping[0].get)[:20]) * 3        # contains the victim: now unmapped (index 0)
+    assert_logp_close(r.rate(text, [5]), o.rate(text, [5]))
+    # removal by index
+    assert r.remove_from_mapping(idx=1) is True
+    assert r.voc_size == voc0 - 2
