@@ -209,6 +209,7 @@ class Rater(object):
         self._lut_src = None
         self._pending_weights = None
         self._pin = None
+        self._worker = None
         self.native_beam = True            # rate_best: run whole lattice edges through klm_beam_edge where possible
         self.device_steps = 0              # klm_step calls / hypotheses advanced so far (bench.py: beam steps/sec)
         self.hypothesis_steps = 0
@@ -396,9 +397,9 @@ class Rater(object):
                 lut[ord(c)] = i
                 known[ord(c)] = True
             self._lut, self._known, self._lut_src = lut, known, self.mapping[0]
-        cps = np.frombuffer(text.encode('utf-32-le', 'surrogatepass'), dtype='<u4').astype(np.int64)
-        cps = np.minimum(cps, len(self._lut) - 1)
-        return self._lut[cps], self._known[cps]
+        cps = np.frombuffer(text.encode('utf-32-le', 'surrogatepass'), dtype='<u4')
+        idx = self._lut[np.minimum(cps, np.uint32(len(self._lut) - 1))]
+        return idx, idx != 0                    # index 0 is never given to a mapped character
 
     def _context_row(self, context):
         if not context:
@@ -492,42 +493,97 @@ class Rater(object):
         norm = [unicodedata.normalize('NFC', t) for t in texts]
         lens = np.array([max(len(t) - 1, 0) for t in norm], dtype=np.int64)
         order = np.argsort(-lens, kind='stable')            # longest first: batches of similar length
-        offsets = np.zeros(n + 1, dtype=np.int64)
-        offsets[1:] = np.cumsum(lens[order])
-        total = int(offsets[-1])
-        chars, targets, logp = self._pinned(total)
-        for j, i in enumerate(order):
-            if lens[i] == 0:
-                continue
-            idx, known = self._indices(norm[i])
-            for t in np.flatnonzero(~known):
-                self.logger.error('unmapped character "%s" at input position %d', norm[i][t], int(t))
-            chars[offsets[j]:offsets[j + 1]] = idx[:-1]
-            targets[offsets[j]:offsets[j + 1]] = idx[1:]
-        if total:
-            slots = self._pool.acquire(n)
-            try:
-                self._native.state_reset(slots)
-                self._native.rate(slots, offsets, chars, targets, None, [rows[i] for i in order], logp)
-            finally:
-                for s in slots:
-                    self._pool.release(s)
-        out = [None] * n
-        for j, i in enumerate(order):
-            seg = logp[offsets[j]:offsets[j + 1]]
-            if return_logp:
-                out[i] = np.concatenate([np.zeros(min(len(norm[i]), 1), np.float32), seg])
+        total = int(lens.sum())
+        out = [np.empty(len(t), dtype=np.float32) for t in norm]
+        for o in out:
+            o[:1] = 0.0 if return_logp else 1.0
+        if total == 0:
+            return out
+        # The positions are cut into segments along time (every stream contributes its share to each segment,
+        # the state is carried in the pool slots), and a worker thread drives the device: while segment k runs,
+        # the host maps the characters of segment k+1 and converts the scores of segment k-1.
+        nseg = int(min(self.MAX_SEGMENTS, max(1, total // self.MIN_SEGMENT_POSITIONS)))
+        bounds = [(lens[order] * k) // nseg for k in range(nseg + 1)]          # [nseg+1][n] position boundaries
+        seg_tot = [int((bounds[k + 1] - bounds[k]).sum()) for k in range(nseg)]
+        bufs = self._pinned(max(seg_tot), 2 if nseg > 1 else 1)
+        ctx_rows = [rows[i] for i in order]
+        slots = self._pool.acquire(n)
+
+        def prepare(k):
+            chars, targets, logp = (a[:seg_tot[k]] for a in bufs[k % len(bufs)])
+            offsets = np.zeros(n + 1, dtype=np.int64)
+            offsets[1:] = np.cumsum(bounds[k + 1] - bounds[k])
+            for j, i in enumerate(order):
+                lo, hi = int(bounds[k][j]), int(bounds[k + 1][j])
+                if hi == lo:
+                    continue
+                idx, known = self._indices(norm[i][lo:hi + 1])
+                if k > 0:
+                    known = known[1:]               # the segment's first character was reported with the previous one
+                    base = lo + 1
+                else:
+                    base = lo
+                for t in np.flatnonzero(~known):
+                    self.logger.error('unmapped character "%s" at input position %d', norm[i][base + int(t)], base + int(t))
+                chars[offsets[j]:offsets[j + 1]] = idx[:-1]
+                targets[offsets[j]:offsets[j + 1]] = idx[1:]
+            return offsets, chars, targets, logp
+
+        def finish(k, offsets, logp):
+            for j, i in enumerate(order):
+                lo, hi = int(bounds[k][j]), int(bounds[k + 1][j])
+                if hi > lo:
+                    seg = logp[offsets[j]:offsets[j + 1]]
+                    if return_logp:
+                        out[i][1 + lo:1 + hi] = seg
+                    else:
+                        np.exp(seg, out=out[i][1 + lo:1 + hi])
+
+        try:
+            self._native.state_reset(slots)
+            if nseg == 1:
+                offsets, chars, targets, logp = prepare(0)
+                self._native.rate(slots, offsets, chars, targets, None, ctx_rows, logp)
+                finish(0, offsets, logp)
             else:
-                out[i] = np.concatenate([np.ones(min(len(norm[i]), 1), np.float32), np.exp(seg)])
+                if self._worker is None:
+                    from concurrent.futures import ThreadPoolExecutor
+                    self._worker = ThreadPoolExecutor(max_workers=1, thread_name_prefix='klm-rate')
+                pending = None                      # (future, k, offsets, logp) of the segment on the device
+                try:
+                    for k in range(nseg):
+                        offsets, chars, targets, logp = prepare(k)
+                        if pending is not None:
+                            pending[0].result()
+                        fut = self._worker.submit(self._native.rate, slots, offsets, chars, targets, None, ctx_rows, logp)
+                        if pending is not None:
+                            finish(*pending[1:])
+                        pending = (fut, k, offsets, logp)
+                    pending[0].result()
+                    finish(*pending[1:])
+                    pending = None
+                finally:
+                    if pending is not None:         # an exception above: never leave the device call running
+                        try:
+                            pending[0].result()
+                        except Exception:           # pylint: disable=broad-except
+                            pass
+        finally:
+            for sl in slots:
+                self._pool.release(sl)
         return out
 
-    def _pinned(self, total):
-        """Page-locked index/score buffers for a batch of `total` positions (grow-only, reused)."""
-        if self._pin is None or len(self._pin[0]) < total:
+    MAX_SEGMENTS = 16                     # rate_many: segments along time for host/device overlap ...
+    MIN_SEGMENT_POSITIONS = 250000        # ... each at least this many positions (a launch costs ~50 us)
+
+    def _pinned(self, total, sets=1):
+        """`sets` groups of page-locked (chars, targets, scores) buffers for `total` positions each
+        (grow-only, reused)."""
+        if self._pin is None or len(self._pin) < sets or len(self._pin[0][0]) < total:
             cap = total + total // 8 + 1024
-            self._pin = (_native.pinned_empty(cap, np.int32), _native.pinned_empty(cap, np.int32),
-                         _native.pinned_empty(cap, np.float32))
-        return tuple(a[:total] for a in self._pin)
+            self._pin = [(_native.pinned_empty(cap, np.int32), _native.pinned_empty(cap, np.int32),
+                          _native.pinned_empty(cap, np.float32)) for _ in range(sets)]
+        return self._pin[:sets]
 
     def test(self, test_data):
         """Perplexity over text files (reference :462-491, :977-1002).
