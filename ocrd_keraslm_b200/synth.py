@@ -148,3 +148,58 @@ def lattice(seed, n_words=200, n_alts=5, mapping_arr=None, words_per_line=10, mi
         g.add_edge(node, node + 1, element=None, alternatives=[Alt(sep, 1.0, 0)])
         node += 1
     return g, 0, node
+
+
+def page_xml(seed, page_id='p0001', n_regions=2, lines_per_region=3, words_per_line=5, n_alts=5, glyphs=False,
+             mapping_arr=None, min_len=2, max_len=7):
+    """Synthetic PAGE-XML (2019 namespace) with OCR alternatives, the input shape of wrapper/rate.py:343-424.
+
+    Words carry `n_alts` TextEquiv alternatives (@index, @conf = 0.90, 0.88, ... : the first four survive the
+    reference's choice filter, the drop stays below 0.1); with `glyphs`, every character of the first alternative
+    is also a Glyph with two alternatives.  Lines and regions carry a (stale) single TextEquiv.
+    """
+    from xml.sax.saxutils import escape
+    mapping_arr = vocabulary() if mapping_arr is None else mapping_arr
+    rng = np.random.default_rng(seed)
+    letters = [chr(int(c)) for c in mapping_arr[1:] if c not in (0x0A, 0x20)]
+    p = 1.0 / (np.arange(len(letters)) + 5.0)
+    p /= p.sum()
+    ns = 'http://schema.primaresearch.org/PAGE/gts/pagecontent/2019-07-15'
+    out = ['<?xml version="1.0" encoding="UTF-8"?>',
+           '<PcGts xmlns="%s" pcGtsId="%s">' % (ns, page_id),
+           '<Metadata><Creator>synth</Creator><Created>2026-01-01T00:00:00</Created>'
+           '<LastChange>2026-01-01T00:00:00</LastChange></Metadata>',
+           '<Page imageFilename="%s.png" imageWidth="1000" imageHeight="1000">' % page_id]
+
+    def te(text, conf, index=None):
+        return '<TextEquiv%s conf="%.2f"><Unicode>%s</Unicode></TextEquiv>' % (
+            ' index="%d"' % index if index is not None else '', conf, escape(text))
+    coords = '<Coords points="0,0 10,0 10,10 0,10"/>'
+    for r in range(n_regions):
+        out.append('<TextRegion id="r%d">%s' % (r, coords))
+        for l in range(lines_per_region):
+            out.append('<TextLine id="r%d_l%d">%s' % (r, l, coords))
+            for w in range(words_per_line):
+                n = int(rng.integers(min_len, max_len + 1))
+                base = ''.join(rng.choice(letters, size=n, p=p))
+                wid = 'r%d_l%d_w%d' % (r, l, w)
+                out.append('<Word id="%s">%s' % (wid, coords))
+                if glyphs:
+                    for g, ch in enumerate(base):
+                        other = letters[int(rng.integers(0, len(letters)))]
+                        out.append('<Glyph id="%s_g%d">%s%s%s</Glyph>' % (wid, g, coords, te(ch, 0.95, 0),
+                                                                           te(other, 0.90, 1)))
+                for a in range(n_alts):
+                    if a == 0:
+                        alt = base
+                    else:
+                        pos = int(rng.integers(0, n))
+                        alt = base[:pos] + letters[int(rng.integers(0, len(letters)))] + base[pos + 1:]
+                    out.append(te(alt, 0.90 - 0.02 * a, a))
+                out.append('</Word>')
+            out.append(te('stale line text', 0.5))
+            out.append('</TextLine>')
+        out.append(te('stale region text', 0.5))
+        out.append('</TextRegion>')
+    out.append('</Page></PcGts>')
+    return '\n'.join(out)
