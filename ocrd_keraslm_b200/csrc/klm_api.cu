@@ -85,6 +85,12 @@ struct klm_model {
     // scratch
     float *hbuf = nullptr, *logits = nullptr;
     unsigned int *barrier = nullptr;
+    // barrier-free K-parallel kernel (klm_seq_fma_ll): rings of {value, tick} words, per-CTA progress, watchdog
+    uint2 *hbuf_ll = nullptr, *logits_ll = nullptr;
+    unsigned int *progress = nullptr;
+    int *ll_err = nullptr;
+    size_t hbuf_ll_bytes = 0, logits_ll_bytes = 0;
+    int ll_launches = 0;
     int bp_cap = 0;
     // state pool
     float *state = nullptr;
@@ -184,7 +190,10 @@ static int make_plan(klm_model *m, bool kpar, KlmPlan *pl) {
     int n_target = avail;
     if (kpar) {
         const int by_smem = (int)((total_bytes + budget - 1) / budget) + (int)segs.size();
-        const int by_warp = (total_items + KLM_WARPS - 1) / KLM_WARPS;
+        // latency path: at most one unit per warp in every stage where the SMs allow it (a second unit per warp doubles
+        // the time a CTA spends between reading h and publishing its slice)
+        int by_warp = 0;
+        for (auto &sg : segs) by_warp += (sg.items + KLM_WARPS - 1) / KLM_WARPS;
         n_target = std::min(avail, std::max(std::max(by_smem, by_warp), (int)segs.size()));
     }
     for (;;) {
@@ -194,7 +203,9 @@ static int make_plan(klm_model *m, bool kpar, KlmPlan *pl) {
             int best = -1; double load = -1;
             for (int i = 0; i < (int)segs.size(); ++i) {
                 if (segs[i].n >= segs[i].items) continue;
-                const double ld = std::ceil((double)segs[i].items / segs[i].n) * segs[i].K;
+                double ld = std::ceil((double)segs[i].items / segs[i].n) * segs[i].K;
+                if (kpar)                                    // rounds of KLM_WARPS units first, then the contraction length
+                    ld = std::ceil(std::ceil((double)segs[i].items / segs[i].n) / KLM_WARPS) * 1e9 + segs[i].K;
                 if (ld > load) { load = ld; best = i; }
             }
             if (best < 0) break;
@@ -545,6 +556,7 @@ extern "C" int klm_destroy(klm_model *m) {
     cudaFree(m->tc2.d_roles); cudaFree(m->tc2.d_wimg); cudaFree(m->tc2.hx); cudaFree(m->tc2.Z); cudaFree(m->tc2.logits);
     cudaFree(m->tc2.err); cudaFree(m->tc2.trace);
     cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
+    cudaFree(m->hbuf_ll); cudaFree(m->logits_ll); cudaFree(m->progress); cudaFree(m->ll_err);
     for (int i = 0; i < KLM_RING; ++i) {
         if (m->h_ring[i]) cudaFreeHost(m->h_ring[i]);
         cudaFree(m->d_ring[i]);
@@ -660,6 +672,15 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
     TRYC(cudaMemset(m->hbuf, 0, (size_t)D * 2 * W * m->bp_cap * 4));
     TRYC(cudaMalloc(&m->logits, (size_t)2 * m->V4 * m->bp_cap * 4));
     TRYC(cudaMemset(m->logits, 0, (size_t)2 * m->V4 * m->bp_cap * 4));
+    if (!getenv("KLM_DISABLE_LL")) {
+        m->hbuf_ll_bytes = (size_t)KLM_LL_RING * D * W * KLM_MODEK_MAXB * sizeof(uint2);
+        m->logits_ll_bytes = (size_t)KLM_LL_RING * 4 * m->V4 * KLM_MODEK_MAXB * sizeof(uint2);
+        TRYC(cudaMalloc(&m->hbuf_ll, m->hbuf_ll_bytes));
+        TRYC(cudaMalloc(&m->logits_ll, m->logits_ll_bytes));
+        TRYC(cudaMalloc(&m->progress, 1024 * sizeof(unsigned int)));
+        TRYC(cudaMalloc(&m->ll_err, 256));
+        TRYC(cudaMemset(m->ll_err, 0, 256));
+    }
     TRYC(cudaMalloc(&m->barrier, 256));
     m->ring_bytes = (size_t)m->bp_cap * (4 * 4 + 8 + 4 * KLM_MAX_CTX) + 64;
     m->ring_bytes = std::max(m->ring_bytes, (size_t)1 << 16);
@@ -891,6 +912,16 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     p.chars = d_chars; p.targets = d_targets; p.n_real = d_nr; p.ctx = d_cx;
     p.out = d_out; p.full_rows = full_rows;
     p.hbuf = m->hbuf; p.logits = m->logits; p.barrier = m->barrier;
+    if (nb <= KLM_MODEK_MAXB && m->hbuf_ll && pl.grid <= 1024) {
+        // exchange rings: no word of an earlier launch may look like one of this launch
+        p.hbuf_ll = m->hbuf_ll; p.logits_ll = m->logits_ll; p.progress = m->progress; p.err = m->ll_err;
+        const size_t used_slots = (size_t)std::min<long long>(KLM_LL_RING, tmax + m->D + 2);   // short launches touch few slots
+        CK(cudaMemsetAsync(m->hbuf_ll, 0xFF, m->hbuf_ll_bytes / KLM_LL_RING * used_slots, m->stream));
+        CK(cudaMemsetAsync(m->logits_ll, 0xFF, m->logits_ll_bytes / KLM_LL_RING * used_slots, m->stream));
+        CK(cudaMemsetAsync(m->progress, 0, 1024 * sizeof(unsigned int), m->stream));
+        m->ll_launches++;
+        p.debug = getenv("KLM_LL_DEBUG") ? atoi(getenv("KLM_LL_DEBUG")) : 0;
+    }
     p.roles = pl.d_roles; p.wsmem = pl.wsmem; p.stage_floats = pl.stage_floats;
     CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
     CK(klm_launch_seq_fma(p, pl.grid, pl.smem, m->stream));
@@ -907,6 +938,11 @@ static int batch_max(klm_model *m, int n) {
 
 // Device-side watchdog of the tensor-core kernel: a wait that timed out leaves a code in tc.err.
 static int check_device_error(klm_model *m) {
+    if (m->ll_launches > 0) {
+        int code = 0;
+        CK(cudaMemcpy(&code, m->ll_err, sizeof code, cudaMemcpyDeviceToHost));
+        if (code != 0) return fail(KLM_ECUDA, "klm_seq_fma_ll: device-side wait timed out (code %d)", code);
+    }
     if (!m->tc.ok || m->tc_launches == 0) return KLM_OK;
     int code = 0;
     CK(cudaMemcpy(&code, m->tc.err, sizeof code, cudaMemcpyDeviceToHost));

@@ -26,6 +26,7 @@
 #define KLM_MAX_ITEMS    8      // (unit, 32-stream group) items per warp in the stream-parallel mode
 #define KLM_MAX_UNITS_K  4      // units per warp in the K-parallel mode
 #define KLM_MODEK_MAXB   8      // K-parallel mode takes up to this many streams
+#define KLM_LL_RING      32     // ticks of exchange words kept by the barrier-free K-parallel kernel
 
 #define KLM_ROLE_LSTM 0
 #define KLM_ROLE_PROJ 1
@@ -64,6 +65,12 @@ struct KlmSeqParams {
     const KlmRole *roles;         // [grid]
     int wsmem;                    // weights slice cached in shared memory
     int stage_floats;             // floats of staging area
+    // barrier-free K-parallel kernel (klm_seq_fma_ll): exchanged values as {value, tick} words in rings of KLM_LL_RING ticks
+    uint2 *hbuf_ll;               // [KLM_LL_RING][D][W][KLM_MODEK_MAXB]; NULL = use the barrier kernels
+    uint2 *logits_ll;             // [KLM_LL_RING][4*V4][KLM_MODEK_MAXB]
+    unsigned int *progress;       // [grid] ticks completed per CTA (zeroed before launch)
+    int *err;                     // device-side watchdog
+    int debug;                    // KLM_LL_DEBUG: every CTA prints its mean clocks per tick spent waiting / computing
 };
 
 // ---------------------------------------------------------------------------------------------
