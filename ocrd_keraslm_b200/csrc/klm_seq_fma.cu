@@ -381,13 +381,17 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_kpar(const KlmSeqP
 // The words live in a ring of KLM_LL_RING ticks; every KLM_LL_RING/2 ticks a CTA checks (one coalesced read of
 // per-CTA progress words, almost never a wait) that nobody is more than half a ring behind before slots are reused.
 // The ring is filled with 0xFF by the host before each launch, so stale words never match.
+#ifndef KLM_LL_WEAK_STORE
+#define KLM_LL_WEAK_STORE 1
+#endif
 __device__ __forceinline__ uint2 ld_volatile_u2(const uint2 *p) {
     uint2 v;
     asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void st_volatile_u2(uint2 *p, unsigned x, unsigned y) {
-    asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(x), "r"(y) : "memory");
+    if (KLM_LL_WEAK_STORE) asm volatile("st.global.cg.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(x), "r"(y) : "memory");
+    else asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(x), "r"(y) : "memory");
 }
 // value of a word once it carries `tick`; gives up (and flags the launch) after ~2^22 polls
 __device__ __forceinline__ float ll_wait(const uint2 *p, unsigned tick, int *err) {
@@ -410,9 +414,10 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
     const int l = role.layer;
     const bool is_lstm = role.kind == KLM_ROLE_LSTM, is_proj = role.kind == KLM_ROLE_PROJ;
     const int K = (is_lstm && l > 0) ? 2 * W : W;
-    constexpr int R = KLM_LL_RING, BS = KLM_MODEK_MAXB;      // ring slots, stream stride of a word row
-    uint2 *hx = p.hbuf_ll;                                   // [R][D][W][BS]
-    uint2 *lgx = p.logits_ll;                                // [R][4*V4][BS]
+    constexpr int R = KLM_LL_RING;                           // ring slots
+    const int BS = B;                                        // words of one unit: one per stream, contiguous (a warp poll = 256 bytes)
+    uint2 *hx = p.hbuf_ll;                                   // [R][D][W][B]
+    uint2 *lgx = p.logits_ll;                                // [R][4*V4][B]
 
     const float4 *wptr = nullptr;
     float *stage = reinterpret_cast<float *>(smem4);
@@ -426,6 +431,7 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
         }
     }
 
+    __shared__ float outbuf[KLM_WARPS * KLM_MAX_UNITS_K * 4 * KLM_MODEK_MAXB];      // this tick's results before they leave
     float c_reg[KLM_MAX_UNITS_K], h_reg[KLM_MAX_UNITS_K];
     long long o0 = 0;
     int len = 0;
@@ -474,10 +480,11 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
         }
     }
     const int nticks = p.T_max + D + 1;
-    long long dbg_wait = 0, dbg_work = 0, dbg_t0 = 0;
+    long long dbg_wait = 0, dbg_work = 0, dbg_t0 = 0, dbg_ph[6] = {0, 0, 0, 0, 0, 0}, dbg_t1 = 0;
+#define LL_DBG(i) if (p.debug > 1) { const long long now_ = clock64(); dbg_ph[i] += now_ - dbg_t1; dbg_t1 = now_; }
     for (int tick = 0; tick < nticks; ++tick) {
         const int slot = tick % R, nslot = (tick + 1) % R;
-        if (p.debug) dbg_t0 = clock64();
+        if (p.debug) dbg_t0 = dbg_t1 = clock64();
         if ((tick % (R / 2)) == 0 && tick > 0) {
             // nobody may be more than half a ring behind before the slots written below are reused
             if (warp == 0) {
@@ -503,12 +510,11 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
                     const int ui = warp + j * KLM_WARPS;
                     if (ui < role.count) {
                         const int u = role.first + ui;
-                        pre[j] = __ldg(p.P + (size_t)x * W + u);
-                        if (tick < nreal) add4(pre[j], qsum[j]);
-                        else for (int k = 0; k < p.Nc; ++k) add4(pre[j], __ldg(p.Q[k] + u));   // padding: context 0
+                        pre[j] = __ldg(p.P + (size_t)x * W + u);      // (consumed only in the cell: no stall here)
                     }
                 }
             }
+            LL_DBG(0)                                          // progress check + gather issue
             // ---- stage the input vector(s): stage[b][K] <- words of this tick ----
             const int nsrc = (is_lstm && l > 0) ? 2 : 1;
             for (int src = 0; src < nsrc; ++src) {
@@ -520,8 +526,10 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
                     stage[b * K + src * W + k] = ll_wait(hsrc + (size_t)k * BS + b, (unsigned)tick, p.err);
                 }
             }
+            LL_DBG(1)                                          // own polls
             __syncthreads();
-            if (threadIdx.x == 0) *(volatile unsigned *)(p.progress + blockIdx.x) = (unsigned)(tick + 1);
+            LL_DBG(2)                                          // everybody's polls
+            if (threadIdx.x == 0) __stcg(p.progress + blockIdx.x, (unsigned)(tick + 1));
             if (p.debug) { const long long now = clock64(); dbg_wait += now - dbg_t0; dbg_t0 = now; }
 #pragma unroll
             for (int j = 0; j < KLM_MAX_UNITS_K; ++j) {
@@ -555,27 +563,39 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
                                     gz = __shfl_sync(0xffffffffu, v, 16), gw = __shfl_sync(0xffffffffu, v, 24);
                         if (lane == bb) mine = make_float4(gx, gy, gz, gw);
                     }
+                    LL_DBG(3)                                  // contraction + reduction
                     if (lane < B) {
                         const int u = role.first + ui, b = lane;
                         if (is_lstm) {
                             const int t = tick - l;
                             if (t >= 0 && t < len) {
                                 add4(mine, pre[j]);
+                                if (l == 0) {
+                                    if (t < nreal) add4(mine, qsum[j]);
+                                    else for (int k = 0; k < p.Nc; ++k) add4(mine, __ldg(p.Q[k] + u));   // padding: context 0
+                                }
                                 lstm_cell_fast(mine, c_reg[j], h_reg[j]);
                             }
-                            st_volatile_u2(hx + ((size_t)(nslot * D + l) * W + u) * BS + b, __float_as_uint(h_reg[j]),
-                                           (unsigned)(tick + 1));
+                            outbuf[ui * B + b] = h_reg[j];
                         } else {
-                            uint2 *lg = lgx + ((size_t)nslot * 4 * p.V4 + 4 * u) * BS + b;
-                            st_volatile_u2(lg, __float_as_uint(mine.x), (unsigned)(tick + 1));
-                            st_volatile_u2(lg + BS, __float_as_uint(mine.y), (unsigned)(tick + 1));
-                            st_volatile_u2(lg + 2 * BS, __float_as_uint(mine.z), (unsigned)(tick + 1));
-                            st_volatile_u2(lg + 3 * BS, __float_as_uint(mine.w), (unsigned)(tick + 1));
+                            outbuf[(4 * ui) * B + b] = mine.x; outbuf[(4 * ui + 1) * B + b] = mine.y;
+                            outbuf[(4 * ui + 2) * B + b] = mine.z; outbuf[(4 * ui + 3) * B + b] = mine.w;
                         }
                     }
                 }
             }
+            LL_DBG(4)                                          // cell
             __syncthreads();                                 // stage[] is rewritten by the next tick
+            {
+                // the CTA's words leave as ONE contiguous, coalesced run (whole sectors): single-lane 8-byte stores
+                // scattered over the warps were measured to reach the pollers thousands of clocks later
+                const int nw = (is_lstm ? role.count : 4 * role.count) * B;
+                uint2 *dst = is_lstm ? hx + ((size_t)(nslot * D + l) * W + role.first) * B
+                                     : lgx + ((size_t)nslot * 4 * p.V4 + 4 * role.first) * B;
+                for (int i = threadIdx.x; i < nw; i += KLM_THREADS)
+                    st_volatile_u2(dst + i, __float_as_uint(outbuf[i]), (unsigned)(tick + 1));
+            }
+            LL_DBG(5)                                          // barrier + publication
             if (p.debug) dbg_work += clock64() - dbg_t0;
         } else if (role.kind == KLM_ROLE_LSE) {
             // ---- log-sum-exp + target pick: one warp per stream, lanes over the vocabulary; ONE pass over the
@@ -613,6 +633,7 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
                             sum = acc; m = mx;
                         }
                     }
+                    if (p.debug && b == 0) { const long long now = clock64(); dbg_wait += now - dbg_t0; dbg_t0 = now; }
                     float mw = m;
                     for (int s = 16; s > 0; s >>= 1) mw = fmaxf(mw, __shfl_xor_sync(0xffffffffu, mw, s));
                     sum = (m > -INFINITY) ? sum * __expf(m - mw) : 0.f;
@@ -631,12 +652,17 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
                 }
             }
             __syncthreads();
-            if (threadIdx.x == 0) *(volatile unsigned *)(p.progress + blockIdx.x) = (unsigned)(tick + 1);
+            if (threadIdx.x == 0) __stcg(p.progress + blockIdx.x, (unsigned)(tick + 1));
+            if (p.debug) dbg_work += clock64() - dbg_t0;
         } else {
-            if (threadIdx.x == 0) *(volatile unsigned *)(p.progress + blockIdx.x) = (unsigned)(tick + 1);
+            if (threadIdx.x == 0) __stcg(p.progress + blockIdx.x, (unsigned)(tick + 1));
         }
     }
 
+    if (p.debug > 1 && (threadIdx.x == 0 || threadIdx.x == 256) && (is_lstm || is_proj))
+        printf("klm_seq_fma_ll cta %d kind %d layer %d thread %d: check+gather %lld, own polls %lld, all polls %lld, contraction %lld, cell %lld, "
+               "sync+publish %lld clk per tick\n", blockIdx.x, role.kind, role.layer, threadIdx.x, dbg_ph[0] / nticks, dbg_ph[1] / nticks,
+               dbg_ph[2] / nticks, dbg_ph[3] / nticks, dbg_ph[4] / nticks, dbg_ph[5] / nticks);
     if (p.debug && threadIdx.x == 0)
         printf("klm_seq_fma_ll cta %d kind %d layer %d first %d count %d: wait %lld work %lld clk per tick\n", blockIdx.x, role.kind,
                role.layer, role.first, role.count, dbg_wait / nticks, dbg_work / nticks);
