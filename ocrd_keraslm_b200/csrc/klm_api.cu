@@ -884,6 +884,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         q.trace = tp.trace; q.trace_t0 = tp.trace_t0;
         q.trace_mode = getenv("KLM_TC_TRACE_MODE") ? atoi(getenv("KLM_TC_TRACE_MODE")) : 0;
         q.debug_skip = getenv("KLM_TC_DEBUG_SKIP") ? atoi(getenv("KLM_TC_DEBUG_SKIP")) : 0;
+        q.poll_mode = getenv("KLM_TC_POLL") ? atoi(getenv("KLM_TC_POLL")) : 0;
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         q.kc = tp.kc; q.ring_bytes = tp.ring_bytes;
         if (&tp == &m->tc2) CK(klm_launch_seq_tc2(q, tp.grid, tp.smem, m->stream));

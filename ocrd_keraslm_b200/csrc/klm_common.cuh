@@ -145,6 +145,7 @@ struct KlmTcParams {
     int *err;                     // device-side watchdog: non-zero = a wait timed out (code says which)
     unsigned long long *trace;    // optional [grid][KLM_TC_TRACE_TICKS][8] SM-clock timeline (klm_tc_trace)
     int trace_t0;
+    int poll_mode;                // grid barrier: 0 = ld.acquire per poll, 1 = relaxed polls + one acquire fence, 2 = relaxed, no fence (experiment)
     int debug_skip;               // timing experiments only (results are wrong): bit 0 = no MMAs, bit 1 = no operand copies
     int trace_mode;               // 0: phase events; 1: arrival of chunk c in event slot c; 2: issue of the copy of chunk c
 };

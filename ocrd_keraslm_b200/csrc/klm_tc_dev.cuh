@@ -13,10 +13,23 @@ __device__ __forceinline__ bool tc_spin_fail(unsigned &n, const KlmTcParams &p, 
     }
     return false;
 }
+// Measured alternatives to the acquire load per poll (KLM_TC_POLL): relaxed polls + one fence.acq_rel.gpu after the
+// successful poll are 8 % SLOWER on cfg2 (the fence costs more than it saves), relaxed polls without any fence are
+// no faster -- the acquire is not what the barrier costs.
 __device__ __forceinline__ bool tc_wait_grid(const KlmTcParams &p, unsigned target, int code) {
     unsigned n = 0;
-    while (tc::ld_acquire(p.barrier) < target)
+    if (p.poll_mode == 0) {
+        while (tc::ld_acquire(p.barrier) < target)
+            if (tc_spin_fail(n, p, code)) return false;
+        return true;
+    }
+    for (;;) {
+        unsigned v;
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p.barrier) : "memory");
+        if (v >= target) break;
         if (tc_spin_fail(n, p, code)) return false;
+    }
+    if (p.poll_mode == 1) asm volatile("fence.acq_rel.gpu;" ::: "memory");
     return true;
 }
 __device__ __forceinline__ bool tc_wait_mbar(uint32_t bar, uint32_t parity, const KlmTcParams &p, int code) {
