@@ -91,6 +91,10 @@ struct klm_model {
     int *ll_err = nullptr;
     size_t hbuf_ll_bytes = 0, logits_ll_bytes = 0;
     int ll_launches = 0;
+    // klm_step with host arrays: page-locked staging (a copy from/to pageable memory blocks in the driver for ~10 us)
+    char *h_step = nullptr;
+    size_t h_step_bytes = 0;
+    int *h_err = nullptr;              // page-locked copies of the device-side watchdog words, fetched with the results
     int bp_cap = 0;
     // state pool
     float *state = nullptr;
@@ -557,6 +561,8 @@ extern "C" int klm_destroy(klm_model *m) {
     cudaFree(m->tc2.err); cudaFree(m->tc2.trace);
     cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
     cudaFree(m->hbuf_ll); cudaFree(m->logits_ll); cudaFree(m->progress); cudaFree(m->ll_err);
+    if (m->h_step) cudaFreeHost(m->h_step);
+    if (m->h_err) cudaFreeHost(m->h_err);
     for (int i = 0; i < KLM_RING; ++i) {
         if (m->h_ring[i]) cudaFreeHost(m->h_ring[i]);
         cudaFree(m->d_ring[i]);
@@ -938,6 +944,24 @@ static int batch_max(klm_model *m, int n) {
 }
 
 // Device-side watchdog of the tensor-core kernel: a wait that timed out leaves a code in tc.err.
+// Error words copied asynchronously in front of a stream synchronisation the caller does anyway.
+static int fetch_errors_async(klm_model *m) {
+    if (!m->h_err) { CK(cudaHostAlloc(&m->h_err, 64, cudaHostAllocDefault)); }
+    m->h_err[0] = m->h_err[1] = m->h_err[2] = 0;
+    if (m->ll_launches > 0) CK(cudaMemcpyAsync(&m->h_err[0], m->ll_err, 4, cudaMemcpyDeviceToHost, m->stream));
+    if (m->tc.ok && m->tc_launches > 0) {
+        CK(cudaMemcpyAsync(&m->h_err[1], m->tc.err, 4, cudaMemcpyDeviceToHost, m->stream));
+        if (m->tc2.ok) CK(cudaMemcpyAsync(&m->h_err[2], m->tc2.err, 4, cudaMemcpyDeviceToHost, m->stream));
+    }
+    return KLM_OK;
+}
+static int check_fetched_errors(klm_model *m) {
+    if (m->h_err[0]) return fail(KLM_ECUDA, "klm_seq_fma_ll: device-side wait timed out (code %d)", m->h_err[0]);
+    if (m->h_err[1] || m->h_err[2])
+        return fail(KLM_ECUDA, "klm_seq_tc: device-side wait timed out (code %d)", m->h_err[1] ? m->h_err[1] : m->h_err[2]);
+    return KLM_OK;
+}
+
 static int check_device_error(klm_model *m) {
     if (m->ll_launches > 0) {
         int code = 0;
@@ -1034,9 +1058,25 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
     const int full = targets ? 0 : 1;
     const size_t nout = full ? (size_t)n * m->V : (size_t)n;
     rc = ensure_pos_cap(m, (size_t)n, mem == KLM_MEM_HOST ? nout : 0); if (rc) return rc;
-    // chars/targets are per-hypothesis host arrays: they ride along as position arrays of length n
-    CK(cudaMemcpyAsync(m->d_chars, chars, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
-    if (targets) CK(cudaMemcpyAsync(m->d_targets, targets, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    // chars/targets are per-hypothesis host arrays: they ride along as position arrays of length n,
+    // through page-locked staging
+    const size_t stage_need = (size_t)n * 8 + nout * 4 + 64;
+    if (mem == KLM_MEM_HOST && stage_need > m->h_step_bytes) {
+        CK(cudaStreamSynchronize(m->stream));
+        if (m->h_step) cudaFreeHost(m->h_step);
+        m->h_step = nullptr; m->h_step_bytes = 0;
+        CK(cudaHostAlloc(&m->h_step, stage_need * 2, cudaHostAllocDefault));
+        m->h_step_bytes = stage_need * 2;
+    }
+    const int32_t *src_chars = chars, *src_targets = targets;
+    if (mem == KLM_MEM_HOST) {
+        int32_t *hs = reinterpret_cast<int32_t *>(m->h_step);
+        memcpy(hs, chars, (size_t)n * 4);
+        if (targets) memcpy(hs + n, targets, (size_t)n * 4);
+        src_chars = hs; src_targets = hs + n;
+    }
+    CK(cudaMemcpyAsync(m->d_chars, src_chars, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    if (targets) CK(cudaMemcpyAsync(m->d_targets, src_targets, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
     float *dout = (mem == KLM_MEM_HOST) ? m->d_out : out;
     CK(cudaEventRecord(m->ev0, m->stream));
     const int bmax = batch_max(m, n);
@@ -1052,9 +1092,12 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
     CK(cudaEventRecord(m->ev1, m->stream));
     m->timed = true;
     if (mem == KLM_MEM_HOST) {
-        CK(cudaMemcpyAsync(out, m->d_out, nout * 4, cudaMemcpyDeviceToHost, m->stream));
+        float *hout = reinterpret_cast<float *>(m->h_step + (size_t)n * 8);
+        CK(cudaMemcpyAsync(hout, m->d_out, nout * 4, cudaMemcpyDeviceToHost, m->stream));
+        rc = fetch_errors_async(m); if (rc) return rc;
         CK(cudaStreamSynchronize(m->stream));
-        return check_device_error(m);
+        memcpy(out, hout, nout * 4);
+        return check_fetched_errors(m);
     }
     return KLM_OK;
 }

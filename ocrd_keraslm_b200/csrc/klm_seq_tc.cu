@@ -636,8 +636,15 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
 
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream) {
     void *args[] = { const_cast<KlmTcParams *>(&p) };
-    cudaError_t e = cudaFuncSetAttribute((const void *)klm_seq_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
+    // (the attribute is per device: set it once per device and size, not at every launch of a beam step)
+    static size_t smem_set[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || smem_set[dev] != smem) {
+        cudaError_t e = cudaFuncSetAttribute((const void *)klm_seq_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        if (dev >= 0 && dev < 64) smem_set[dev] = smem;
+    }
     return cudaLaunchCooperativeKernel((const void *)klm_seq_tc, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
 }
 
