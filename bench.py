@@ -541,12 +541,21 @@ def main():
     ap.add_argument('--no-cpu', action='store_true', help='skip the CPU baseline leg')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
-    if args.workload == 'cfg3':
-        run_beam(args)
-    elif args.impl == 'reference':
-        run_reference(args)
-    else:
-        run_ours(args)
+    # stdout carries exactly ONE JSON line: libraries that write to file descriptor 1 on their own (NCCL prints its
+    # version there when the process group comes up) are sent to stderr, the JSON goes to the original descriptor
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, 'w', buffering=1)
+    try:
+        if args.workload == 'cfg3':
+            run_beam(args)
+        elif args.impl == 'reference':
+            run_reference(args)
+        else:
+            run_ours(args)
+    finally:
+        sys.stdout.flush()
 
 
 if __name__ == '__main__':
