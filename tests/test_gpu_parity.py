@@ -208,6 +208,49 @@ def test_rate_many_matches_oracle(width, depth, n_docs):
         assert_logp_close(got[i], [p for _, p in ref])
 
 
+@pytest.mark.parametrize('width,depth,n_docs,nseg', [(64, 2, 5, 7), (128, 3, 40, 16), (512, 3, 64, 3)])
+def test_rate_many_in_time_segments_matches_one_launch_and_oracle(width, depth, n_docs, nseg):
+    """The pipelined form of rate_many (segments along time, state carried in the pool slots, worker thread) on
+    inputs small enough for the oracle: must equal the one-launch form bit for bit, and the oracle in tolerance.
+    Ragged lengths include streams that contribute nothing to some segments (length < number of segments)."""
+    wd = synth.weights(5 + width, width=width, depth=depth, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 32)
+    rng = np.random.default_rng(width * 3 + n_docs)
+    sizes = rng.integers(2, 50 if width < 512 else 20, n_docs)
+    sizes[0], sizes[1] = 1, 3
+    texts = [synth.text(2000 + i, int(s)) for i, s in enumerate(sizes)]
+    ctxs = [[int(rng.integers(0, 200))] for _ in texts]
+    one = r.rate_many(texts, ctxs, return_logp=True)
+    r.MAX_SEGMENTS, r.MIN_SEGMENT_POSITIONS = nseg, 1       # instance overrides: force nseg segments
+    seg = r.rate_many(texts, ctxs, return_logp=True)
+    for a, b in zip(one, seg):
+        np.testing.assert_array_equal(a, b)
+    o = oracle_for(wd, maparr, 32)
+    for i in (0, 1, 2, n_docs - 1):
+        ref, _ = o.rate2(texts[i], ctxs[i])
+        assert_logp_close(np.exp(seg[i]), [p for _, p in ref])
+
+
+@pytest.mark.parametrize('n_docs', [1, 2, 5, 8])
+def test_value_tick_exchange_kernel_over_many_ring_turns(n_docs):
+    """<= 8 streams run on the barrier-free {value, tick} exchange kernel: ragged lengths from 1 to several
+    hundred ticks (the exchange ring holds 32), against the oracle, twice in a row (ring words re-armed)."""
+    wd = synth.weights(91, width=128, depth=3, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 32)
+    o = oracle_for(wd, maparr, 32)
+    sizes = [700, 2, 33, 65, 310, 32, 129, 500][:n_docs]
+    texts = [synth.text(3000 + i, s) for i, s in enumerate(sizes)]
+    ctxs = [[i * 7] for i in range(n_docs)]
+    first = r.rate_many(texts, ctxs)
+    again = r.rate_many(texts, ctxs)
+    for i, (t, c) in enumerate(zip(texts, ctxs)):
+        np.testing.assert_array_equal(first[i], again[i])
+        ref, _ = o.rate2(t, c)
+        assert_logp_close(first[i], [p for _, p in ref])
+
+
 def test_states_after_rate_match_oracle():
     wd = synth.weights(3, width=128, depth=3, voc_size=256, style='trained')
     maparr = synth.vocabulary()
