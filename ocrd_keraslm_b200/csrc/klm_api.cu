@@ -65,6 +65,7 @@ struct KlmTcPlan {
     int *err = nullptr;
     int ingest_bulk = 0, kc = KLM_TC_KC, ring_bytes = 0;     // CTA-pair kernel
     int pub = 0, n_lse = 0, consumer_fence = 1;              // single-CTA kernel
+    int stream_b = 0;                                        // single-CTA kernel, streamed-weights form (klm_seq_tcs)
     unsigned long long *trace = nullptr;
     int trace_t0 = 0;
 };
@@ -292,23 +293,20 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
     struct Ty { int kind, layer, src, sigma, items, gran, n; double weight; const float *mat; };
     std::vector<Ty> tys;
     bool planned = false;
-    // attempts: (aligned REC slices, 16/32 KB chunks), (aligned, any chunk size), (single pairs, ...), (single pairs, any)
-    for (int attempt = (pub_mode ? 0 : 2); attempt < 4 && !planned; ++attempt) {
-        const int gran = attempt < 2 ? 4 : 1;                // pairs per indivisible REC item
-        g_last = (attempt & 1) ? 6 : 3;
-        pmax = 0;
-        for (int np = 1; np <= KLM_TC1_MAX_PAIRS; ++np) if (geom_for(np) >= 0) pmax = np;
-        if (getenv("KLM_TC_PMAX")) pmax = std::min(pmax, atoi(getenv("KLM_TC_PMAX")));
-        if (gran > pmax) continue;
+    // distributes the slices of every stage over the SMs: REC items of gran_rec pairs, IN / PROJ items of gran_oth pairs,
+    // at most pmax_ pairs per CTA; refines the stage with the largest weighted slice while SMs are left
+    auto plan_with = [&](int gran_rec, int gran_oth, int pmax_) -> bool {
+        if (gran_rec > pmax_ || gran_oth > pmax_ || (W / 2) % gran_rec != 0 || (W / 2) % gran_oth != 0 || (pl.Vp / 8) % gran_oth != 0)
+            return false;
         tys.clear();
         for (int l = 0; l < D; ++l) {
-            if (l > 0) tys.push_back({KLM_TC_IN, l, l - 1, 2 * l - 1, W / 2, 1, 0, 1.0, L[3 * l]});
-            tys.push_back({KLM_TC_REC, l, l, 2 * l, W / 2 / gran, gran, 0, 1.5, L[3 * l + 1]});
+            if (l > 0) tys.push_back({KLM_TC_IN, l, l - 1, 2 * l - 1, W / 2 / gran_oth, gran_oth, 0, 1.0, L[3 * l]});
+            tys.push_back({KLM_TC_REC, l, l, 2 * l, W / 2 / gran_rec, gran_rec, 0, 1.5, L[3 * l + 1]});
         }
-        tys.push_back({KLM_TC_PROJ, 0, D - 1, 2 * D - 1, pl.Vp / 8, 1, 0, 1.0, E});
+        tys.push_back({KLM_TC_PROJ, 0, D - 1, 2 * D - 1, pl.Vp / 8 / gran_oth, gran_oth, 0, 1.0, E});
         int used = 0;
-        for (auto &t : tys) { const int cap = pmax / t.gran; t.n = (t.items + cap - 1) / cap; used += t.n; }
-        if (used + 1 > sm_avail) continue;
+        for (auto &t : tys) { const int cap = pmax_ / t.gran; t.n = (t.items + cap - 1) / cap; used += t.n; }
+        if (used + 1 > sm_avail) return false;
         const int lse_want = getenv("KLM_TC_NLSE") ? std::max(1, atoi(getenv("KLM_TC_NLSE"))) : 2;
         int n_lse = std::max(1, std::min(lse_want, sm_avail - used));
         used += n_lse;
@@ -332,9 +330,38 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
             }
             if (done) break;
         }
-        pl.pub = attempt < 2 ? pub_mode : 0;
         pl.n_lse = n_lse;
+        return true;
+    };
+    // attempts: (aligned REC slices, 16/32 KB chunks), (aligned, any chunk size), (single pairs, ...), (single pairs, any)
+    for (int attempt = (pub_mode ? 0 : 2); attempt < 4 && !planned; ++attempt) {
+        const int gran = attempt < 2 ? 4 : 1;                // pairs per indivisible REC item
+        g_last = (attempt & 1) ? 6 : 3;
+        pmax = 0;
+        for (int np = 1; np <= KLM_TC1_MAX_PAIRS; ++np) if (geom_for(np) >= 0) pmax = np;
+        if (getenv("KLM_TC_PMAX")) pmax = std::min(pmax, atoi(getenv("KLM_TC_PMAX")));
+        if (!plan_with(gran, 1, pmax)) continue;
+        pl.pub = attempt < 2 ? pub_mode : 0;
         planned = true;
+    }
+    // streamed-weights form: the B images stay in global memory; every ring slot carries an A chunk of 64 k and the
+    // matching part of the image.  Slices are even numbers of pairs (a slice of more than 16 pairs is multiplied in two
+    // MMAs of N = 8 * pairs columns, and N must be a multiple of 16); compile-time ring geometries exist for W = 1024.
+    auto stream_slot = [&](int np) { return 64 * 256 + 64 * 32 * np; };
+    auto stream_stages = [&](int np) {
+        return (int)std::min<size_t>(4, (m->smem_optin - 128 - KLM_TCS_RING_OFS) / (size_t)stream_slot(np)); };
+    if (!planned && W / 64 == 16 && !getenv("KLM_DISABLE_TCS")) {
+        pl.Vp = (V + 15) / 16 * 16;
+        pmax = 0;
+        for (int np = 2; np <= KLM_TCS_MAX_PAIRS; np += 2) if (stream_stages(np) >= 3) pmax = np;
+        if (getenv("KLM_TC_PMAX")) pmax = std::min(pmax, atoi(getenv("KLM_TC_PMAX")));
+        if (plan_with(4, 2, pmax)) {
+            pl.pub = pub_mode ? pub_mode : 2;
+            pl.stream_b = 1;
+            planned = true;
+        } else {
+            pl.Vp = (V + 7) / 8 * 8;
+        }
     }
     if (!planned) return KLM_OK;
     // fp16 range check
@@ -354,15 +381,19 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
         for (int c = 0; c < t.n; ++c) {
             const int np = (base + (c < rem ? 1 : 0)) * t.gran;
             const int N = 8 * np;                            // image rows: [0,N) hi, [N,2N) lo
-            const int g = geom_for(np);
+            const int g = pl.stream_b ? 0 : geom_for(np);
             KlmTcRole r;
             memset(&r, 0, sizeof r);
             r.kind = t.kind; r.layer = t.layer; r.src_layer = t.src; r.sigma = t.sigma;
             r.first_pair = first; r.npairs = np; r.wofs = (long long)(img.size() * sizeof(__half)); r.npm = np;
-            r.kc = geoms[g][0]; r.stages = std::min(geoms[g][1], W / r.kc); r.ring_bytes = ring_bytes_of(g);
+            if (pl.stream_b) {
+                r.kc = 64; r.stages = stream_stages(np); r.ring_bytes = KLM_TCS_RING_OFS + r.stages * stream_slot(np);
+            } else {
+                r.kc = geoms[g][0]; r.stages = std::min(geoms[g][1], W / r.kc); r.ring_bytes = ring_bytes_of(g);
+            }
             r.pub = t.kind == KLM_TC_REC ? pl.pub : 0;
             pl.roles.push_back(r);
-            smem = std::max(smem, (size_t)r.ring_bytes + 128 + (size_t)32 * W * np);
+            smem = std::max(smem, (size_t)r.ring_bytes + 128 + (pl.stream_b ? 0 : (size_t)32 * W * np));
             const size_t o = img.size();
             img.resize(o + (size_t)W * 2 * N, __float2half_rn(0.f));
             for (int j = 0; j < N; ++j) {
@@ -397,7 +428,8 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
         for (size_t i = 0; i < tys.size(); ++i)
             fprintf(stderr, "klm tc plan: %s l%d: %d CTAs, largest slice %d pairs\n", kn[tys[i].kind], tys[i].layer, tys[i].n,
                     (tys[i].items + tys[i].n - 1) / tys[i].n * tys[i].gran);
-        fprintf(stderr, "klm tc plan: LSE %d CTAs; grid %d, smem %zu, pub %d\n", pl.n_lse, pl.grid, pl.smem, pl.pub);
+        fprintf(stderr, "klm tc plan: LSE %d CTAs; grid %d, smem %zu, pub %d%s\n", pl.n_lse, pl.grid, pl.smem, pl.pub,
+                pl.stream_b ? ", streamed weights" : "");
         for (auto &r : pl.roles)
             if (r.kind != KLM_TC_LSE && r.first_pair == 0)
                 fprintf(stderr, "klm tc plan:   %s l%d first CTA: %d pairs, ring %d x %d k (%d B)\n", kn[r.kind], r.layer, r.npairs,
@@ -891,6 +923,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         q.trace_mode = getenv("KLM_TC_TRACE_MODE") ? atoi(getenv("KLM_TC_TRACE_MODE")) : 0;
         q.debug_skip = getenv("KLM_TC_DEBUG_SKIP") ? atoi(getenv("KLM_TC_DEBUG_SKIP")) : 0;
         q.poll_mode = getenv("KLM_TC_POLL") ? atoi(getenv("KLM_TC_POLL")) : 0;
+        q.stream_b = tp.stream_b;
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         q.kc = tp.kc; q.ring_bytes = tp.ring_bytes;
         if (&tp == &m->tc2) CK(klm_launch_seq_tc2(q, tp.grid, tp.smem, m->stream));

@@ -94,6 +94,13 @@ struct KlmSeqParams {
 #define KLM_TC1_PUB_OFS     KLM_TC1_XCHG_BYTES
 #define KLM_TC1_PUB_BYTES   (KLM_TC1_MAX_PAIRS / 4 * 2048)
 #define KLM_TC1_ALIAS_BYTES (KLM_TC1_PUB_OFS + KLM_TC1_PUB_BYTES)
+// streamed-weights form of the single-CTA kernel (models whose B images do not fit shared memory, e.g. width 1024):
+// up to 24 pairs per CTA finished in two epilogue rounds of <= 12; every ring slot holds the A chunk and, behind it,
+// the matching k-rows of the CTA's B image; hand-over buffer and publication staging sit in FRONT of the ring (not
+// aliased), so that the B parts of the next tick's first chunks can be fetched while the epilogue still runs
+#define KLM_TCS_MAX_PAIRS   24
+#define KLM_TCS_PUB_BYTES   (KLM_TCS_MAX_PAIRS / 4 * 2048)
+#define KLM_TCS_RING_OFS    (KLM_TC1_PUB_OFS + KLM_TCS_PUB_BYTES)
 #define KLM_TC_TRACE_TICKS  16
 
 #define KLM_TC_REC  0
@@ -148,4 +155,5 @@ struct KlmTcParams {
     int poll_mode;                // grid barrier: 0 = ld.acquire per poll, 1 = relaxed polls + one acquire fence, 2 = relaxed, no fence (experiment)
     int debug_skip;               // timing experiments only (results are wrong): bit 0 = no MMAs, bit 1 = no operand copies
     int trace_mode;               // 0: phase events; 1: arrival of chunk c in event slot c; 2: issue of the copy of chunk c
+    int stream_b;                 // 1: streamed-weights form (B chunks travel through the ring with the A chunks)
 };

@@ -30,6 +30,7 @@
 // scattered 4-byte stores (scripts/ubench/fetch_paths.cu), so REC CTAs own slices aligned to 8 units
 // (one 16-byte row piece of the operand layout), stage the new hi/lo halves in shared memory and write
 // them out as whole 2 KB blocks (coalesced 16-byte stores or one bulk async store).
+#include <cstdio>
 #include "klm_tc_dev.cuh"
 
 // ---------------------------------------------------------------------------------------------
@@ -39,18 +40,27 @@
 // KLM_TC_DEBUG_SKIP) cost more than the four MMAs of the chunk (~290 clk), and because the MMA queue is shallow
 // the two add up.  Here slot numbers, shared-memory offsets and the K loop are unrolled constants; the only
 // running state is the chunk rotation and one phase bit per slot.
+//
+// STREAM = streamed-weights form: a ring slot is [A chunk | the same k-rows of this CTA's B image]; both copies
+// complete on the slot's barrier.  The B parts of the first ring round do not depend on the tick, so they are
+// issued before the grid barrier and land while the previous tick's epilogue and hand-over are still going on.
+// With more than 128 columns per half the chunk is multiplied in two MMAs (hi columns, lo columns) of N = 8 * pairs.
 struct TcLoopCtx {
     uint32_t ring_a, bar_full, bar_empty, bar_tfull, bar_tempty, bar_go, tmem_base, wsm_a;
     int nticks, N, crot, src_layer, W;
     unsigned G;
+    uint32_t slot_bytes, cbb;              // STREAM: bytes per ring slot (A chunk + B chunk), bytes of a B chunk
+    const unsigned char *bsrc;             // STREAM: this CTA's B image in global memory
 };
 
-template <int KC, int NCH, int S, bool TRACE>
+template <int KC, int NCH, int S, bool TRACE, bool STREAM>
 __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoopCtx &x) {
     constexpr uint32_t CB = KC * 256;
     // everything the loop needs sits in registers: the asm statements clobber memory, so anything left in the
     // context struct or the kernel parameters would be re-loaded after each of them
     const uint32_t ring_a = x.ring_a, bar_full = x.bar_full, bar_empty = x.bar_empty, bar_go = x.bar_go;
+    const uint32_t slot_bytes = STREAM ? x.slot_bytes : CB, cbb = STREAM ? x.cbb : 0u;
+    const unsigned char *bsrc = x.bsrc;
     const int nticks = x.nticks, crot = x.crot;
     const unsigned G = x.G;
     const int trace_mode = p.trace_mode, skip = p.debug_skip, cfence = p.consumer_fence;
@@ -67,7 +77,13 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
         for (int c0 = 0; c0 < NPRE; ++c0) {
             int okw = tc_wait_mbar(bar_empty + 8 * c0, ((phbits >> c0) & 1u) ^ 1u, p, 2) ? 1 : 0;
             if (!__all_sync(0xffffffffu, okw)) return;
-            if (tc::elect_one() && !(skip & 2)) tc::mbar_arrive_expect_tx(bar_full + 8 * c0, CB);
+            if (tc::elect_one() && !(skip & 2)) {
+                tc::mbar_arrive_expect_tx(bar_full + 8 * c0, CB + cbb);
+                if (STREAM) {
+                    const int cb = crot + c0 >= NCH ? crot + c0 - NCH : crot + c0;
+                    tc::bulk_g2s(ring_a + c0 * slot_bytes + CB, bsrc + (size_t)cb * cbb, cbb, bar_full + 8 * c0);
+                }
+            }
             __syncwarp();
         }
         int okg = 1;
@@ -96,8 +112,10 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
                 if (TRACE && trace_mode == 3 && c0 == 0) tc_trace(p, tick, 3);
                 if (skip & 2) tc::mbar_arrive(bar_full + 8 * st);
                 else {
-                    if (c0 >= NPRE) tc::mbar_arrive_expect_tx(bar_full + 8 * st, CB);
-                    tc::bulk_g2s(ring_a + st * CB, src + (size_t)c * CB, CB, bar_full + 8 * st);
+                    if (c0 >= NPRE) tc::mbar_arrive_expect_tx(bar_full + 8 * st, CB + cbb);
+                    tc::bulk_g2s(ring_a + st * slot_bytes, src + (size_t)c * CB, CB, bar_full + 8 * st);
+                    if (STREAM && c0 >= NPRE)
+                        tc::bulk_g2s(ring_a + st * slot_bytes + CB, bsrc + (size_t)c * cbb, cbb, bar_full + 8 * st);
                 }
                 if (TRACE && trace_mode == 3 && c0 < 4) tc_trace(p, tick, 4 + c0);
                 if (TRACE) {
@@ -112,15 +130,18 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
     }
 }
 
-template <int KC, int NCH, int S, bool TRACE>
+template <int KC, int NCH, int S, bool TRACE, bool STREAM>
 __device__ __noinline__ void tc_mma_fixed(const KlmTcParams &p, const TcLoopCtx &x) {
     constexpr uint32_t CB = KC * 256;
-    const uint32_t idesc = tc::idesc_f16(128, 2 * x.N);
+    const bool split = STREAM && 2 * x.N > 256;            // two MMAs per k step: hi columns, lo columns
+    const uint32_t idesc = tc::idesc_f16(128, split ? x.N : 2 * x.N);
     const uint32_t lbo_a = 128 * 16, lbo_b = 2 * x.N * 16;
+    const uint32_t slot16 = (STREAM ? x.slot_bytes : CB) >> 4;
     const uint64_t a_base = tc::smem_desc(x.ring_a, lbo_a, 128);
-    const uint64_t b_base = tc::smem_desc(x.wsm_a, lbo_b, 128);
+    const uint64_t b_base = tc::smem_desc(STREAM ? x.ring_a + CB : x.wsm_a, lbo_b, 128);
     constexpr uint32_t a_k16 = (2 * 128 * 16) >> 4;
     const uint32_t b_k16 = (2 * lbo_b) >> 4, b_chunk = ((uint32_t)(KC / 8) * lbo_b) >> 4;
+    const uint32_t b_lo = (uint32_t)x.N;                   // lo rows start N * 16 bytes into a k group; also the TMEM column
     const uint32_t bar_full = x.bar_full, bar_empty = x.bar_empty, bar_tfull = x.bar_tfull, bar_tempty = x.bar_tempty;
     const uint32_t tmem_base = x.tmem_base;
     const int nticks = x.nticks, crot = x.crot;
@@ -137,17 +158,25 @@ __device__ __noinline__ void tc_mma_fixed(const KlmTcParams &p, const TcLoopCtx 
             const int st = c0 % S;
             okw = tc_wait_mbar(bar_full + 8 * st, (phbits >> st) & 1u, p, 4) ? 1 : 0;
             if (!__all_sync(0xffffffffu, okw)) return;
-            const uint64_t ad = a_base + (uint32_t)(st * (CB >> 4));
-            const uint64_t bd = b_base + (uint32_t)c * b_chunk;
+            const uint64_t ad = a_base + (uint32_t)(st * slot16);
+            const uint64_t bd = STREAM ? b_base + (uint32_t)(st * slot16) : b_base + (uint32_t)c * b_chunk;
             if (tc::elect_one()) {
                 if (TRACE) {
                     if (trace_mode == 1) tc_trace(p, tick, c0 & 7);
                     else if (trace_mode == 0 && (c0 == 0 || c0 == NCH - 1)) tc_trace(p, tick, c0 == 0 ? 2 : 3);
                 }
                 if (!(skip & 1)) {
+                    if (STREAM && split) {
 #pragma unroll
-                    for (int kk = 0; kk < KC / 16; ++kk)
-                        tc::mma_f16(tmem_base, ad + kk * a_k16, bd + kk * b_k16, idesc, (c0 | kk) != 0 ? 1u : 0u);
+                        for (int kk = 0; kk < KC / 16; ++kk) {
+                            tc::mma_f16(tmem_base, ad + kk * a_k16, bd + kk * b_k16, idesc, (c0 | kk) != 0 ? 1u : 0u);
+                            tc::mma_f16(tmem_base + b_lo, ad + kk * a_k16, bd + kk * b_k16 + b_lo, idesc, (c0 | kk) != 0 ? 1u : 0u);
+                        }
+                    } else {
+#pragma unroll
+                        for (int kk = 0; kk < KC / 16; ++kk)
+                            tc::mma_f16(tmem_base, ad + kk * a_k16, bd + kk * b_k16, idesc, (c0 | kk) != 0 ? 1u : 0u);
+                    }
                 }
                 tc::mma_commit(bar_empty + 8 * st);       // ring slot free once these MMAs have read it
                 if (c0 == NCH - 1) tc::mma_commit(bar_tfull);   // accumulators of this tick complete
@@ -160,22 +189,45 @@ __device__ __noinline__ void tc_mma_fixed(const KlmTcParams &p, const TcLoopCtx 
 }
 
 #define TC_FIXED_GEOMS(F) F(64, 8, 4) F(64, 8, 3) F(32, 16, 4) F(64, 4, 4) F(128, 4, 3) F(128, 4, 2)
+#define TC_STREAM_GEOMS(F) F(64, 16, 4) F(64, 16, 3) F(64, 16, 2)
 
+template <bool STREAM>
 static __device__ __forceinline__ bool tc_run_fixed(bool producer, const KlmTcParams &p, const TcLoopCtx &x, int kc, int nch, int S) {
 #define TC_TRY(KC_, NCH_, S_)                                                                                   \
     if (kc == KC_ && nch == NCH_ && S == S_) {                                                                  \
-        if (p.trace) { if (producer) tc_produce_fixed<KC_, NCH_, S_, true>(p, x); else tc_mma_fixed<KC_, NCH_, S_, true>(p, x); }   \
-        else { if (producer) tc_produce_fixed<KC_, NCH_, S_, false>(p, x); else tc_mma_fixed<KC_, NCH_, S_, false>(p, x); }         \
+        if (p.trace) { if (producer) tc_produce_fixed<KC_, NCH_, S_, true, STREAM>(p, x); else tc_mma_fixed<KC_, NCH_, S_, true, STREAM>(p, x); }   \
+        else { if (producer) tc_produce_fixed<KC_, NCH_, S_, false, STREAM>(p, x); else tc_mma_fixed<KC_, NCH_, S_, false, STREAM>(p, x); }         \
         return true;                                                                                            \
     }
-    TC_FIXED_GEOMS(TC_TRY)
+    if (STREAM) { TC_STREAM_GEOMS(TC_TRY) }
+    else { TC_FIXED_GEOMS(TC_TRY) }
 #undef TC_TRY
     return false;
 }
 
+// One epilogue round = up to KLM_TC1_MAX_PAIRS pairs of the CTA's slice.  The pairs of a round are split between the
+// hi-row and the lo-row threads, and between the two warps that share a TMEM lane quarter; all indices below are
+// relative to the round's first pair `pb`.
+struct TcRound { int pb, my_first, oth_first, own_first, nown, send_first, nsend; };
+static __device__ __forceinline__ TcRound tc_round(int NP, int r, int half, int ch) {
+    TcRound o;
+    o.pb = r * KLM_TC1_MAX_PAIRS;
+    const int npr = min(max(NP - o.pb, 0), KLM_TC1_MAX_PAIRS);
+    const int Ph = (npr + 1) / 2;                    // pairs [0,Ph) are finished by hi-row threads, the rest by lo-row threads
+    const int my_n = half ? npr - Ph : Ph, oth_n = half ? Ph : npr - Ph;
+    o.my_first = half ? Ph : 0;
+    o.oth_first = half ? 0 : Ph;
+    o.own_first = o.my_first + (ch ? (my_n + 1) / 2 : 0);
+    o.nown = ch ? my_n - (my_n + 1) / 2 : (my_n + 1) / 2;
+    o.send_first = o.oth_first + (ch ? (oth_n + 1) / 2 : 0);
+    o.nsend = ch ? oth_n - (oth_n + 1) / 2 : (oth_n + 1) / 2;
+    return o;
+}
+
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_constant__ KlmTcParams p) {
-    extern __shared__ __align__(1024) unsigned char smem[];
+// NR = epilogue rounds (pairs per CTA <= NR * KLM_TC1_MAX_PAIRS), STREAM = streamed-weights form.
+template <int NR, bool STREAM>
+static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigned char *smem) {
     const KlmTcRole role = p.roles[blockIdx.x];
     if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }
 
@@ -186,20 +238,22 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
     const int NP = role.npairs, N = 8 * NP;
     const int nchunks = W / kc;
     const uint32_t chunk_bytes = (uint32_t)kc * 256u;
+    constexpr int TMEM_COLS = STREAM ? 512 : KLM_TC_TMEM_COLS;
 
     // ---- shared memory carve-up ----
-    unsigned char *ring = smem;                                          // S chunks of the A operand
-    float *xchg = reinterpret_cast<float *>(smem);                       // hi<->lo hand-over and ...
-    __half *pubbuf = reinterpret_cast<__half *>(smem + KLM_TC1_PUB_OFS); // ... publication staging alias the idle ring
+    // resident form: [ring, aliased by hand-over + publication staging][barriers][B image]
+    // streamed form: [hand-over][publication staging][ring of (A chunk | B chunk) slots][barriers]
+    unsigned char *ring = smem + (STREAM ? KLM_TCS_RING_OFS : 0);        // S chunks of the A operand
+    float *xchg = reinterpret_cast<float *>(smem);                       // hi<->lo hand-over
+    __half *pubbuf = reinterpret_cast<__half *>(smem + KLM_TC1_PUB_OFS); // publication staging
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + role.ring_bytes);
-    unsigned char *wsm = smem + role.ring_bytes + 128;                   // B image
+    unsigned char *wsm = smem + role.ring_bytes + 128;                   // B image (resident form)
     const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + 4);
     const uint32_t bar_tfull = tc::smem_u32(bars + 8), bar_tempty = tc::smem_u32(bars + 9);
     const uint32_t bar_go = tc::smem_u32(bars + 10);       // producer -> epilogue: grid barrier of this tick passed
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 11);
-
     if (warp == 0) {
-        tc::tmem_alloc(tc::smem_u32(tmem_slot), KLM_TC_TMEM_COLS);
+        tc::tmem_alloc(tc::smem_u32(tmem_slot), TMEM_COLS);
         tc::tmem_relinquish();
     }
     if (tid == 32) {
@@ -209,7 +263,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
         tc::mbar_init(bar_go, 1);
         tc::fence_mbar_init();
     }
-    {   // B image: global -> shared, once per launch
+    if (!STREAM) {   // B image: global -> shared, once per launch
         const uint4 *src = reinterpret_cast<const uint4 *>(p.wimg + role.wofs);
         uint4 *dst = reinterpret_cast<uint4 *>(wsm);
         const int n16 = (W / 8) * 2 * N;
@@ -222,41 +276,41 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
     const int row = 32 * q + lane;                   // accumulator row: 0..63 hi part, 64..127 lo part
     const int half = row >> 6, s = row & 63;
     const int ch = (warp - 2) >> 2;                  // two warps share a lane quarter and split its pairs
-    const int Ph = (NP + 1) / 2;                     // pairs [0,Ph) are finished by hi-row threads, the rest by lo-row threads
-    const int my_first = half ? Ph : 0, my_n = half ? NP - Ph : Ph;          // this half's pairs
-    const int oth_first = half ? 0 : Ph, oth_n = half ? Ph : NP - Ph;        // the other half's pairs
-    const int own_first = my_first + (ch ? (my_n + 1) / 2 : 0), nown = ch ? my_n - (my_n + 1) / 2 : (my_n + 1) / 2;
-    const int send_first = oth_first + (ch ? (oth_n + 1) / 2 : 0), nsend = ch ? oth_n - (oth_n + 1) / 2 : (oth_n + 1) / 2;
+    TcRound rd[NR];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) rd[r] = tc_round(NP, r, half, ch);
     const bool is_epi = warp >= 2;
     const bool is_rec = role.kind == KLM_TC_REC;
     const int l = role.layer;
 
-    float c_reg[KLM_TC_OWN][2], h_reg[KLM_TC_OWN][2];
+    float c_reg[NR][KLM_TC_OWN][2], h_reg[NR][KLM_TC_OWN][2];
     long long o0 = 0;
     int len = 0;
     if (is_epi) {
         if (s < p.B) { o0 = p.offsets[s]; len = (int)(p.offsets[s + 1] - o0); }
 #pragma unroll
-        for (int i = 0; i < KLM_TC_OWN; ++i) {
-            c_reg[i][0] = c_reg[i][1] = h_reg[i][0] = h_reg[i][1] = 0.f;
-            if (is_rec && i < nown) {
-                const int u = 2 * (role.first_pair + own_first + i);
-                if (s < p.B) {
-                    const int slot = p.slots_in[s];
-                    if (slot >= 0) {
-                        const float *st = p.state + ((size_t)slot * p.D + l) * 2 * W;
-                        h_reg[i][0] = st[u]; h_reg[i][1] = st[u + 1];
-                        c_reg[i][0] = st[W + u]; c_reg[i][1] = st[W + u + 1];
+        for (int r = 0; r < NR; ++r)
+#pragma unroll
+            for (int i = 0; i < KLM_TC_OWN; ++i) {
+                c_reg[r][i][0] = c_reg[r][i][1] = h_reg[r][i][0] = h_reg[r][i][1] = 0.f;
+                if (is_rec && i < rd[r].nown) {
+                    const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
+                    if (s < p.B) {
+                        const int slot = p.slots_in[s];
+                        if (slot >= 0) {
+                            const float *st = p.state + ((size_t)slot * p.D + l) * 2 * W;
+                            h_reg[r][i][0] = st[u]; h_reg[r][i][1] = st[u + 1];
+                            c_reg[r][i][0] = st[W + u]; c_reg[r][i][1] = st[W + u + 1];
+                        }
                     }
+                    // publish the carried hidden state for tick 0 (parity 0)
+                    __half hi0, lo0, hi1, lo1;
+                    tc_split(h_reg[r][i][0], hi0, lo0); tc_split(h_reg[r][i][1], hi1, lo1);
+                    __half *dst = p.hx + ((size_t)(l * 2 + 0) * (W / 8) + u / 8) * (128 * 8) + (u & 7);
+                    *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
+                    *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
                 }
-                // publish the carried hidden state for tick 0 (parity 0)
-                __half hi0, lo0, hi1, lo1;
-                tc_split(h_reg[i][0], hi0, lo0); tc_split(h_reg[i][1], hi1, lo1);
-                __half *dst = p.hx + ((size_t)(l * 2 + 0) * (W / 8) + u / 8) * (128 * 8) + (u & 7);
-                *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
-                *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
             }
-        }
         tc::fence_proxy_async();                    // generic global writes -> later bulk (async proxy) reads
     }
     tc::tc_fence_before();
@@ -269,13 +323,17 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
     lx.bar_tempty = bar_tempty; lx.bar_go = bar_go; lx.tmem_base = tmem_base; lx.wsm_a = tc::smem_u32(wsm);
     lx.nticks = nticks; lx.N = N; lx.crot = (int)(blockIdx.x % (unsigned)nchunks); lx.src_layer = role.src_layer; lx.W = W;
     lx.G = G;
+    lx.cbb = (uint32_t)kc * 32u * (uint32_t)NP;            // kc/8 k groups x 2N rows x 16 bytes
+    lx.slot_bytes = chunk_bytes + lx.cbb;
+    lx.bsrc = p.wimg + role.wofs;
 
     if (warp == 0) {
         // =============================== producer ===============================
         // (one thread: everything in these loops is a dependent chain of ~5 clk per instruction, so the ring
         //  position, phase and chunk index are running counters -- an integer division per chunk costs more
         //  than the copy itself)
-        if (!tc_run_fixed(true, p, lx, kc, nchunks, S) && lane == 0) {
+        if (!tc_run_fixed<STREAM>(true, p, lx, kc, nchunks, S) && lane == 0) {
+            if (STREAM) { atomicExch(p.err, 90); return; }   // the streamed form has compile-time geometries only
             uint32_t st = 0, ph = 0, ring_ofs = 0;
             const int crot = (int)(blockIdx.x % (unsigned)nchunks);    // spread the CTAs over the chunks
             const uint32_t ring_a = tc::smem_u32(ring);
@@ -306,7 +364,7 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
         }
     } else if (warp == 1) {
         // =============================== MMA issuer ===============================
-        if (!tc_run_fixed(false, p, lx, kc, nchunks, S) && lane == 0) {
+        if (!tc_run_fixed<STREAM>(false, p, lx, kc, nchunks, S) && lane == 0 && !STREAM) {
             const uint32_t idesc = tc::idesc_f16(128, 2 * N);
             const uint32_t lbo_a = 128 * 16, lbo_b = 2 * N * 16;
             // descriptors differ only in the start address field (bits 0-13, 16-byte units): add offsets to a base
@@ -348,21 +406,33 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
     } else {
         // =============================== epilogue ===============================
         const uint32_t trow = tmem_base + ((uint32_t)(32 * q) << 16);
-        float4 bias4[KLM_TC_OWN][2];
-        if (role.kind == KLM_TC_IN) {
+        // with one round the tick-invariant addends (bias, context part of layer 1's input) live in registers; with two
+        // rounds that would spill (a 320-thread CTA gets 168 registers per thread), so they are re-read every tick
+        // (the same few lines each time: L1 hits)
+        constexpr bool KEEP = NR == 1;
+        constexpr int NRK = KEEP ? NR : 1;
+        float4 bias4[NRK][KLM_TC_OWN][2];
+        if (KEEP && role.kind == KLM_TC_IN) {
 #pragma unroll
-            for (int i = 0; i < KLM_TC_OWN; ++i)
-                if (i < nown) {
-                    const int u = 2 * (role.first_pair + own_first + i);
-                    bias4[i][0] = __ldg(p.bias[l] + u); bias4[i][1] = __ldg(p.bias[l] + u + 1);
-                }
+            for (int r = 0; r < NRK; ++r)
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (i < rd[r].nown) {
+                        const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
+                        bias4[r][i][0] = __ldg(p.bias[l] + u); bias4[r][i][1] = __ldg(p.bias[l] + u + 1);
+                    }
         }
         // REC layer 1: first character index, number of real (non-padding) positions, and the context part of the
         // input contraction sum_k Q_k[z_k][u], which does not change over the ticks
         int x_next = 0, nreal_s = 0x7fffffff;
-        float4 qsum[KLM_TC_OWN][2];
+        float4 qsum[NRK][KLM_TC_OWN][2];
+        int zk[KLM_MAX_CTX];
 #pragma unroll
-        for (int i = 0; i < KLM_TC_OWN; ++i) qsum[i][0] = qsum[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = 0; k < KLM_MAX_CTX; ++k) zk[k] = 0;
+#pragma unroll
+        for (int r = 0; r < NRK; ++r)
+#pragma unroll
+            for (int i = 0; i < KLM_TC_OWN; ++i) qsum[r][i][0] = qsum[r][i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (is_rec && l == 0 && s < p.B) {
             if (len > 0) x_next = __ldg(p.chars + o0);
             if (p.n_real) nreal_s = __ldg(p.n_real + s);
@@ -371,16 +441,19 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
                 if (k < p.Nc) {
                     int z = __ldg(p.ctx + s * p.Nc + k);
                     z = min(max(z, 0), p.ctx_rows[k] - 1);
+                    zk[k] = z;
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
-                        if (i < nown) {
-                            const int u = 2 * (role.first_pair + own_first + i);
+                    for (int r = 0; r < (KEEP ? NRK : 0); ++r)
 #pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                const float4 b = __ldg(p.Q[k] + (size_t)z * W + u + e);
-                                qsum[i][e].x += b.x; qsum[i][e].y += b.y; qsum[i][e].z += b.z; qsum[i][e].w += b.w;
+                        for (int i = 0; i < KLM_TC_OWN; ++i)
+                            if (i < rd[r].nown) {
+                                const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
+#pragma unroll
+                                for (int e = 0; e < 2; ++e) {
+                                    const float4 b = __ldg(p.Q[k] + (size_t)z * W + u + e);
+                                    qsum[r][i][e].x += b.x; qsum[r][i][e].y += b.y; qsum[r][i][e].z += b.z; qsum[r][i][e].w += b.w;
+                                }
                             }
-                        }
                 }
         }
         for (int tick = 0; tick < nticks; ++tick) {
@@ -393,32 +466,38 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
             const bool active = s < p.B && t >= 0 && t < len;
             const int par_in = tick & 1, par_out = (tick + 1) & 1;
 
-            // ---- addends, fetched while the MMAs run ----
-            float4 add4[KLM_TC_OWN][2];
+            // REC layer 1: the character index was fetched a tick ahead
+            int x = 0;
+            bool real = true;
+            if (is_rec && l == 0 && active) {
+                x = min(max(x_next, 0), p.V - 1);
+                if (t + 1 < len) x_next = __ldg(p.chars + o0 + t + 1);
+                real = t < nreal_s;
+            }
+            // ---- addends of one round (fetched while the MMAs run / while the previous round is finished) ----
+            auto load_add = [&](const int r, float4 (&add4)[KLM_TC_OWN][2]) {
 #pragma unroll
-            for (int i = 0; i < KLM_TC_OWN; ++i) add4[i][0] = add4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (is_rec && active) {
+                for (int i = 0; i < KLM_TC_OWN; ++i) add4[i][0] = add4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (!(is_rec && active)) return;
+                const int pr0 = role.first_pair + rd[r].pb + rd[r].own_first;
                 if (l == 0) {
-                    // fused char + context embedding gather / concat / input contraction (rating.py:103-115,125)
-                    // the character index was fetched a tick ahead, the context part is tick-invariant (qsum)
-                    int x = min(max(x_next, 0), p.V - 1);
-                    if (t + 1 < len) x_next = __ldg(p.chars + o0 + t + 1);
-                    const bool real = t < nreal_s;
+                    // fused char + context embedding gather / concat / input contraction (rating.py:103-115,125);
+                    // the context part is tick-invariant (qsum)
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i)
-                        if (i < nown) {
-                            const int u = 2 * (role.first_pair + own_first + i);
+                        if (i < rd[r].nown) {
+                            const int u = 2 * (pr0 + i);
 #pragma unroll
                             for (int e = 0; e < 2; ++e) {
                                 float4 a = __ldg(p.P + (size_t)x * W + u + e);
-                                if (real) {
-                                    const float4 b = qsum[i][e];
+                                if (real && KEEP) {
+                                    const float4 b = qsum[KEEP ? r : 0][i][e];
                                     a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
                                 } else {                     // padding position: context 0 (:1141-1143)
 #pragma unroll
                                     for (int k = 0; k < KLM_MAX_CTX; ++k)
                                         if (k < p.Nc) {
-                                            const float4 b = __ldg(p.Q[k] + u + e);
+                                            const float4 b = __ldg(p.Q[k] + (real ? (size_t)zk[k] * W : (size_t)0) + u + e);
                                             a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
                                         }
                                 }
@@ -431,12 +510,14 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
                     const float4 *zrow = reinterpret_cast<const float4 *>(p.Z) + (size_t)(l * 2 + par_in) * W * 64 + s;
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i)
-                        if (i < nown) {
-                            const int u = 2 * (role.first_pair + own_first + i);
+                        if (i < rd[r].nown) {
+                            const int u = 2 * (pr0 + i);
                             add4[i][0] = __ldcg(zrow + (size_t)u * 64); add4[i][1] = __ldcg(zrow + (size_t)(u + 1) * 64);
                         }
                 }
-            }
+            };
+            float4 add4[KLM_TC_OWN][2];
+            load_add(0, add4);
 
             // ---- accumulators ----
             ok = tc_wait_mbar(bar_tfull, tick & 1, p, 6) ? 1 : 0;
@@ -444,114 +525,170 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
             if (!ok) break;
             if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 4);
             tc::tc_fence_after();
-            float acc[KLM_TC_OWN][8];
 #pragma unroll
-            for (int i = 0; i < KLM_TC_OWN; ++i)
-#pragma unroll
-                for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-            // own pairs: this row's part (hi rows: hi.hi + hi.lo columns; lo rows: lo.hi columns)
-#pragma unroll
-            for (int i = 0; i < KLM_TC_OWN; ++i)
-                if (i < nown) {
-                    const int pr = own_first + i;
-                    tc::tmem_ld8(trow + 8 * pr, acc[i]);
-                    if (half == 0) {
-                        float b[8];
-                        tc::tmem_ld8(trow + N + 8 * pr, b);
-                        tc::tmem_ld_wait();
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) acc[i][j] += b[j];
-                    } else {
-                        tc::tmem_ld_wait();
-                    }
-                }
-            // the other half's pairs: hand this row's part over through shared memory (both directions at once)
-            {
-                float *xs = xchg + (half ? 0 : KLM_TC1_MAX_PAIRS / 2 * 8 * 64);
+            for (int r = 0; r < NR; ++r) {
+                const TcRound R = rd[r];
+                if (r > 0) tc_bar_epi();                      // the hand-over buffer is reused: round r-1 has been read
+                float acc[KLM_TC_OWN][8];
 #pragma unroll
                 for (int i = 0; i < KLM_TC_OWN; ++i)
-                    if (i < nsend) {
-                        const int pr = send_first + i, xi = pr - oth_first;
-                        float v[8];
-                        tc::tmem_ld8(trow + 8 * pr, v);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+                // own pairs: this row's part (hi rows: hi.hi + hi.lo columns; lo rows: lo.hi columns)
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (i < R.nown) {
+                        const int pr = R.pb + R.own_first + i;
+                        tc::tmem_ld8(trow + 8 * pr, acc[i]);
                         if (half == 0) {
                             float b[8];
                             tc::tmem_ld8(trow + N + 8 * pr, b);
                             tc::tmem_ld_wait();
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) v[j] += b[j];
+                            for (int j = 0; j < 8; ++j) acc[i][j] += b[j];
                         } else {
                             tc::tmem_ld_wait();
                         }
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) xs[(xi * 8 + j) * 64 + s] = v[j];
                     }
-            }
-            tc::tc_fence_before();
-            tc::mbar_arrive(bar_tempty);                      // this thread is done reading TMEM
-            tc_bar_epi();
-            {
-                const float *xr = xchg + (half ? KLM_TC1_MAX_PAIRS / 2 * 8 * 64 : 0);
-#pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
-                    if (i < nown) {
-                        const int xi = own_first + i - my_first;
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) acc[i][j] += xr[(xi * 8 + j) * 64 + s];
-                    }
-                // the hand-over buffer aliases the ring: order these generic accesses before the next bulk copies
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            }
-
-            // ---- finish and hand over ----
-            if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 5);
-            if (is_rec) {
-                // LSTM cell for all owned units, staged so that the MUFU chains of different units overlap
-                float e1[KLM_TC_OWN][2], e2[KLM_TC_OWN][2], e3[KLM_TC_OWN][2], e4[KLM_TC_OWN][2];
-#pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        if (i >= nown) continue;             // (warp-uniform)
-                        const float4 a = add4[i][e];
-                        e1[i][e] = tc_exp(-tc_clamp(acc[i][4 * e] + a.x));
-                        e2[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 1] + a.y));
-                        e3[i][e] = tc_exp(-2.f * tc_clamp(acc[i][4 * e + 2] + a.z));
-                        e4[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 3] + a.w));
-                    }
-#pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        if (i >= nown) continue;
-                        const float ig = __fdividef(1.f - e3[i][e], (1.f + e1[i][e]) * (1.f + e3[i][e]));
-                        const float f = __fdividef(1.f, 1.f + e2[i][e]);
-                        e1[i][e] = fmaf(f, c_reg[i][e], ig);                       // new cell state
-                        e2[i][e] = tc_exp(-2.f * tc_clamp(e1[i][e]));
-                    }
-#pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        if (i >= nown) continue;
-                        const float hn = __fdividef(1.f - e2[i][e], (1.f + e4[i][e]) * (1.f + e2[i][e]));
-                        if (active) { c_reg[i][e] = e1[i][e]; h_reg[i][e] = hn; }
-                    }
-                // publish the new hidden vector as fp16 hi/lo in the operand layout of its readers
-                __half *hx_out = p.hx + ((size_t)(l * 2 + par_out) * (W / 8)) * (128 * 8);
-                if (role.pub) {
-                    // slice = whole groups of 8 units: stage [group][128 rows][8], then write whole 2 KB blocks
+                // the other half's pairs: hand this row's part over through shared memory (both directions at once)
+                {
+                    float *xs = xchg + (half ? 0 : KLM_TC1_MAX_PAIRS / 2 * 8 * 64);
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i)
-                        if (i < nown) {
-                            const int ul = 2 * (own_first + i);
-                            __half hi0, lo0, hi1, lo1;
-                            tc_split(h_reg[i][0], hi0, lo0); tc_split(h_reg[i][1], hi1, lo1);
-                            __half *dst = pubbuf + (ul / 8) * (128 * 8) + (ul & 7);
-                            *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
-                            *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
+                        if (i < R.nsend) {
+                            const int pr = R.pb + R.send_first + i, xi = R.send_first + i - R.oth_first;
+                            float v[8];
+                            tc::tmem_ld8(trow + 8 * pr, v);
+                            if (half == 0) {
+                                float b[8];
+                                tc::tmem_ld8(trow + N + 8 * pr, b);
+                                tc::tmem_ld_wait();
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) v[j] += b[j];
+                            } else {
+                                tc::tmem_ld_wait();
+                            }
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) xs[(xi * 8 + j) * 64 + s] = v[j];
                         }
-                    __half *gdst = hx_out + (size_t)(role.first_pair / 4) * (128 * 8);
+                }
+                if (r == NR - 1) {
+                    tc::tc_fence_before();
+                    tc::mbar_arrive(bar_tempty);                  // this thread is done reading TMEM
+                }
+                tc_bar_epi();
+                {
+                    const float *xr = xchg + (half ? KLM_TC1_MAX_PAIRS / 2 * 8 * 64 : 0);
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                        if (i < R.nown) {
+                            const int xi = R.own_first + i - R.my_first;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) acc[i][j] += xr[(xi * 8 + j) * 64 + s];
+                        }
+                    // resident form: the hand-over buffer aliases the ring: order these generic accesses before the
+                    // next bulk copies
+                    if (!STREAM) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                }
+                // addends of the next round: in flight while this round is finished
+                float4 add_nxt[KLM_TC_OWN][2];
+                if (r + 1 < NR) load_add(r + 1, add_nxt);
+
+                // ---- finish the round ----
+                if (r == NR - 1 && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 5);
+                const int pr0 = role.first_pair + R.pb + R.own_first;        // first own pair of the round (layer-wide index)
+                if (is_rec) {
+                    // LSTM cell for all owned units, staged so that the MUFU chains of different units overlap
+                    float e1[KLM_TC_OWN][2], e2[KLM_TC_OWN][2], e3[KLM_TC_OWN][2], e4[KLM_TC_OWN][2];
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            if (i >= R.nown) continue;             // (warp-uniform)
+                            const float4 a = add4[i][e];
+                            e1[i][e] = tc_exp(-tc_clamp(acc[i][4 * e] + a.x));
+                            e2[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 1] + a.y));
+                            e3[i][e] = tc_exp(-2.f * tc_clamp(acc[i][4 * e + 2] + a.z));
+                            e4[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 3] + a.w));
+                        }
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            if (i >= R.nown) continue;
+                            const float ig = __fdividef(1.f - e3[i][e], (1.f + e1[i][e]) * (1.f + e3[i][e]));
+                            const float f = __fdividef(1.f, 1.f + e2[i][e]);
+                            e1[i][e] = fmaf(f, c_reg[r][i][e], ig);                    // new cell state
+                            e2[i][e] = tc_exp(-2.f * tc_clamp(e1[i][e]));
+                        }
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            if (i >= R.nown) continue;
+                            const float hn = __fdividef(1.f - e2[i][e], (1.f + e4[i][e]) * (1.f + e2[i][e]));
+                            if (active) { c_reg[r][i][e] = e1[i][e]; h_reg[r][i][e] = hn; }
+                        }
+                    // the new hidden vector as fp16 hi/lo in the operand layout of its readers
+                    if (role.pub) {
+                        // slice = whole groups of 8 units: stage [group][128 rows][8]; whole 2 KB blocks are written below
+#pragma unroll
+                        for (int i = 0; i < KLM_TC_OWN; ++i)
+                            if (i < R.nown) {
+                                const int ul = 2 * (R.pb + R.own_first + i);
+                                __half hi0, lo0, hi1, lo1;
+                                tc_split(h_reg[r][i][0], hi0, lo0); tc_split(h_reg[r][i][1], hi1, lo1);
+                                __half *dst = pubbuf + (ul / 8) * (128 * 8) + (ul & 7);
+                                *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
+                                *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
+                            }
+                    } else {
+                        __half *hx_out = p.hx + ((size_t)(l * 2 + par_out) * (W / 8)) * (128 * 8);
+#pragma unroll
+                        for (int i = 0; i < KLM_TC_OWN; ++i)
+                            if (i < R.nown) {
+                                const int u = 2 * (pr0 + i);
+                                __half hi0, lo0, hi1, lo1;
+                                tc_split(h_reg[r][i][0], hi0, lo0); tc_split(h_reg[r][i][1], hi1, lo1);
+                                __half *dst = hx_out + (size_t)(u / 8) * (128 * 8) + (u & 7);
+                                *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
+                                *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
+                            }
+                    }
+                } else if (role.kind == KLM_TC_IN) {
+                    float4 *zrow = reinterpret_cast<float4 *>(p.Z) + (size_t)(l * 2 + par_out) * W * 64 + s;
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                        if (i < R.nown) {
+                            const int u = 2 * (pr0 + i);
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const float4 b = KEEP ? bias4[KEEP ? r : 0][i][e] : __ldg(p.bias[l] + u + e);
+                                __stcg(zrow + (size_t)(u + e) * 64, make_float4(acc[i][4 * e] + b.x, acc[i][4 * e + 1] + b.y,
+                                                                 acc[i][4 * e + 2] + b.z, acc[i][4 * e + 3] + b.w));
+                            }
+                        }
+                } else {   // PROJ: logits of vocabulary rows 8*(first_pair + pair) ..
+                    // logits are [parity][Vp/4][64 streams] float4: coalesced over the streams of a warp (read by the LSE stage)
+                    float4 *lrow = reinterpret_cast<float4 *>(p.logits) + (size_t)par_out * (p.Vp / 4) * 64 + s;
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                        if (i < R.nown) {
+                            const int g8 = pr0 + i;
+                            __stcg(lrow + (size_t)(2 * g8) * 64, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
+                            __stcg(lrow + (size_t)(2 * g8 + 1) * 64, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
+                        }
+                }
+                if (r + 1 < NR) {
+#pragma unroll
+                    for (int i = 0; i < KLM_TC_OWN; ++i) { add4[i][0] = add_nxt[i][0]; add4[i][1] = add_nxt[i][1]; }
+                }
+            }
+
+            // ---- hand over ----
+            if (is_rec) {
+                if (role.pub) {
+                    __half *gdst = p.hx + ((size_t)(l * 2 + par_out) * (W / 8) + role.first_pair / 4) * (128 * 8);
                     const int n16 = (NP / 4) * 128;                       // 16-byte pieces of the slice
                     if (role.pub == 2) {
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // staging writes -> bulk store reads
@@ -572,42 +709,8 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
                     uint4 *gp = reinterpret_cast<uint4 *>(gdst);
                     for (int i = tid - 64; i < n16; i += 256) __stcg(gp + i, sp[i]);
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // staging reads -> next bulk copies into the ring
-                } else {
-#pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
-                        if (i < nown) {
-                            const int u = 2 * (role.first_pair + own_first + i);
-                            __half hi0, lo0, hi1, lo1;
-                            tc_split(h_reg[i][0], hi0, lo0); tc_split(h_reg[i][1], hi1, lo1);
-                            __half *dst = hx_out + (size_t)(u / 8) * (128 * 8) + (u & 7);
-                            *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
-                            *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
-                        }
                 }
                 tc::fence_proxy_async();             // generic global writes -> bulk (async proxy) reads of other CTAs
-            } else if (role.kind == KLM_TC_IN) {
-                float4 *zrow = reinterpret_cast<float4 *>(p.Z) + (size_t)(l * 2 + par_out) * W * 64 + s;
-#pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
-                    if (i < nown) {
-                        const int u = 2 * (role.first_pair + own_first + i);
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const float4 b = bias4[i][e];
-                            __stcg(zrow + (size_t)(u + e) * 64, make_float4(acc[i][4 * e] + b.x, acc[i][4 * e + 1] + b.y,
-                                                             acc[i][4 * e + 2] + b.z, acc[i][4 * e + 3] + b.w));
-                        }
-                    }
-            } else {   // PROJ: logits of vocabulary rows 8*(first_pair + pair) ..
-                // logits are [parity][Vp/4][64 streams] float4: coalesced over the streams of a warp (read by the LSE stage)
-                float4 *lrow = reinterpret_cast<float4 *>(p.logits) + (size_t)par_out * (p.Vp / 4) * 64 + s;
-#pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
-                    if (i < nown) {
-                        const int g8 = role.first_pair + own_first + i;
-                        __stcg(lrow + (size_t)(2 * g8) * 64, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
-                        __stcg(lrow + (size_t)(2 * g8 + 1) * 64, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
-                    }
             }
             if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
             tc_bar_epi();
@@ -617,12 +720,14 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
         if (is_rec && s < p.B) {
             float *st = p.state + ((size_t)p.slots_out[s] * p.D + l) * 2 * W;
 #pragma unroll
-            for (int i = 0; i < KLM_TC_OWN; ++i)
-                if (i < nown) {
-                    const int u = 2 * (role.first_pair + own_first + i);
-                    st[u] = h_reg[i][0]; st[u + 1] = h_reg[i][1];
-                    st[W + u] = c_reg[i][0]; st[W + u + 1] = c_reg[i][1];
-                }
+            for (int r = 0; r < NR; ++r)
+#pragma unroll
+                for (int i = 0; i < KLM_TC_OWN; ++i)
+                    if (i < rd[r].nown) {
+                        const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
+                        st[u] = h_reg[r][i][0]; st[u + 1] = h_reg[r][i][1];
+                        st[W + u] = c_reg[r][i][0]; st[W + u + 1] = c_reg[r][i][1];
+                    }
         }
     }
 
@@ -630,22 +735,46 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_con
     __syncthreads();
     if (warp == 0) {
         __syncwarp();
-        tc::tmem_dealloc(tmem_base, KLM_TC_TMEM_COLS);
+        tc::tmem_dealloc(tmem_base, TMEM_COLS);
     }
+}
+
+__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_constant__ KlmTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    tc_seq_body<1, false>(p, smem);
+}
+
+// Streamed-weights form: the B images stay in global memory (L2) and travel through the ring with the A chunks.
+__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tcs(const __grid_constant__ KlmTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    tc_seq_body<2, true>(p, smem);
 }
 
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream) {
     void *args[] = { const_cast<KlmTcParams *>(&p) };
     // (the attribute is per device: set it once per device and size, not at every launch of a beam step)
-    static size_t smem_set[64] = {0};
+    static size_t smem_set[2][64] = {{0}};
+    const void *fn = p.stream_b ? (const void *)klm_seq_tcs : (const void *)klm_seq_tc;
+    const int which = p.stream_b ? 1 : 0;
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64 || smem_set[dev] != smem) {
-        cudaError_t e = cudaFuncSetAttribute((const void *)klm_seq_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (dev < 0 || dev >= 64 || smem_set[which][dev] != smem) {
+        cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64) smem_set[dev] = smem;
+        if (dev >= 0 && dev < 64) smem_set[which][dev] = smem;
     }
-    return cudaLaunchCooperativeKernel((const void *)klm_seq_tc, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
+    cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
+    if (e != cudaSuccess) {
+        cudaFuncAttributes fa;
+        int occ = -1;
+        if (cudaFuncGetAttributes(&fa, fn) == cudaSuccess) {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, KLM_TC_THREADS, smem);
+            fprintf(stderr, "klm_launch_seq_tc: %s; grid %d, %d threads, %zu B dynamic + %zu B static shared memory (limit %d), "
+                    "%d registers, %zu B local, max threads %d, blocks per SM %d\n", cudaGetErrorString(e), grid, KLM_TC_THREADS,
+                    smem, fa.sharedSizeBytes, fa.maxDynamicSharedSizeBytes, fa.numRegs, fa.localSizeBytes, fa.maxThreadsPerBlock, occ);
+        }
+    }
+    return e;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -66,6 +66,31 @@ def test_tc_rate_many_matches_oracle(width, depth, n_docs, nctx):
     assert worst <= 1e-3, worst
 
 
+@pytest.mark.parametrize('depth,n_docs,nctx', [(1, 9, 1), (3, 64, 1), (2, 40, 2)])
+def test_tc_streamed_weights_width_1024_matches_oracle(depth, n_docs, nctx):
+    """Width 1024 (BASELINE config 5): the B images do not fit shared memory, klm_seq_tcs streams them through the
+    operand ring (slices of up to 22 pairs, two epilogue rounds, split hi / lo MMAs).  Ragged lengths, carried
+    state out of the launch, same tolerance as the resident form."""
+    wd = synth.weights(77 + depth, width=1024, depth=depth, voc_size=256, contexts=((200, 10),) * nctx, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 32)
+    assert r._native.info()['tc_enabled'] >= 1
+    rng = np.random.default_rng(1024 + n_docs)
+    sizes = rng.integers(2, 14, n_docs)
+    sizes[1] = 1
+    texts = [synth.text(3500 + i, int(s)) for i, s in enumerate(sizes)]
+    ctxs = [[int(x) for x in rng.integers(0, 200, nctx)] for _ in texts]
+    before = r._native.info()['tc_launches']
+    got = r.rate_many(texts, ctxs)
+    assert r._native.info()['tc_launches'] > before
+    o = OracleRater(util.to_model(wd), synth.mapping_from_array(maparr), 32, logger=quiet)
+    worst = 0.0
+    for i in sorted({0, 1, 2, n_docs // 2, n_docs - 1}):
+        ref, _ = o.rate2(texts[i], ctxs[i])
+        worst = max(worst, logp_err(got[i], [p for _, p in ref]))
+    assert worst <= 1e-3, worst
+
+
 def test_tc_states_and_carry_match_oracle():
     """Hidden and cell states after a launch (1e-4 relative) and a second launch continuing from them."""
     width, depth, n = 128, 2, 12
