@@ -499,14 +499,14 @@ def run_ours(args):
     except Exception:
         pass
     roofline = {
-        'bound': 'tensor', 'kernel': 'klm_seq_tc' if info.get('tc_launches', 0) > 0 else 'klm_seq_fma', 'achieved': achieved, 'peak': peak,
+        'bound': 'tensor', 'kernel': ('klm_seq_tcs' if info.get('tc_enabled') == 3 else 'klm_seq_tc') if info.get('tc_launches', 0) > 0 else 'klm_seq_fma', 'achieved': achieved, 'peak': peak,
         'unit': 'TFLOP/s', 'frac': achieved / peak, 'traffic': traffic, 'peak_source': pk_src + ', bf16 sustained',
         'kernel_ms': k_ms, 'algorithmic_flops_per_launch': chars_per_step * F,
         'algorithmic_hbm_bytes_per_launch': 8 * chars_per_step,
         'hbm_frac': (8 * chars_per_step / (k_ms / 1000.0) / 1e9) / float(pk.get('hbm_gbs', FALLBACK_PEAKS['hbm_gbs'])),
         'grid': info['tc_grid'] if info.get('tc_launches', 0) > 0 else info['grid'],
         'smem_bytes': info['tc_smem_bytes'] if info.get('tc_launches', 0) > 0 else info['smem_bytes'],
-        'weights_in_smem': 1 if info.get('tc_launches', 0) > 0 else info['weights_in_smem'],
+        'weights_in_smem': (0 if info.get('tc_enabled') == 3 else 1) if info.get('tc_launches', 0) > 0 else info['weights_in_smem'],
     }
 
     line = base_line(args, value, total_ms / args.steps)

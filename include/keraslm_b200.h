@@ -160,7 +160,8 @@ typedef struct klm_info {
     int64_t kernel_launches;    /* kernels of this library launched so far on this model */
     double  last_kernel_ms;     /* device time of the last klm_rate/klm_step main kernel (CUDA events) */
     int32_t max_streams;        /* largest n one launch takes; larger calls are split */
-    int32_t tc_enabled;         /* 1 if the tcgen05 sequence kernel serves 9..64 streams for this model */
+    int32_t tc_enabled;         /* tcgen05 sequence kernel serving 9..64 streams: 0 none (FMA kernels), 1 weights resident in
+                                 * shared memory, 2 CTA-pair variant, 3 weights streamed through the operand ring */
     int32_t tc_grid;            /* CTAs of the tcgen05 kernel */
     int32_t tc_smem_bytes;      /* dynamic shared memory per CTA of the tcgen05 kernel */
     int64_t tc_launches;        /* launches of the tcgen05 kernel so far */

@@ -1144,7 +1144,7 @@ extern "C" int klm_get_info(klm_model *m, klm_info *out) {
     out->smem_bytes = (int32_t)m->plan_b.smem;
     out->kernel_launches = m->launches;
     out->max_streams = m->tc.ok ? KLM_TC_STREAMS : m->plan_b.max_streams;
-    out->tc_enabled = m->tc.ok ? 1 : 0;
+    out->tc_enabled = m->tc.ok ? (m->tc.stream_b ? 3 : 1) : 0; // 3: streamed-weights form (images stay in global memory / L2)
     out->tc_enabled = m->tc2.ok ? 2 : out->tc_enabled;        // 2: the CTA-pair kernel (cta_group::2) is the one in use
     out->tc_grid = m->tc2.ok ? m->tc2.grid : m->tc.grid;
     out->tc_smem_bytes = (int32_t)(m->tc2.ok ? m->tc2.smem : m->tc.smem);

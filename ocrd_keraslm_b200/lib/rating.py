@@ -412,6 +412,32 @@ class Rater(object):
                 raise ValueError('context value %d outside embedding table of %d rows' % (c, rows))
         return context
 
+    def _context_rows(self, contexts, n):
+        """[n][number of context variables] int32; same checks as `_context_row`, done on the whole array."""
+        if contexts is None:
+            contexts = [None] * n
+        if len(contexts) != n:
+            raise ValueError('%d texts but %d contexts' % (n, len(contexts)))
+        default = None
+        try:
+            rows = []
+            for c in contexts:
+                if not c:
+                    if default is None:
+                        default = [int(x) for x in self.underspecify_contexts()]
+                    c = default
+                rows.append(c)
+            arr = np.asarray(rows, dtype=np.int64)
+            ok = arr.shape == (n, len(self.context_shapes))
+            if ok and n:
+                limit = np.array([r for r, _ in self.context_shapes], dtype=np.int64)
+                ok = bool(((arr >= 0) & (arr < limit)).all())
+        except (ValueError, TypeError):
+            ok = False
+        if not ok:                              # let the per-row check name the offending value
+            arr = np.array([self._context_row(c) for c in contexts], dtype=np.int64).reshape(n, len(self.context_shapes))
+        return arr.astype(np.int32)
+
     # ------------------------------------------------------------------ stateful rating
     def rate(self, text, context=None):
         """Probability of every character of `text` given its left context (reference :493-529).
@@ -487,32 +513,60 @@ class Rater(object):
         assert self.status > 1
         assert self.incremental is False
         n = len(texts)
-        if contexts is None:
-            contexts = [None] * n
-        rows = [self._context_row(c) for c in contexts]
+        ctx_rows = self._context_rows(contexts, n)
         norm = [unicodedata.normalize('NFC', t) for t in texts]
-        lens = np.array([max(len(t) - 1, 0) for t in norm], dtype=np.int64)
+        nchar = np.fromiter((len(t) for t in norm), dtype=np.int64, count=n)
+        lens = np.maximum(nchar - 1, 0)
         order = np.argsort(-lens, kind='stable')            # longest first: batches of similar length
         total = int(lens.sum())
-        out = [np.empty(len(t), dtype=np.float32) for t in norm]
-        for o in out:
-            o[:1] = 0.0 if return_logp else 1.0
+        # Many short texts (lines, words): ONE table lookup for the characters of all texts, and the segments are
+        # gathered / scattered with index arithmetic -- no per-text Python work.  Few long texts (documents): every
+        # segment maps its slices itself, so that this work overlaps the device (a lookup over all characters up
+        # front would not).
+        gather = total < n * self.GATHER_MAX_MEAN_LENGTH
+        cstart = np.zeros(n + 1, dtype=np.int64)
+        np.cumsum(nchar, out=cstart[1:])
+        if gather:
+            # text i occupies [cstart[i], cstart[i+1]) of idx_all / out_all
+            idx_all, known_all = self._indices(''.join(norm))
+            if not known_all.all():
+                for g in np.flatnonzero(~known_all):
+                    i = int(np.searchsorted(cstart, g, side='right')) - 1
+                    self.logger.error('unmapped character "%s" at input position %d', norm[i][int(g - cstart[i])],
+                                      int(g - cstart[i]))
+            out_all = np.empty(int(cstart[-1]), dtype=np.float32)
+            out_all[cstart[:-1][nchar > 0]] = 0.0 if return_logp else 1.0
+            out = [out_all[cstart[i]:cstart[i + 1]] for i in range(n)]
+        else:
+            out = [np.empty(len(t), dtype=np.float32) for t in norm]
+            for o in out:
+                o[:1] = 0.0 if return_logp else 1.0
         if total == 0:
             return out
         # The positions are cut into segments along time (every stream contributes its share to each segment,
         # the state is carried in the pool slots), and a worker thread drives the device: while segment k runs,
         # the host maps the characters of segment k+1 and converts the scores of segment k-1.
         nseg = int(min(self.MAX_SEGMENTS, max(1, total // self.MIN_SEGMENT_POSITIONS)))
-        bounds = [(lens[order] * k) // nseg for k in range(nseg + 1)]          # [nseg+1][n] position boundaries
+        lens_o, cstart_o = lens[order], cstart[:-1][order]
+        bounds = [(lens_o * k) // nseg for k in range(nseg + 1)]               # [nseg+1][n] position boundaries
         seg_tot = [int((bounds[k + 1] - bounds[k]).sum()) for k in range(nseg)]
         bufs = self._pinned(max(seg_tot), 2 if nseg > 1 else 1)
-        ctx_rows = [rows[i] for i in order]
+        ctx_rows = ctx_rows[order]
         slots = self._pool.acquire(n)
 
         def prepare(k):
             chars, targets, logp = (a[:seg_tot[k]] for a in bufs[k % len(bufs)])
+            counts = bounds[k + 1] - bounds[k]
             offsets = np.zeros(n + 1, dtype=np.int64)
-            offsets[1:] = np.cumsum(bounds[k + 1] - bounds[k])
+            np.cumsum(counts, out=offsets[1:])
+            if gather:
+                # position p of stream j in this segment is character cstart_o[j] + bounds[k][j] + (p - offsets[j])
+                src = np.repeat(cstart_o + bounds[k] - offsets[:-1], counts)
+                src += np.arange(seg_tot[k], dtype=np.int64)
+                np.take(idx_all, src, out=chars, mode='clip')
+                src += 1
+                np.take(idx_all, src, out=targets, mode='clip')
+                return offsets, logp, src                                       # src now addresses the scored characters
             for j, i in enumerate(order):
                 lo, hi = int(bounds[k][j]), int(bounds[k + 1][j])
                 if hi == lo:
@@ -527,9 +581,12 @@ class Rater(object):
                     self.logger.error('unmapped character "%s" at input position %d', norm[i][base + int(t)], base + int(t))
                 chars[offsets[j]:offsets[j + 1]] = idx[:-1]
                 targets[offsets[j]:offsets[j + 1]] = idx[1:]
-            return offsets, chars, targets, logp
+            return offsets, logp, None
 
-        def finish(k, offsets, logp):
+        def finish(k, offsets, logp, dst):
+            if gather:
+                out_all[dst] = logp if return_logp else np.exp(logp)
+                return
             for j, i in enumerate(order):
                 lo, hi = int(bounds[k][j]), int(bounds[k + 1][j])
                 if hi > lo:
@@ -542,9 +599,10 @@ class Rater(object):
         try:
             self._native.state_reset(slots)
             if nseg == 1:
-                offsets, chars, targets, logp = prepare(0)
+                offsets, logp, dst = prepare(0)
+                chars, targets = (a[:seg_tot[0]] for a in bufs[0][:2])
                 self._native.rate(slots, offsets, chars, targets, None, ctx_rows, logp)
-                finish(0, offsets, logp)
+                finish(0, offsets, logp, dst)
             else:
                 if self._worker is None:
                     from concurrent.futures import ThreadPoolExecutor
@@ -552,13 +610,14 @@ class Rater(object):
                 pending = None                      # (future, k, offsets, logp) of the segment on the device
                 try:
                     for k in range(nseg):
-                        offsets, chars, targets, logp = prepare(k)
+                        offsets, logp, dst = prepare(k)
+                        chars, targets = (a[:seg_tot[k]] for a in bufs[k % len(bufs)][:2])
                         if pending is not None:
                             pending[0].result()
                         fut = self._worker.submit(self._native.rate, slots, offsets, chars, targets, None, ctx_rows, logp)
                         if pending is not None:
                             finish(*pending[1:])
-                        pending = (fut, k, offsets, logp)
+                        pending = (fut, k, offsets, logp, dst)
                     pending[0].result()
                     finish(*pending[1:])
                     pending = None
@@ -573,6 +632,7 @@ class Rater(object):
                 self._pool.release(sl)
         return out
 
+    GATHER_MAX_MEAN_LENGTH = 4096         # rate_many: one lookup + index arithmetic below this mean text length
     MAX_SEGMENTS = 16                     # rate_many: segments along time for host/device overlap ...
     MIN_SEGMENT_POSITIONS = 250000        # ... each at least this many positions (a launch costs ~50 us)
 

@@ -224,8 +224,11 @@ def test_rate_many_in_time_segments_matches_one_launch_and_oracle(width, depth, 
     one = r.rate_many(texts, ctxs, return_logp=True)
     r.MAX_SEGMENTS, r.MIN_SEGMENT_POSITIONS = nseg, 1       # instance overrides: force nseg segments
     seg = r.rate_many(texts, ctxs, return_logp=True)
-    for a, b in zip(one, seg):
+    r.GATHER_MAX_MEAN_LENGTH = 0                             # the host path for few long texts (per-text slices)
+    sliced = r.rate_many(texts, ctxs, return_logp=True)
+    for a, b, c in zip(one, seg, sliced):
         np.testing.assert_array_equal(a, b)
+        np.testing.assert_array_equal(a, c)
     o = oracle_for(wd, maparr, 32)
     for i in (0, 1, 2, n_docs - 1):
         ref, _ = o.rate2(texts[i], ctxs[i])
