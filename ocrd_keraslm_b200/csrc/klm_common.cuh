@@ -154,6 +154,8 @@ struct KlmTcParams {
     int trace_t0;
     int poll_mode;                // grid barrier: 0 = ld.acquire per poll, 1 = relaxed polls + one acquire fence, 2 = relaxed, no fence (experiment)
     int debug_skip;               // timing experiments only (results are wrong): bit 0 = no MMAs, bit 1 = no operand copies
-    int trace_mode;               // 0: phase events; 1: arrival of chunk c in event slot c; 2: issue of the copy of chunk c
+    int trace_mode;               // 0: phase events; 1: arrival of chunk c in event slot c; 2: issue of the copy of chunk c;
+                                  // 3: producer steps; 4: epilogue phases of one thread (accumulators complete, per round: drained,
+                                  //    hand-over read, finished; arrive)
     int stream_b;                 // 1: streamed-weights form (B chunks travel through the ring with the A chunks)
 };

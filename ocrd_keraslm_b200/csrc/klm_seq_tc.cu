@@ -523,7 +523,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
             ok = tc_wait_mbar(bar_tfull, tick & 1, p, 6) ? 1 : 0;
             ok = __all_sync(0xffffffffu, ok);
             if (!ok) break;
-            if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 4);
+            if (tid == 64 && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, p.trace_mode == 4 ? 0 : 4);
             tc::tc_fence_after();
 #pragma unroll
             for (int r = 0; r < NR; ++r) {
@@ -576,6 +576,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     tc::tc_fence_before();
                     tc::mbar_arrive(bar_tempty);                  // this thread is done reading TMEM
                 }
+                if (tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 1 + 3 * r);      // epilogue phases: round drained
                 tc_bar_epi();
                 {
                     const float *xr = xchg + (half ? KLM_TC1_MAX_PAIRS / 2 * 8 * 64 : 0);
@@ -590,6 +591,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     // next bulk copies
                     if (!STREAM) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 }
+                if (tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 2 + 3 * r);      // ... hand-over read
                 // addends of the next round: in flight while this round is finished
                 float4 add_nxt[KLM_TC_OWN][2];
                 if (r + 1 < NR) load_add(r + 1, add_nxt);
@@ -679,6 +681,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                             __stcg(lrow + (size_t)(2 * g8 + 1) * 64, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
                         }
                 }
+                if (tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 3 + 3 * r);      // ... round finished
                 if (r + 1 < NR) {
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i) { add4[i][0] = add_nxt[i][0]; add4[i][1] = add_nxt[i][1]; }
@@ -700,7 +703,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                             asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // writes complete (not just read)
                             tc::red_release_add(p.barrier, 1u);
-                            if (p.trace_mode == 0) tc_trace(p, tick, 7);
+                            if (p.trace_mode == 0 || p.trace_mode == 4) tc_trace(p, tick, 7);
                         }
                         continue;
                     }
@@ -714,7 +717,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
             }
             if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
             tc_bar_epi();
-            if (tid == 64) { tc::red_release_add(p.barrier, 1u); if (p.trace_mode == 0) tc_trace(p, tick, 7); }
+            if (tid == 64) { tc::red_release_add(p.barrier, 1u); if (p.trace_mode == 0 || p.trace_mode == 4) tc_trace(p, tick, 7); }
         }
         // ---- write the final state back ----
         if (is_rec && s < p.B) {

@@ -29,6 +29,8 @@ print('grid', info['tc_grid'], 'last kernel ms', info['last_kernel_ms'], 'per ti
 names = {0: 'REC', 1: 'IN', 2: 'PROJ', 3: 'LSE'}
 tr = tr.astype(np.int64)
 ev = ['start', 'issue0', 'chunk0', 'chunkN', 'mma_done', 'drained', 'stored', 'arrive']
+if os.environ.get('KLM_TC_TRACE_MODE') == '4':      # epilogue phases of one epilogue thread, relative to the accumulators being complete
+    ev = ['mma_done', 'r0_drain', 'r0_xchg', 'r0_fin', 'r1_drain', 'r1_xchg', 'r1_fin', 'arrive']
 for kind in (0, 1, 2, 3):
     for layer in range(depth):
         sel = [i for i in range(len(roles)) if roles[i, 0] == kind and roles[i, 1] == layer]
