@@ -191,12 +191,12 @@ __device__ __noinline__ void tc_mma_fixed(const KlmTcParams &p, const TcLoopCtx 
 #define TC_FIXED_GEOMS(F) F(64, 8, 4) F(64, 8, 3) F(32, 16, 4) F(64, 4, 4) F(128, 4, 3) F(128, 4, 2)
 #define TC_STREAM_GEOMS(F) F(64, 16, 4) F(64, 16, 3) F(64, 16, 2)
 
-template <bool STREAM>
+template <bool STREAM, bool TRACE>
 static __device__ __forceinline__ bool tc_run_fixed(bool producer, const KlmTcParams &p, const TcLoopCtx &x, int kc, int nch, int S) {
 #define TC_TRY(KC_, NCH_, S_)                                                                                   \
     if (kc == KC_ && nch == NCH_ && S == S_) {                                                                  \
-        if (p.trace) { if (producer) tc_produce_fixed<KC_, NCH_, S_, true, STREAM>(p, x); else tc_mma_fixed<KC_, NCH_, S_, true, STREAM>(p, x); }   \
-        else { if (producer) tc_produce_fixed<KC_, NCH_, S_, false, STREAM>(p, x); else tc_mma_fixed<KC_, NCH_, S_, false, STREAM>(p, x); }         \
+        if (producer) tc_produce_fixed<KC_, NCH_, S_, TRACE, STREAM>(p, x);                                     \
+        else tc_mma_fixed<KC_, NCH_, S_, TRACE, STREAM>(p, x);                                                  \
         return true;                                                                                            \
     }
     if (STREAM) { TC_STREAM_GEOMS(TC_TRY) }
@@ -226,7 +226,9 @@ static __device__ __forceinline__ TcRound tc_round(int NP, int r, int half, int 
 
 // ---------------------------------------------------------------------------------------------
 // NR = epilogue rounds (pairs per CTA <= NR * KLM_TC1_MAX_PAIRS), STREAM = streamed-weights form.
-template <int NR, bool STREAM>
+// TRACE = timeline instrumentation compiled in (klm_tc_trace armed): the production instantiations carry none of it --
+// a handful of run-time-disabled checks in the epilogue cost the resident kernel 3 % on cfg2.
+template <int NR, bool STREAM, bool TRACE>
 static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigned char *smem) {
     const KlmTcRole role = p.roles[blockIdx.x];
     if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }
@@ -332,7 +334,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
         // (one thread: everything in these loops is a dependent chain of ~5 clk per instruction, so the ring
         //  position, phase and chunk index are running counters -- an integer division per chunk costs more
         //  than the copy itself)
-        if (!tc_run_fixed<STREAM>(true, p, lx, kc, nchunks, S) && lane == 0) {
+        if (!tc_run_fixed<STREAM, TRACE>(true, p, lx, kc, nchunks, S) && lane == 0) {
             if (STREAM) { atomicExch(p.err, 90); return; }   // the streamed form has compile-time geometries only
             uint32_t st = 0, ph = 0, ring_ofs = 0;
             const int crot = (int)(blockIdx.x % (unsigned)nchunks);    // spread the CTAs over the chunks
@@ -341,7 +343,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
             for (int tick = 0; tick < nticks && ok; ++tick) {
                 if (!tc_wait_grid(p, (unsigned)(tick + 1) * G, 1)) break;
                 tc::mbar_arrive(bar_go);
-                if (p.trace_mode == 0) tc_trace(p, tick, 0);
+                if (TRACE && p.trace_mode == 0) tc_trace(p, tick, 0);
                 // operand fetch by the bulk-copy engine
                 if (p.consumer_fence) tc::fence_proxy_async();   // generic global writes of other CTAs -> async-proxy reads
                 const unsigned char *src = reinterpret_cast<const unsigned char *>(
@@ -354,8 +356,8 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                         tc::mbar_arrive_expect_tx(bar_full + 8 * st, chunk_bytes);
                         tc::bulk_g2s(ring_a + ring_ofs, src + (size_t)c * chunk_bytes, chunk_bytes, bar_full + 8 * st);
                     }
-                    if (p.trace_mode == 2) tc_trace(p, tick, c0 & 7);
-                    else if (c0 == 0 && p.trace_mode == 0) tc_trace(p, tick, 1);
+                    if (TRACE && p.trace_mode == 2) tc_trace(p, tick, c0 & 7);
+                    else if (TRACE && c0 == 0 && p.trace_mode == 0) tc_trace(p, tick, 1);
                     ring_ofs += chunk_bytes;
                     if (++st == (uint32_t)S) { st = 0; ph ^= 1; ring_ofs = 0; }
                     if (++c == nchunks) c = 0;
@@ -364,7 +366,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
         }
     } else if (warp == 1) {
         // =============================== MMA issuer ===============================
-        if (!tc_run_fixed<STREAM>(false, p, lx, kc, nchunks, S) && lane == 0 && !STREAM) {
+        if (!tc_run_fixed<STREAM, TRACE>(false, p, lx, kc, nchunks, S) && lane == 0 && !STREAM) {
             const uint32_t idesc = tc::idesc_f16(128, 2 * N);
             const uint32_t lbo_a = 128 * 16, lbo_b = 2 * N * 16;
             // descriptors differ only in the start address field (bits 0-13, 16-byte units): add offsets to a base
@@ -384,8 +386,8 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 uint32_t acc = 0;
                 for (int c0 = 0; c0 < nchunks; ++c0) {
                     if (!tc_wait_mbar(bar_full + 8 * st, ph, p, 4)) { ok = false; break; }
-                    if (p.trace_mode == 1) tc_trace(p, tick, c0 & 7);
-                    else if (p.trace_mode == 0) tc_trace(p, tick, c0 == 0 ? 2 : 3);
+                    if (TRACE && p.trace_mode == 1) tc_trace(p, tick, c0 & 7);
+                    else if (TRACE && p.trace_mode == 0) tc_trace(p, tick, c0 == 0 ? 2 : 3);
                     tc::tc_fence_after();
                     uint64_t ad = a_base + a_ofs, bd = b_base + b_ofs;
 #pragma unroll 1
@@ -523,7 +525,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
             ok = tc_wait_mbar(bar_tfull, tick & 1, p, 6) ? 1 : 0;
             ok = __all_sync(0xffffffffu, ok);
             if (!ok) break;
-            if (tid == 64 && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, p.trace_mode == 4 ? 0 : 4);
+            if (TRACE && tid == 64 && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, p.trace_mode == 4 ? 0 : 4);
             tc::tc_fence_after();
 #pragma unroll
             for (int r = 0; r < NR; ++r) {
@@ -576,7 +578,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     tc::tc_fence_before();
                     tc::mbar_arrive(bar_tempty);                  // this thread is done reading TMEM
                 }
-                if (tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 1 + 3 * r);      // epilogue phases: round drained
+                if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 1 + 3 * r);      // epilogue phases: round drained
                 tc_bar_epi();
                 {
                     const float *xr = xchg + (half ? KLM_TC1_MAX_PAIRS / 2 * 8 * 64 : 0);
@@ -591,13 +593,13 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     // next bulk copies
                     if (!STREAM) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 }
-                if (tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 2 + 3 * r);      // ... hand-over read
+                if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 2 + 3 * r);      // ... hand-over read
                 // addends of the next round: in flight while this round is finished
                 float4 add_nxt[KLM_TC_OWN][2];
                 if (r + 1 < NR) load_add(r + 1, add_nxt);
 
                 // ---- finish the round ----
-                if (r == NR - 1 && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 5);
+                if (TRACE && r == NR - 1 && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 5);
                 const int pr0 = role.first_pair + R.pb + R.own_first;        // first own pair of the round (layer-wide index)
                 if (is_rec) {
                     // LSTM cell for all owned units, staged so that the MUFU chains of different units overlap
@@ -681,7 +683,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                             __stcg(lrow + (size_t)(2 * g8 + 1) * 64, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
                         }
                 }
-                if (tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 3 + 3 * r);      // ... round finished
+                if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 3 + 3 * r);      // ... round finished
                 if (r + 1 < NR) {
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i) { add4[i][0] = add_nxt[i][0]; add4[i][1] = add_nxt[i][1]; }
@@ -695,7 +697,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     const int n16 = (NP / 4) * 128;                       // 16-byte pieces of the slice
                     if (role.pub == 2) {
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // staging writes -> bulk store reads
-                        if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
+                        if (TRACE && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
                         tc_bar_epi();
                         if (tid == 64) {
                             asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
@@ -703,7 +705,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                             asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // writes complete (not just read)
                             tc::red_release_add(p.barrier, 1u);
-                            if (p.trace_mode == 0 || p.trace_mode == 4) tc_trace(p, tick, 7);
+                            if (TRACE && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, 7);
                         }
                         continue;
                     }
@@ -715,9 +717,9 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 }
                 tc::fence_proxy_async();             // generic global writes -> bulk (async proxy) reads of other CTAs
             }
-            if (tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
+            if (TRACE && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
             tc_bar_epi();
-            if (tid == 64) { tc::red_release_add(p.barrier, 1u); if (p.trace_mode == 0 || p.trace_mode == 4) tc_trace(p, tick, 7); }
+            if (tid == 64) { tc::red_release_add(p.barrier, 1u); if (TRACE && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, 7); }
         }
         // ---- write the final state back ----
         if (is_rec && s < p.B) {
@@ -744,21 +746,31 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
 
 __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    tc_seq_body<1, false>(p, smem);
+    tc_seq_body<1, false, false>(p, smem);
+}
+__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc_traced(const __grid_constant__ KlmTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    tc_seq_body<1, false, true>(p, smem);
 }
 
 // Streamed-weights form: the B images stay in global memory (L2) and travel through the ring with the A chunks.
 __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tcs(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    tc_seq_body<2, true>(p, smem);
+    tc_seq_body<2, true, false>(p, smem);
+}
+__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tcs_traced(const __grid_constant__ KlmTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    tc_seq_body<2, true, true>(p, smem);
 }
 
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream) {
     void *args[] = { const_cast<KlmTcParams *>(&p) };
     // (the attribute is per device: set it once per device and size, not at every launch of a beam step)
-    static size_t smem_set[2][64] = {{0}};
-    const void *fn = p.stream_b ? (const void *)klm_seq_tcs : (const void *)klm_seq_tc;
-    const int which = p.stream_b ? 1 : 0;
+    static size_t smem_set[4][64] = {{0}};
+    const void *fns[4] = {(const void *)klm_seq_tc, (const void *)klm_seq_tcs, (const void *)klm_seq_tc_traced,
+                          (const void *)klm_seq_tcs_traced};
+    const int which = (p.stream_b ? 1 : 0) + (p.trace ? 2 : 0);     // the traced instantiations only while klm_tc_trace is armed
+    const void *fn = fns[which];
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64 || smem_set[which][dev] != smem) {

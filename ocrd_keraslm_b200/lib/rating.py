@@ -543,30 +543,49 @@ class Rater(object):
                 o[:1] = 0.0 if return_logp else 1.0
         if total == 0:
             return out
-        # The positions are cut into segments along time (every stream contributes its share to each segment,
-        # the state is carried in the pool slots), and a worker thread drives the device: while segment k runs,
-        # the host maps the characters of segment k+1 and converts the scores of segment k-1.
+        # The work is cut into segments and a worker thread drives the device: while segment k runs, the host maps
+        # the characters of segment k+1 and converts the scores of segment k-1.  Long texts are cut along time (every
+        # stream contributes its share to each segment, the state is carried in the pool slots); many short texts
+        # are cut into groups of whole streams (at multiples of the launch width, so that launches stay full) -- cut
+        # along time they would pay the pipeline fill of a launch once per segment.
         nseg = int(min(self.MAX_SEGMENTS, max(1, total // self.MIN_SEGMENT_POSITIONS)))
         lens_o, cstart_o = lens[order], cstart[:-1][order]
-        bounds = [(lens_o * k) // nseg for k in range(nseg + 1)]               # [nseg+1][n] position boundaries
-        seg_tot = [int((bounds[k + 1] - bounds[k]).sum()) for k in range(nseg)]
+        if gather:
+            cum = np.cumsum(lens_o)
+            cuts = [0]
+            for k in range(1, nseg):
+                c = int(np.searchsorted(cum, total * k // nseg, side='left')) + 1
+                c = min(n, -(-c // self.LAUNCH_STREAMS) * self.LAUNCH_STREAMS)
+                if c > cuts[-1]:
+                    cuts.append(c)
+            if cuts[-1] < n:
+                cuts.append(n)
+            nseg = len(cuts) - 1
+            seg_tot = [int(lens_o[cuts[k]:cuts[k + 1]].sum()) for k in range(nseg)]
+        else:
+            bounds = [(lens_o * k) // nseg for k in range(nseg + 1)]           # [nseg+1][n] position boundaries
+            seg_tot = [int((bounds[k + 1] - bounds[k]).sum()) for k in range(nseg)]
         bufs = self._pinned(max(seg_tot), 2 if nseg > 1 else 1)
         ctx_rows = ctx_rows[order]
         slots = self._pool.acquire(n)
 
         def prepare(k):
             chars, targets, logp = (a[:seg_tot[k]] for a in bufs[k % len(bufs)])
-            counts = bounds[k + 1] - bounds[k]
-            offsets = np.zeros(n + 1, dtype=np.int64)
-            np.cumsum(counts, out=offsets[1:])
             if gather:
-                # position p of stream j in this segment is character cstart_o[j] + bounds[k][j] + (p - offsets[j])
-                src = np.repeat(cstart_o + bounds[k] - offsets[:-1], counts)
+                a, b = cuts[k], cuts[k + 1]
+                counts = lens_o[a:b]
+                offsets = np.zeros(b - a + 1, dtype=np.int64)
+                np.cumsum(counts, out=offsets[1:])
+                # position p of stream j is character cstart_o[j] + (p - offsets[j]) of idx_all
+                src = np.repeat(cstart_o[a:b] - offsets[:-1], counts)
                 src += np.arange(seg_tot[k], dtype=np.int64)
                 np.take(idx_all, src, out=chars, mode='clip')
                 src += 1
                 np.take(idx_all, src, out=targets, mode='clip')
-                return offsets, logp, src                                       # src now addresses the scored characters
+                return slots[a:b], offsets, ctx_rows[a:b], logp, src            # src now addresses the scored characters
+            counts = bounds[k + 1] - bounds[k]
+            offsets = np.zeros(n + 1, dtype=np.int64)
+            np.cumsum(counts, out=offsets[1:])
             for j, i in enumerate(order):
                 lo, hi = int(bounds[k][j]), int(bounds[k + 1][j])
                 if hi == lo:
@@ -581,7 +600,7 @@ class Rater(object):
                     self.logger.error('unmapped character "%s" at input position %d', norm[i][base + int(t)], base + int(t))
                 chars[offsets[j]:offsets[j + 1]] = idx[:-1]
                 targets[offsets[j]:offsets[j + 1]] = idx[1:]
-            return offsets, logp, None
+            return slots, offsets, ctx_rows, logp, None
 
         def finish(k, offsets, logp, dst):
             if gather:
@@ -599,9 +618,9 @@ class Rater(object):
         try:
             self._native.state_reset(slots)
             if nseg == 1:
-                offsets, logp, dst = prepare(0)
+                sl, offsets, cx, logp, dst = prepare(0)
                 chars, targets = (a[:seg_tot[0]] for a in bufs[0][:2])
-                self._native.rate(slots, offsets, chars, targets, None, ctx_rows, logp)
+                self._native.rate(sl, offsets, chars, targets, None, cx, logp)
                 finish(0, offsets, logp, dst)
             else:
                 if self._worker is None:
@@ -610,11 +629,11 @@ class Rater(object):
                 pending = None                      # (future, k, offsets, logp) of the segment on the device
                 try:
                     for k in range(nseg):
-                        offsets, logp, dst = prepare(k)
+                        sl, offsets, cx, logp, dst = prepare(k)
                         chars, targets = (a[:seg_tot[k]] for a in bufs[k % len(bufs)][:2])
                         if pending is not None:
                             pending[0].result()
-                        fut = self._worker.submit(self._native.rate, slots, offsets, chars, targets, None, ctx_rows, logp)
+                        fut = self._worker.submit(self._native.rate, sl, offsets, chars, targets, None, cx, logp)
                         if pending is not None:
                             finish(*pending[1:])
                         pending = (fut, k, offsets, logp, dst)
@@ -633,7 +652,8 @@ class Rater(object):
         return out
 
     GATHER_MAX_MEAN_LENGTH = 4096         # rate_many: one lookup + index arithmetic below this mean text length
-    MAX_SEGMENTS = 16                     # rate_many: segments along time for host/device overlap ...
+    LAUNCH_STREAMS = 64                   # rate_many: streams per launch of the sequence kernels
+    MAX_SEGMENTS = 16                     # rate_many: segments for host/device overlap ...
     MIN_SEGMENT_POSITIONS = 250000        # ... each at least this many positions (a launch costs ~50 us)
 
     def _pinned(self, total, sets=1):
