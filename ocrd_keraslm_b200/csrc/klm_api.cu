@@ -348,12 +348,17 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
     // matching part of the image.  Slices are even numbers of pairs (a slice of more than 16 pairs is multiplied in two
     // MMAs of N = 8 * pairs columns, and N must be a multiple of 16); compile-time ring geometries exist for W = 1024.
     auto stream_slot = [&](int np) { return 64 * 256 + 64 * 32 * np; };
-    auto stream_stages = [&](int np) {
-        return (int)std::min<size_t>(4, (m->smem_optin - 128 - KLM_TCS_RING_OFS) / (size_t)stream_slot(np)); };
+    // in front of the ring: the hi<->lo hand-over buffer and, in REC CTAs, the publication staging of the slice
+    auto stream_ring_ofs = [&](int np, bool rec) { return KLM_TC1_PUB_OFS + (rec ? (np + 3) / 4 * 2048 : 0); };
+    // (1 KB of static shared memory belongs to the LSE role; a 4th slot fits REC slices of 16 pairs but made the
+    //  tick 3 % slower: cfg5 3.99 M -> 3.88 M chars/s)
+    const size_t stream_max_stages = getenv("KLM_TCS_STAGES") ? (size_t)atoi(getenv("KLM_TCS_STAGES")) : 3;
+    auto stream_stages = [&](int np, bool rec) {
+        return (int)std::min<size_t>(stream_max_stages, (m->smem_optin - 1024 - 128 - stream_ring_ofs(np, rec)) / (size_t)stream_slot(np)); };
     if (!planned && W / 64 == 16 && !getenv("KLM_DISABLE_TCS")) {
         pl.Vp = (V + 15) / 16 * 16;
         pmax = 0;
-        for (int np = 2; np <= KLM_TCS_MAX_PAIRS; np += 2) if (stream_stages(np) >= 3) pmax = np;
+        for (int np = 2; np <= KLM_TCS_MAX_PAIRS; np += 2) if (stream_stages(np, true) >= 3) pmax = np;
         if (getenv("KLM_TC_PMAX")) pmax = std::min(pmax, atoi(getenv("KLM_TC_PMAX")));
         if (plan_with(4, 2, pmax)) {
             pl.pub = pub_mode ? pub_mode : 2;
@@ -387,7 +392,9 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
             r.kind = t.kind; r.layer = t.layer; r.src_layer = t.src; r.sigma = t.sigma;
             r.first_pair = first; r.npairs = np; r.wofs = (long long)(img.size() * sizeof(__half)); r.npm = np;
             if (pl.stream_b) {
-                r.kc = 64; r.stages = stream_stages(np); r.ring_bytes = KLM_TCS_RING_OFS + r.stages * stream_slot(np);
+                const bool rec = t.kind == KLM_TC_REC;
+                r.kc = 64; r.stages = stream_stages(np, rec); r.ring_ofs = stream_ring_ofs(np, rec);
+                r.ring_bytes = r.ring_ofs + r.stages * stream_slot(np);
             } else {
                 r.kc = geoms[g][0]; r.stages = std::min(geoms[g][1], W / r.kc); r.ring_bytes = ring_bytes_of(g);
             }

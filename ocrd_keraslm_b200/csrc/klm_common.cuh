@@ -98,9 +98,8 @@ struct KlmSeqParams {
 // up to 24 pairs per CTA finished in two epilogue rounds of <= 12; every ring slot holds the A chunk and, behind it,
 // the matching k-rows of the CTA's B image; hand-over buffer and publication staging sit in FRONT of the ring (not
 // aliased), so that the B parts of the next tick's first chunks can be fetched while the epilogue still runs
+// (KlmTcRole::ring_ofs = KLM_TC1_PUB_OFS + 2 KB per group of 8 units of a REC slice)
 #define KLM_TCS_MAX_PAIRS   24
-#define KLM_TCS_PUB_BYTES   (KLM_TCS_MAX_PAIRS / 4 * 2048)
-#define KLM_TCS_RING_OFS    (KLM_TC1_PUB_OFS + KLM_TCS_PUB_BYTES)
 #define KLM_TC_TRACE_TICKS  16
 
 #define KLM_TC_REC  0
@@ -123,7 +122,8 @@ struct KlmTcRole {
     int ring_bytes;    // bytes in front of the barriers (>= stages * chunk and >= KLM_TC1_ALIAS_BYTES)
     int pub;           // REC: 0 = scattered 4-byte stores, 1 = staged in shared memory + coalesced 16-byte stores,
                        //      2 = staged + one bulk async store (1 and 2 need slices aligned to 8 units)
-    int pad_;
+    int ring_ofs;      // streamed-weights form: byte offset of the ring (behind the hand-over buffer and, REC only, the
+                       // publication staging of this CTA's slice)
 };
 
 struct KlmTcParams {

@@ -63,7 +63,7 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
     const unsigned char *bsrc = x.bsrc;
     const int nticks = x.nticks, crot = x.crot;
     const unsigned G = x.G;
-    const int trace_mode = p.trace_mode, skip = p.debug_skip, cfence = p.consumer_fence;
+    const int trace_mode = p.trace_mode, skip = TRACE ? p.debug_skip : 0, cfence = p.consumer_fence;   // (timing experiments: traced instantiations only)
     const unsigned char *hx0 = reinterpret_cast<const unsigned char *>(p.hx + (size_t)(x.src_layer * 2) * x.W * 128);
     const size_t hx_par = (size_t)x.W * 128 * sizeof(__half);
     uint32_t phbits = 0;                                   // bit st: uses of slot st so far, mod 2
@@ -145,7 +145,7 @@ __device__ __noinline__ void tc_mma_fixed(const KlmTcParams &p, const TcLoopCtx 
     const uint32_t bar_full = x.bar_full, bar_empty = x.bar_empty, bar_tfull = x.bar_tfull, bar_tempty = x.bar_tempty;
     const uint32_t tmem_base = x.tmem_base;
     const int nticks = x.nticks, crot = x.crot;
-    const int trace_mode = p.trace_mode, skip = p.debug_skip;
+    const int trace_mode = p.trace_mode, skip = TRACE ? p.debug_skip : 0;
     uint32_t phbits = 0;
     for (int tick = 0; tick < nticks; ++tick) {
         // the whole warp runs this loop converged; the elected lane (always lane 0) issues
@@ -245,7 +245,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
     // ---- shared memory carve-up ----
     // resident form: [ring, aliased by hand-over + publication staging][barriers][B image]
     // streamed form: [hand-over][publication staging][ring of (A chunk | B chunk) slots][barriers]
-    unsigned char *ring = smem + (STREAM ? KLM_TCS_RING_OFS : 0);        // S chunks of the A operand
+    unsigned char *ring = smem + (STREAM ? role.ring_ofs : 0);           // S chunks of the A operand
     float *xchg = reinterpret_cast<float *>(smem);                       // hi<->lo hand-over
     __half *pubbuf = reinterpret_cast<__half *>(smem + KLM_TC1_PUB_OFS); // publication staging
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + role.ring_bytes);
