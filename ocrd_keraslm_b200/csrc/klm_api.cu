@@ -346,16 +346,19 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
     }
     // streamed-weights form: the B images stay in global memory; every ring slot carries an A chunk of 64 k and the
     // matching part of the image.  Slices are even numbers of pairs (a slice of more than 16 pairs is multiplied in two
-    // MMAs of N = 8 * pairs columns, and N must be a multiple of 16); compile-time ring geometries exist for W = 1024.
+    // MMAs of N = 8 * pairs columns, and N must be a multiple of 16); compile-time ring geometries (3 slots) exist for
+    // W = 512, 768, 1024, 1536 and 2048.
     auto stream_slot = [&](int np) { return 64 * 256 + 64 * 32 * np; };
     // in front of the ring: the hi<->lo hand-over buffer and, in REC CTAs, the publication staging of the slice
     auto stream_ring_ofs = [&](int np, bool rec) { return KLM_TC1_PUB_OFS + (rec ? (np + 3) / 4 * 2048 : 0); };
     // (1 KB of static shared memory belongs to the LSE role; a 4th slot fits REC slices of 16 pairs but made the
     //  tick 3 % slower: cfg5 3.99 M -> 3.88 M chars/s)
-    const size_t stream_max_stages = getenv("KLM_TCS_STAGES") ? (size_t)atoi(getenv("KLM_TCS_STAGES")) : 3;
+    const size_t stream_max_stages = 3;
     auto stream_stages = [&](int np, bool rec) {
         return (int)std::min<size_t>(stream_max_stages, (m->smem_optin - 1024 - 128 - stream_ring_ofs(np, rec)) / (size_t)stream_slot(np)); };
-    if (!planned && W / 64 == 16 && !getenv("KLM_DISABLE_TCS")) {
+    const int nch64 = W / 64;
+    const bool stream_geom = W % 64 == 0 && (nch64 == 8 || nch64 == 12 || nch64 == 16 || nch64 == 24 || nch64 == 32);
+    if (!planned && stream_geom && !getenv("KLM_DISABLE_TCS")) {
         pl.Vp = (V + 15) / 16 * 16;
         pmax = 0;
         for (int np = 2; np <= KLM_TCS_MAX_PAIRS; np += 2) if (stream_stages(np, true) >= 3) pmax = np;

@@ -189,7 +189,7 @@ __device__ __noinline__ void tc_mma_fixed(const KlmTcParams &p, const TcLoopCtx 
 }
 
 #define TC_FIXED_GEOMS(F) F(64, 8, 4) F(64, 8, 3) F(32, 16, 4) F(64, 4, 4) F(128, 4, 3) F(128, 4, 2)
-#define TC_STREAM_GEOMS(F) F(64, 16, 4) F(64, 16, 3) F(64, 16, 2)
+#define TC_STREAM_GEOMS(F) F(64, 8, 3) F(64, 12, 3) F(64, 16, 3) F(64, 24, 3) F(64, 32, 3)     // widths 512, 768, 1024, 1536, 2048
 
 template <bool STREAM, bool TRACE>
 static __device__ __forceinline__ bool tc_run_fixed(bool producer, const KlmTcParams &p, const TcLoopCtx &x, int kc, int nch, int S) {

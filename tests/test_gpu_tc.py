@@ -91,6 +91,28 @@ def test_tc_streamed_weights_width_1024_matches_oracle(depth, n_docs, nctx):
     assert worst <= 1e-3, worst
 
 
+@pytest.mark.parametrize('width,depth,n_docs', [(512, 4, 64), (768, 2, 30), (1536, 2, 12)])
+def test_tc_streamed_weights_other_widths_match_oracle(width, depth, n_docs):
+    """Models that do not fit the resident plan at other widths (ring geometries of 8, 12, 24 chunks)."""
+    wd = synth.weights(13 + width, width=width, depth=depth, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 32)
+    assert r._native.info()['tc_enabled'] == 3
+    rng = np.random.default_rng(width + depth)
+    sizes = rng.integers(2, 12, n_docs)
+    texts = [synth.text(3700 + i, int(s)) for i, s in enumerate(sizes)]
+    ctxs = [[int(rng.integers(0, 200))] for _ in texts]
+    before = r._native.info()['tc_launches']
+    got = r.rate_many(texts, ctxs)
+    assert r._native.info()['tc_launches'] > before
+    o = OracleRater(util.to_model(wd), synth.mapping_from_array(maparr), 32, logger=quiet)
+    worst = 0.0
+    for i in sorted({0, 1, n_docs // 2, n_docs - 1}):
+        ref, _ = o.rate2(texts[i], ctxs[i])
+        worst = max(worst, logp_err(got[i], [p for _, p in ref]))
+    assert worst <= 1e-3, worst
+
+
 def test_tc_states_and_carry_match_oracle():
     """Hidden and cell states after a launch (1e-4 relative) and a second launch continuing from them."""
     width, depth, n = 128, 2, 12
