@@ -165,6 +165,9 @@ typedef struct klm_info {
     int32_t tc_grid;            /* CTAs of the tcgen05 kernel */
     int32_t tc_smem_bytes;      /* dynamic shared memory per CTA of the tcgen05 kernel */
     int64_t tc_launches;        /* launches of the tcgen05 kernel so far */
+    int64_t cl_launches;        /* launches of the one-cluster kernel (<= 8 streams, small models) so far */
+    int32_t cl_cluster;         /* CTAs of that cluster (8 or 16); 0 = the model does not fit one cluster */
+    int32_t reserved_;
 } klm_info;
 int klm_get_info(klm_model *m, klm_info *out);
 

@@ -67,7 +67,8 @@ class KlmInfo(ctypes.Structure):
     _fields_ = [('sm_count', ctypes.c_int32), ('grid', ctypes.c_int32), ('weights_in_smem', ctypes.c_int32),
                 ('smem_bytes', ctypes.c_int32), ('kernel_launches', ctypes.c_int64),
                 ('last_kernel_ms', ctypes.c_double), ('max_streams', ctypes.c_int32), ('tc_enabled', ctypes.c_int32),
-                ('tc_grid', ctypes.c_int32), ('tc_smem_bytes', ctypes.c_int32), ('tc_launches', ctypes.c_int64)]
+                ('tc_grid', ctypes.c_int32), ('tc_smem_bytes', ctypes.c_int32), ('tc_launches', ctypes.c_int64),
+                ('cl_launches', ctypes.c_int64), ('cl_cluster', ctypes.c_int32), ('reserved_', ctypes.c_int32)]
 
 
 # every symbol include/keraslm_b200.h declares: (name, restype, argtypes)

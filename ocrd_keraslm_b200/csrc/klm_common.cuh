@@ -73,6 +73,18 @@ struct KlmSeqParams {
     int debug;                    // KLM_LL_DEBUG: every CTA prints its mean clocks per tick spent waiting / computing
 };
 
+// One-cluster kernel (klm_seq_cl): geometry chosen by the host
+#define KLM_CL_RING   4      // ticks of exchange words kept in every CTA's shared memory
+#define KLM_CL_MAXT   4      // tasks (units / groups of 4 vocabulary rows) per warp
+#define KLM_CL_PUBS   8      // words a thread publishes per tick at most ((D U C + 4 PU) B <= 8 * 512)
+struct KlmClGeom {
+    int C;         // CTAs in the cluster (8 or 16)
+    int U;         // units of every layer owned by one CTA (W / C)
+    int PU;        // groups of 4 vocabulary rows owned by one CTA (ceil(V4 / C))
+    int ntask;     // D * U + PU
+    int w4;        // float4s of one CTA's weight slices
+};
+
 // ---------------------------------------------------------------------------------------------
 // Tensor-core sequence kernel (klm_seq_tc.cu)
 #define KLM_TC_THREADS      320                    // producer warp, MMA warp, 8 epilogue warps

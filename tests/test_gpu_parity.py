@@ -257,6 +257,35 @@ def test_value_tick_exchange_kernel_over_many_ring_turns(n_docs):
         assert_logp_close(first[i], [p for _, p in ref])
 
 
+@pytest.mark.parametrize('width,depth,n_docs', [(128, 2, 1), (128, 3, 2), (64, 2, 5), (128, 1, 3)])
+def test_one_cluster_kernel_matches_oracle(monkeypatch, width, depth, n_docs):
+    """klm_seq_cl (opt-in): the model in one thread-block cluster, recurrence exchanged through distributed shared
+    memory; ragged streams, carried state out of the launch, twice in a row."""
+    monkeypatch.setenv('KLM_ENABLE_CL', '1')
+    wd = synth.weights(41 + width, width=width, depth=depth, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 32)
+    assert r._native.info()['cl_cluster'] in (8, 16)
+    o = oracle_for(wd, maparr, 32)
+    sizes = [150, 2, 40, 33, 90][:n_docs]
+    texts = [synth.text(3300 + i, s) for i, s in enumerate(sizes)]
+    ctxs = [[i * 11] for i in range(n_docs)]
+    first = r.rate_many(texts, ctxs)
+    assert r._native.info()['cl_launches'] >= 1
+    again = r.rate_many(texts, ctxs)
+    for i, (t, c) in enumerate(zip(texts, ctxs)):
+        np.testing.assert_array_equal(first[i], again[i])
+        ref, _ = o.rate2(t, c)
+        assert_logp_close(first[i], [p for _, p in ref])
+    # stateful single-text rating with carry (Rater.rate), against the oracle
+    r.reset_states()
+    o.reset_states()
+    a = r.rate(texts[0], ctxs[0])
+    b = r.rate(texts[0], ctxs[0])
+    assert_logp_close(a, o.rate(texts[0], ctxs[0]))
+    assert_logp_close(b, o.rate(texts[0], ctxs[0]))
+
+
 def test_states_after_rate_match_oracle():
     wd = synth.weights(3, width=128, depth=3, voc_size=256, style='trained')
     maparr = synth.vocabulary()
