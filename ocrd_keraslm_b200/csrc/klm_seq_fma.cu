@@ -540,6 +540,7 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
 #pragma unroll
                     for (int bb = 0; bb < BT; ++bb) acc[bb] = make_float4(0.f, 0.f, 0.f, 0.f);
                     const float4 *wrow = wptr + (size_t)ui * K;
+#pragma unroll 4
                     for (int k = lane; k < K; k += 32) {
                         const float4 w = wrow[k];
 #pragma unroll
