@@ -68,6 +68,10 @@ int klm_destroy(klm_model *m);
 /* Message of the last failure on this thread ("" if none). */
 const char *klm_last_error(void);
 
+/* sizeof(klm_config) (what = 0) / sizeof(klm_info) (what = 1) as this library was compiled: lets a binding check its
+ * own struct declarations before it passes them in. */
+int klm_abi_sizeof(int what);
+
 /* Run subsequent work on this CUDA stream (a cudaStream_t; NULL = the library's own stream). */
 int klm_set_stream(klm_model *m, void *cuda_stream);
 /* Block until everything enqueued on the model's stream has finished. */

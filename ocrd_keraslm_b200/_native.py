@@ -78,6 +78,7 @@ SYMBOLS = [
     ('klm_create', ctypes.c_int, [ctypes.POINTER(KlmConfig), ctypes.POINTER(_P), ctypes.c_int, ctypes.POINTER(_P)]),
     ('klm_destroy', ctypes.c_int, [_P]),
     ('klm_last_error', ctypes.c_char_p, []),
+    ('klm_abi_sizeof', ctypes.c_int, [ctypes.c_int]),
     ('klm_set_stream', ctypes.c_int, [_P, _P]),
     ('klm_sync', ctypes.c_int, [_P]),
     ('klm_state_pool_resize', ctypes.c_int, [_P, _I]),

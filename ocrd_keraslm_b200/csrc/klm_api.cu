@@ -42,6 +42,7 @@ static int fail(int code, const char *fmt, ...) {
     } while (0)
 
 extern "C" const char *klm_last_error(void) { return g_err.c_str(); }
+extern "C" int klm_abi_sizeof(int what) { return what == 0 ? (int)sizeof(klm_config) : what == 1 ? (int)sizeof(klm_info) : -1; }
 
 // ------------------------------------------------------------------------------------------
 struct KlmPlan {

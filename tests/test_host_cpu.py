@@ -1,6 +1,7 @@
 """CPU-only tests: the C-ABI library loads and exports every declared symbol, host logic of the
 drop-in Rater that needs no device (model file round trip, vocabulary mapping, CuDNN weight
 conversion, Node semantics), and the multi-rank sharding logic over gloo (world_size 2)."""
+import ctypes
 import os
 import re
 import subprocess
@@ -32,6 +33,13 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), name
     bound = set(n for n, _, _ in _native.SYMBOLS)
     assert set(names) <= bound, set(names) - bound
+
+
+def test_ctypes_structs_have_the_size_the_library_was_compiled_with():
+    lib = _native.load()
+    assert lib.klm_abi_sizeof(0) == ctypes.sizeof(_native.KlmConfig)
+    assert lib.klm_abi_sizeof(1) == ctypes.sizeof(_native.KlmInfo)
+    assert lib.klm_abi_sizeof(7) == -1
 
 
 def test_no_cpu_fallback_without_device():
