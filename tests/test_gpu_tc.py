@@ -167,6 +167,28 @@ def test_tc_step_full_rows_match_fma():
     np.testing.assert_allclose(np.stack(p2).sum(axis=1), 1.0, rtol=1e-5)
 
 
+def test_tcs_step_full_rows_and_states_match_fma():
+    """klm_step (Rater.predict: one tick, full softmax rows, states handed back) through the streamed-weights kernel at
+    width 1024 against the FMA K-parallel kernel (n <= 8) on the same inputs."""
+    wd = synth.weights(79, width=1024, depth=2, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 8, stateful=False, incremental=True)
+    assert r._native.info()['tc_enabled'] == 3
+    cands = [chr(97 + i % 26) for i in range(24)]
+    p1, s1 = r.predict(list(cands), [None] * 24, [3])
+    p2, s2 = r.predict(list(cands), list(s1), [3])
+    assert r._native.info()['tc_launches'] >= 2
+    for lo in range(0, 24, 8):
+        q1, t1 = r.predict(cands[lo:lo + 8], [None] * 8, [3])
+        q2, t2 = r.predict(cands[lo:lo + 8], list(t1), [3])
+        assert logp_err(np.stack(p1[lo:lo + 8]), np.stack(q1)) <= 1e-3
+        assert logp_err(np.stack(p2[lo:lo + 8]), np.stack(q2)) <= 1e-3
+        a = np.stack([np.concatenate(list(s), 0) for s in s2[lo:lo + 8]])
+        b = np.stack([np.concatenate(list(s), 0) for s in t2])
+        assert np.abs(a - b).max() <= 1e-4 * np.abs(b).max()
+    np.testing.assert_allclose(np.stack(p2).sum(axis=1), 1.0, rtol=1e-5)
+
+
 def test_umma2_selftest_cta_pair_layout():
     """tcgen05.mma.cta_group::2 (M = 128 over a CTA pair): operand split, multicast commit and the 2x2 accumulator layout."""
     from ocrd_keraslm_b200 import _native
