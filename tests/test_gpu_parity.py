@@ -286,6 +286,26 @@ def test_one_cluster_kernel_matches_oracle(monkeypatch, width, depth, n_docs):
     assert_logp_close(b, o.rate(texts[0], ctxs[0]))
 
 
+def test_rate_many_degenerate_inputs():
+    """Empty list, empty strings and one-character texts next to ordinary ones; non-BMP characters (one code point,
+    unmapped -> logged, index 0 like the reference's unknown characters)."""
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, 8)
+    assert r.rate_many([]) == []
+    texts = ['', 'a', 'abc', '', 'ab\U0001F600cd', 'x']
+    got = r.rate_many(texts)
+    assert [len(g) for g in got] == [len(t) for t in texts]
+    assert all(g[0] == 1.0 for g in got if len(g))
+    o = oracle_for(wd, maparr, 8)
+    for i in (2, 4):
+        ref, _ = o.rate2(texts[i])
+        assert_logp_close(got[i], [p for _, p in ref])
+    r.GATHER_MAX_MEAN_LENGTH = 0              # the per-text slicing path
+    again = r.rate_many(texts)
+    for a, b in zip(got, again):
+        np.testing.assert_array_equal(a, b)
+
+
 def test_states_after_rate_match_oracle():
     wd = synth.weights(3, width=128, depth=3, voc_size=256, style='trained')
     maparr = synth.vocabulary()
