@@ -16,6 +16,8 @@ Our arm prints ONE JSON line with
   roofline     the persistent sequence kernel against the measured tensor peak (MEASURED_PEAKS.json)
   cpu_baseline the CPU oracle (oracle/, a port: the reference's Keras CPU path cannot be installed
                here) timed on the host cores on a bounded sample (rank 0, N=1 only)
+  cpu_baseline_torch  a second, stronger CPU line: all documents batched through torch CPU
+               (oracle/lstm_torch_cpu.py), so that the speed-up is not inflated by a slow baseline
 `--impl reference` times that CPU arm alone, on the same config, with every host core.
 Multi-GPU (torchrun): documents are independent, every rank rates its own batch, no data-path
 collective; NCCL only carries the timing reduction and a checksum.
@@ -143,6 +145,37 @@ class CpuArm(object):
             self.pool.close()
             self.pool.join()
             self.pool = None
+
+
+def torch_cpu_line(workload, rater_indices, seconds=8.0):
+    """Second, stronger CPU line: ALL documents of the workload advance together through
+    oracle/lstm_torch_cpu.py (one addmm per layer and tick, torch CPU on all host cores) -- not the reference's
+    call structure (batch 1), so it is reported beside `cpu_baseline`, not in its place.  Bounded sample: the first
+    characters of every document, sized from a short calibration run to about `seconds` of CPU work."""
+    import torch
+    from tests import util
+    from oracle.lstm_torch_cpu import TorchCpuModel
+    width, depth, length, contexts, docs, chars, what = WORKLOADS[workload]
+    if workload in ('cfg3', 'cfg5'):
+        return None                                   # beams / ragged lines: the batched form has no fixed shape
+    model = TorchCpuModel(util.to_model(model_weights(workload)))
+    cal = 24
+    n_max = min(chars, 4096)
+    texts, ctxs = make_docs(workload, docs, n_max + 1, 0)
+    idx = np.stack([rater_indices(t)[:n_max + 1] for t in texts]).astype(np.int64)
+    zs = [np.array([c[k] for c in ctxs], dtype=np.int64) for k in range(len(contexts))]
+    model.rate(idx[:, :cal], zs, idx[:, 1:cal + 1])
+    t0 = time.perf_counter()
+    model.rate(idx[:, :cal], zs, idx[:, 1:cal + 1])
+    per_tick = (time.perf_counter() - t0) / cal
+    n = int(max(64, min(n_max, seconds / per_tick)))
+    t0 = time.perf_counter()
+    logp, _ = model.rate(idx[:, :n], zs, idx[:, 1:n + 1])
+    dt = time.perf_counter() - t0
+    return {'value': docs * n / dt, 'unit': 'chars/s', 'cores': torch.get_num_threads(),
+            'kind': 'port (batched: all %d documents per addmm, torch CPU / MKL; stronger than the reference call structure)' % docs,
+            'sample': '%d documents x first %d chars together (of %s), %.1f s' % (docs, n, what, dt),
+            'checksum_logp': float(logp.astype(np.float64).sum())}
 
 
 def cpu_sample_chars(workload):
@@ -367,7 +400,7 @@ def run_ours(args):
             raise SystemExit('bench.py --gpus %d must be launched with torchrun (one rank per GPU)' % args.gpus)
         args.gpus = world
     # ---- CPU baseline beside it (rank 0, N=1 only); runs first, before CUDA is initialised (it forks) ----
-    cpu_line = None
+    cpu_line = torch_line = None
     if world == 1 and not args.no_cpu:
         arm = CpuArm(args.workload)
         n_chars = cpu_sample_chars(args.workload)
@@ -375,6 +408,8 @@ def run_ours(args):
         arm.step(min(n_chars, 129))
         c, dt = arm.step(n_chars)
         arm.close()
+        vocab_map = synth.mapping_from_array(synth.vocabulary())[0]
+        torch_line = torch_cpu_line(args.workload, lambda t: np.array([vocab_map.get(ch, 0) for ch in t], dtype=np.int64))
         cpu_line = {
             'value': c / dt, 'unit': 'chars/s', 'cores': arm.procs, 'kind': 'port',
             'sample': '%d processes x 1 document x %d chars (of %s), %.1f s' % (arm.procs, n_chars,
@@ -523,6 +558,8 @@ def run_ours(args):
 
     if cpu_line is not None:
         line['cpu_baseline'] = cpu_line
+        if torch_line is not None:
+            line['cpu_baseline_torch'] = torch_line
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

@@ -178,3 +178,22 @@ def test_cell_math_against_torch_lstm():
         np.testing.assert_allclose(c[0].numpy(), states[2 * l + 1], rtol=2e-5, atol=2e-6)
     ref = torch.softmax(inp @ torch.from_numpy(m.E).T, dim=-1).numpy()
     np.testing.assert_allclose(probs, ref, rtol=1e-4, atol=1e-7)
+
+
+def test_torch_cpu_baseline_matches_numpy_oracle():
+    """bench.py's second CPU line (oracle/lstm_torch_cpu.py: all streams batched, torch CPU) computes what the
+    numpy oracle computes: log-probabilities of the targets and the final states, 3 context variables."""
+    from oracle.lstm_torch_cpu import TorchCpuModel
+    wd = synth.weights(11, width=40, depth=3, voc_size=64, contexts=((200, 16),) * 3, style='trained')
+    m = util.to_model(wd)
+    rng = np.random.default_rng(3)
+    n, T = 5, 33
+    x = rng.integers(0, 64, (n, T))
+    y = rng.integers(0, 64, (n, T))
+    z = [rng.integers(0, 200, n) for _ in range(3)]
+    p, states = ln.run_sequence(m.astype(np.float64), x, [np.repeat(v[:, None], T, axis=1) for v in z],
+                                ln.zero_states(m, n, np.float64), want='target', targets=y)
+    logp, st = TorchCpuModel(m).rate(x, z, y)
+    np.testing.assert_allclose(logp, np.log(p), atol=1e-4)          # the bar of the GPU path is 1e-3 nats
+    for a, b in zip(st, states):
+        np.testing.assert_allclose(a.numpy(), b, rtol=1e-4, atol=1e-5)
