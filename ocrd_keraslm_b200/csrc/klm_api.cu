@@ -407,6 +407,11 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
                 r.kc = geoms[g][0]; r.stages = std::min(geoms[g][1], W / r.kc); r.ring_bytes = ring_bytes_of(g);
             }
             r.pub = t.kind == KLM_TC_REC ? pl.pub : 0;
+            // IN / PROJ of the resident form: the slice of Z / of the logits (2 KB per pair) staged behind the hand-over
+            // buffer on the idle ring and written with one bulk async store (KLM_TC_ZPUB=0: per-thread stores + release)
+            if (t.kind != KLM_TC_REC && !pl.stream_b && pl.pub == 2 && r.ring_bytes >= KLM_TC1_PUB_OFS + np * 2048 &&
+                !(getenv("KLM_TC_ZPUB") && atoi(getenv("KLM_TC_ZPUB")) == 0))
+                r.pub = 2;
             pl.roles.push_back(r);
             smem = std::max(smem, (size_t)r.ring_bytes + 128 + (pl.stream_b ? 0 : (size_t)32 * W * np));
             const size_t o = img.size();
@@ -458,8 +463,8 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
     CK(cudaMalloc(&pl.d_wimg, img.size() * sizeof(__half)));
     CK(cudaMemcpy(pl.d_wimg, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
     const size_t hx_bytes = (size_t)D * 2 * W * 128 * sizeof(__half);
-    const size_t z_bytes = (size_t)D * 2 * 64 * 4 * W * sizeof(float);
-    const size_t lg_bytes = (size_t)2 * 64 * pl.Vp * sizeof(float);
+    const size_t z_bytes = (size_t)D * 4 * 64 * 4 * W * sizeof(float);       // 4 slots (skew 3; skew 2 uses two)
+    const size_t lg_bytes = (size_t)4 * 64 * pl.Vp * sizeof(float);
     CK(cudaMalloc(&pl.hx, hx_bytes)); CK(cudaMemset(pl.hx, 0, hx_bytes));
     CK(cudaMalloc(&pl.Z, z_bytes)); CK(cudaMemset(pl.Z, 0, z_bytes));
     CK(cudaMalloc(&pl.logits, lg_bytes)); CK(cudaMemset(pl.logits, 0, lg_bytes));
@@ -930,7 +935,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     if (rc) return rc;
     if (m->tc.ok && nb > KLM_MODEK_MAXB && nb <= KLM_TC_STREAMS) {
         KlmTcPlan &tp = m->tc2.ok ? m->tc2 : m->tc;
-        if ((double)(tmax + 2 * m->D + 2) * tp.grid >= 4.0e9)
+        if ((double)(tmax + 3 * m->D + 2) * tp.grid >= 4.0e9)
             return fail(KLM_EINVAL, "stream of %lld positions is too long for one launch", tmax);
         KlmTcParams q;
         memset(&q, 0, sizeof q);
@@ -960,6 +965,16 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         q.debug_skip = getenv("KLM_TC_DEBUG_SKIP") ? atoi(getenv("KLM_TC_DEBUG_SKIP")) : 0;
         q.poll_mode = getenv("KLM_TC_POLL") ? atoi(getenv("KLM_TC_POLL")) : 0;
         q.stream_b = tp.stream_b;
+        // long launches: skew 3 (the recurrence does not wait for the IN / PROJ epilogues; D more ticks of pipeline fill);
+        // short ones (beam steps) and the CTA-pair kernel: skew 2
+        {
+            // (streamed-weights form: measured slower with skew 3 on the short lines of cfg5, 3.73 M against 3.90 M chars/s)
+            const int want = getenv("KLM_TC_SKEW") ? atoi(getenv("KLM_TC_SKEW")) : (tmax >= 64 && !tp.stream_b ? 3 : 2);
+            q.skew = (want == 3 && &tp != &m->tc2) ? 3 : 2;
+            q.zmask = q.skew == 3 ? 3 : 1; q.zlag = q.skew == 3 ? 2 : 1;
+        }
+        q.zpub_early = getenv("KLM_TC_ZPUB") && atoi(getenv("KLM_TC_ZPUB")) == 2;
+        q.pub_release = getenv("KLM_TC_PUB_RELEASE") ? atoi(getenv("KLM_TC_PUB_RELEASE")) : 0;
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         q.kc = tp.kc; q.ring_bytes = tp.ring_bytes;
         if (&tp == &m->tc2) CK(klm_launch_seq_tc2(q, tp.grid, tp.smem, m->stream));

@@ -169,5 +169,14 @@ struct KlmTcParams {
     int trace_mode;               // 0: phase events; 1: arrival of chunk c in event slot c; 2: issue of the copy of chunk c;
                                   // 3: producer steps; 4: epilogue phases of one thread (accumulators complete, per round: drained,
                                   //    hand-over read, finished; arrive)
+    int skew;                     // ticks between the REC stages of consecutive layers: 2 = every CTA signals the grid barrier at the
+                                  //   end of its tick; 3 = IN / PROJ CTAs signal as soon as their MMAs have read the operand, their
+                                  //   epilogue runs into the next tick and Z / the logits are consumed two ticks after the GEMM
+                                  //   (stages: REC l at skew*l, IN l at skew*l - (skew-1), PROJ at skew*D - (skew-1), LSE at skew*D)
+    int zmask, zlag;              // Z / logits slots: written at slot (tick+1) & zmask, read at (tick+1-zlag) & zmask
+                                  //   (skew 2: zmask 1, zlag 1; skew 3: zmask 3, zlag 2)
+    int zpub_early;               // 1: IN / PROJ stage their slice and bulk-store it also with the early signal (KLM_TC_ZPUB=2)
+    int pub_release;              // 1: a REC CTA signals with red.release.gpu after its bulk store (default 0: the store has been
+                                  //    waited for, a relaxed add follows it; KLM_TC_PUB_RELEASE=1 restores the release)
     int stream_b;                 // 1: streamed-weights form (B chunks travel through the ring with the A chunks)
 };

@@ -46,8 +46,8 @@
 // issued before the grid barrier and land while the previous tick's epilogue and hand-over are still going on.
 // With more than 128 columns per half the chunk is multiplied in two MMAs (hi columns, lo columns) of N = 8 * pairs.
 struct TcLoopCtx {
-    uint32_t ring_a, bar_full, bar_empty, bar_tfull, bar_tempty, bar_go, tmem_base, wsm_a;
-    int nticks, N, crot, src_layer, W;
+    uint32_t ring_a, bar_full, bar_empty, bar_tfull, bar_tempty, bar_go, tmem_base, wsm_a, bar_epid;
+    int nticks, N, crot, src_layer, W, guard;
     unsigned G;
     uint32_t slot_bytes, cbb;              // STREAM: bytes per ring slot (A chunk + B chunk), bytes of a B chunk
     const unsigned char *bsrc;             // STREAM: this CTA's B image in global memory
@@ -63,6 +63,8 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
     const unsigned char *bsrc = x.bsrc;
     const int nticks = x.nticks, crot = x.crot;
     const unsigned G = x.G;
+    const int guard = x.guard;
+    const uint32_t bar_epid = x.bar_epid;
     const int trace_mode = p.trace_mode, skip = TRACE ? p.debug_skip : 0, cfence = p.consumer_fence;   // (timing experiments: traced instantiations only)
     const unsigned char *hx0 = reinterpret_cast<const unsigned char *>(p.hx + (size_t)(x.src_layer * 2) * x.W * 128);
     const size_t hx_par = (size_t)x.W * 128 * sizeof(__half);
@@ -85,6 +87,10 @@ __device__ __noinline__ void tc_produce_fixed(const KlmTcParams &p, const TcLoop
                 }
             }
             __syncwarp();
+        }
+        if (guard && tick > 0) {       // (IN / PROJ with the early signal: the previous epilogue has left the aliased buffers)
+            int oke = tc_wait_mbar(bar_epid, (uint32_t)(tick - 1) & 1u, p, 7) ? 1 : 0;
+            if (!__all_sync(0xffffffffu, oke)) return;
         }
         int okg = 1;
         if (lane0) {
@@ -236,7 +242,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int W = p.W, S = role.stages, kc = role.kc;
     const unsigned G = gridDim.x;
-    const int nticks = p.T_max + 2 * p.D;
+    const int nticks = p.T_max + p.skew * p.D;
     const int NP = role.npairs, N = 8 * NP;
     const int nchunks = W / kc;
     const uint32_t chunk_bytes = (uint32_t)kc * 256u;
@@ -248,12 +254,14 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
     unsigned char *ring = smem + (STREAM ? role.ring_ofs : 0);           // S chunks of the A operand
     float *xchg = reinterpret_cast<float *>(smem);                       // hi<->lo hand-over
     __half *pubbuf = reinterpret_cast<__half *>(smem + KLM_TC1_PUB_OFS); // publication staging
+    float4 *zstage = reinterpret_cast<float4 *>(smem + KLM_TC1_PUB_OFS); // IN / PROJ with pub == 2: the slice of Z / of the logits
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + role.ring_bytes);
     unsigned char *wsm = smem + role.ring_bytes + 128;                   // B image (resident form)
     const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + 4);
     const uint32_t bar_tfull = tc::smem_u32(bars + 8), bar_tempty = tc::smem_u32(bars + 9);
     const uint32_t bar_go = tc::smem_u32(bars + 10);       // producer -> epilogue: grid barrier of this tick passed
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 11);
+    const uint32_t bar_epid = tc::smem_u32(bars + 12);     // epilogue -> producer: done with the buffers that alias the ring
     if (warp == 0) {
         tc::tmem_alloc(tc::smem_u32(tmem_slot), TMEM_COLS);
         tc::tmem_relinquish();
@@ -263,6 +271,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
         tc::mbar_init(bar_tfull, 1);
         tc::mbar_init(bar_tempty, 256);
         tc::mbar_init(bar_go, 1);
+        tc::mbar_init(bar_epid, 1);
         tc::fence_mbar_init();
     }
     if (!STREAM) {   // B image: global -> shared, once per launch
@@ -284,6 +293,19 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
     const bool is_epi = warp >= 2;
     const bool is_rec = role.kind == KLM_TC_REC;
     const int l = role.layer;
+    // wavefront stage of this CTA (see KlmTcParams::skew)
+    const int sigma = is_rec ? p.skew * l : role.kind == KLM_TC_IN ? p.skew * l - (p.skew - 1) : p.skew * p.D - (p.skew - 1);
+    // skew 3: an IN / PROJ CTA signals the grid barrier once its MMAs have read the operand (the only thing of this tick the
+    // other CTAs wait for: the buffer it read is overwritten next tick); what it writes is consumed two ticks later and is
+    // covered by the signal of the next tick.  The recurrence (REC) no longer waits for the IN / PROJ epilogues.
+    const bool early = p.skew == 3 && !is_rec;
+    // resident form: hand-over buffer and staging alias the ring, so with the early signal the producer must not refill
+    // the ring before the epilogue of the previous tick is through
+    const bool guard = early && !STREAM;
+    // IN / PROJ: slice of Z / of the logits staged in shared memory and written by one bulk async store.  Pays when the
+    // signal follows the stores (skew 2: cfg2 12.88 M -> 13.38 M chars/s); with the early signal the stores are off the
+    // critical path and plain coalesced stores are as good or better (14.37 M against 14.23 M)
+    const bool zpub = !is_rec && role.pub == 2 && (!early || p.zpub_early);
 
     float c_reg[NR][KLM_TC_OWN][2], h_reg[NR][KLM_TC_OWN][2];
     long long o0 = 0;
@@ -324,7 +346,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
     lx.ring_a = tc::smem_u32(ring); lx.bar_full = bar_full; lx.bar_empty = bar_empty; lx.bar_tfull = bar_tfull;
     lx.bar_tempty = bar_tempty; lx.bar_go = bar_go; lx.tmem_base = tmem_base; lx.wsm_a = tc::smem_u32(wsm);
     lx.nticks = nticks; lx.N = N; lx.crot = (int)(blockIdx.x % (unsigned)nchunks); lx.src_layer = role.src_layer; lx.W = W;
-    lx.G = G;
+    lx.G = G; lx.guard = guard ? 1 : 0; lx.bar_epid = bar_epid;
     lx.cbb = (uint32_t)kc * 32u * (uint32_t)NP;            // kc/8 k groups x 2N rows x 16 bytes
     lx.slot_bytes = chunk_bytes + lx.cbb;
     lx.bsrc = p.wimg + role.wofs;
@@ -341,6 +363,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
             const uint32_t ring_a = tc::smem_u32(ring);
             bool ok = true;
             for (int tick = 0; tick < nticks && ok; ++tick) {
+                if (guard && tick > 0 && !tc_wait_mbar(bar_epid, (uint32_t)(tick - 1) & 1u, p, 7)) break;
                 if (!tc_wait_grid(p, (unsigned)(tick + 1) * G, 1)) break;
                 tc::mbar_arrive(bar_go);
                 if (TRACE && p.trace_mode == 0) tc_trace(p, tick, 0);
@@ -464,9 +487,10 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
             int ok = tc_wait_mbar(bar_go, tick & 1, p, 5) ? 1 : 0;
             ok = __all_sync(0xffffffffu, ok);
             if (!ok) break;
-            const int t = tick - role.sigma;
+            const int t = tick - sigma;
             const bool active = s < p.B && t >= 0 && t < len;
-            const int par_in = tick & 1, par_out = (tick + 1) & 1;
+            const int par_out = (tick + 1) & 1;                                         // hidden vectors: always one tick
+            const int nz = p.zmask + 1, zs_in = (tick + 1 - p.zlag) & p.zmask, zs_out = (tick + 1) & p.zmask;   // Z, logits
 
             // REC layer 1: the character index was fetched a tick ahead
             int x = 0;
@@ -509,7 +533,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 } else {
                     // Z is [layer][parity][unit][64 streams] float4: the lanes of a warp (consecutive streams) touch 512
                     // contiguous bytes per unit, on the IN side (stores) as well as here
-                    const float4 *zrow = reinterpret_cast<const float4 *>(p.Z) + (size_t)(l * 2 + par_in) * W * 64 + s;
+                    const float4 *zrow = reinterpret_cast<const float4 *>(p.Z) + (size_t)(l * nz + zs_in) * W * 64 + s;
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i)
                         if (i < rd[r].nown) {
@@ -526,6 +550,13 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
             ok = __all_sync(0xffffffffu, ok);
             if (!ok) break;
             if (TRACE && tid == 64 && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, p.trace_mode == 4 ? 0 : 4);
+            if (early && tid == 64) {
+                // the operand of this tick has been read.  What this CTA wrote in the previous tick: one bulk store that this
+                // thread has waited for (pub == 2), else generic stores of all epilogue threads, ordered in front of this
+                // release by the bar.sync that ended the previous tick
+                if (zpub && !p.pub_release) tc::red_relaxed_add(p.barrier, 1u);
+                else tc::red_release_add(p.barrier, 1u);
+            }
             tc::tc_fence_after();
 #pragma unroll
             for (int r = 0; r < NR; ++r) {
@@ -660,7 +691,11 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                             }
                     }
                 } else if (role.kind == KLM_TC_IN) {
-                    float4 *zrow = reinterpret_cast<float4 *>(p.Z) + (size_t)(l * 2 + par_out) * W * 64 + s;
+                    // a CTA's slice of Z ([unit][64 streams] float4) is one contiguous block of 2 KB per pair: with
+                    // role.pub == 2 it is staged in shared memory and leaves as one bulk async store (below), like the
+                    // hidden-vector slice of a REC CTA
+                    float4 *zrow = zpub ? zstage - (ptrdiff_t)(2 * role.first_pair) * 64 + s
+                                                 : reinterpret_cast<float4 *>(p.Z) + (size_t)(l * nz + zs_out) * W * 64 + s;
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i)
                         if (i < R.nown) {
@@ -668,19 +703,24 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
 #pragma unroll
                             for (int e = 0; e < 2; ++e) {
                                 const float4 b = KEEP ? bias4[KEEP ? r : 0][i][e] : __ldg(p.bias[l] + u + e);
-                                __stcg(zrow + (size_t)(u + e) * 64, make_float4(acc[i][4 * e] + b.x, acc[i][4 * e + 1] + b.y,
-                                                                 acc[i][4 * e + 2] + b.z, acc[i][4 * e + 3] + b.w));
+                                const float4 v = make_float4(acc[i][4 * e] + b.x, acc[i][4 * e + 1] + b.y,
+                                                             acc[i][4 * e + 2] + b.z, acc[i][4 * e + 3] + b.w);
+                                if (zpub) zrow[(size_t)(u + e) * 64] = v;
+                                else __stcg(zrow + (size_t)(u + e) * 64, v);
                             }
                         }
                 } else {   // PROJ: logits of vocabulary rows 8*(first_pair + pair) ..
                     // logits are [parity][Vp/4][64 streams] float4: coalesced over the streams of a warp (read by the LSE stage)
-                    float4 *lrow = reinterpret_cast<float4 *>(p.logits) + (size_t)par_out * (p.Vp / 4) * 64 + s;
+                    float4 *lrow = zpub ? zstage - (ptrdiff_t)(2 * role.first_pair) * 64 + s
+                                                 : reinterpret_cast<float4 *>(p.logits) + (size_t)zs_out * (p.Vp / 4) * 64 + s;
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i)
                         if (i < R.nown) {
                             const int g8 = pr0 + i;
-                            __stcg(lrow + (size_t)(2 * g8) * 64, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
-                            __stcg(lrow + (size_t)(2 * g8 + 1) * 64, make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]));
+                            const float4 v0 = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+                            const float4 v1 = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+                            if (zpub) { lrow[(size_t)(2 * g8) * 64] = v0; lrow[(size_t)(2 * g8 + 1) * 64] = v1; }
+                            else { __stcg(lrow + (size_t)(2 * g8) * 64, v0); __stcg(lrow + (size_t)(2 * g8 + 1) * 64, v1); }
                         }
                 }
                 if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 3 + 3 * r);      // ... round finished
@@ -704,7 +744,11 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                                          ::"l"(gdst), "r"(tc::smem_u32(pubbuf)), "r"((uint32_t)n16 * 16u) : "memory");
                             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                             asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // writes complete (not just read)
-                            tc::red_release_add(p.barrier, 1u);
+                            // everything this CTA hands over in a tick went through that one bulk store, and it has been
+                            // performed: a release (a gpu-scope fence in front of the add, ~900 clk on the recurrence:
+                            // scripts/ubench/pingpong.cu) has nothing left to order
+                            if (p.pub_release) tc::red_release_add(p.barrier, 1u);
+                            else tc::red_relaxed_add(p.barrier, 1u);
                             if (TRACE && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, 7);
                         }
                         continue;
@@ -717,9 +761,36 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 }
                 tc::fence_proxy_async();             // generic global writes -> bulk (async proxy) reads of other CTAs
             }
+            if (zpub) {
+                // IN / PROJ: the staged slice of Z / of the logits as one bulk async store; once it has been performed a
+                // relaxed add signals it (no generic global store of this CTA is outstanding)
+                float4 *gdst = role.kind == KLM_TC_IN
+                    ? reinterpret_cast<float4 *>(p.Z) + ((size_t)(l * nz + zs_out) * W + 2 * role.first_pair) * 64
+                    : reinterpret_cast<float4 *>(p.logits) + ((size_t)zs_out * (p.Vp / 4) + 2 * role.first_pair) * 64;
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // staging writes -> bulk store reads
+                if (TRACE && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
+                tc_bar_epi();
+                if (tid == 64) {
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                                 ::"l"(gdst), "r"(tc::smem_u32(zstage)), "r"((uint32_t)NP * 2048u) : "memory");
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+                    if (!early) {
+                        if (p.pub_release) tc::red_release_add(p.barrier, 1u);
+                        else tc::red_relaxed_add(p.barrier, 1u);
+                    }
+                    if (guard) tc::mbar_arrive(bar_epid);
+                    if (TRACE && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, 7);
+                }
+                continue;
+            }
             if (TRACE && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 6);
             tc_bar_epi();
-            if (tid == 64) { tc::red_release_add(p.barrier, 1u); if (TRACE && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, 7); }
+            if (tid == 64) {
+                if (!early) tc::red_release_add(p.barrier, 1u);
+                if (guard) tc::mbar_arrive(bar_epid);
+                if (TRACE && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, 7);
+            }
         }
         // ---- write the final state back ----
         if (is_rec && s < p.B) {

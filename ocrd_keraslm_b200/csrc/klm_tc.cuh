@@ -71,6 +71,12 @@ __device__ __forceinline__ void red_release_add(unsigned *p, unsigned v) {
     asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// relaxed form: for a thread whose only outstanding global writes are bulk async stores it has already waited for
+// (cp.async.bulk.wait_group 0: the writes have been performed at L2, the point of coherence of gpu scope)
+__device__ __forceinline__ void red_relaxed_add(unsigned *p, unsigned v) {
+    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 // ---- TMEM ----
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {      // whole warp
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");

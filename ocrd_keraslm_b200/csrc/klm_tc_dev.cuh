@@ -85,8 +85,8 @@ __device__ __forceinline__ void tc_split(float v, __half &hi, __half &lo) {
 static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role, unsigned char *dyn_smem) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const unsigned G = gridDim.x;
-    const int nticks = p.T_max + 2 * p.D;
-    const int V = p.V, Vq = p.Vp / 4, V4 = (V + 3) / 4, B = p.B, sigma = role.sigma, full_rows = p.full_rows;
+    const int nticks = p.T_max + p.skew * p.D;
+    const int V = p.V, Vq = p.Vp / 4, V4 = (V + 3) / 4, B = p.B, sigma = p.skew * p.D, full_rows = p.full_rows;
     const float4 *logits4 = reinterpret_cast<const float4 *>(p.logits);
     const int *targets = p.targets;
     float *out = p.out;
@@ -115,7 +115,7 @@ static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role, 
         if (p.trace && p.trace_mode == 0 && tid == 0) tc_trace(p, tick, 0);
         const int t = tick - sigma;
         const bool act = warp_on && s < B && t >= 0 && t < len;
-        const float4 *base = logits4 + (size_t)(tick & 1) * Vq * 64 + s;
+        const float4 *base = logits4 + (size_t)((tick + 1 - p.zlag) & p.zmask) * Vq * 64 + s;
         float tl = 0.f;
         if (act && sl == 0 && !full_rows) {
             int tg = __ldg(targets + o0 + t);

@@ -212,3 +212,57 @@ def test_cta_pair_kernel_matches_single_cta_kernel(monkeypatch):
     b = r.rate_many(texts, ctxs)
     for x, y in zip(a, b):
         assert logp_err(x, y) <= 1e-4
+
+
+@pytest.mark.parametrize('width,depth,nctx', [(128, 2, 1), (256, 3, 3), (512, 3, 1)])
+def test_tc_skew3_early_signal_matches_skew2_and_oracle(width, depth, nctx, monkeypatch):
+    """Launches of >= 64 positions run with skew 3 (IN / PROJ CTAs signal the grid barrier before their epilogue, Z and
+    the logits are consumed two ticks after the GEMM, 4 slots): bit-equal to the skew 2 schedule on ragged streams
+    (incl. empty and one-position ones) over two launches with carried state, final states equal, and oracle-close."""
+    from oracle import lstm_numpy as ln
+    n = 37
+    wd = synth.weights(77 + width, width=width, depth=depth, voc_size=256, contexts=((200, 10),) * nctx, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 64)
+    nat = r._native
+    assert nat.info()['tc_enabled'] == 1
+    rng = np.random.default_rng(width)
+    sizes = rng.integers(2, 200, n)
+    sizes[0], sizes[1], sizes[2] = 199, 1, 2                   # the longest decides the schedule; empty and single positions
+    texts = [synth.text(9000 + i, int(s)) for i, s in enumerate(sizes)]
+    ctx = [[int(x) for x in rng.integers(0, 200, nctx)] for _ in range(n)]
+    slots = r._pool.acquire(n)
+    results = {}
+    for skew in ('2', '3'):
+        monkeypatch.setenv('KLM_TC_SKEW', skew)
+        nat.state_reset(slots)
+        outs = []
+        for piece in (slice(0, 90), slice(89, None)):          # second launch continues from the carried state
+            idx = [r._indices(t[piece])[0] if len(t[piece]) else np.zeros(1, dtype=np.int32) for t in texts]
+            lens = np.array([max(len(i) - 1, 0) for i in idx])
+            offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+            chars = np.concatenate([i[:-1] for i in idx]).astype(np.int32)
+            targets = np.concatenate([i[1:] for i in idx]).astype(np.int32)
+            logp = np.full(len(chars), np.nan, dtype=np.float32)
+            nat.rate(slots, offsets, chars, targets, None, ctx, logp)
+            outs.append((idx, offsets, logp))
+        results[skew] = (outs, nat.state_to_host(slots))
+    monkeypatch.delenv('KLM_TC_SKEW')
+    (o2, s2), (o3, s3) = results['2'], results['3']
+    for (_, _, a), (_, _, b) in zip(o2, o3):
+        assert not np.isnan(b).any()
+        np.testing.assert_array_equal(a, b)
+    np.testing.assert_array_equal(s2, s3)
+    # oracle on a few streams (fp64), both launches chained
+    m = util.to_model(wd).astype(np.float64)
+    for k in (0, 2, 5, 11):
+        states = ln.zero_states(m, 1, np.float64)
+        for idx, offsets, logp in o3:
+            if len(idx[k]) < 2:
+                continue
+            x = idx[k][:-1][None, :].astype(np.int64)
+            z = [np.full_like(x, c) for c in ctx[k]]
+            out, states = ln.run_sequence(m, x, z, states, want='target', targets=idx[k][1:][None, :].astype(np.int64))
+            assert np.abs(logp[offsets[k]:offsets[k + 1]] - np.log(out[0])).max() <= 1e-3
+        ref = np.concatenate(states, axis=0)
+        assert np.abs(s3[k] - ref).max() <= 1e-4 * np.abs(ref).max()
