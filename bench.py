@@ -173,7 +173,7 @@ def torch_cpu_line(workload, rater_indices, seconds=8.0):
     logp, _ = model.rate(idx[:, :n], zs, idx[:, 1:n + 1])
     dt = time.perf_counter() - t0
     return {'value': docs * n / dt, 'unit': 'chars/s', 'cores': torch.get_num_threads(),
-            'kind': 'port (batched: all %d documents per addmm, torch CPU / MKL; stronger than the reference call structure)' % docs,
+            'kind': 'port (batched: all %d documents per addmm, torch CPU / MKL -- not the reference call structure)' % docs,
             'sample': '%d documents x first %d chars together (of %s), %.1f s' % (docs, n, what, dt),
             'checksum_logp': float(logp.astype(np.float64).sum())}
 
