@@ -6,6 +6,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -118,6 +119,10 @@ struct klm_model {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
     long long launches = 0, tc_launches = 0;
+    // KLM_STEP_TIMING=1: host-clock breakdown of klm_step / klm_beam_edge, printed by klm_destroy
+    int timing = 0;
+    long long t_steps = 0, t_edges = 0;
+    double t_step_total = 0, t_step_submit = 0, t_step_wait = 0, t_step_kernel_ms = 0, t_edge_total = 0;
 };
 
 // ------------------------------------------------------------------------------------------
@@ -602,6 +607,12 @@ template <typename T> static int upload(T **dst, const std::vector<T> &src) {
 extern "C" int klm_destroy(klm_model *m) {
     if (!m) return KLM_OK;
     cudaSetDevice(m->device);
+    if (m->timing && m->t_steps)
+        fprintf(stderr, "klm timing: %lld klm_step calls: %.1f us each (submit %.1f, wait for the device %.1f; kernels %.1f us on the "
+                "device); %lld klm_beam_edge calls: %.1f us each, of which klm_step %.1f %%\n", m->t_steps,
+                1e6 * m->t_step_total / m->t_steps, 1e6 * m->t_step_submit / m->t_steps, 1e6 * m->t_step_wait / m->t_steps,
+                1e3 * m->t_step_kernel_ms / m->t_steps, m->t_edges, m->t_edges ? 1e6 * m->t_edge_total / m->t_edges : 0.0,
+                m->t_edge_total > 0 ? 100.0 * m->t_step_total / m->t_edge_total : 0.0);
     if (m->stream) cudaStreamSynchronize(m->stream);
     cudaFree(m->P); cudaFree(m->Ep);
     for (int i = 0; i < KLM_MAX_CTX; ++i) cudaFree(m->Q[i]);
@@ -730,6 +741,7 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
     TRYC(cudaMemset(m->hbuf, 0, (size_t)D * 2 * W * m->bp_cap * 4));
     TRYC(cudaMalloc(&m->logits, (size_t)2 * m->V4 * m->bp_cap * 4));
     TRYC(cudaMemset(m->logits, 0, (size_t)2 * m->V4 * m->bp_cap * 4));
+    m->timing = getenv("KLM_STEP_TIMING") ? atoi(getenv("KLM_STEP_TIMING")) : 0;
     if (!getenv("KLM_DISABLE_LL")) {
         m->hbuf_ll_bytes = (size_t)KLM_LL_RING * D * W * KLM_MODEK_MAXB * sizeof(uint2);
         m->logits_ll_bytes = (size_t)KLM_LL_RING * 4 * m->V4 * KLM_MODEK_MAXB * sizeof(uint2);
@@ -1145,6 +1157,7 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
     if (!chars || !out) return fail(KLM_EINVAL, "klm_step: NULL argument");
     if (m->Nc > 0 && !ctx) return fail(KLM_EINVAL, "klm_step: model has %d context variables but ctx is NULL", m->Nc);
     CK(cudaSetDevice(m->device));
+    const auto tm0 = std::chrono::steady_clock::now();
     int rc = check_slots(m, slots_in, n, true, "klm_step"); if (rc) return rc;
     rc = check_slots(m, slots_out, n, false, "klm_step"); if (rc) return rc;
     for (int k = 0; k < m->Nc; ++k)
@@ -1192,8 +1205,18 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
         float *hout = reinterpret_cast<float *>(m->h_step + (size_t)n * 8);
         CK(cudaMemcpyAsync(hout, m->d_out, nout * 4, cudaMemcpyDeviceToHost, m->stream));
         rc = fetch_errors_async(m); if (rc) return rc;
+        const auto tm1 = std::chrono::steady_clock::now();
         CK(cudaStreamSynchronize(m->stream));
         memcpy(out, hout, nout * 4);
+        if (m->timing) {
+            const auto tm2 = std::chrono::steady_clock::now();
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, m->ev0, m->ev1);
+            m->t_steps++; m->t_step_kernel_ms += ms;
+            m->t_step_submit += std::chrono::duration<double>(tm1 - tm0).count();
+            m->t_step_wait += std::chrono::duration<double>(tm2 - tm1).count();
+            m->t_step_total += std::chrono::duration<double>(std::chrono::steady_clock::now() - tm0).count();
+        }
         return check_fetched_errors(m);
     }
     return KLM_OK;
@@ -1310,6 +1333,9 @@ extern "C" int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slo
         return fail(KLM_EINVAL, "klm_beam_edge: NULL argument");
     if (n_hyp < 0 || n_alt < 1 || batch_size < 1 || max_out < 0) return fail(KLM_EINVAL, "klm_beam_edge: bad sizes");
     *n_out = 0;
+    const auto te0 = std::chrono::steady_clock::now();
+    struct EdgeTimer { klm_model *m; std::chrono::steady_clock::time_point t0;
+        ~EdgeTimer() { if (m->timing) { m->t_edges++; m->t_edge_total += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); } } } edge_timer{m, te0};
     if (n_steps) *n_steps = 0;
     if (n_hyp_steps) *n_hyp_steps = 0;
     BeamLists L;

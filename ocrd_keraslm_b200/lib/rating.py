@@ -154,11 +154,17 @@ class _StatePool(object):
     def acquire(self, n):
         if len(self.free) < n:
             self._grow(max(2 * self.capacity, self.capacity + n))
-        out = [self.free.pop() for _ in range(n)]
+        if n <= 0:
+            return []
+        out = self.free[:-n - 1:-1]                # the same slots, in the same order, as n pops
+        del self.free[len(self.free) - n:]
         return out
 
     def release(self, slot):
         self.free.append(slot)
+
+    def release_many(self, slots):
+        self.free.extend(slots)
 
 
 class _DeviceModelView(object):
@@ -916,15 +922,12 @@ class Rater(object):
                 slots, last, cum, offsets, np.asarray(chars, dtype=np.int32), conf, context, lm_weight, self.batch_size,
                 scratch, beam_width)
         except Exception:
-            for sl in scratch:
-                self._pool.release(sl)
+            self._pool.release_many(scratch)
             raise
         self.device_steps += steps
         self.hypothesis_steps += hsteps
-        kept = set(int(x) for x in osl if x >= 0)
-        for sl in scratch:
-            if sl not in kept:
-                self._pool.release(sl)
+        kept = set(osl[osl >= 0].tolist())
+        self._pool.release_many([sl for sl in scratch if sl not in kept])
         del temps
         out = []
         for h, a, cost, sl in zip(oh, oa, oc, osl):
