@@ -20,6 +20,10 @@
 //   REC l: sigma = 2l, IN l: 2l-1, PROJ: 2D-1, LSE: 2D.   IN l writes Z_l[t] (+ bias), REC l adds it
 // one tick later, so each CTA needs exactly one hidden vector per tick.  One grid-wide barrier per
 // tick (release/acquire counter); everything handed over is double-buffered by tick parity.
+// Launches of >= 64 positions run with skew 3 instead (KlmTcParams::skew): REC l at 3l, IN l at 3l-2,
+// PROJ at 3D-2, LSE at 3D; IN / PROJ CTAs signal the barrier as soon as their MMAs have read the operand,
+// their epilogue runs into the next tick, Z and the logits live in 4 slots and are consumed two ticks
+// after the GEMM -- the recurrence (REC) never waits for an IN / PROJ epilogue.
 //
 // Warp roles in a GEMM CTA (320 threads): warp 0 lane 0 = producer (grid barrier wait + bulk
 // copies), warp 1 lane 0 = MMA issuer, warps 2..9 = epilogue (TMEM -> registers, hi/lo halves
