@@ -147,7 +147,7 @@ class CpuArm(object):
             self.pool = None
 
 
-def torch_cpu_line(workload, rater_indices, seconds=8.0):
+def torch_cpu_line(workload, rater_indices, seconds=8.0, n_docs=0, n_chars=0):
     """Second, stronger CPU line: ALL documents of the workload advance together through
     oracle/lstm_torch_cpu.py (one addmm per layer and tick, torch CPU on all host cores) -- not the reference's
     call structure (batch 1), so it is reported beside `cpu_baseline`, not in its place.  Bounded sample: the first
@@ -156,13 +156,14 @@ def torch_cpu_line(workload, rater_indices, seconds=8.0):
     from tests import util
     from oracle.lstm_torch_cpu import TorchCpuModel
     width, depth, length, contexts, docs, chars, what = WORKLOADS[workload]
-    if workload in ('cfg3', 'cfg5'):
+    docs, chars = n_docs or docs, n_chars or chars
+    if workload in ('cfg3', 'cfg5') or chars < 66:
         return None                                   # beams / ragged lines: the batched form has no fixed shape
     model = TorchCpuModel(util.to_model(model_weights(workload)))
     cal = 24
-    n_max = min(chars, 4096)
-    texts, ctxs = make_docs(workload, docs, n_max + 1, 0)
-    idx = np.stack([rater_indices(t)[:n_max + 1] for t in texts]).astype(np.int64)
+    n_max = min(chars - 1, 4096)
+    texts, ctxs = make_docs(workload, docs, chars, 0)      # the GPU arm's documents (their prefixes are what is compared)
+    idx = np.stack([rater_indices(t[:n_max + 1]) for t in texts]).astype(np.int64)
     zs = [np.array([c[k] for c in ctxs], dtype=np.int64) for k in range(len(contexts))]
     model.rate(idx[:, :cal], zs, idx[:, 1:cal + 1])
     t0 = time.perf_counter()
@@ -172,10 +173,17 @@ def torch_cpu_line(workload, rater_indices, seconds=8.0):
     t0 = time.perf_counter()
     logp, _ = model.rate(idx[:, :n], zs, idx[:, 1:n + 1])
     dt = time.perf_counter() - t0
-    return {'value': docs * n / dt, 'unit': 'chars/s', 'cores': torch.get_num_threads(),
+    line = {'value': docs * n / dt, 'unit': 'chars/s', 'cores': torch.get_num_threads(),
             'kind': 'port (batched: all %d documents per addmm, torch CPU / MKL -- not the reference call structure)' % docs,
             'sample': '%d documents x first %d chars together (of %s), %.1f s' % (docs, n, what, dt),
             'checksum_logp': float(logp.astype(np.float64).sum())}
+    # the same positions once more in fp64: the truth the GPU scores of this very run are compared with (`parity`)
+    t0 = time.perf_counter()
+    ref64, _ = TorchCpuModel(util.to_model(model_weights(workload)), dtype=np.float64).rate(idx[:, :n], zs, idx[:, 1:n + 1])
+    line['_ref64'] = ref64
+    line['_ref64_s'] = time.perf_counter() - t0
+    line['fp32_vs_fp64_max_abs_dlogp'] = float(np.abs(logp.astype(np.float64) - ref64).max())
+    return line
 
 
 def cpu_sample_chars(workload):
@@ -409,7 +417,8 @@ def run_ours(args):
         c, dt = arm.step(n_chars)
         arm.close()
         vocab_map = synth.mapping_from_array(synth.vocabulary())[0]
-        torch_line = torch_cpu_line(args.workload, lambda t: np.array([vocab_map.get(ch, 0) for ch in t], dtype=np.int64))
+        torch_line = torch_cpu_line(args.workload, lambda t: np.array([vocab_map.get(ch, 0) for ch in t], dtype=np.int64),
+                                    n_docs=args.docs, n_chars=args.chars)
         cpu_line = {
             'value': c / dt, 'unit': 'chars/s', 'cores': arm.procs, 'kind': 'port',
             'sample': '%d processes x 1 document x %d chars (of %s), %.1f s' % (arm.procs, n_chars,
@@ -559,6 +568,23 @@ def run_ours(args):
     if cpu_line is not None:
         line['cpu_baseline'] = cpu_line
         if torch_line is not None:
+            # parity at the bench configuration itself: the scores this run produced (device-resident leg and the
+            # end-to-end leg) against the fp64 CPU oracle on the first n positions of every document
+            ref64 = torch_line.pop('_ref64')
+            n_par = ref64.shape[1]
+            inv = np.empty(docs, dtype=np.int64)
+            inv[order] = np.arange(docs)
+            h_out = d_out.cpu().numpy()
+            dev = np.stack([h_out[offsets[inv[i]]:offsets[inv[i]] + n_par] for i in range(docs)]).astype(np.float64)
+            e2e = np.stack([np.log(np.maximum(res[i][1:n_par + 1].astype(np.float64), 1e-300)) for i in range(docs)])
+            line['parity'] = {
+                'positions': int(ref64.size), 'max_abs_dlogp': float(np.abs(dev - ref64).max()),
+                'max_abs_dlogp_e2e': float(np.abs(e2e - ref64).max()), 'tolerance': 1e-3,
+                'reference': 'oracle/lstm_torch_cpu.py in fp64, first %d positions of all %d documents (%.1f s)' % (
+                    n_par, docs, torch_line.pop('_ref64_s')),
+                'checksum_logp_gpu_same_positions': float(dev.sum()), 'checksum_logp_ref': float(ref64.sum())}
+            if not line['parity']['max_abs_dlogp'] <= 1e-3 or not line['parity']['max_abs_dlogp_e2e'] <= 1e-3:
+                line['parity']['FAILED'] = True
             line['cpu_baseline_torch'] = torch_line
     if rank == 0:
         print(json.dumps(line))

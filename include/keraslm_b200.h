@@ -74,8 +74,15 @@ int klm_abi_sizeof(int what);
 
 /* Run subsequent work on this CUDA stream (a cudaStream_t; NULL = the library's own stream). */
 int klm_set_stream(klm_model *m, void *cuda_stream);
-/* Block until everything enqueued on the model's stream has finished. */
+/* Block until everything enqueued on the model's stream has finished; reports a device-side watchdog error
+ * (a hand-over wait inside a persistent kernel that timed out) of any launch so far -- the place where
+ * KLM_MEM_DEVICE callers, whose klm_rate / klm_step only enqueue, learn about it. */
 int klm_sync(klm_model *m);
+/* Run-time switches of the library (diagnostics and timing experiments; the defaults are the product configuration).
+ * Initial values come from the environment variables of the same name in upper case with the prefix KLM_
+ * (e.g. KLM_TC_SKEW), read once in klm_create.  Names: tc_skew, tc_trace_mode, tc_debug_skip, tc_poll, tc_zpub,
+ * tc_pub_release, tc_spin_limit, tc_fault, tc_df, tc_consumer_fence, ll_debug, step_timing. */
+int klm_set_option(klm_model *m, const char *name, int64_t value);
 
 /*
  * State pool.  Replaces the Keras backend variables of the stateful LSTM layers
@@ -107,7 +114,8 @@ int klm_state_l2_distance(klm_model *m, const int32_t *a, const int32_t *b, int3
  *                     (:1141-1143); NULL = all positions real
  *   ctx      [n][n_ctx] context indices per stream (time-constant, :1142)
  *   out_logp [total]  natural-log probability of targets[] at each position (float32)
- * offsets is int64, the others int32; all five live where `mem` says.
+ * offsets is int64, the others int32.  chars, targets and out_logp live where `mem` says; slots, offsets, n_real
+ * and ctx are ALWAYS host pointers (they are read on the host to plan the launches).
  */
 int klm_rate(klm_model *m, int32_t n_streams, const int32_t *slots, const int64_t *offsets,
              const int32_t *chars, const int32_t *targets, const int32_t *n_real,
@@ -125,7 +133,7 @@ int klm_rate(klm_model *m, int32_t n_streams, const int32_t *slots, const int64_
  *   targets   [n] or NULL
  *   out       targets != NULL: [n] natural-log probability of targets[i]
  *             targets == NULL: [n][voc_size] full softmax rows (what predict returns, :632)
- * chars, ctx, targets, out live where `mem` says.
+ * chars, targets and out live where `mem` says; ctx, slots_in and slots_out are ALWAYS host pointers.
  */
 int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx,
              const int32_t *slots_in, const int32_t *slots_out, const int32_t *targets,

@@ -41,19 +41,42 @@ def needs_build():
 
 
 def build(force=False, verbose=False):
-    """Compile the CUDA sources for sm_100a into ocrd_keraslm_b200/libkeraslm_b200.so (in-tree)."""
+    """Compile the CUDA sources for sm_100a into ocrd_keraslm_b200/libkeraslm_b200.so (in-tree).
+
+    Every source is compiled to an object on its own (in parallel; only the ones whose source or a header is newer
+    than the object), then linked."""
     if not force and not needs_build():
         return LIB_PATH
+    from concurrent.futures import ThreadPoolExecutor
     nvcc = os.environ.get('NVCC') or '/usr/local/cuda/bin/nvcc'
     if not os.path.exists(nvcc):
         nvcc = 'nvcc'
-    srcs, _ = _sources()
-    cmd = [nvcc] + NVCC_FLAGS + ['-o', LIB_PATH] + srcs
+    srcs, hdrs = _sources()
+    objdir = os.path.join(HERE, 'build')
+    os.makedirs(objdir, exist_ok=True)
+    newest_hdr = max(os.path.getmtime(h) for h in hdrs)
+
+    def compile_one(src):
+        obj = os.path.join(objdir, os.path.basename(src)[:-3] + '.o')
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(src), newest_hdr):
+            return obj, 0, ''
+        cmd = [nvcc] + [f for f in NVCC_FLAGS if f != '-shared'] + ['-c', '-o', obj, src]
+        if verbose:
+            print(' '.join(cmd), file=sys.stderr)
+        res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, universal_newlines=True)
+        return obj, res.returncode, res.stdout
+
+    with ThreadPoolExecutor(max_workers=len(srcs)) as ex:
+        results = list(ex.map(compile_one, srcs))
+    for obj, rc, out in results:
+        if rc != 0:
+            raise NativeError('nvcc failed:\n' + out)
+    cmd = [nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-o', LIB_PATH] + [r[0] for r in results]
     if verbose:
         print(' '.join(cmd), file=sys.stderr)
     res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, universal_newlines=True)
     if res.returncode != 0:
-        raise NativeError('nvcc failed:\n' + res.stdout)
+        raise NativeError('nvcc (link) failed:\n' + res.stdout)
     return LIB_PATH
 
 
@@ -81,6 +104,7 @@ SYMBOLS = [
     ('klm_abi_sizeof', ctypes.c_int, [ctypes.c_int]),
     ('klm_set_stream', ctypes.c_int, [_P, _P]),
     ('klm_sync', ctypes.c_int, [_P]),
+    ('klm_set_option', ctypes.c_int, [_P, ctypes.c_char_p, ctypes.c_int64]),
     ('klm_state_pool_resize', ctypes.c_int, [_P, _I]),
     ('klm_state_reset', ctypes.c_int, [_P, _P, _I]),
     ('klm_state_copy', ctypes.c_int, [_P, _P, _P, _I]),
@@ -227,6 +251,10 @@ class Model(object):
 
     def sync(self):
         self.check(self._lib.klm_sync(self._h))
+
+    def set_option(self, name, value):
+        """Run-time switch of the library (see klm_set_option)."""
+        self.check(self._lib.klm_set_option(self._h, name.encode('ascii'), int(value)))
 
     def info(self):
         inf = KlmInfo()

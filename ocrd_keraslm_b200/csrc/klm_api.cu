@@ -74,8 +74,39 @@ struct KlmTcPlan {
     int trace_t0 = 0;
 };
 
+// Run-time switches: read from the environment ONCE (klm_create), changed afterwards with klm_set_option -- no getenv on
+// the launch path.
+struct KlmKnobs {
+    int tc_trace_mode = 0;        // KLM_TC_TRACE_MODE
+    int tc_debug_skip = 0;        // KLM_TC_DEBUG_SKIP (timing experiments, traced instantiations only)
+    int tc_poll = 0;              // KLM_TC_POLL
+    int tc_skew = 0;              // KLM_TC_SKEW: 0 = by launch length, 2 / 3 = forced
+    int tc_zpub = -1;             // KLM_TC_ZPUB: 2 = IN / PROJ stage + bulk-store their slice also with the early signal
+    int tc_pub_release = 0;       // KLM_TC_PUB_RELEASE
+    int tc_fault = 0;             // KLM_TC_FAULT (test hook: one CTA withholds a hand-over signal; the watchdog must fire)
+    unsigned tc_spin_limit = 1u << 24;   // KLM_TC_SPIN_LIMIT
+    int ll_debug = 0;             // KLM_LL_DEBUG
+    int cl_debug = 0;             // KLM_CL_DEBUG
+    int step_timing = 0;          // KLM_STEP_TIMING
+};
+static int env_int(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
+static void read_knobs(KlmKnobs &k) {
+    k.tc_trace_mode = env_int("KLM_TC_TRACE_MODE", 0);
+    k.tc_debug_skip = env_int("KLM_TC_DEBUG_SKIP", 0);
+    k.tc_poll = env_int("KLM_TC_POLL", 0);
+    k.tc_skew = env_int("KLM_TC_SKEW", 0);
+    k.tc_zpub = env_int("KLM_TC_ZPUB", -1);
+    k.tc_pub_release = env_int("KLM_TC_PUB_RELEASE", 0);
+    k.tc_fault = env_int("KLM_TC_FAULT", 0);
+    if (getenv("KLM_TC_SPIN_LIMIT")) k.tc_spin_limit = (unsigned)strtoul(getenv("KLM_TC_SPIN_LIMIT"), nullptr, 10);
+    k.ll_debug = env_int("KLM_LL_DEBUG", 0);
+    k.cl_debug = env_int("KLM_CL_DEBUG", 0);
+    k.step_timing = env_int("KLM_STEP_TIMING", 0);
+}
+
 #define KLM_RING 4
 struct klm_model {
+    KlmKnobs knobs;
     int device = 0;
     klm_config cfg{};
     int W = 0, D = 0, V = 0, V4 = 0, Nc = 0;
@@ -656,6 +687,7 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
                                      device, prop.major, prop.minor);
     klm_model *m = new klm_model();
     m->device = device; m->cfg = *cfg;
+    read_knobs(m->knobs);
     const int W = m->W = cfg->width, D = m->D = cfg->depth, V = m->V = cfg->voc_size, Nc = m->Nc = cfg->n_ctx;
     m->V4 = (V + 3) / 4 * 4;
     m->sm_count = prop.multiProcessorCount;
@@ -741,7 +773,7 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
     TRYC(cudaMemset(m->hbuf, 0, (size_t)D * 2 * W * m->bp_cap * 4));
     TRYC(cudaMalloc(&m->logits, (size_t)2 * m->V4 * m->bp_cap * 4));
     TRYC(cudaMemset(m->logits, 0, (size_t)2 * m->V4 * m->bp_cap * 4));
-    m->timing = getenv("KLM_STEP_TIMING") ? atoi(getenv("KLM_STEP_TIMING")) : 0;
+    m->timing = m->knobs.step_timing;
     if (!getenv("KLM_DISABLE_LL")) {
         m->hbuf_ll_bytes = (size_t)KLM_LL_RING * D * W * KLM_MODEK_MAXB * sizeof(uint2);
         m->logits_ll_bytes = (size_t)KLM_LL_RING * 4 * m->V4 * KLM_MODEK_MAXB * sizeof(uint2);
@@ -797,6 +829,24 @@ extern "C" int klm_sync(klm_model *m) {
     CK(cudaSetDevice(m->device));
     CK(cudaStreamSynchronize(m->stream));
     return check_device_error(m);
+}
+
+extern "C" int klm_set_option(klm_model *m, const char *name, int64_t value) {
+    if (!m || !name) return fail(KLM_EINVAL, "klm_set_option: NULL argument");
+    KlmKnobs &k = m->knobs;
+    const std::string n(name);
+    if (n == "tc_trace_mode") k.tc_trace_mode = (int)value;
+    else if (n == "tc_debug_skip") k.tc_debug_skip = (int)value;
+    else if (n == "tc_poll") k.tc_poll = (int)value;
+    else if (n == "tc_skew") k.tc_skew = (int)value;
+    else if (n == "tc_zpub") k.tc_zpub = (int)value;
+    else if (n == "tc_pub_release") k.tc_pub_release = (int)value;
+    else if (n == "tc_fault") k.tc_fault = (int)value;
+    else if (n == "tc_spin_limit") k.tc_spin_limit = (unsigned)value;
+    else if (n == "ll_debug") k.ll_debug = (int)value;
+    else if (n == "step_timing") { k.step_timing = (int)value; m->timing = (int)value; }
+    else return fail(KLM_EINVAL, "klm_set_option: unknown option '%s'", name);
+    return KLM_OK;
 }
 
 // Small per-call arrays travel through a ring of pinned buffers: one H2D copy per call.
@@ -973,20 +1023,22 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         q.out = d_out; q.full_rows = full_rows;
         q.barrier = m->barrier; q.err = tp.err;
         q.trace = tp.trace; q.trace_t0 = tp.trace_t0;
-        q.trace_mode = getenv("KLM_TC_TRACE_MODE") ? atoi(getenv("KLM_TC_TRACE_MODE")) : 0;
-        q.debug_skip = getenv("KLM_TC_DEBUG_SKIP") ? atoi(getenv("KLM_TC_DEBUG_SKIP")) : 0;
-        q.poll_mode = getenv("KLM_TC_POLL") ? atoi(getenv("KLM_TC_POLL")) : 0;
+        q.trace_mode = m->knobs.tc_trace_mode;
+        q.debug_skip = m->knobs.tc_debug_skip;
+        q.poll_mode = m->knobs.tc_poll;
         q.stream_b = tp.stream_b;
         // long launches: skew 3 (the recurrence does not wait for the IN / PROJ epilogues; D more ticks of pipeline fill);
         // short ones (beam steps) and the CTA-pair kernel: skew 2
         {
             // (streamed-weights form: measured slower with skew 3 on the short lines of cfg5, 3.73 M against 3.90 M chars/s)
-            const int want = getenv("KLM_TC_SKEW") ? atoi(getenv("KLM_TC_SKEW")) : (tmax >= 64 && !tp.stream_b ? 3 : 2);
+            const int want = m->knobs.tc_skew ? m->knobs.tc_skew : (tmax >= 64 && !tp.stream_b ? 3 : 2);
             q.skew = (want == 3 && &tp != &m->tc2) ? 3 : 2;
             q.zmask = q.skew == 3 ? 3 : 1; q.zlag = q.skew == 3 ? 2 : 1;
         }
-        q.zpub_early = getenv("KLM_TC_ZPUB") && atoi(getenv("KLM_TC_ZPUB")) == 2;
-        q.pub_release = getenv("KLM_TC_PUB_RELEASE") ? atoi(getenv("KLM_TC_PUB_RELEASE")) : 0;
+        q.zpub_early = m->knobs.tc_zpub == 2;
+        q.pub_release = m->knobs.tc_pub_release;
+        q.spin_limit = m->knobs.tc_spin_limit;
+        q.fault = m->knobs.tc_fault;
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         q.kc = tp.kc; q.ring_bytes = tp.ring_bytes;
         if (&tp == &m->tc2) CK(klm_launch_seq_tc2(q, tp.grid, tp.smem, m->stream));
@@ -1019,9 +1071,9 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         (m->D * m->W + 4 * m->cl.PU) * nb <= KLM_CL_PUBS * KLM_THREADS) {
         // the whole model in one thread-block cluster, recurrence exchanged through distributed shared memory
         p.err = m->ll_err;
-        p.debug = getenv("KLM_LL_DEBUG") ? atoi(getenv("KLM_LL_DEBUG")) : 0;
+        p.debug = m->knobs.ll_debug;
         cudaError_t e = klm_launch_seq_cl(p, m->cl, m->stream);
-        if (getenv("KLM_CL_DEBUG"))
+        if (m->knobs.cl_debug)
             fprintf(stderr, "klm cluster launch: B %d T %d smem %zu -> %s\n", nb, (int)tmax, klm_cl_smem_bytes(p, m->cl), cudaGetErrorString(e));
         if (e == cudaSuccess) { m->launches++; m->ll_launches++; m->cl_launches++; return KLM_OK; }
         fprintf(stderr, "klm: cluster kernel cannot be launched (%s), using the grid-wide kernel\n", cudaGetErrorString(e));
@@ -1036,7 +1088,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         CK(cudaMemsetAsync(m->logits_ll, 0xFF, m->logits_ll_bytes / KLM_LL_RING * used_slots, m->stream));
         CK(cudaMemsetAsync(m->progress, 0, 1024 * sizeof(unsigned int), m->stream));
         m->ll_launches++;
-        p.debug = getenv("KLM_LL_DEBUG") ? atoi(getenv("KLM_LL_DEBUG")) : 0;
+        p.debug = m->knobs.ll_debug;
     }
     p.roles = pl.d_roles; p.wsmem = pl.wsmem; p.stage_floats = pl.stage_floats;
     CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
@@ -1185,8 +1237,8 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
         if (targets) memcpy(hs + n, targets, (size_t)n * 4);
         src_chars = hs; src_targets = hs + n;
     }
-    CK(cudaMemcpyAsync(m->d_chars, src_chars, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
-    if (targets) CK(cudaMemcpyAsync(m->d_targets, src_targets, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    CK(cudaMemcpyAsync(m->d_chars, src_chars, (size_t)n * 4, cudaMemcpyDefault, m->stream));       // (host or device, by `mem`)
+    if (targets) CK(cudaMemcpyAsync(m->d_targets, src_targets, (size_t)n * 4, cudaMemcpyDefault, m->stream));
     float *dout = (mem == KLM_MEM_HOST) ? m->d_out : out;
     CK(cudaEventRecord(m->ev0, m->stream));
     const int bmax = batch_max(m, n);

@@ -179,4 +179,6 @@ struct KlmTcParams {
     int pub_release;              // 1: a REC CTA signals with red.release.gpu after its bulk store (default 0: the store has been
                                   //    waited for, a relaxed add follows it; KLM_TC_PUB_RELEASE=1 restores the release)
     int stream_b;                 // 1: streamed-weights form (B chunks travel through the ring with the A chunks)
+    unsigned spin_limit;          // device-side watchdog: polls of one wait before it gives up (klm_set_option "tc_spin_limit")
+    int fault;                    // test hook (klm_set_option "tc_fault"): CTA 0 withholds its hand-over signal of tick 2
 };

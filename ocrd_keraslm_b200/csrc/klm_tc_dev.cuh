@@ -4,12 +4,12 @@
 #include "klm_common.cuh"
 #include "klm_tc.cuh"
 
-#define TC_SPIN_LIMIT (1u << 24)
+#define TC_SPIN_LIMIT (1u << 24)          // default of KlmTcParams::spin_limit
 
 __device__ __forceinline__ bool tc_spin_fail(unsigned &n, const KlmTcParams &p, int code) {
     if ((++n & 0x3FFu) == 0) {
         if (*(volatile int *)p.err != 0) return true;
-        if (n > TC_SPIN_LIMIT) { atomicCAS(p.err, 0, code); return true; }
+        if (n > p.spin_limit) { atomicCAS(p.err, 0, code); return true; }
     }
     return false;
 }

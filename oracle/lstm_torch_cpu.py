@@ -15,10 +15,12 @@ import torch
 
 
 class TorchCpuModel(object):
-    """fp32 weights of a ``lstm_numpy.ModelWeights`` as torch CPU tensors; K and R stacked per layer."""
+    """Weights of a ``lstm_numpy.ModelWeights`` as torch CPU tensors (fp32: the timed baseline; fp64: the truth the
+    long parity runs compare with -- bench.py's in-line parity check, tests/test_gpu_long.py); K and R stacked per layer."""
 
-    def __init__(self, w):
-        f = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))
+    def __init__(self, w, dtype=np.float32):
+        self.dtype = torch.float64 if np.dtype(dtype) == np.float64 else torch.float32
+        f = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=dtype))
         self.E = f(w.E)
         self.Et = self.E.t().contiguous()
         self.ctx = [f(c) for c in w.ctx]
@@ -27,13 +29,13 @@ class TorchCpuModel(object):
         self.width, self.depth, self.voc_size = w.width, w.depth, w.voc_size
 
     def zero_states(self, n):
-        return [torch.zeros(n, self.width) for _ in range(2 * self.depth)]
+        return [torch.zeros(n, self.width, dtype=self.dtype) for _ in range(2 * self.depth)]
 
     @torch.no_grad()
     def rate(self, x, zs, targets, states=None):
         """Teacher-forced run.  x, targets: int64 [B, T]; zs: list of int64 [B] (one row per stream).
 
-        Returns (log p of the targets [B, T] float32, states list h1,c1,h2,c2,.. of [B, W])."""
+        Returns (log p of the targets [B, T] (model dtype), states list h1,c1,h2,c2,.. of [B, W])."""
         B, T = x.shape
         W = self.width
         x = torch.as_tensor(x, dtype=torch.int64)
@@ -43,7 +45,7 @@ class TorchCpuModel(object):
         c = [states[2 * l + 1] for l in range(self.depth)]
         # the context part of layer 1's input does not change over the ticks
         cpart = [tab[torch.as_tensor(z, dtype=torch.int64)] for tab, z in zip(self.ctx, zs)]
-        out = torch.empty(B, T)
+        out = torch.empty(B, T, dtype=self.dtype)
         for t in range(T):
             inp = torch.cat([self.E[x[:, t]]] + cpart, dim=1)
             for l in range(self.depth):

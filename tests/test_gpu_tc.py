@@ -234,7 +234,7 @@ def test_tc_skew3_early_signal_matches_skew2_and_oracle(width, depth, nctx, monk
     slots = r._pool.acquire(n)
     results = {}
     for skew in ('2', '3'):
-        monkeypatch.setenv('KLM_TC_SKEW', skew)
+        nat.set_option('tc_skew', int(skew))
         nat.state_reset(slots)
         outs = []
         for piece in (slice(0, 90), slice(89, None)):          # second launch continues from the carried state
@@ -247,7 +247,7 @@ def test_tc_skew3_early_signal_matches_skew2_and_oracle(width, depth, nctx, monk
             nat.rate(slots, offsets, chars, targets, None, ctx, logp)
             outs.append((idx, offsets, logp))
         results[skew] = (outs, nat.state_to_host(slots))
-    monkeypatch.delenv('KLM_TC_SKEW')
+    nat.set_option('tc_skew', 0)
     (o2, s2), (o3, s3) = results['2'], results['3']
     for (_, _, a), (_, _, b) in zip(o2, o3):
         assert not np.isnan(b).any()
