@@ -17,7 +17,6 @@ cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cud
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_cl(const KlmSeqParams &p, const KlmClGeom &g, cudaStream_t stream);
 size_t klm_cl_smem_bytes(const KlmSeqParams &p, const KlmClGeom &g);
-cudaError_t klm_launch_seq_tc2(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_umma2_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
 cudaError_t klm_launch_umma_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
 
@@ -117,7 +116,7 @@ struct klm_model {
     float4 *P = nullptr, *Q[KLM_MAX_CTX] = {}, *Wl[KLM_MAX_DEPTH] = {}, *bias[KLM_MAX_DEPTH] = {}, *Ep = nullptr;
     // plans
     KlmPlan plan_k, plan_b;
-    KlmTcPlan tc, tc2;                 // single-CTA MMA plan, CTA-pair (cta_group::2) plan
+    KlmTcPlan tc;                      // plan of the tensor-core sequence kernel
     // scratch
     float *hbuf = nullptr, *logits = nullptr;
     unsigned int *barrier = nullptr;
@@ -427,6 +426,15 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
     for (auto &t : tys) {
         const int base = t.items / t.n, rem = t.items % t.n;
         int first = 0;
+        // power-of-two scale of this matrix (see KLM_TC_HSCALE): the largest that keeps |w| below KLM_TC_WMAX
+        float wmax = 0.f;
+        {
+            const size_t cnt = t.kind == KLM_TC_PROJ ? (size_t)V * W : (size_t)W * 4 * W;
+            for (size_t i = 0; i < cnt; ++i) wmax = std::max(wmax, std::fabs(t.mat[i]));
+        }
+        int wexp = 0;
+        if (wmax > 0.f) wexp = std::min(24, std::max(0, (int)std::floor(std::log2(KLM_TC_WMAX / wmax))));
+        const float wscale = std::ldexp(1.0f, wexp);
         for (int c = 0; c < t.n; ++c) {
             const int np = (base + (c < rem ? 1 : 0)) * t.gran;
             const int N = 8 * np;                            // image rows: [0,N) hi, [N,2N) lo
@@ -443,6 +451,7 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
                 r.kc = geoms[g][0]; r.stages = std::min(geoms[g][1], W / r.kc); r.ring_bytes = ring_bytes_of(g);
             }
             r.pub = t.kind == KLM_TC_REC ? pl.pub : 0;
+            r.scale = 1.0f / (KLM_TC_HSCALE * wscale);
             // IN / PROJ of the resident form: the slice of Z / of the logits (2 KB per pair) staged behind the hand-over
             // buffer on the idle ring and written with one bulk async store (KLM_TC_ZPUB=0: per-thread stores + release)
             if (t.kind != KLM_TC_REC && !pl.stream_b && pl.pub == 2 && r.ring_bytes >= KLM_TC1_PUB_OFS + np * 2048 &&
@@ -462,6 +471,7 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
                         const int u = 2 * first + j / 4, gate = j % 4;
                         val = t.mat[(size_t)k * 4 * W + gate * W + u];
                     }
+                    val *= wscale;
                     const __half hi = __float2half_rn(val);
                     const __half lo = __float2half_rn(val - __half2float(hi));
                     img[o + ((size_t)(k / 8) * 2 * N + j) * 8 + (k % 8)] = hi;
@@ -509,126 +519,6 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
     return KLM_OK;
 }
 
-// ------------------------------------------------------------------------------------------
-// Tensor-core plan: distributes the columns of R_l (REC), K_l (IN, l >= 1) and the rows of E (PROJ)
-// over the SMs in pairs of units (8 columns), builds each CTA's fp16 hi/lo B image in the shared
-// memory operand layout [W/8][2N][8], and allocates the exchange buffers.  Not eligible (ok stays
-// false, the FMA kernels take over) if W is not a multiple of 64, a weight overflows fp16, or the
-// images do not fit the shared memory of the device.
-// pair = true plans the CTA-pair kernel (klm_seq_tc2.cu): even CTA counts per stage, the two CTAs of a cluster
-// get B images padded to the same number of pairs.
-static int make_tc_plan(klm_model *m, const float *E, const float *const *L, bool pair, KlmTcPlan &pl) {
-    const int W = m->W, D = m->D, V = m->V;
-    if (getenv("KLM_DISABLE_TC")) return KLM_OK;
-    // measured on cfg2: the pair kernel is slower (9.5 vs 8.0 us per tick) -- with only 64 accumulator rows per CTA the
-    // tensor cores run at half rate -- so it is opt-in; it pays for >= 128 streams per launch (not implemented yet)
-    if (pair && !getenv("KLM_ENABLE_TC2")) return KLM_OK;
-    if (W % KLM_TC_KC != 0 || W < KLM_TC_KC) return KLM_OK;
-    pl.kc = (pair && W % 128 == 0) ? 128 : KLM_TC_KC;
-    const int nchunks = W / pl.kc;
-    pl.stages = std::min(4, nchunks);
-    pl.Vp = (V + 7) / 8 * 8;
-    pl.ring_bytes = std::max(pl.stages * pl.kc * 128, KLM_TC_XCHG_BYTES);
-    const size_t fixed = pair ? (size_t)pl.ring_bytes + 256 : KLM_TC_FIXED_BYTES((size_t)pl.stages);
-    if (fixed + 32 * (size_t)W > m->smem_optin) return KLM_OK;
-    const int pairs_max = (int)std::min<size_t>(KLM_TC_MAX_PAIRS, (m->smem_optin - fixed) / (32 * (size_t)W));
-    if (pairs_max < 1) return KLM_OK;
-
-    const int sm_avail = getenv("KLM_TC_MAX_CTAS") ? std::min(m->sm_count, atoi(getenv("KLM_TC_MAX_CTAS"))) : m->sm_count;
-    struct Ty { int kind, layer, src, sigma, pairs, n; const float *mat; };
-    std::vector<Ty> tys;
-    for (int l = 0; l < D; ++l) {
-        if (l > 0) tys.push_back({KLM_TC_IN, l, l - 1, 2 * l - 1, W / 2, 0, L[3 * l]});
-        tys.push_back({KLM_TC_REC, l, l, 2 * l, W / 2, 0, L[3 * l + 1]});
-    }
-    tys.push_back({KLM_TC_PROJ, 0, D - 1, 2 * D - 1, pl.Vp / 8, 0, E});
-    const int q = pair ? 2 : 1;                              // CTAs come in clusters of q
-    int n_lse = q, used = 0;
-    for (auto &t : tys) { t.n = (t.pairs + pairs_max - 1) / pairs_max; t.n = (t.n + q - 1) / q * q; used += t.n; }
-    if (used + n_lse > sm_avail) return KLM_OK;
-    n_lse = std::max(q, std::min(4, (sm_avail - used) / q * q));      // the LSE stage must not be the slowest one
-    used += n_lse;
-    while (used + q <= sm_avail) {                           // spare SMs go to the stage with the widest slices
-        int best = -1; double load = 0;
-        for (int i = 0; i < (int)tys.size(); ++i) {
-            if (tys[i].n + q > tys[i].pairs) continue;
-            const double ld = std::ceil((double)tys[i].pairs / tys[i].n);
-            if (ld > load) { load = ld; best = i; }
-        }
-        if (best < 0 || load <= 1) break;
-        tys[best].n += q; used += q;
-    }
-    // fp16 range check
-    {
-        float mx = 0.f;
-        for (auto &t : tys) {
-            const size_t cnt = t.kind == KLM_TC_PROJ ? (size_t)V * W : (size_t)W * 4 * W;
-            for (size_t i = 0; i < cnt; ++i) mx = std::max(mx, std::fabs(t.mat[i]));
-        }
-        if (!(mx < 60000.f)) return KLM_OK;
-    }
-    std::vector<__half> img;
-    int max_pairs = 0;
-    for (auto &t : tys) {
-        const int base = t.pairs / t.n, rem = t.pairs % t.n;
-        int first = 0;
-        for (int c = 0; c < t.n; ++c) {
-            const int np = base + (c < rem ? 1 : 0);
-            const int c2 = pair ? (c ^ 1) : c;               // the other CTA of the cluster
-            const int npm = std::max(np, base + (c2 < rem ? 1 : 0));
-            const int N = 8 * npm;                           // image rows: [0,N) hi, [N,2N) lo; rows >= 8*np are zero padding
-            KlmTcRole r;
-            memset(&r, 0, sizeof r);
-            r.kind = t.kind; r.layer = t.layer; r.src_layer = t.src; r.sigma = t.sigma;
-            r.first_pair = first; r.npairs = np; r.wofs = (long long)(img.size() * sizeof(__half)); r.npm = npm;
-            pl.roles.push_back(r);
-            const size_t o = img.size();
-            img.resize(o + (size_t)W * 2 * N, __float2half_rn(0.f));
-            for (int j = 0; j < 8 * np; ++j) {
-                for (int k = 0; k < W; ++k) {
-                    float val;
-                    if (t.kind == KLM_TC_PROJ) {
-                        const int v = 8 * first + j;
-                        val = v < V ? t.mat[(size_t)v * W + k] : 0.f;
-                    } else {
-                        const int u = 2 * first + j / 4, g = j % 4;
-                        val = t.mat[(size_t)k * 4 * W + g * W + u];
-                    }
-                    const __half hi = __float2half_rn(val);
-                    const __half lo = __float2half_rn(val - __half2float(hi));
-                    img[o + ((size_t)(k / 8) * 2 * N + j) * 8 + (k % 8)] = hi;
-                    img[o + ((size_t)(k / 8) * 2 * N + N + j) * 8 + (k % 8)] = lo;
-                }
-            }
-            first += np;
-            max_pairs = std::max(max_pairs, npm);
-        }
-    }
-    for (int i = 0; i < n_lse; ++i) {
-        KlmTcRole r;
-        memset(&r, 0, sizeof r);
-        r.kind = KLM_TC_LSE; r.sigma = 2 * D; r.first_pair = i; r.npairs = n_lse;
-        pl.roles.push_back(r);
-    }
-    pl.grid = (int)pl.roles.size();
-    pl.smem = fixed + (size_t)32 * W * max_pairs;
-    CK(cudaMalloc(&pl.d_roles, pl.roles.size() * sizeof(KlmTcRole)));
-    CK(cudaMemcpy(pl.d_roles, pl.roles.data(), pl.roles.size() * sizeof(KlmTcRole), cudaMemcpyHostToDevice));
-    CK(cudaMalloc(&pl.d_wimg, img.size() * sizeof(__half)));
-    CK(cudaMemcpy(pl.d_wimg, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice));
-    pl.ingest_bulk = getenv("KLM_TC_INGEST_BULK") ? atoi(getenv("KLM_TC_INGEST_BULK")) : 1;
-    const size_t hx_bytes = (size_t)D * 2 * W * 128 * sizeof(__half);
-    const size_t z_bytes = (size_t)D * 2 * 64 * 4 * W * sizeof(float);
-    const size_t lg_bytes = (size_t)2 * 64 * pl.Vp * sizeof(float);
-    CK(cudaMalloc(&pl.hx, hx_bytes)); CK(cudaMemset(pl.hx, 0, hx_bytes));
-    CK(cudaMalloc(&pl.Z, z_bytes)); CK(cudaMemset(pl.Z, 0, z_bytes));
-    CK(cudaMalloc(&pl.logits, lg_bytes)); CK(cudaMemset(pl.logits, 0, lg_bytes));
-    CK(cudaMalloc(&pl.err, 256)); CK(cudaMemset(pl.err, 0, 256));
-    // the kernel is launched cooperatively: all CTAs must be co-resident
-    pl.ok = true;
-    return KLM_OK;
-}
-
 template <typename T> static int upload(T **dst, const std::vector<T> &src) {
     CK(cudaMalloc(dst, src.size() * sizeof(T)));
     CK(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
@@ -651,8 +541,6 @@ extern "C" int klm_destroy(klm_model *m) {
     cudaFree(m->plan_k.d_roles); cudaFree(m->plan_b.d_roles);
     cudaFree(m->tc.d_roles); cudaFree(m->tc.d_wimg); cudaFree(m->tc.hx); cudaFree(m->tc.Z); cudaFree(m->tc.logits);
     cudaFree(m->tc.err); cudaFree(m->tc.trace);
-    cudaFree(m->tc2.d_roles); cudaFree(m->tc2.d_wimg); cudaFree(m->tc2.hx); cudaFree(m->tc2.Z); cudaFree(m->tc2.logits);
-    cudaFree(m->tc2.err); cudaFree(m->tc2.trace);
     cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
     cudaFree(m->hbuf_ll); cudaFree(m->logits_ll); cudaFree(m->progress); cudaFree(m->ll_err);
     if (m->h_step) cudaFreeHost(m->h_step);
@@ -766,7 +654,6 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
     TRY(make_plan(m, true, &m->plan_k));
     TRY(make_plan(m, false, &m->plan_b));
     TRY(make_tc1_plan(m, E, L, m->tc));
-    TRY(make_tc_plan(m, E, L, true, m->tc2));
 
     m->bp_cap = std::max(32, m->plan_b.max_streams);
     TRYC(cudaMalloc(&m->hbuf, (size_t)D * 2 * W * m->bp_cap * 4));
@@ -996,7 +883,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     int rc = ring_acquire(m, &rs, (size_t)nb * (4 * 3 + 4 * m->Nc) + (nb + 1) * 8 + 128);
     if (rc) return rc;
     if (m->tc.ok && nb > KLM_MODEK_MAXB && nb <= KLM_TC_STREAMS) {
-        KlmTcPlan &tp = m->tc2.ok ? m->tc2 : m->tc;
+        KlmTcPlan &tp = m->tc;
         if ((double)(tmax + 3 * m->D + 2) * tp.grid >= 4.0e9)
             return fail(KLM_EINVAL, "stream of %lld positions is too long for one launch", tmax);
         KlmTcParams q;
@@ -1032,7 +919,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         {
             // (streamed-weights form: measured slower with skew 3 on the short lines of cfg5, 3.73 M against 3.90 M chars/s)
             const int want = m->knobs.tc_skew ? m->knobs.tc_skew : (tmax >= 64 && !tp.stream_b ? 3 : 2);
-            q.skew = (want == 3 && &tp != &m->tc2) ? 3 : 2;
+            q.skew = want == 3 ? 3 : 2;
             q.zmask = q.skew == 3 ? 3 : 1; q.zlag = q.skew == 3 ? 2 : 1;
         }
         q.zpub_early = m->knobs.tc_zpub == 2;
@@ -1041,8 +928,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         q.fault = m->knobs.tc_fault;
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         q.kc = tp.kc; q.ring_bytes = tp.ring_bytes;
-        if (&tp == &m->tc2) CK(klm_launch_seq_tc2(q, tp.grid, tp.smem, m->stream));
-        else CK(klm_launch_seq_tc(q, tp.grid, tp.smem, m->stream));
+        CK(klm_launch_seq_tc(q, tp.grid, tp.smem, m->stream));
         m->launches++; m->tc_launches++;
         return KLM_OK;
     }
@@ -1112,7 +998,6 @@ static int fetch_errors_async(klm_model *m) {
     if (m->ll_launches > 0) CK(cudaMemcpyAsync(&m->h_err[0], m->ll_err, 4, cudaMemcpyDeviceToHost, m->stream));
     if (m->tc.ok && m->tc_launches > 0) {
         CK(cudaMemcpyAsync(&m->h_err[1], m->tc.err, 4, cudaMemcpyDeviceToHost, m->stream));
-        if (m->tc2.ok) CK(cudaMemcpyAsync(&m->h_err[2], m->tc2.err, 4, cudaMemcpyDeviceToHost, m->stream));
     }
     return KLM_OK;
 }
@@ -1132,7 +1017,6 @@ static int check_device_error(klm_model *m) {
     if (!m->tc.ok || m->tc_launches == 0) return KLM_OK;
     int code = 0;
     CK(cudaMemcpy(&code, m->tc.err, sizeof code, cudaMemcpyDeviceToHost));
-    if (code == 0 && m->tc2.ok) CK(cudaMemcpy(&code, m->tc2.err, sizeof code, cudaMemcpyDeviceToHost));
     if (code != 0) return fail(KLM_ECUDA, "klm_seq_tc: device-side wait timed out (code %d)", code);
     return KLM_OK;
 }
@@ -1284,9 +1168,8 @@ extern "C" int klm_get_info(klm_model *m, klm_info *out) {
     out->kernel_launches = m->launches;
     out->max_streams = m->tc.ok ? KLM_TC_STREAMS : m->plan_b.max_streams;
     out->tc_enabled = m->tc.ok ? (m->tc.stream_b ? 3 : 1) : 0; // 3: streamed-weights form (images stay in global memory / L2)
-    out->tc_enabled = m->tc2.ok ? 2 : out->tc_enabled;        // 2: the CTA-pair kernel (cta_group::2) is the one in use
-    out->tc_grid = m->tc2.ok ? m->tc2.grid : m->tc.grid;
-    out->tc_smem_bytes = (int32_t)(m->tc2.ok ? m->tc2.smem : m->tc.smem);
+    out->tc_grid = m->tc.grid;
+    out->tc_smem_bytes = (int32_t)m->tc.smem;
     out->tc_launches = m->tc_launches;
     out->cl_launches = m->cl_launches; out->cl_cluster = m->cl.C;
     if (m->timed) {
@@ -1330,7 +1213,7 @@ extern "C" int klm_tc_trace(klm_model *m, int32_t first_tick, uint64_t *out, int
     if (!m) return fail(KLM_EINVAL, "NULL model");
     if (!m->tc.ok) return fail(KLM_EINVAL, "klm_tc_trace: the tensor-core plan is not enabled for this model");
     CK(cudaSetDevice(m->device));
-    KlmTcPlan &tp = m->tc2.ok ? m->tc2 : m->tc;
+    KlmTcPlan &tp = m->tc;
     const size_t n = (size_t)tp.grid * KLM_TC_TRACE_TICKS * 8;
     if (!out) {
         if (!tp.trace) CK(cudaMalloc(&tp.trace, n * 8));

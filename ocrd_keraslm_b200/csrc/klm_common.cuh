@@ -113,6 +113,13 @@ struct KlmClGeom {
 // (KlmTcRole::ring_ofs = KLM_TC1_PUB_OFS + 2 KB per group of 8 units of a REC slice)
 #define KLM_TCS_MAX_PAIRS   24
 #define KLM_TC_TRACE_TICKS  16
+// fp16 has 5 exponent bits: the lo part of a hi/lo split (|lo| <= 2^-11 |x|) falls into the subnormal range (below
+// 6.1e-5) for |x| < 0.125, and with Keras-default initialisation hidden values are ~1e-3 and weights ~0.05 -- the split
+// then keeps 14 instead of 22 bits (states 1.8e-4 off after 20 000 positions, tests/test_gpu_long.py).  Operands are
+// therefore scaled by powers of two before the split (exact), hidden values by KLM_TC_HSCALE (|h| < 1), every weight
+// matrix by the largest power of two that keeps it below KLM_TC_WMAX, and the fp32 accumulator is scaled back.
+#define KLM_TC_HSCALE       4096.f
+#define KLM_TC_WMAX         16384.f
 
 #define KLM_TC_REC  0
 #define KLM_TC_IN   1
@@ -136,6 +143,7 @@ struct KlmTcRole {
                        //      2 = staged + one bulk async store (1 and 2 need slices aligned to 8 units)
     int ring_ofs;      // streamed-weights form: byte offset of the ring (behind the hand-over buffer and, REC only, the
                        // publication staging of this CTA's slice)
+    float scale;       // accumulator -> pre-activation: 1 / (KLM_TC_HSCALE * weight scale of this CTA's matrix), a power of two
 };
 
 struct KlmTcParams {
@@ -152,7 +160,7 @@ struct KlmTcParams {
     int ring_bytes;               // CTA-pair kernel: bytes of the ring region (>= the hand-over buffer aliased on it)
     int ingest_bulk;              // CTA-pair kernel only (the single-CTA kernel always uses bulk copies)
     int consumer_fence;           // single-CTA kernel: fence.proxy.async between the grid barrier and the bulk reads
-    float *Z;                     // pre-activations of the IN stages: klm_seq_tc [D][2][W][64] float4 (i,f,c,o), klm_seq_tc2 [D][2][64][4W]
+    float *Z;                     // pre-activations of the IN stages: [D][slots][W][64] float4 (i,f,c,o)
     float *logits;                // [2][Vp/4][64] float4
     float *state;
     const int *slots_in, *slots_out;

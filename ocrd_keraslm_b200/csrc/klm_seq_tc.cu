@@ -622,7 +622,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                         if (i < R.nown) {
                             const int xi = R.own_first + i - R.my_first;
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) acc[i][j] += xr[(xi * 8 + j) * 64 + s];
+                            for (int j = 0; j < 8; ++j) acc[i][j] = (acc[i][j] + xr[(xi * 8 + j) * 64 + s]) * role.scale;   // (operand scaling undone)
                         }
                     // resident form: the hand-over buffer aliases the ring: order these generic accesses before the
                     // next bulk copies

@@ -1,4 +1,4 @@
-// Device helpers shared by the tensor-core sequence kernels (klm_seq_tc.cu, klm_seq_tc2.cu):
+// Device helpers shared by the tensor-core sequence kernels (klm_seq_tc.cu, klm_seq_df.cu):
 // bounded waits with a device-side watchdog, timeline tracing, the LSTM cell, the LSE stage.
 #pragma once
 #include "klm_common.cuh"
@@ -70,7 +70,9 @@ __device__ __forceinline__ void tc_cell(float ai, float af, float ag, float ao, 
     h = __fdividef(1.f - ec, (1.f + eo) * (1.f + ec));
 }
 
+// hidden value -> fp16 hi/lo operand pair, scaled by KLM_TC_HSCALE so that the lo part stays a normal fp16 number
 __device__ __forceinline__ void tc_split(float v, __half &hi, __half &lo) {
+    v *= KLM_TC_HSCALE;
     hi = __float2half_rn(v);
     lo = __float2half_rn(v - __half2float(hi));
 }

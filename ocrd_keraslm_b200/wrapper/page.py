@@ -9,7 +9,9 @@ top of this package's ``Rater``; this module exists so that the
 PAGE files where ocrd is not installed (benchmarks, tests), on ``xml.etree`` only.
 
 Not reproduced: the tokenisation repair that needs ocrd's PageValidator (:592-610, :646-660) -- white space is
-always inserted by the plain rules --, and ReadingOrder groups (document order is used).
+always inserted by the plain rules.  The hierarchy is walked generically over a table of levels (one recursive walk
+builds the graph, one bottom-up pass rebuilds the higher levels), ``ReadingOrder`` is honoured where the reference
+honours it (the order of nested regions, :510-531).
 """
 import logging
 import math
@@ -54,20 +56,21 @@ class Segment(object):
         self.node = node
         self.id = node.get('id')
 
-    def _children(self, tag):
+    def children(self, tag):
+        """Direct child segments of one kind ('TextRegion', 'TextLine', 'Word', 'Glyph'), in document order."""
         return [Segment(self.doc, n) for n in self.node.findall(self.doc.q(tag))]
 
     def get_TextRegion(self):
-        return self._children('TextRegion')
+        return self.children('TextRegion')
 
     def get_TextLine(self):
-        return self._children('TextLine')
+        return self.children('TextLine')
 
     def get_Word(self):
-        return self._children('Word')
+        return self.children('Word')
 
     def get_Glyph(self):
-        return self._children('Glyph')
+        return self.children('Glyph')
 
     def get_TextEquiv(self):
         """Alternatives in document order (OCR engines write them best first, with @index)."""
@@ -157,6 +160,28 @@ class PageDoc(object):
                         out.append((s.get('regionRef'), t.get('regionRef')))
         return out
 
+    def reading_order(self):
+        """{region id: (kind of the ReadingOrder entry, its @index or None)} for every reference below Page/ReadingOrder,
+        groups included and followed recursively (reference :457-476)."""
+        out = {}
+
+        def collect(group):
+            for entry in group:
+                kind = entry.tag.rsplit('}', 1)[-1]
+                if kind not in ('RegionRef', 'RegionRefIndexed', 'OrderedGroup', 'OrderedGroupIndexed', 'UnorderedGroup',
+                                'UnorderedGroupIndexed'):
+                    continue
+                index = entry.get('index')
+                out[entry.get('regionRef')] = (kind, int(index) if index is not None else None)
+                if 'Group' in kind:
+                    collect(entry)
+
+        ro = self.page.find(self.q('ReadingOrder'))
+        if ro is not None:
+            for top in ro:
+                collect(top)
+        return out
+
     def tostring(self):
         return ET.tostring(self.root, encoding='unicode')
 
@@ -176,189 +201,196 @@ def mets_get_context(identifier):
     return context
 
 
+# ---------------------------------------------------------------------------------------------------------------
+# The PAGE hierarchy as data: everything below walks these tables instead of spelling the four levels out.
+_SEGMENT_TAGS = ('TextRegion', 'TextLine', 'Word', 'Glyph')            # depth 0..3
+_LEVEL_DEPTH = dict((name, depth) for depth, name in enumerate(LEVELS))
+_NOUNS = ('Region', 'Line', 'Word', 'Glyph')                           # for the log messages
+_PARTS = ('text regions', 'text lines', 'words', 'glyphs')
+_WORD_DEPTH = 2
+# what joins the first texts of a segment's children into its own text, and the attribute that can reverse their order
+_JOINER = ('\n', ' ', '')                                               # region <- lines, line <- words, word <- glyphs
+_ORDER_ATTR = (('textLineOrder', 'bottom-to-top'), ('readingDirection', 'right-to-left'),
+               ('readingDirection', 'right-to-left'))
+
+
 def _filter_choices(textequivs):
-    """At most CHOICE_THRESHOLD_NUM alternatives, none more than CHOICE_THRESHOLD_CONF below the first (:657-672)."""
-    if not textequivs:
-        return []
-    textequivs = textequivs[:min(CHOICE_THRESHOLD_NUM, len(textequivs))]
-    for te in textequivs:
+    """The alternatives worth searching (reference :657-672): the first CHOICE_THRESHOLD_NUM of the element, confidences
+    as floats (missing = 1.0), minus those that fall CHOICE_THRESHOLD_CONF or more below the first."""
+    kept = []
+    for te in textequivs[:CHOICE_THRESHOLD_NUM]:
         te.set_conf(float(te.conf) if te.conf else 1.0)
-    conf0 = textequivs[0].conf
-    return [te for te in textequivs if conf0 - te.conf < CHOICE_THRESHOLD_CONF]
+        if kept and kept[0].conf - te.conf >= CHOICE_THRESHOLD_CONF:
+            continue
+        kept.append(te)
+    return kept
 
 
-def _add_element(graph, start_node, element, textequivs):
-    graph.add_node(start_node + 1)
-    graph.add_edge(start_node, start_node + 1, element=element, alternatives=_filter_choices(textequivs))
-    return start_node + 1
+def _reading_sequence(doc, target, warn):
+    """The page as the language model reads it, for elements at depth `target`: yields (separator, None) for the implicit
+    white space and (None, segment) for the elements, in document order.
 
+    White space hangs on regions (region level), lines (line level) or words (word and glyph level): every such carrier
+    except the one whose sibling indices are all zero is preceded by a newline -- or by a blank, if it is a word that is
+    not the first of its line (reference :343-424: the ``first_*`` flags there are positional, so a page whose first
+    region is empty starts with a separator; kept)."""
+    carrier = min(target, _WORD_DEPTH)
 
-def _add_space(graph, start_node, space):
-    """Pseudo-element edge for the implicit white space between two tokens (:623-644, without the repair)."""
-    return _add_element(graph, start_node, None, [TextEquiv(Unicode=space, conf=1.0)])
+    def descend(segment, depth, path):
+        if depth == carrier and any(path):
+            yield ' ' if depth == _WORD_DEPTH and path[-1] else '\n', None
+        if depth == target:
+            yield None, segment
+            return
+        children = segment.children(_SEGMENT_TAGS[depth + 1])
+        if not children:
+            warn("%s '%s' contains no %s", _NOUNS[depth], segment.id, _PARTS[depth + 1])
+        for i, child in enumerate(children):
+            for item in descend(child, depth + 1, path + (i,)):
+                yield item
 
-
-def _get_edges(graph, start_node):
-    return [graph.edges[in_, out] for in_, out in nx.bfs_edges(graph, start_node)]
+    regions = doc.get_TextRegion()
+    if not regions:
+        warn("Page contains no %s", _PARTS[0])
+    for i, region in enumerate(regions):
+        for item in descend(region, 0, (i,)):
+            yield item
 
 
 def page_get_linear_graph_at(level, doc, logger=None):
-    """Linear graph of the page's elements at `level`: one edge per element with its (filtered) alternatives, plus
-    one edge per implicit white space: a newline between lines and regions, a space between words (:343-424).
-    Returns (graph, start node, end node)."""
+    """Linear graph of the page at `level` (reference :343-424): nodes 0..n, one edge per element that has text results
+    (attributes ``element`` and ``alternatives``: its filtered TextEquivs) and one per implicit white space (``element``
+    None, a single alternative with confidence 1).  Returns (graph, start node, end node)."""
     assert level in LEVELS
     logger = logger or logging.getLogger(__name__)
     graph = nx.DiGraph(level=level)
     graph.add_node(0)
-    start_node = 0
-    regions = doc.get_TextRegion()
-    if not regions:
-        logger.warning("Page contains no text regions")
-    page_start_node = start_node
-    first_region = True
-    for region in regions:
-        if level == 'region':
-            textequivs = region.get_TextEquiv()
-            if not first_region:
-                start_node = _add_space(graph, start_node, '\n')
-            if textequivs:
-                start_node = _add_element(graph, start_node, region, textequivs)
-            else:
-                logger.warning("Region '%s' contains no text results", region.id)
-            first_region = False
-            continue
-        lines = region.get_TextLine()
-        if not lines:
-            logger.warning("Region '%s' contains no text lines", region.id)
-        first_line = True
-        for line in lines:
-            if level == 'line':
-                textequivs = line.get_TextEquiv()
-                if not first_line or not first_region:
-                    start_node = _add_space(graph, start_node, '\n')
-                if textequivs:
-                    start_node = _add_element(graph, start_node, line, textequivs)
-                else:
-                    logger.warning("Line '%s' contains no text results", line.id)
-                first_line = False
+    end = 0
+    for separator, segment in _reading_sequence(doc, _LEVEL_DEPTH[level], logger.warning):
+        if segment is None:
+            alternatives = [TextEquiv(Unicode=separator, conf=1.0)]
+        else:
+            alternatives = _filter_choices(segment.get_TextEquiv())
+            if not alternatives:
+                logger.warning("%s '%s' contains no text results", _NOUNS[_LEVEL_DEPTH[level]], segment.id)
                 continue
-            words = line.get_Word()
-            if not words:
-                logger.warning("Line '%s' contains no words", line.id)
-            first_word = True
-            for word in words:
-                textequivs = word.get_TextEquiv()
-                if not first_word or not first_line or not first_region:
-                    start_node = _add_space(graph, start_node, '\n' if first_word else ' ')
-                if level == 'word':
-                    if textequivs:
-                        start_node = _add_element(graph, start_node, word, textequivs)
-                    else:
-                        logger.warning("Word '%s' contains no text results", word.id)
-                    first_word = False
-                    continue
-                glyphs = word.get_Glyph()
-                if not glyphs:
-                    logger.warning("Word '%s' contains no glyphs", word.id)
-                for glyph in glyphs:
-                    textequivs = glyph.get_TextEquiv()
-                    if textequivs:
-                        start_node = _add_element(graph, start_node, glyph, textequivs)
-                    else:
-                        logger.warning("Glyph '%s' contains no text results", glyph.id)
-                first_word = False
-            first_line = False
-        first_region = False
-    return graph, page_start_node, start_node
+        graph.add_edge(end, end + 1, element=segment, alternatives=alternatives)
+        end += 1
+    return graph, 0, end
+
+
+def _get_edges(graph, start_node):
+    """Edge attribute dicts of a linear graph, in path order."""
+    out = []
+    node = start_node
+    while True:
+        successors = list(graph.successors(node))
+        if not successors:
+            return out
+        out.append(graph.edges[node, successors[0]])
+        node = successors[0]
 
 
 def page_update_from_path(level, path, entropy, logger=None):
-    """Apply a decided path: keep only the chosen alternative on every element, with its score as confidence
-    (:426-441).  Returns (average probability, character perplexity, element perplexity)."""
+    """Write a decided path [(element, alternative, score)] back (reference :426-441): every element keeps the chosen
+    alternative only, with the score as its confidence.  Returns (average probability, character perplexity,
+    perplexity per element incl. white space) from the path's entropy in bits."""
     logger = logger or logging.getLogger(__name__)
-    strlen = 0
+    n_chars = 0
     for element, textequiv, score in path:
-        if element:                                 # not just space
-            textequiv.set_conf(score)
-            element.set_TextEquiv([textequiv])      # delete others
-            strlen += len(textequiv.Unicode)
-        else:
-            strlen += 1
-    ent = entropy / strlen
-    avg = pow(2.0, -ent)
-    ppl = pow(2.0, ent)                             # character level
-    ppll = pow(2.0, ent * strlen / len(path))       # textequiv level (including spaces/newlines)
-    logger.info("avg: %.3f, char ppl: %.3f, %s ppl: %.3f", avg, ppl, level, ppll)
-    return avg, ppl, ppll
+        if element is None:                         # implicit white space: one character, nothing to write
+            n_chars += 1
+            continue
+        textequiv.set_conf(score)
+        element.set_TextEquiv([textequiv])
+        n_chars += len(textequiv.Unicode)
+    bits_per_char = entropy / n_chars
+    stats = (2.0 ** -bits_per_char, 2.0 ** bits_per_char, 2.0 ** (entropy / len(path)))
+    logger.info("avg: %.3f, char ppl: %.3f, %s ppl: %.3f", stats[0], stats[1], level, stats[2])
+    return stats
 
 
 def page_element_unicode0(element):
-    tes = element.get_TextEquiv()
-    return (tes[0].Unicode or '') if tes else ''
+    """Text of the element's first alternative ('' if it has none)."""
+    for te in element.get_TextEquiv():
+        return te.Unicode or ''
+    return ''
 
 
 def page_element_conf0(element):
-    tes = element.get_TextEquiv()
-    return float(tes[0].conf or "1.0") if tes else 1.0
+    """Confidence of the element's first alternative (1.0 if missing)."""
+    for te in element.get_TextEquiv():
+        return float(te.conf) if te.conf else 1.0
+    return 1.0
+
+
+def _first_texts(segments):
+    return [page_element_unicode0(seg) for seg in segments]
+
+
+def _mean_conf(segments):
+    return sum(page_element_conf0(seg) for seg in segments) / len(segments) if segments else 0
+
+
+def _glue(texts, glued):
+    """Concatenate with the level's joiner except where `glued[i]` says that texts i and i+1 belong together."""
+    out = texts[0]
+    for text, (joiner, skip) in zip(texts[1:], glued):
+        out += text if skip else joiner + text
+    return out
 
 
 def page_update_higher_textequiv_levels(level, doc, overwrite=True):
-    """Make the TextEquivs of all hierarchy levels above `level` consistent with it: concatenate the first
-    alternatives (glyphs directly, words by space, lines and regions by newline, nothing where a ``join`` Relation
-    links two neighbours), average their confidences; right-to-left / bottom-to-top orders are honoured (:478-590)."""
-    if level == 'region':
+    """Make the text of every hierarchy level above `level` the concatenation of the level below it (reference :478-590).
+
+    Bottom-up over the tables above: a word is its glyphs' first texts, a line its words joined by blanks, a region its
+    lines joined by newlines; confidences are averaged.  Children are taken in the order their ``readingDirection`` /
+    ``textLineOrder`` (own, else inherited from the enclosing segments and the page) asks for; regions that contain
+    regions are the newline-joined texts of those, in ``ReadingOrder`` where the page defines one for all of them, and
+    are visited after them; a ``Relation`` of type join between two neighbours (regions, or the last and first word of
+    two lines) drops the newline.  `overwrite` False keeps text that is already there."""
+    bottom = _LEVEL_DEPTH[level]
+    if bottom == 0:
         return
-    joins = doc.joins()
-    page = doc.page
-    for region in doc.get_AllTextRegions():
-        subregions = region.get_TextRegion()
-        if subregions:                              # already visited: concatenate them
-            region_unicode = page_element_unicode0(subregions[0])
-            for sub, nxt in zip(subregions, subregions[1:]):
-                if (sub.id, nxt.id) not in joins:
-                    region_unicode += '\n'
-                region_unicode += page_element_unicode0(nxt)
-            region_conf = sum(page_element_conf0(sub) for sub in subregions) / len(subregions)
+    joins = set(doc.joins())
+    order = doc.reading_order()
+
+    def put(segment, text, conf):
+        if overwrite or not segment.get_TextEquiv():
+            segment.set_TextEquiv([TextEquiv(Unicode=text, conf=conf)])
+
+    def ordered_children(segment, depth, inherited):
+        children = segment.children(_SEGMENT_TAGS[depth + 1])
+        attr, reverse_value = _ORDER_ATTR[depth]
+        wanted = next((n.get(attr) for n in (segment,) + inherited if n.get(attr)), None)
+        return list(reversed(children)) if wanted == reverse_value else children
+
+    def rebuild(segment, depth, inherited):
+        """Text and confidence of `segment` from its children, after rebuilding those (down to the rated level)."""
+        children = ordered_children(segment, depth, inherited)
+        if depth + 1 < bottom:
+            for child in children:
+                rebuild(child, depth + 1, (segment,) + inherited)
+        if depth == 0:
+            if not children:
+                return put(segment, '', 0)
+            # between two lines the newline goes if their adjoining words (in document order) are joined
+            edge_words = [line.children('Word') for line in children]
+            glued = [('\n', bool(a and b and (a[-1].id, b[0].id) in joins)) for a, b in zip(edge_words, edge_words[1:])]
         else:
-            lines = region.get_TextLine()
-            if (region.get('textLineOrder') or page.get('textLineOrder')) == 'bottom-to-top':
-                lines = list(reversed(lines))
-            if level != 'line':
-                for line in lines:
-                    words = line.get_Word()
-                    if (line.get('readingDirection') or region.get('readingDirection') or
-                            page.get('readingDirection')) == 'right-to-left':
-                        words = list(reversed(words))
-                    if level != 'word':
-                        for word in words:
-                            glyphs = word.get_Glyph()
-                            if (word.get('readingDirection') or line.get('readingDirection') or
-                                    region.get('readingDirection') or page.get('readingDirection')) == 'right-to-left':
-                                glyphs = list(reversed(glyphs))
-                            word_unicode = ''.join(page_element_unicode0(glyph) for glyph in glyphs)
-                            word_conf = sum(page_element_conf0(glyph) for glyph in glyphs)
-                            if glyphs:
-                                word_conf /= len(glyphs)
-                            if not word.get_TextEquiv() or overwrite:
-                                word.set_TextEquiv([TextEquiv(Unicode=word_unicode, conf=word_conf)])
-                    line_unicode = ' '.join(page_element_unicode0(word) for word in words)
-                    line_conf = sum(page_element_conf0(word) for word in words)
-                    if words:
-                        line_conf /= len(words)
-                    if not line.get_TextEquiv() or overwrite:
-                        line.set_TextEquiv([TextEquiv(Unicode=line_unicode, conf=line_conf)])
-            region_unicode = ''
-            region_conf = 0
-            if lines:
-                region_unicode = page_element_unicode0(lines[0])
-                for line, next_line in zip(lines, lines[1:]):
-                    words, next_words = line.get_Word(), next_line.get_Word()
-                    if not (words and next_words and (words[-1].id, next_words[0].id) in joins):
-                        region_unicode += '\n'
-                    region_unicode += page_element_unicode0(next_line)
-                region_conf = sum(page_element_conf0(line) for line in lines) / len(lines)
-        if not region.get_TextEquiv() or overwrite:
-            region.set_TextEquiv([TextEquiv(Unicode=region_unicode, conf=region_conf)])
+            glued = [(_JOINER[depth], False)] * max(len(children) - 1, 0)
+        put(segment, _glue(_first_texts(children), glued) if children else '', _mean_conf(children))
+
+    for region in doc.get_AllTextRegions():             # nested regions come before the regions that contain them
+        inner = region.get_TextRegion()
+        if not inner:
+            rebuild(region, 0, (doc.page,))
+            continue
+        ranks = [order.get(sub.id) for sub in inner]
+        if all(r is not None and r[1] is not None for r in ranks) and ranks[0][0].startswith('OrderedGroup'):
+            inner = [sub for _, sub in sorted(zip((r[1] for r in ranks), inner), key=lambda pair: pair[0])]
+        glued = [('\n', (a.id, b.id) in joins) for a, b in zip(inner, inner[1:])]
+        put(region, _glue(_first_texts(inner), glued), _mean_conf(inner))
 
 
 class PageRater(object):

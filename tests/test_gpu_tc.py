@@ -199,21 +199,6 @@ def test_umma2_selftest_cta_pair_layout():
         np.testing.assert_array_equal(_native.selftest_umma2(A, B), A.astype(np.float32) @ B.astype(np.float32).T)
 
 
-def test_cta_pair_kernel_matches_single_cta_kernel(monkeypatch):
-    """klm_seq_tc2 (opt-in) against klm_seq_tc on the same inputs."""
-    wd = synth.weights(13, width=128, depth=2, voc_size=256, style='trained')
-    maparr = synth.vocabulary()
-    texts = [synth.text(800 + i, 20 + i) for i in range(40)]
-    ctxs = [[i % 200] for i in range(40)]
-    a = product(wd, maparr, 32).rate_many(texts, ctxs)
-    monkeypatch.setenv('KLM_ENABLE_TC2', '1')
-    r = product(wd, maparr, 32)
-    assert r._native.info()['tc_enabled'] == 2
-    b = r.rate_many(texts, ctxs)
-    for x, y in zip(a, b):
-        assert logp_err(x, y) <= 1e-4
-
-
 @pytest.mark.parametrize('width,depth,nctx', [(128, 2, 1), (256, 3, 3), (512, 3, 1)])
 def test_tc_skew3_early_signal_matches_skew2_and_oracle(width, depth, nctx, monkeypatch):
     """Launches of >= 64 positions run with skew 3 (IN / PROJ CTAs signal the grid barrier before their epilogue, Z and
