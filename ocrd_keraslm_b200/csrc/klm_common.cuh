@@ -21,6 +21,19 @@
 #include <stdint.h>
 #include "../../include/keraslm_b200.h"
 
+// tanh(x) as a quotient num / den with e = exp(-2x): num = 1 - e, den = 1 + e.  For small |x| the numerator cancels
+// (e ~ 1: an absolute error of ~1e-7 in a value of ~2|x|; with Keras-default initialisation cell values are ~1e-3 and
+// the states drifted 1.7e-4 relative, tests/test_gpu_long.py), so below 1/8 the odd polynomial
+// x - x^3/3 + 2x^5/15 - 17x^7/315 takes its place (truncation error 1e-9 relative).  The callers fold the quotient into
+// the division they do anyway (sigmoid(i) * tanh(g) = num / ((1 + e_i) * den)).
+__device__ __forceinline__ void klm_tanh_parts(float x, float e, float &num, float &den) {
+    const float x2 = x * x;
+    const float poly = x * fmaf(x2, fmaf(x2, fmaf(x2, -17.f / 315.f, 2.f / 15.f), -1.f / 3.f), 1.f);
+    const bool small = fabsf(x) < 0.125f;
+    num = small ? poly : 1.f - e;
+    den = small ? 1.f : 1.f + e;
+}
+
 #define KLM_THREADS      512
 #define KLM_WARPS        (KLM_THREADS / 32)
 #define KLM_MAX_ITEMS    8      // (unit, 32-stream group) items per warp in the stream-parallel mode

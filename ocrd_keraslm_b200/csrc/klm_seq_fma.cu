@@ -77,11 +77,14 @@ __device__ __forceinline__ float klm_clamp30(float x) { return fminf(fmaxf(x, -3
 __device__ __forceinline__ void lstm_cell_fast(const float4 a, float &c, float &h) {
     const float ei = klm_ex2(-klm_clamp30(a.x)), ef = klm_ex2(-klm_clamp30(a.y)), eg = klm_ex2(-2.f * klm_clamp30(a.z)),
                 eo = klm_ex2(-klm_clamp30(a.w));
-    const float ig = __fdividef(1.f - eg, (1.f + ei) * (1.f + eg));
+    float num, den;
+    klm_tanh_parts(a.z, eg, num, den);
+    const float ig = __fdividef(num, (1.f + ei) * den);
     const float f = __fdividef(1.f, 1.f + ef);
     c = fmaf(f, c, ig);
     const float ec = klm_ex2(-2.f * klm_clamp30(c));
-    h = __fdividef(1.f - ec, (1.f + eo) * (1.f + ec));
+    klm_tanh_parts(c, ec, num, den);
+    h = __fdividef(num, (1.f + eo) * den);
 }
 
 // ---------------------------------------------------------------------------------------------

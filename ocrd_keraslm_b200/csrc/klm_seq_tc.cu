@@ -638,16 +638,17 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 const int pr0 = role.first_pair + R.pb + R.own_first;        // first own pair of the round (layer-wide index)
                 if (is_rec) {
                     // LSTM cell for all owned units, staged so that the MUFU chains of different units overlap
-                    float e1[KLM_TC_OWN][2], e2[KLM_TC_OWN][2], e3[KLM_TC_OWN][2], e4[KLM_TC_OWN][2];
+                    float e1[KLM_TC_OWN][2], e2[KLM_TC_OWN][2], e3[KLM_TC_OWN][2], e4[KLM_TC_OWN][2], ag[KLM_TC_OWN][2];
 #pragma unroll
                     for (int i = 0; i < KLM_TC_OWN; ++i)
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             if (i >= R.nown) continue;             // (warp-uniform)
                             const float4 a = add4[i][e];
+                            ag[i][e] = acc[i][4 * e + 2] + a.z;
                             e1[i][e] = tc_exp(-tc_clamp(acc[i][4 * e] + a.x));
                             e2[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 1] + a.y));
-                            e3[i][e] = tc_exp(-2.f * tc_clamp(acc[i][4 * e + 2] + a.z));
+                            e3[i][e] = tc_exp(-2.f * tc_clamp(ag[i][e]));
                             e4[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 3] + a.w));
                         }
 #pragma unroll
@@ -655,7 +656,9 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             if (i >= R.nown) continue;
-                            const float ig = __fdividef(1.f - e3[i][e], (1.f + e1[i][e]) * (1.f + e3[i][e]));
+                            float num, den;
+                            klm_tanh_parts(ag[i][e], e3[i][e], num, den);      // (small arguments: no cancellation)
+                            const float ig = __fdividef(num, (1.f + e1[i][e]) * den);
                             const float f = __fdividef(1.f, 1.f + e2[i][e]);
                             e1[i][e] = fmaf(f, c_reg[r][i][e], ig);                    // new cell state
                             e2[i][e] = tc_exp(-2.f * tc_clamp(e1[i][e]));
@@ -665,7 +668,9 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             if (i >= R.nown) continue;
-                            const float hn = __fdividef(1.f - e2[i][e], (1.f + e4[i][e]) * (1.f + e2[i][e]));
+                            float num, den;
+                            klm_tanh_parts(e1[i][e], e2[i][e], num, den);
+                            const float hn = __fdividef(num, (1.f + e4[i][e]) * den);
                             if (active) { c_reg[r][i][e] = e1[i][e]; h_reg[r][i][e] = hn; }
                         }
                     // the new hidden vector as fp16 hi/lo in the operand layout of its readers

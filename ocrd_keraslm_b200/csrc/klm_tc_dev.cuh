@@ -63,11 +63,14 @@ __device__ __forceinline__ float tc_clamp(float x) { return fminf(fmaxf(x, -30.f
 __device__ __forceinline__ void tc_cell(float ai, float af, float ag, float ao, float &c, float &h) {
     const float ei = tc_exp(-tc_clamp(ai)), ef = tc_exp(-tc_clamp(af)), eg = tc_exp(-2.f * tc_clamp(ag)),
                 eo = tc_exp(-tc_clamp(ao));
-    const float ig = __fdividef(1.f - eg, (1.f + ei) * (1.f + eg));
+    float num, den;
+    klm_tanh_parts(ag, eg, num, den);
+    const float ig = __fdividef(num, (1.f + ei) * den);
     const float f = __fdividef(1.f, 1.f + ef);
     c = fmaf(f, c, ig);
     const float ec = tc_exp(-2.f * tc_clamp(c));
-    h = __fdividef(1.f - ec, (1.f + eo) * (1.f + ec));
+    klm_tanh_parts(c, ec, num, den);
+    h = __fdividef(num, (1.f + eo) * den);
 }
 
 // hidden value -> fp16 hi/lo operand pair, scaled by KLM_TC_HSCALE so that the lo part stays a normal fp16 number

@@ -353,43 +353,36 @@ class Rater(object):
         raise NotImplementedError('training is outside the B200 rating path; train with the reference and load the file')
 
     def remove_from_mapping(self, char=None, idx=None):
-        """Remove one character from the vocabulary and the matching row of the (tied) embedding,
-        shifting all higher indices down by one (reference :416-460); the device model is rebuilt
-        from the pruned weights.  Returns False (after logging) if there is nothing to remove."""
+        """Prune one character from the vocabulary (reference :416-460, CLI ``prune-charset``): its row leaves the
+        (tied) embedding, every higher index moves down by one, and the device model is rebuilt from the pruned
+        weights.  Done as array surgery on the stored code-point array (index = vocabulary id) and the embedding
+        matrix, not entry by entry.  Returns False (after logging) if there is nothing to remove."""
         assert self.status > 1
         assert self.voc_size > 0
-        if not char and not idx:
-            return False
+        c_i, i_c = self.mapping
         if char:
-            if char in self.mapping[0]:
-                idx = self.mapping[0][char]
-            else:
+            idx = c_i.get(char)
+            if idx is None:
                 self.logger.error('unmapped character "%s" cannot be removed', char)
                 return False
-        else:
-            if idx in self.mapping[1]:
-                char = self.mapping[1][idx]
-            else:
+        elif idx:
+            char = i_c.get(idx)
+            if char is None:
                 self.logger.error('unmapped index "%d" cannot be removed', idx)
                 return False
+        else:
+            return False
         embedding = np.asarray(self._host_weights['char_embedding'], dtype=np.float32)
-        norm = np.linalg.norm(embedding[idx, :])
-        self.logger.warning('pruning character "%s" [%d] with norm %f', char, idx, norm)
-        self.mapping[0].pop(char)
-        self.mapping[1].pop(idx)
-        for i in range(idx + 1, self.voc_size):
-            otherchar = self.mapping[1][i]
-            self.mapping[0][otherchar] -= 1
-            self.mapping[1][i - 1] = otherchar
-            self.mapping[1].pop(i)
-        self.voc_size -= 1
+        self.logger.warning('pruning character "%s" [%d] with norm %f', char, idx, np.linalg.norm(embedding[idx]))
+        codepoints = np.zeros(embedding.shape[0], dtype=np.uint32)
+        known = np.fromiter(i_c.keys(), dtype=np.int64, count=len(i_c))
+        codepoints[known] = [ord(i_c[int(i)]) for i in known]
         wd = dict(self._host_weights)
-        wd['char_embedding'] = np.delete(embedding, idx, 0)
-        self._lut = None                     # char -> index table cache is stale now
-        self._lut_src = None
+        wd['char_embedding'] = np.delete(embedding, idx, axis=0)
+        self.set_mapping(np.delete(codepoints, idx))        # rebuilds both dictionaries and voc_size
+        self._lut = self._lut_src = None                    # the char -> index lookup table is stale now
         self.configure()
         self.set_weights(wd)
-        self.status = 2
         return True
 
     # ------------------------------------------------------------------ vocabulary

@@ -35,9 +35,16 @@ def rate_sharded(rater, texts, contexts=None, gather=True, group=None):
     gather=True  : every rank returns the full list (one float32 array of probabilities per text)
     gather=False : every rank returns a list with its own units filled in and None elsewhere
     Without an initialised process group this is just ``rater.rate_many``.
+
+    Texts are NFC-normalised HERE, once, so that the partition, the buffer sizes and the unpacking offsets on every
+    rank are derived from the lengths ``rate_many`` will return (it normalises, too: a decomposed sequence shrinks).
+    A rank whose local rating fails still takes part in the collectives: an error flag is reduced first, and every
+    rank raises if any rank failed -- nobody is left waiting in the gather.
     """
+    import unicodedata
     import torch
     import torch.distributed as dist
+    texts = [unicodedata.normalize('NFC', t) for t in texts]
     n = len(texts)
     if contexts is None:
         contexts = [None] * n
@@ -47,31 +54,45 @@ def rate_sharded(rater, texts, contexts=None, gather=True, group=None):
     lengths = [len(t) for t in texts]
     parts = partition(lengths, world)
     mine = parts[rank]
-    res = rater.rate_many([texts[i] for i in mine], [contexts[i] for i in mine]) if mine else []
     out = [None] * n
-    for i, r in zip(mine, res):
-        out[i] = np.asarray(r, dtype=np.float32)
-    if not gather or world == 1:
+    failure = None
+    try:
+        res = rater.rate_many([texts[i] for i in mine], [contexts[i] for i in mine]) if mine else []
+        for i, r in zip(mine, res):
+            out[i] = np.asarray(r, dtype=np.float32)
+            if out[i].shape != (lengths[i],):
+                raise ValueError('rate_many returned %d scores for a text of %d characters' % (len(out[i]), lengths[i]))
+    except Exception as e:                                 # pylint: disable=broad-except
+        failure = e
+    if world == 1:
+        if failure is not None:
+            raise failure
+        return out
+    backend = dist.get_backend(group)
+    dev = torch.device('cuda', torch.cuda.current_device()) if backend == 'nccl' else torch.device('cpu')
+    flag = torch.tensor([1 if failure is not None else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=group)
+    if failure is not None:
+        raise failure
+    if int(flag.item()):
+        raise RuntimeError('rate_sharded: rating failed on another rank')
+    if not gather:
         return out
     # one padded all-gather of the flat score arrays; sizes are known to everybody
     sizes = [sum(lengths[i] for i in p) for p in parts]
     cap = max(max(sizes), 1)
-    backend = dist.get_backend(group)
-    dev = torch.device('cuda', torch.cuda.current_device()) if backend == 'nccl' else torch.device('cpu')
     flat = np.zeros(cap, dtype=np.float32)
-    pos = 0
-    for i in mine:
-        flat[pos:pos + lengths[i]] = out[i]
-        pos += lengths[i]
+    if mine and sizes[rank]:
+        np.concatenate([out[i] for i in mine], out=flat[:sizes[rank]])
     send = torch.from_numpy(flat).to(dev)
-    recv = [torch.empty(cap, dtype=torch.float32, device=dev) for _ in range(world)]
-    dist.all_gather(recv, send, group=group)
+    recv = torch.empty(world * cap, dtype=torch.float32, device=dev)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    everything = recv.cpu().numpy().reshape(world, cap)
     for r, p in enumerate(parts):
         if r == rank:
             continue
-        buf = recv[r].cpu().numpy()
         pos = 0
         for i in p:
-            out[i] = buf[pos:pos + lengths[i]].copy()
+            out[i] = everything[r, pos:pos + lengths[i]].copy()
             pos += lengths[i]
     return out

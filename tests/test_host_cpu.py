@@ -146,10 +146,15 @@ WORKER = textwrap.dedent('''
     class FakeRater(object):
         """Stand-in with rate_many semantics: score of position t of a text depends on the text only."""
         calls = 0
+        fail_on_rank = None
         def rate_many(self, texts, contexts=None):
+            import unicodedata
+            if FakeRater.fail_on_rank == dist.get_rank():
+                raise RuntimeError('device lost')
             FakeRater.calls += len(texts)
             out = []
             for t, c in zip(texts, contexts):
+                t = unicodedata.normalize('NFC', t)          # like Rater.rate_many: one score per NFC character
                 v = np.array([((ord(ch) * 31 + k + (c[0] if c else 0)) %% 97) / 97.0 for k, ch in enumerate(t)], dtype=np.float32)
                 if len(v):
                     v[0] = 1.0
@@ -159,12 +164,16 @@ WORKER = textwrap.dedent('''
     dist.init_process_group('gloo', init_method='tcp://127.0.0.1:%(port)d', rank=int(sys.argv[1]), world_size=2)
     rng = np.random.default_rng(11)
     texts = [''.join(chr(97 + int(x)) for x in rng.integers(0, 26, int(n))) for n in rng.integers(0, 40, 23)]
+    texts[3] = 'a\u0308bc' + texts[3]            # decomposed sequences: NFC makes these texts shorter
+    texts[17] = 'e\u0301' * 9
     ctxs = [[int(rng.integers(0, 200))] for _ in texts]
     full = FakeRater().rate_many(texts, ctxs)
+    assert len(full[17]) == 9
     FakeRater.calls = 0
     r = FakeRater()
     got = shard.rate_sharded(r, texts, ctxs, gather=True)
-    mine = shard.partition([len(t) for t in texts], 2)[dist.get_rank()]
+    import unicodedata
+    mine = shard.partition([len(unicodedata.normalize('NFC', t)) for t in texts], 2)[dist.get_rank()]
     assert FakeRater.calls == len(mine), (FakeRater.calls, len(mine))
     assert len(got) == len(full)
     for a, b in zip(got, full):
@@ -172,6 +181,14 @@ WORKER = textwrap.dedent('''
     part = shard.rate_sharded(r, texts, ctxs, gather=False)
     for i, a in enumerate(part):
         assert (a is not None) == (i in mine)
+    # a rank whose rating fails must not leave the other one hanging in the gather: both raise
+    FakeRater.fail_on_rank = 1
+    try:
+        shard.rate_sharded(r, texts, ctxs, gather=True)
+        raise SystemExit('no exception on rank %%d' %% dist.get_rank())
+    except RuntimeError as e:
+        assert ('device lost' in str(e)) == (dist.get_rank() == 1), str(e)
+    FakeRater.fail_on_rank = None
     dist.barrier()
     dist.destroy_process_group()
     print('rank', sys.argv[1], 'ok')
