@@ -179,7 +179,8 @@ typedef struct klm_info {
     int64_t tc_launches;        /* launches of the tcgen05 kernel so far */
     int64_t cl_launches;        /* launches of the one-cluster kernel (<= 8 streams, small models) so far */
     int32_t cl_cluster;         /* CTAs of that cluster (8 or 16); 0 = the model does not fit one cluster */
-    int32_t reserved_;
+    int32_t tc_dataflow;        /* 1: the tcgen05 kernel in use is the dataflow form (a flag per hand-over, no grid barrier;
+                                 * also serves klm_step for up to 256 hypotheses per launch), 0: the grid-barrier form */
 } klm_info;
 int klm_get_info(klm_model *m, klm_info *out);
 

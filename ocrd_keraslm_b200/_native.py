@@ -13,7 +13,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB_PATH = os.path.join(HERE, 'libkeraslm_b200.so')
-SOURCES = ['klm_api.cu', 'klm_seq_fma.cu', 'klm_seq_tc.cu']
+SOURCES = ['klm_api.cu', 'klm_seq_fma.cu', 'klm_seq_tc.cu', 'klm_seq_df.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-shared', '-Xcompiler', '-fPIC']
 
@@ -91,7 +91,7 @@ class KlmInfo(ctypes.Structure):
                 ('smem_bytes', ctypes.c_int32), ('kernel_launches', ctypes.c_int64),
                 ('last_kernel_ms', ctypes.c_double), ('max_streams', ctypes.c_int32), ('tc_enabled', ctypes.c_int32),
                 ('tc_grid', ctypes.c_int32), ('tc_smem_bytes', ctypes.c_int32), ('tc_launches', ctypes.c_int64),
-                ('cl_launches', ctypes.c_int64), ('cl_cluster', ctypes.c_int32), ('reserved_', ctypes.c_int32)]
+                ('cl_launches', ctypes.c_int64), ('cl_cluster', ctypes.c_int32), ('tc_dataflow', ctypes.c_int32)]
 
 
 # every symbol include/keraslm_b200.h declares: (name, restype, argtypes)

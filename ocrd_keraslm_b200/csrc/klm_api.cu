@@ -15,6 +15,7 @@
 
 cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
+cudaError_t klm_launch_seq_df(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_cl(const KlmSeqParams &p, const KlmClGeom &g, cudaStream_t stream);
 size_t klm_cl_smem_bytes(const KlmSeqParams &p, const KlmClGeom &g);
 cudaError_t klm_launch_umma2_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
@@ -71,6 +72,14 @@ struct KlmTcPlan {
     int stream_b = 0;                                        // single-CTA kernel, streamed-weights form (klm_seq_tcs)
     unsigned long long *trace = nullptr;
     int trace_t0 = 0;
+    // dataflow kernel (klm_seq_df.cu): flags / counters that are never reset, its own exchange buffers
+    bool df_ok = false;
+    size_t df_smem = 0;
+    unsigned int *sync = nullptr;
+    unsigned epoch = 0, tick_base = 0;
+    __half *hx_df = nullptr, *hx0 = nullptr;
+    float *Z_df = nullptr, *logits_df = nullptr;
+    int n_proj = 0;
 };
 
 // Run-time switches: read from the environment ONCE (klm_create), changed afterwards with klm_set_option -- no getenv on
@@ -82,6 +91,8 @@ struct KlmKnobs {
     int tc_skew = 0;              // KLM_TC_SKEW: 0 = by launch length, 2 / 3 = forced
     int tc_zpub = -1;             // KLM_TC_ZPUB: 2 = IN / PROJ stage + bulk-store their slice also with the early signal
     int tc_pub_release = 0;       // KLM_TC_PUB_RELEASE
+    int tc_df = 1;                // KLM_TC_DF: 1 = dataflow kernel (flags per hand-over) where the plan allows it, 0 = grid-barrier kernel
+    int tc_consumer_fence = 0;    // KLM_TC_CONSUMER_FENCE: fence.proxy.async between the flag polls and the bulk reads
     int tc_fault = 0;             // KLM_TC_FAULT (test hook: one CTA withholds a hand-over signal; the watchdog must fire)
     unsigned tc_spin_limit = 1u << 24;   // KLM_TC_SPIN_LIMIT
     int ll_debug = 0;             // KLM_LL_DEBUG
@@ -96,6 +107,8 @@ static void read_knobs(KlmKnobs &k) {
     k.tc_skew = env_int("KLM_TC_SKEW", 0);
     k.tc_zpub = env_int("KLM_TC_ZPUB", -1);
     k.tc_pub_release = env_int("KLM_TC_PUB_RELEASE", 0);
+    k.tc_df = env_int("KLM_TC_DF", 1);
+    k.tc_consumer_fence = env_int("KLM_TC_CONSUMER_FENCE", 0);
     k.tc_fault = env_int("KLM_TC_FAULT", 0);
     if (getenv("KLM_TC_SPIN_LIMIT")) k.tc_spin_limit = (unsigned)strtoul(getenv("KLM_TC_SPIN_LIMIT"), nullptr, 10);
     k.ll_debug = env_int("KLM_LL_DEBUG", 0);
@@ -148,7 +161,7 @@ struct klm_model {
     // stats
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
-    long long launches = 0, tc_launches = 0;
+    long long launches = 0, tc_launches = 0, df_launches = 0;
     // KLM_STEP_TIMING=1: host-clock breakdown of klm_step / klm_beam_edge, printed by klm_destroy
     int timing = 0;
     long long t_steps = 0, t_edges = 0;
@@ -503,7 +516,65 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
     }
     // the writers order their stores against the async proxy themselves (bulk stores, or fence.proxy.async before
     // the release), so the readers need no proxy fence of their own; KLM_TC_CONSUMER_FENCE=1 adds one (~600 clk per tick)
-    pl.consumer_fence = getenv("KLM_TC_CONSUMER_FENCE") ? atoi(getenv("KLM_TC_CONSUMER_FENCE")) : 0;
+    pl.consumer_fence = m->knobs.tc_consumer_fence;
+    // ---- dataflow kernel: who waits for whom (klm_seq_df.cu) ----
+    if (!pl.stream_b && pl.pub == 2) {
+        bool ok = true;
+        std::vector<std::vector<int>> rec_of(D), in_of(D);
+        std::vector<int> proj;
+        for (int i = 0; i < (int)pl.roles.size(); ++i) {
+            const KlmTcRole &r = pl.roles[i];
+            if (r.kind == KLM_TC_REC) rec_of[r.layer].push_back(i);
+            else if (r.kind == KLM_TC_IN) in_of[r.layer].push_back(i);
+            else if (r.kind == KLM_TC_PROJ) proj.push_back(i);
+        }
+        static const int df_geoms[7][2] = {{128, 3}, {64, 3}, {64, 4}, {128, 2}, {128, 1}, {64, 2}, {64, 1}};
+        size_t df_smem = 0;
+        for (int l = 0; l < D && ok; ++l) if (rec_of[l].size() > 64 || rec_of[l].empty()) ok = false;
+        for (int i = 0; i < (int)pl.roles.size() && ok; ++i) {
+            KlmTcRole &r = pl.roles[i];
+            if (r.kind == KLM_TC_LSE) continue;
+            bool geom = false;
+            for (auto &g : df_geoms) if (r.kc == g[0] && r.stages == g[1]) geom = true;
+            const int nch = W / r.kc;
+            if (!geom || nch > 16 || r.npairs > KLM_TC1_MAX_PAIRS) { ok = false; break; }
+            const std::vector<int> &src = rec_of[r.src_layer];
+            r.n_src = (int)src.size();
+            for (int c = 0; c < 16; ++c) r.ch_mask[c] = 0;
+            for (int c = 0; c < nch; ++c)
+                for (int j = 0; j < (int)src.size(); ++j) {
+                    const int u0 = 2 * pl.roles[src[j]].first_pair, u1 = u0 + 2 * pl.roles[src[j]].npairs;
+                    if (u0 < (c + 1) * r.kc && u1 > c * r.kc) r.ch_mask[c] |= 1ull << j;
+                }
+            r.idx = 0; r.n_readers = r.n_zprod = r.n_zcons = 0; r.alias_slot = 0; r.guard = 0;
+            if (r.kind == KLM_TC_REC) {
+                const std::vector<int> &mine = rec_of[r.layer];
+                r.idx = (int)(std::find(mine.begin(), mine.end(), i) - mine.begin());
+                r.n_readers = r.layer + 1 < D ? (int)in_of[r.layer + 1].size() : (int)proj.size();
+                r.n_zprod = r.layer > 0 ? (int)in_of[r.layer].size() : 0;
+                // the chunk with this CTA's own slice is fetched last of the first ring round; its slot holds the hand-over
+                // buffer and the publication staging while the ring is idle
+                const int c_own = 2 * r.first_pair / r.kc, c_end = (2 * (r.first_pair + r.npairs) - 1) / r.kc;
+                const int s_eff = std::min(r.stages, nch);
+                const size_t alias_bytes = (size_t)2 * ((r.npairs + 1) / 2) * 2048 + (size_t)(r.npairs / 4) * 2048;
+                if (c_own == c_end && alias_bytes <= (size_t)r.kc * 256) {
+                    r.alias_slot = s_eff - 1;
+                    r.sigma = (c_own - r.alias_slot + nch) % nch;           // chunk rotation: first chunk fetched each tick
+                } else {
+                    r.guard = 1; r.alias_slot = 0; r.sigma = r.idx % nch;
+                    if (alias_bytes > (size_t)r.ring_bytes) ok = false;
+                }
+            } else if (r.kind == KLM_TC_IN) {
+                r.n_zcons = (int)rec_of[r.layer].size();
+            }
+            df_smem = std::max(df_smem, (size_t)r.ring_bytes + 256 + (size_t)32 * W * r.npairs);
+        }
+        if (ok && df_smem <= m->smem_optin && !getenv("KLM_DISABLE_DF")) {
+            pl.df_ok = true;
+            pl.df_smem = df_smem;
+            pl.n_proj = (int)proj.size();
+        }
+    }
     CK(cudaMalloc(&pl.d_roles, pl.roles.size() * sizeof(KlmTcRole)));
     CK(cudaMemcpy(pl.d_roles, pl.roles.data(), pl.roles.size() * sizeof(KlmTcRole), cudaMemcpyHostToDevice));
     CK(cudaMalloc(&pl.d_wimg, img.size() * sizeof(__half)));
@@ -515,6 +586,16 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
     CK(cudaMalloc(&pl.Z, z_bytes)); CK(cudaMemset(pl.Z, 0, z_bytes));
     CK(cudaMalloc(&pl.logits, lg_bytes)); CK(cudaMemset(pl.logits, 0, lg_bytes));
     CK(cudaMalloc(&pl.err, 256)); CK(cudaMemset(pl.err, 0, 256));
+    if (pl.df_ok) {
+        const size_t hxv = (size_t)W * 128 * sizeof(__half);                               // one version of one layer
+        const size_t zdf = (size_t)D * KLM_DF_NZ * 2 * W * 64 * sizeof(float4);
+        const size_t ldf = (size_t)KLM_DF_NL * 2 * (pl.Vp / 4) * 64 * sizeof(float4);
+        CK(cudaMalloc(&pl.sync, KLM_DF_WORDS * sizeof(unsigned))); CK(cudaMemset(pl.sync, 0, KLM_DF_WORDS * sizeof(unsigned)));
+        CK(cudaMalloc(&pl.hx_df, (size_t)D * KLM_DF_R * hxv)); CK(cudaMemset(pl.hx_df, 0, (size_t)D * KLM_DF_R * hxv));
+        CK(cudaMalloc(&pl.hx0, (size_t)D * KLM_DF_MAXG * hxv)); CK(cudaMemset(pl.hx0, 0, (size_t)D * KLM_DF_MAXG * hxv));
+        CK(cudaMalloc(&pl.Z_df, zdf)); CK(cudaMemset(pl.Z_df, 0, zdf));
+        CK(cudaMalloc(&pl.logits_df, ldf)); CK(cudaMemset(pl.logits_df, 0, ldf));
+    }
     pl.ok = true;                                            // launched cooperatively: all CTAs are co-resident
     return KLM_OK;
 }
@@ -541,6 +622,7 @@ extern "C" int klm_destroy(klm_model *m) {
     cudaFree(m->plan_k.d_roles); cudaFree(m->plan_b.d_roles);
     cudaFree(m->tc.d_roles); cudaFree(m->tc.d_wimg); cudaFree(m->tc.hx); cudaFree(m->tc.Z); cudaFree(m->tc.logits);
     cudaFree(m->tc.err); cudaFree(m->tc.trace);
+    cudaFree(m->tc.sync); cudaFree(m->tc.hx_df); cudaFree(m->tc.hx0); cudaFree(m->tc.Z_df); cudaFree(m->tc.logits_df);
     cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
     cudaFree(m->hbuf_ll); cudaFree(m->logits_ll); cudaFree(m->progress); cudaFree(m->ll_err);
     if (m->h_step) cudaFreeHost(m->h_step);
@@ -729,6 +811,8 @@ extern "C" int klm_set_option(klm_model *m, const char *name, int64_t value) {
     else if (n == "tc_zpub") k.tc_zpub = (int)value;
     else if (n == "tc_pub_release") k.tc_pub_release = (int)value;
     else if (n == "tc_fault") k.tc_fault = (int)value;
+    else if (n == "tc_df") k.tc_df = (int)value;
+    else if (n == "tc_consumer_fence") k.tc_consumer_fence = (int)value;
     else if (n == "tc_spin_limit") k.tc_spin_limit = (unsigned)value;
     else if (n == "ll_debug") k.ll_debug = (int)value;
     else if (n == "step_timing") { k.step_timing = (int)value; m->timing = (int)value; }
@@ -864,6 +948,24 @@ extern "C" int klm_state_l2_distance(klm_model *m, const int32_t *a, const int32
     return KLM_OK;
 }
 
+// Fields of the dataflow kernel (klm_seq_df.cu) that do not depend on the batch.
+static void tc_df_params(klm_model *m, KlmTcParams &q) {
+    KlmTcPlan &tp = m->tc;
+    q.sync = tp.sync; q.epoch = tp.epoch; q.tick_base = tp.tick_base;
+    q.hx = tp.hx_df; q.hx0 = tp.hx0; q.Z = tp.Z_df; q.logits = tp.logits_df;
+    q.n_proj = tp.n_proj; q.n_lse_warps = tp.n_lse * (KLM_TC_THREADS / 32);
+    q.consumer_fence = m->knobs.tc_consumer_fence;
+    q.step_groups = 0; q.n_hyp = 0;
+}
+
+// After a device-side watchdog error the hand-over words are in an unknown state: start over from zero.
+static void tc_df_reset(klm_model *m) {
+    KlmTcPlan &tp = m->tc;
+    if (tp.sync) cudaMemset(tp.sync, 0, KLM_DF_WORDS * sizeof(unsigned));
+    tp.epoch = tp.tick_base = 0;
+    if (tp.err) cudaMemset(tp.err, 0, 256);
+}
+
 // ------------------------------------------------------------------------------------------
 // One cooperative launch over nb streams (nb <= plan.max_streams).  offsets0 are relative to
 // d_chars / d_targets / d_out.
@@ -926,8 +1028,17 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         q.pub_release = m->knobs.tc_pub_release;
         q.spin_limit = m->knobs.tc_spin_limit;
         q.fault = m->knobs.tc_fault;
-        CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         q.kc = tp.kc; q.ring_bytes = tp.ring_bytes;
+        if (tp.df_ok && m->knobs.tc_df) {
+            // dataflow kernel: flags / counters continue above the values the earlier launches left (no memset)
+            tc_df_params(m, q);
+            q.T_max = (int)tmax;
+            CK(klm_launch_seq_df(q, tp.grid, tp.df_smem, m->stream));
+            tp.tick_base += (unsigned)tmax; tp.epoch += (unsigned)tmax + 1u;
+            m->launches++; m->tc_launches++; m->df_launches++;
+            return KLM_OK;
+        }
+        CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         CK(klm_launch_seq_tc(q, tp.grid, tp.smem, m->stream));
         m->launches++; m->tc_launches++;
         return KLM_OK;
@@ -983,6 +1094,43 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     return KLM_OK;
 }
 
+// Step mode of the dataflow kernel: ONE position for nb <= 64 * KLM_DF_MAXG hypotheses in one launch (tick g advances
+// hypotheses 64g .. 64g+63; states in / out through the pool).
+static int run_step_df(klm_model *m, int nb, const int32_t *slots_in, const int32_t *slots_out, const int32_t *ctx,
+                       const int *d_chars, const int *d_targets, float *d_out, int full_rows) {
+    KlmTcPlan &tp = m->tc;
+    RingSlot rs;
+    int rc = ring_acquire(m, &rs, (size_t)nb * (4 * 2 + 4 * m->Nc) + 128);
+    if (rc) return rc;
+    int *d_si, *d_so, *d_cx;
+    ring_put(&rs, slots_in, nb, &d_si);
+    ring_put(&rs, slots_out, nb, &d_so);
+    int *hcx = ring_put<int>(&rs, nullptr, (size_t)nb * std::max(1, m->Nc), &d_cx);
+    for (int i = 0; i < nb * m->Nc; ++i) hcx[i] = ctx ? ctx[i] : 0;
+    rc = ring_commit(m, &rs); if (rc) return rc;
+    KlmTcParams q;
+    memset(&q, 0, sizeof q);
+    q.W = m->W; q.D = m->D; q.V = m->V; q.Vp = tp.Vp; q.Nc = m->Nc;
+    q.B = std::min(nb, KLM_TC_STREAMS); q.T_max = 1; q.stages = tp.stages;
+    for (int k = 0; k < m->Nc; ++k) { q.ctx_rows[k] = m->cfg.ctx_rows[k]; q.Q[k] = m->Q[k]; }
+    q.P = m->P;
+    for (int l = 0; l < m->D; ++l) q.bias[l] = m->bias[l];
+    q.wimg = tp.d_wimg; q.roles = tp.d_roles;
+    q.state = m->state; q.slots_in = d_si; q.slots_out = d_so; q.offsets = nullptr;
+    q.chars = d_chars; q.targets = d_targets; q.n_real = nullptr; q.ctx = d_cx;
+    q.out = d_out; q.full_rows = full_rows;
+    q.barrier = m->barrier; q.err = tp.err;
+    q.trace = tp.trace; q.trace_t0 = tp.trace_t0; q.trace_mode = m->knobs.tc_trace_mode;
+    q.pub_release = m->knobs.tc_pub_release; q.spin_limit = m->knobs.tc_spin_limit; q.fault = m->knobs.tc_fault;
+    tc_df_params(m, q);
+    q.step_groups = (nb + KLM_TC_STREAMS - 1) / KLM_TC_STREAMS;
+    q.n_hyp = nb;
+    CK(klm_launch_seq_df(q, tp.grid, tp.df_smem, m->stream));
+    tp.tick_base += (unsigned)q.step_groups; tp.epoch += (unsigned)q.step_groups + 1u;
+    m->launches++; m->tc_launches++; m->df_launches++;
+    return KLM_OK;
+}
+
 // Largest number of streams one launch takes for a call of n streams.
 static int batch_max(klm_model *m, int n) {
     if (n <= KLM_MODEK_MAXB) return KLM_MODEK_MAXB;
@@ -1003,8 +1151,12 @@ static int fetch_errors_async(klm_model *m) {
 }
 static int check_fetched_errors(klm_model *m) {
     if (m->h_err[0]) return fail(KLM_ECUDA, "klm_seq_fma_ll: device-side wait timed out (code %d)", m->h_err[0]);
-    if (m->h_err[1] || m->h_err[2])
-        return fail(KLM_ECUDA, "klm_seq_tc: device-side wait timed out (code %d)", m->h_err[1] ? m->h_err[1] : m->h_err[2]);
+    if (m->h_err[1] || m->h_err[2]) {
+        const int code = m->h_err[1] ? m->h_err[1] : m->h_err[2];
+        cudaStreamSynchronize(m->stream);
+        tc_df_reset(m);                                      // the model stays usable: hand-over words and error word start over
+        return fail(KLM_ECUDA, "klm_seq_tc: device-side wait timed out (code %d)", code);
+    }
     return KLM_OK;
 }
 
@@ -1017,7 +1169,11 @@ static int check_device_error(klm_model *m) {
     if (!m->tc.ok || m->tc_launches == 0) return KLM_OK;
     int code = 0;
     CK(cudaMemcpy(&code, m->tc.err, sizeof code, cudaMemcpyDeviceToHost));
-    if (code != 0) return fail(KLM_ECUDA, "klm_seq_tc: device-side wait timed out (code %d)", code);
+    if (code != 0) {
+        cudaStreamSynchronize(m->stream);
+        tc_df_reset(m);
+        return fail(KLM_ECUDA, "klm_seq_tc: device-side wait timed out (code %d)", code);
+    }
     return KLM_OK;
 }
 
@@ -1125,15 +1281,26 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
     if (targets) CK(cudaMemcpyAsync(m->d_targets, src_targets, (size_t)n * 4, cudaMemcpyDefault, m->stream));
     float *dout = (mem == KLM_MEM_HOST) ? m->d_out : out;
     CK(cudaEventRecord(m->ev0, m->stream));
-    const int bmax = batch_max(m, n);
-    std::vector<int64_t> off0;
-    for (int s0 = 0; s0 < n; s0 += bmax) {
-        const int nb = std::min(bmax, n - s0);
-        off0.resize(nb + 1);
-        for (int i = 0; i <= nb; ++i) off0[i] = s0 + i;
-        rc = run_batch(m, nb, slots_in + s0, slots_out + s0, off0.data(), nullptr, ctx ? ctx + (size_t)s0 * m->Nc : nullptr,
-                       m->d_chars, targets ? m->d_targets : nullptr, dout, full);
-        if (rc) return rc;
+    if (n > KLM_MODEK_MAXB && m->tc.ok && m->tc.df_ok && m->knobs.tc_df) {
+        // beams: the dataflow kernel's step mode, up to 256 hypotheses per launch
+        const int bmax = KLM_TC_STREAMS * KLM_DF_MAXG;
+        for (int s0 = 0; s0 < n; s0 += bmax) {
+            const int nb = std::min(bmax, n - s0);
+            rc = run_step_df(m, nb, slots_in + s0, slots_out + s0, ctx ? ctx + (size_t)s0 * m->Nc : nullptr, m->d_chars + s0,
+                             targets ? m->d_targets + s0 : nullptr, dout + (full ? (size_t)s0 * m->V : (size_t)s0), full);
+            if (rc) return rc;
+        }
+    } else {
+        const int bmax = batch_max(m, n);
+        std::vector<int64_t> off0;
+        for (int s0 = 0; s0 < n; s0 += bmax) {
+            const int nb = std::min(bmax, n - s0);
+            off0.resize(nb + 1);
+            for (int i = 0; i <= nb; ++i) off0[i] = s0 + i;
+            rc = run_batch(m, nb, slots_in + s0, slots_out + s0, off0.data(), nullptr, ctx ? ctx + (size_t)s0 * m->Nc : nullptr,
+                           m->d_chars, targets ? m->d_targets : nullptr, dout, full);
+            if (rc) return rc;
+        }
     }
     CK(cudaEventRecord(m->ev1, m->stream));
     m->timed = true;
@@ -1172,6 +1339,7 @@ extern "C" int klm_get_info(klm_model *m, klm_info *out) {
     out->tc_smem_bytes = (int32_t)m->tc.smem;
     out->tc_launches = m->tc_launches;
     out->cl_launches = m->cl_launches; out->cl_cluster = m->cl.C;
+    out->tc_dataflow = (m->tc.ok && m->tc.df_ok && m->knobs.tc_df) ? 1 : 0;
     if (m->timed) {
         CK(cudaSetDevice(m->device));
         CK(cudaEventSynchronize(m->ev1));

@@ -134,6 +134,21 @@ struct KlmClGeom {
 #define KLM_TC_HSCALE       4096.f
 #define KLM_TC_WMAX         16384.f
 
+// dataflow kernel: ring depths and the layout of KlmTcParams::sync (32-bit words)
+#define KLM_DF_R        4                      // versions of a layer's hidden vector kept (hx [D][R][W/8][128][8] halves)
+#define KLM_DF_NZ       4                      // slots of Z per layer ([D][NZ][2 parts][W][64] float4)
+#define KLM_DF_NL       16                     // slots of the logits ([NL][2 parts][Vp/4][64] float4)
+#define KLM_DF_MAXG     4                      // step mode: hypothesis groups of 64 per launch
+#define KLM_DF_HFLAG    0                      // [KLM_MAX_DEPTH][64] version of every REC CTA's slice
+#define KLM_DF_HFLAG0   (KLM_MAX_DEPTH * 64)   // [KLM_MAX_DEPTH][64] step mode: initial hidden vectors published
+#define KLM_DF_CNT      (2 * KLM_MAX_DEPTH * 64)
+#define KLM_DF_ZCNT(l)  (KLM_DF_CNT + 32 * (l))                        // IN l: ticks whose Z is complete (x CTAs)
+#define KLM_DF_ZRD(l)   (KLM_DF_CNT + 32 * (KLM_MAX_DEPTH + (l)))      // REC l: ticks whose Z has been consumed (x CTAs)
+#define KLM_DF_HRD(l)   (KLM_DF_CNT + 32 * (2 * KLM_MAX_DEPTH + (l)))  // IN l+1 / PROJ: ticks whose operand has been read (x CTAs)
+#define KLM_DF_PCNT     (KLM_DF_CNT + 32 * (3 * KLM_MAX_DEPTH))        // PROJ: ticks whose logits are complete (x CTAs)
+#define KLM_DF_LPROG    (KLM_DF_CNT + 32 * (3 * KLM_MAX_DEPTH + 1))    // [32] LSE warps: ticks completed
+#define KLM_DF_WORDS    (KLM_DF_LPROG + 32)
+
 #define KLM_TC_REC  0
 #define KLM_TC_IN   1
 #define KLM_TC_PROJ 2
@@ -157,6 +172,16 @@ struct KlmTcRole {
     int ring_ofs;      // streamed-weights form: byte offset of the ring (behind the hand-over buffer and, REC only, the
                        // publication staging of this CTA's slice)
     float scale;       // accumulator -> pre-activation: 1 / (KLM_TC_HSCALE * weight scale of this CTA's matrix), a power of two
+    // dataflow kernel (klm_seq_df.cu): who this CTA waits for and who waits for it
+    int idx;           // index of this CTA within its stage (REC: index of its hand-over flag)
+    int n_src;         // REC CTAs of the source layer (flags watched by the producer warp)
+    int n_readers;     // REC: CTAs of other stages that read this layer's hidden vector (IN l+1 or PROJ)
+    int n_zprod;       // REC l > 0: IN CTAs of this layer (producers of Z)
+    int n_zcons;       // IN: REC CTAs of this layer (consumers of Z)
+    int alias_slot;    // REC: ring slot that holds the hi/lo hand-over buffer and the publication staging while the ring is idle:
+                       //      the slot of the chunk with this CTA's own slice, whose refill is gated by the CTA's own flag
+    int guard;         // 1: the aliased buffers do not fit that slot (or step mode): the producer waits for the epilogue instead
+    unsigned long long ch_mask[16];   // per operand chunk (natural order): flags of the source-layer CTAs whose slices lie in it
 };
 
 struct KlmTcParams {
@@ -200,6 +225,15 @@ struct KlmTcParams {
     int pub_release;              // 1: a REC CTA signals with red.release.gpu after its bulk store (default 0: the store has been
                                   //    waited for, a relaxed add follows it; KLM_TC_PUB_RELEASE=1 restores the release)
     int stream_b;                 // 1: streamed-weights form (B chunks travel through the ring with the A chunks)
+    // ---- dataflow kernel (klm_seq_df.cu): no grid barrier, every hand-over has its own flag / counter ----
+    unsigned int *sync;           // flags and counters (layout: KLM_DF_* below); never reset between launches:
+    unsigned epoch;               //   flag values of this launch start above `epoch`, counters above n * `tick_base`
+    unsigned tick_base;           //   ticks of all earlier launches
+    __half *hx0;                  // step mode: initial hidden vectors of all hypothesis groups [D][KLM_DF_MAXG][W/8][128][8]
+    int step_groups;              // 0: sequence mode (position = tick); G > 0: step mode -- ONE position for up to 64 * G
+                                  //    hypotheses, tick g advances hypotheses 64 g .. 64 g + 63 (state in / out through the pool)
+    int n_hyp;                    // step mode: number of hypotheses
+    int n_proj, n_lse_warps;      // PROJ CTAs; LSE warps at work
     unsigned spin_limit;          // device-side watchdog: polls of one wait before it gives up (klm_set_option "tc_spin_limit")
     int fault;                    // test hook (klm_set_option "tc_fault"): CTA 0 withholds its hand-over signal of tick 2
 };

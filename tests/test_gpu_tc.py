@@ -211,6 +211,7 @@ def test_tc_skew3_early_signal_matches_skew2_and_oracle(width, depth, nctx, monk
     r = product(wd, maparr, 64)
     nat = r._native
     assert nat.info()['tc_enabled'] == 1
+    nat.set_option('tc_df', 0)                                  # the grid-barrier kernel (the dataflow kernel has no skew)
     rng = np.random.default_rng(width)
     sizes = rng.integers(2, 200, n)
     sizes[0], sizes[1], sizes[2] = 199, 1, 2                   # the longest decides the schedule; empty and single positions
@@ -251,3 +252,108 @@ def test_tc_skew3_early_signal_matches_skew2_and_oracle(width, depth, nctx, monk
             assert np.abs(logp[offsets[k]:offsets[k + 1]] - np.log(out[0])).max() <= 1e-3
         ref = np.concatenate(states, axis=0)
         assert np.abs(s3[k] - ref).max() <= 1e-4 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize('width,depth,nctx,n', [(64, 1, 1, 9), (128, 2, 1, 37), (256, 3, 3, 64), (384, 2, 1, 20), (512, 3, 1, 64)])
+def test_dataflow_kernel_matches_barrier_kernel_and_oracle(width, depth, nctx, n):
+    """klm_seq_df (a flag per hand-over, no grid barrier, partial sums of Z / logits added by the consumer) against
+    klm_seq_tc (one grid barrier per tick) on ragged streams incl. empty and single positions, over two launches with
+    carried state: scores and final states agree to rounding, both are oracle-close; the hand-over words survive the
+    launches in between (running epochs, no reset)."""
+    from oracle import lstm_numpy as ln
+    wd = synth.weights(177 + width, width=width, depth=depth, voc_size=256, contexts=((200, 10),) * nctx, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 64)
+    nat = r._native
+    info = nat.info()
+    assert info['tc_enabled'] == 1 and info['tc_dataflow'] == 1
+    rng = np.random.default_rng(width + n)
+    sizes = rng.integers(2, 300, n)
+    sizes[0], sizes[1], sizes[2] = 299, 1, 2
+    texts = [synth.text(9500 + i, int(s)) for i, s in enumerate(sizes)]
+    ctx = [[int(x) for x in rng.integers(0, 200, nctx)] for _ in range(n)]
+    slots = r._pool.acquire(n)
+    results = {}
+    for df in (1, 0, 1):                                         # dataflow, barrier, dataflow again (epochs keep running)
+        nat.set_option('tc_df', df)
+        nat.state_reset(slots)
+        outs = []
+        for piece in (slice(0, 120), slice(119, None)):          # second launch continues from the carried state
+            idx = [r._indices(t[piece])[0] if len(t[piece]) else np.zeros(1, dtype=np.int32) for t in texts]
+            lens = np.array([max(len(i) - 1, 0) for i in idx])
+            offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+            chars = np.concatenate([i[:-1] for i in idx]).astype(np.int32)
+            targets = np.concatenate([i[1:] for i in idx]).astype(np.int32)
+            logp = np.full(len(chars), np.nan, dtype=np.float32)
+            nat.rate(slots, offsets, chars, targets, None, ctx, logp)
+            outs.append((idx, offsets, logp))
+        if df in results:                                        # the second dataflow run: bit-identical to the first
+            for (_, _, a), (_, _, b) in zip(results[df][0], outs):
+                np.testing.assert_array_equal(a, b)
+            np.testing.assert_array_equal(results[df][1], nat.state_to_host(slots))
+        results[df] = (outs, nat.state_to_host(slots))
+    nat.set_option('tc_df', 1)
+    (o1, s1), (o0, s0) = results[1], results[0]
+    for (_, _, a), (_, _, b) in zip(o1, o0):
+        assert not np.isnan(a).any()
+        assert np.abs(a.astype(np.float64) - b).max() <= 2e-5
+    assert np.abs(s1 - s0).max() <= 2e-5 * max(np.abs(s0).max(), 1.0)
+    m = util.to_model(wd).astype(np.float64)
+    for k in (0, 2, 5, min(n - 1, 11)):
+        states = ln.zero_states(m, 1, np.float64)
+        for idx, offsets, logp in o1:
+            if len(idx[k]) < 2:
+                continue
+            x = idx[k][:-1][None, :].astype(np.int64)
+            z = [np.full_like(x, c) for c in ctx[k]]
+            out, states = ln.run_sequence(m, x, z, states, want='target', targets=idx[k][1:][None, :].astype(np.int64))
+            assert np.abs(logp[offsets[k]:offsets[k + 1]] - np.log(out[0])).max() <= 1e-3
+        ref = np.concatenate(states, axis=0)
+        assert np.abs(s1[k] - ref).max() <= 1e-4 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize('n', [9, 64, 65, 117, 200, 256, 300])
+def test_dataflow_step_mode_matches_fma_step(n):
+    """klm_step with targets and with full rows through the dataflow kernel's step mode (one launch for up to 256
+    hypotheses, states through the pool, ragged group sizes, zero and carried input states) against the FP32 FMA kernels
+    advancing the same hypotheses eight at a time."""
+    wd = synth.weights(61, width=256, depth=3, voc_size=200, contexts=((200, 10),), style='trained')
+    maparr = synth.vocabulary()[:200]
+    r = product(wd, maparr, 32, stateful=False, incremental=True)
+    nat = r._native
+    assert nat.info()['tc_dataflow'] == 1
+    rng = np.random.default_rng(n)
+    V = 200
+    prev = r._pool.acquire(n)
+    nat.state_reset(prev)
+    # a first step from zero states (slot -1 for some), then a second one from the states of the first
+    ref_states = None
+    for step in range(2):
+        chars = rng.integers(0, V, n).astype(np.int32)
+        targets = rng.integers(0, V, n).astype(np.int32)
+        ctx = rng.integers(0, 200, (n, 1)).astype(np.int32)
+        s_in = np.array(prev, dtype=np.int32)
+        if step == 0:
+            s_in[::3] = -1
+        out_a, out_b = r._pool.acquire(n), r._pool.acquire(n)
+        got = np.full(n, np.nan, dtype=np.float32)
+        nat.step(chars, ctx, s_in, out_a, targets, got)
+        full = np.full((n, V), np.nan, dtype=np.float32)
+        nat.step(chars, ctx, s_in, out_b, None, full)
+        launches = nat.info()['tc_launches']
+        want = np.empty(n, dtype=np.float32)
+        out_c = r._pool.acquire(n)
+        for k in range(0, n, 8):                                 # <= 8 hypotheses per call: the FMA kernels
+            sl = slice(k, min(k + 8, n))
+            tmp = np.empty(sl.stop - sl.start, dtype=np.float32)
+            nat.step(chars[sl], ctx[sl], s_in[sl], out_c[sl], targets[sl], tmp)
+            want[sl] = tmp
+        assert nat.info()['tc_launches'] == launches
+        assert not np.isnan(got).any() and not np.isnan(full).any()
+        assert np.abs(got.astype(np.float64) - want).max() <= 1e-4
+        assert np.abs(np.log(full[np.arange(n), targets].astype(np.float64)) - want).max() <= 1e-4
+        np.testing.assert_allclose(full.sum(axis=1), 1.0, rtol=1e-5)
+        sa, sb, sc = nat.state_to_host(out_a), nat.state_to_host(out_b), nat.state_to_host(out_c)
+        np.testing.assert_array_equal(sa, sb)
+        assert np.abs(sa - sc).max() <= 1e-4 * np.abs(sc).max()
+        prev = out_a
