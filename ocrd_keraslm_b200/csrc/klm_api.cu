@@ -530,7 +530,8 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
         }
         static const int df_geoms[7][2] = {{128, 3}, {64, 3}, {64, 4}, {128, 2}, {128, 1}, {64, 2}, {64, 1}};
         size_t df_smem = 0;
-        for (int l = 0; l < D && ok; ++l) if (rec_of[l].size() > 64 || rec_of[l].empty()) ok = false;
+        for (int l = 0; l < D && ok; ++l) if (rec_of[l].size() > 64 || rec_of[l].empty() || in_of[l].size() > 64) ok = false;
+        if (proj.size() > 64 || proj.empty() || pl.n_lse * (KLM_TC_THREADS / 32) > 64) ok = false;
         for (int i = 0; i < (int)pl.roles.size() && ok; ++i) {
             KlmTcRole &r = pl.roles[i];
             if (r.kind == KLM_TC_LSE) continue;
@@ -566,6 +567,9 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
                 }
             } else if (r.kind == KLM_TC_IN) {
                 r.n_zcons = (int)rec_of[r.layer].size();
+                r.idx = (int)(std::find(in_of[r.layer].begin(), in_of[r.layer].end(), i) - in_of[r.layer].begin());
+            } else {
+                r.idx = (int)(std::find(proj.begin(), proj.end(), i) - proj.begin());
             }
             df_smem = std::max(df_smem, (size_t)r.ring_bytes + 256 + (size_t)32 * W * r.npairs);
         }

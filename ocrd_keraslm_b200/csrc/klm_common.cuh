@@ -139,15 +139,16 @@ struct KlmClGeom {
 #define KLM_DF_NZ       4                      // slots of Z per layer ([D][NZ][2 parts][W][64] float4)
 #define KLM_DF_NL       16                     // slots of the logits ([NL][2 parts][Vp/4][64] float4)
 #define KLM_DF_MAXG     4                      // step mode: hypothesis groups of 64 per launch
-#define KLM_DF_HFLAG    0                      // [KLM_MAX_DEPTH][64] version of every REC CTA's slice
-#define KLM_DF_HFLAG0   (KLM_MAX_DEPTH * 64)   // [KLM_MAX_DEPTH][64] step mode: initial hidden vectors published
-#define KLM_DF_CNT      (2 * KLM_MAX_DEPTH * 64)
-#define KLM_DF_ZCNT(l)  (KLM_DF_CNT + 32 * (l))                        // IN l: ticks whose Z is complete (x CTAs)
-#define KLM_DF_ZRD(l)   (KLM_DF_CNT + 32 * (KLM_MAX_DEPTH + (l)))      // REC l: ticks whose Z has been consumed (x CTAs)
-#define KLM_DF_HRD(l)   (KLM_DF_CNT + 32 * (2 * KLM_MAX_DEPTH + (l)))  // IN l+1 / PROJ: ticks whose operand has been read (x CTAs)
-#define KLM_DF_PCNT     (KLM_DF_CNT + 32 * (3 * KLM_MAX_DEPTH))        // PROJ: ticks whose logits are complete (x CTAs)
-#define KLM_DF_LPROG    (KLM_DF_CNT + 32 * (3 * KLM_MAX_DEPTH + 1))    // [32] LSE warps: ticks completed
-#define KLM_DF_WORDS    (KLM_DF_LPROG + 32)
+#define KLM_DF_HFLAG    0                      // [KLM_MAX_DEPTH][64] REC CTA j of layer l: version of its slice that is published
+#define KLM_DF_HFLAG0   (1 * KLM_MAX_DEPTH * 64)   // [..][64] step mode: its initial hidden vectors are published
+#define KLM_DF_ZPROG    (2 * KLM_MAX_DEPTH * 64)   // [..][64] IN CTA j of layer l: ticks whose slice of Z is complete
+#define KLM_DF_ZRD      (3 * KLM_MAX_DEPTH * 64)   // [..][64] REC CTA j of layer l: ticks whose Z it has consumed
+#define KLM_DF_HRD      (4 * KLM_MAX_DEPTH * 64)   // [..][64] reader j (IN l+1 / PROJ CTA) of layer l's hidden vector: ticks read
+#define KLM_DF_PPROG    (5 * KLM_MAX_DEPTH * 64)   // [64] PROJ CTA j: ticks whose logits are complete
+#define KLM_DF_LPROG    (KLM_DF_PPROG + 64)        // [64] LSE warp j: ticks consumed
+#define KLM_DF_WORDS    (KLM_DF_LPROG + 64)
+// (one word per CTA, never a shared counter: CTAs of one stage may be several ticks apart, a sum would not say that the
+//  slowest one is through)
 
 #define KLM_TC_REC  0
 #define KLM_TC_IN   1

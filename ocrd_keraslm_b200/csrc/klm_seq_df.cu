@@ -62,6 +62,26 @@ __device__ __forceinline__ bool df_wait_word(const KlmTcParams &p, const unsigne
     return true;
 }
 
+// all lanes of the calling warp: wait until the words w[0 .. n) (n <= 64) have ALL reached `target`; false = watchdog
+__device__ __forceinline__ bool df_wait_all(const KlmTcParams &p, const unsigned *w, int n, unsigned target, int code) {
+    const int lane = threadIdx.x & 31;
+    unsigned cnt = 0;
+    for (;;) {
+        bool ok = lane >= n || df_reached(df_ld_acquire(w + lane), target);
+        if (n > 32) ok = (lane + 32 >= n || df_reached(df_ld_acquire(w + 32 + lane), target)) && ok;
+        if (__all_sync(0xffffffffu, ok ? 1 : 0)) return true;
+        const int bad = tc_spin_fail(cnt, p, code) ? 1 : 0;
+        if (__any_sync(0xffffffffu, bad)) return false;
+    }
+}
+// one look, no waiting
+__device__ __forceinline__ bool df_check_all(const unsigned *w, int n, unsigned target) {
+    const int lane = threadIdx.x & 31;
+    bool ok = lane >= n || df_reached(df_ld_acquire(w + lane), target);
+    if (n > 32) ok = (lane + 32 >= n || df_reached(df_ld_acquire(w + 32 + lane), target)) && ok;
+    return __all_sync(0xffffffffu, ok ? 1 : 0) != 0;
+}
+
 struct DfCtx {
     uint32_t ring_a, bar_full, bar_empty, bar_tfull, bar_tempty, bar_epid, tmem_base, wsm_a, masks_a;
     int T, N, NP, crot, W, guard, nch;
@@ -318,8 +338,8 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         // back-pressure on the version ring: version tick+2 overwrites version tick+2-R, read by the IN / PROJ CTAs in tick
         // tick-R.  Polled here, needed only at the very end of the tick.
         bool bp_ok = true;
-        if (tid == 64 && tick >= KLM_DF_R && role.n_readers > 0)
-            bp_ok = df_reached(df_ld_acquire(p.sync + KLM_DF_HRD(l)), (unsigned)role.n_readers * (tick_base + (unsigned)(tick - KLM_DF_R + 1)));
+        if (warp == 2 && tick >= KLM_DF_R && role.n_readers > 0)
+            bp_ok = df_check_all(p.sync + KLM_DF_HRD + l * 64, role.n_readers, tick_base + (unsigned)(tick - KLM_DF_R + 1));
 
         // ---- addends: layer 0 = fused char + context embedding gather (tables P, Q: rating.py:103-115,125); else Z ----
         float4 add4[OWN][2];
@@ -356,11 +376,8 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
                     }
             }
         } else {
-            // Z_l[tick] complete?  (one lane per warp polls; in steady state the IN stage is ahead)
-            int ok = 1;
-            if (lane == 0 && alive)
-                ok = df_wait_word(p, p.sync + KLM_DF_ZCNT(l), (unsigned)role.n_zprod * (tick_base + (unsigned)tick + 1u), 8) ? 1 : 0;
-            alive = alive && __all_sync(0xffffffffu, ok);
+            // Z_l[tick] complete?  Every IN CTA of the layer has its own progress word (in steady state the IN stage is ahead)
+            if (alive) alive = df_wait_all(p, p.sync + KLM_DF_ZPROG + l * 64, role.n_zprod, tick_base + (unsigned)tick + 1u, 8);
             const float4 *za = reinterpret_cast<const float4 *>(p.Z) + ((size_t)(l * KLM_DF_NZ + (tick & (KLM_DF_NZ - 1))) * 2) * W * 64 + s;
             const float4 *zb = za + (size_t)W * 64;
 #pragma unroll
@@ -498,9 +515,9 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         stage();
         if (TRACE && tid == 64) tc_trace(p, tick, 6);
         tc_bar_epi();
+        if (warp == 2 && !bp_ok && alive)
+            alive = df_wait_all(p, p.sync + KLM_DF_HRD + l * 64, role.n_readers, tick_base + (unsigned)(tick - KLM_DF_R + 1), 9);
         if (tid == 64) {
-            if (!bp_ok && alive)
-                alive = df_wait_word(p, p.sync + KLM_DF_HRD(l), (unsigned)role.n_readers * (tick_base + (unsigned)(tick - KLM_DF_R + 1)), 9);
             const unsigned version = (unsigned)tick + 2u;
             bulk_out(hx_l + (size_t)(version & (KLM_DF_R - 1)) * hx_slice + (size_t)(role.first_pair / 4) * (128 * 8));
             // everything this CTA hands over went through that one bulk store and it has been performed (wait_group 0): a
@@ -508,7 +525,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
             if (p.fault && blockIdx.x == 0 && tick == 2) { }                       // (test hook: the watchdog must end the launch)
             else if (p.pub_release) df_st_release(my_flag, epoch + version);
             else df_st_relaxed(my_flag, epoch + version);
-            if (l > 0) tc::red_relaxed_add(p.sync + KLM_DF_ZRD(l), 1u);          // Z of this tick has been consumed (all threads: bar.sync above)
+            if (l > 0) df_st_relaxed(p.sync + KLM_DF_ZRD + l * 64 + role.idx, tick_base + (unsigned)tick + 1u);   // Z of this tick consumed (all threads: bar.sync above)
             if (x.guard) tc::mbar_arrive(x.bar_epid);
             if (TRACE) tc_trace(p, tick, 7);
         }
@@ -539,32 +556,31 @@ __device__ __noinline__ void df_epi_inproj(const KlmTcParams &p, const KlmTcRole
     const uint32_t trow = x.tmem_base + ((uint32_t)(32 * q) << 16);
     const float scale = role.scale;
     const unsigned tick_base = p.tick_base;
-    unsigned *done_cnt = p.sync + (is_in ? KLM_DF_ZCNT(l) : KLM_DF_PCNT);
-    unsigned *read_cnt = p.sync + KLM_DF_HRD(role.src_layer);
+    unsigned *done_word = p.sync + (is_in ? KLM_DF_ZPROG + l * 64 : KLM_DF_PPROG) + role.idx;
+    unsigned *read_word = p.sync + KLM_DF_HRD + role.src_layer * 64 + role.idx;
     const int nslots = is_in ? KLM_DF_NZ : KLM_DF_NL;
     bool alive = true;
     for (int tick = 0; tick < T; ++tick) {
         // back-pressure: the slot written now was last read in tick - nslots (IN: by the REC CTAs of the layer, a counter;
         // PROJ: by the LSE warps, one progress word each)
         if (tick >= nslots && alive) {
-            int ok = 1;
             if (is_in) {
-                if (lane == 0)
-                    ok = df_wait_word(p, p.sync + KLM_DF_ZRD(l), (unsigned)role.n_zcons * (tick_base + (unsigned)(tick - nslots + 1)), 11) ? 1 : 0;
-            } else if (lane < p.n_lse_warps) {
+                alive = df_wait_all(p, p.sync + KLM_DF_ZRD + l * 64, role.n_zcons, tick_base + (unsigned)(tick - nslots + 1), 11);
+            } else {
                 // LSE warp w works on ticks w, w + n, w + 2n, ...: its word holds tick_base + (last finished tick + 1)
                 const unsigned need_tick = (unsigned)(tick - nslots);          // must be finished by whoever owns it
                 const int owner = (int)(need_tick % (unsigned)p.n_lse_warps);
-                if (lane == owner) ok = df_wait_word(p, p.sync + KLM_DF_LPROG + lane, tick_base + need_tick + 1u, 12) ? 1 : 0;
+                int ok = 1;
+                if (lane == 0) ok = df_wait_word(p, p.sync + KLM_DF_LPROG + owner, tick_base + need_tick + 1u, 12) ? 1 : 0;
+                alive = __all_sync(0xffffffffu, ok) != 0;
             }
-            alive = __all_sync(0xffffffffu, ok) != 0;
         }
         {
             int ok = alive ? (tc_wait_mbar(x.bar_tfull, tick & 1, p, 6) ? 1 : 0) : 1;
             alive = alive && __all_sync(0xffffffffu, ok);
         }
         if (tid == 64) {
-            tc::red_relaxed_add(read_cnt, 1u);                       // every MMA of the tick is complete: the operand has been read
+            df_st_relaxed(read_word, tick_base + (unsigned)tick + 1u);   // every MMA of the tick is complete: the operand has been read
             if (TRACE) tc_trace(p, tick, 4);
         }
         tc::tc_fence_after();
@@ -595,7 +611,7 @@ __device__ __noinline__ void df_epi_inproj(const KlmTcParams &p, const KlmTcRole
         if (TRACE && tid == 64) tc_trace(p, tick, 5);
         tc_bar_epi();                                                // all stores of the CTA issued ...
         if (tid == 64) {
-            tc::red_release_add(done_cnt, 1u);                       // ... and published (release: cumulative over the bar.sync)
+            df_st_release(done_word, tick_base + (unsigned)tick + 1u);   // ... and published (release: cumulative over the bar.sync)
             if (TRACE) tc_trace(p, tick, 7);
         }
     }
@@ -619,9 +635,7 @@ __device__ void df_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
     // work items: (tick, group) pairs, item k = tick * ngroups + group; warp gw takes the ticks gw, gw + nw, ... and all
     // groups of a tick (so that "tick finished" is one word per warp)
     for (int tick = gw; tick < T; tick += nw) {
-        int ok = 1;
-        if (lane == 0) ok = df_wait_word(p, p.sync + KLM_DF_PCNT, (unsigned)p.n_proj * (tick_base + (unsigned)tick + 1u), 10) ? 1 : 0;
-        if (!__all_sync(0xffffffffu, ok)) return;
+        if (!df_wait_all(p, p.sync + KLM_DF_PPROG, p.n_proj, tick_base + (unsigned)tick + 1u, 10)) return;
         for (int g = 0; g < ngroups; ++g) {
             const int s = 32 * g + lane;
             const int hyp = step ? 64 * tick + s : s;
