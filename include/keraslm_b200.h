@@ -163,6 +163,29 @@ int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slot, const in
                   int32_t *out_alt, double *out_cum_cost, int32_t *out_slot, int32_t *n_out, int64_t *n_steps,
                   int64_t *n_hyp_steps);
 
+/*
+ * A whole LINEAR lattice in one call -- the chain of edges wrapper/rate.py:343-424 builds from a PAGE: klm_beam_edge's
+ * search edge after edge, the first `beam_width` finished candidates of an edge being the incoming hypotheses of the next
+ * (rating.py:763-852 for a graph without branches and without history clustering).  Replaces one Python round trip per
+ * edge; the caller builds its back-pointer tree from the table it gets.
+ *
+ *   edge_alt_first [n_edges+1]                   alternatives edge_alt_first[e] .. edge_alt_first[e+1]-1 belong to edge e
+ *   alt_offsets [n_alts+1], alt_chars, alt_conf  character indices and confidences of all alternatives of all edges
+ *   out_first [n_edges+1]                        the kept candidates of edge e are rows out_first[e] .. out_first[e+1]-1 of
+ *   out_hyp / out_alt / out_cum_cost [max_out]   (row of the previous edge -- for edge 0: incoming hypothesis --,
+ *                                                alternative index within the edge, cumulative cost), in beam order
+ *   final_slot [beam_width]                      state of each candidate of the last edge: one of scratch_slots (now the
+ *                                                caller's), or -2 - i = the untouched state of incoming hypothesis i
+ *   scratch_slots [n_scratch]                    free state slots: >= beam_width * (most alternatives of an edge + 1) + batch_size
+ * All pointers are host pointers; the call returns when the lattice is finished.
+ */
+int klm_beam_lattice(klm_model *m, int32_t n_hyp, const int32_t *hyp_slot, const int32_t *hyp_last_char,
+                     const double *hyp_cum_cost, int32_t n_edges, const int32_t *edge_alt_first,
+                     const int32_t *alt_offsets, const int32_t *alt_chars, const double *alt_conf, const int32_t *ctx,
+                     double lm_weight, int32_t batch_size, int32_t beam_width, int32_t n_scratch,
+                     const int32_t *scratch_slots, int32_t max_out, int32_t *out_first, int32_t *out_hyp,
+                     int32_t *out_alt, double *out_cum_cost, int32_t *final_slot, int64_t *n_steps, int64_t *n_hyp_steps);
+
 /* Introspection for bench.py / tests. */
 typedef struct klm_info {
     int32_t sm_count;

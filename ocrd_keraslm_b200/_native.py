@@ -117,6 +117,8 @@ SYMBOLS = [
     ('klm_selftest_umma', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
     ('klm_selftest_umma2', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
     ('klm_tc_trace', ctypes.c_int, [_P, _I, _P, _P]),
+    ('klm_beam_lattice', ctypes.c_int, [_P, _I, _P, _P, _P, _I, _P, _P, _P, _P, _P, ctypes.c_double, _I, _I, _I, _P, _I,
+                                        _P, _P, _P, _P, _P, _P, _P]),
     ('klm_beam_edge', ctypes.c_int, [_P, _I, _P, _P, _P, _I, _P, _P, _P, _P, ctypes.c_double, _I, _I, _P, _I,
                                      _P, _P, _P, _P, _P, _P, _P]),
 ]
@@ -281,6 +283,28 @@ class Model(object):
                                            ctypes.byref(st), ctypes.byref(hst)))
         k = n_out.value
         return oh[:k], oa[:k], oc[:k], os_[:k], st.value, hst.value
+
+    def beam_lattice(self, hyp_slot, hyp_last_char, hyp_cum_cost, edge_alt_first, alt_offsets, alt_chars, alt_conf, ctx,
+                     lm_weight, batch_size, beam_width, scratch_slots):
+        """See klm_beam_lattice.  Returns (out_first, out_hyp, out_alt, out_cum_cost, final_slot, steps, hypothesis steps)."""
+        hs, hl = _i32(hyp_slot), _i32(hyp_last_char)
+        hc = np.ascontiguousarray(hyp_cum_cost, dtype=np.float64)
+        ef, ao, ac = _i32(edge_alt_first), _i32(alt_offsets), _i32(alt_chars)
+        af = np.ascontiguousarray(alt_conf, dtype=np.float64)
+        cx = None if ctx is None or len(ctx) == 0 else _i32(ctx)
+        sc = _i32(scratch_slots)
+        n_edges = len(ef) - 1
+        max_out = n_edges * int(beam_width)
+        of = np.zeros(n_edges + 1, np.int32)
+        oh, oa = np.empty(max(max_out, 1), np.int32), np.empty(max(max_out, 1), np.int32)
+        oc = np.empty(max(max_out, 1), np.float64)
+        fs = np.empty(int(beam_width), np.int32)
+        st, hst = ctypes.c_int64(0), ctypes.c_int64(0)
+        self.check(self._lib.klm_beam_lattice(self._h, len(hs), _ptr(hs), _ptr(hl), _ptr(hc), n_edges, _ptr(ef), _ptr(ao),
+                                              _ptr(ac), _ptr(af), _ptr(cx), float(lm_weight), int(batch_size),
+                                              int(beam_width), len(sc), _ptr(sc), max_out, _ptr(of), _ptr(oh), _ptr(oa),
+                                              _ptr(oc), _ptr(fs), ctypes.byref(st), ctypes.byref(hst)))
+        return of, oh, oa, oc, fs, st.value, hst.value
 
     def tc_trace_arm(self, first_tick):
         self.check(self._lib.klm_tc_trace(self._h, first_tick, None, None))

@@ -90,9 +90,14 @@ struct KlmKnobs {
     int tc_poll = 0;              // KLM_TC_POLL
     int tc_skew = 0;              // KLM_TC_SKEW: 0 = by launch length, 2 / 3 = forced
     int tc_zpub = -1;             // KLM_TC_ZPUB: 2 = IN / PROJ stage + bulk-store their slice also with the early signal
-    int tc_pub_release = 0;       // KLM_TC_PUB_RELEASE
-    int tc_df = 1;                // KLM_TC_DF: 1 = dataflow kernel (flags per hand-over) where the plan allows it, 0 = grid-barrier kernel
+    int tc_pub_release = 1;       // KLM_TC_PUB_RELEASE: 1 = a published slice is signalled with a gpu-scope RELEASE.  0 (a relaxed
+                                  //   store / add after cp.async.bulk.wait_group 0) is NOT safe: the flag can become visible before the
+                                  //   data of the completed bulk store (measured with the dataflow kernel: scripts/exp/df_race.py)
+    int tc_df = 1;                // KLM_TC_DF: dataflow kernel (a flag per hand-over, klm_seq_df.cu) where the plan allows it:
+                                  //   0 = never, 1 = for klm_step (beam steps: one launch for up to 256 hypotheses, no pipeline fill),
+                                  //   2 = for sequences as well (measured slower than the grid-barrier kernel there: DESIGN 3.2d)
     int tc_consumer_fence = 0;    // KLM_TC_CONSUMER_FENCE: fence.proxy.async between the flag polls and the bulk reads
+    int tc_exp = 0;               // KLM_TC_EXP: experiment switches of the dataflow kernel (KlmTcParams::exp)
     int tc_fault = 0;             // KLM_TC_FAULT (test hook: one CTA withholds a hand-over signal; the watchdog must fire)
     unsigned tc_spin_limit = 1u << 24;   // KLM_TC_SPIN_LIMIT
     int ll_debug = 0;             // KLM_LL_DEBUG
@@ -106,9 +111,10 @@ static void read_knobs(KlmKnobs &k) {
     k.tc_poll = env_int("KLM_TC_POLL", 0);
     k.tc_skew = env_int("KLM_TC_SKEW", 0);
     k.tc_zpub = env_int("KLM_TC_ZPUB", -1);
-    k.tc_pub_release = env_int("KLM_TC_PUB_RELEASE", 0);
+    k.tc_pub_release = env_int("KLM_TC_PUB_RELEASE", 1);
     k.tc_df = env_int("KLM_TC_DF", 1);
     k.tc_consumer_fence = env_int("KLM_TC_CONSUMER_FENCE", 0);
+    k.tc_exp = env_int("KLM_TC_EXP", 0);
     k.tc_fault = env_int("KLM_TC_FAULT", 0);
     if (getenv("KLM_TC_SPIN_LIMIT")) k.tc_spin_limit = (unsigned)strtoul(getenv("KLM_TC_SPIN_LIMIT"), nullptr, 10);
     k.ll_debug = env_int("KLM_LL_DEBUG", 0);
@@ -815,6 +821,7 @@ extern "C" int klm_set_option(klm_model *m, const char *name, int64_t value) {
     else if (n == "tc_zpub") k.tc_zpub = (int)value;
     else if (n == "tc_pub_release") k.tc_pub_release = (int)value;
     else if (n == "tc_fault") k.tc_fault = (int)value;
+    else if (n == "tc_exp") k.tc_exp = (int)value;
     else if (n == "tc_df") k.tc_df = (int)value;
     else if (n == "tc_consumer_fence") k.tc_consumer_fence = (int)value;
     else if (n == "tc_spin_limit") k.tc_spin_limit = (unsigned)value;
@@ -959,6 +966,7 @@ static void tc_df_params(klm_model *m, KlmTcParams &q) {
     q.hx = tp.hx_df; q.hx0 = tp.hx0; q.Z = tp.Z_df; q.logits = tp.logits_df;
     q.n_proj = tp.n_proj; q.n_lse_warps = tp.n_lse * (KLM_TC_THREADS / 32);
     q.consumer_fence = m->knobs.tc_consumer_fence;
+    q.exp = m->knobs.tc_exp;
     q.step_groups = 0; q.n_hyp = 0;
 }
 
@@ -1033,7 +1041,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         q.spin_limit = m->knobs.tc_spin_limit;
         q.fault = m->knobs.tc_fault;
         q.kc = tp.kc; q.ring_bytes = tp.ring_bytes;
-        if (tp.df_ok && m->knobs.tc_df) {
+        if (tp.df_ok && m->knobs.tc_df >= 2) {
             // dataflow kernel: flags / counters continue above the values the earlier launches left (no memset)
             tc_df_params(m, q);
             q.T_max = (int)tmax;
@@ -1429,27 +1437,18 @@ struct BeamLists {
 };
 }  // namespace
 
-extern "C" int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slot, const int32_t *hyp_last_char,
-                             const double *hyp_cum_cost, int32_t n_alt, const int32_t *alt_offsets,
-                             const int32_t *alt_chars, const double *alt_conf, const int32_t *ctx, double lm_weight,
-                             int32_t batch_size, int32_t n_scratch, const int32_t *scratch_slots, int32_t max_out,
-                             int32_t *out_hyp, int32_t *out_alt, double *out_cum_cost, int32_t *out_slot, int32_t *n_out,
-                             int64_t *n_steps, int64_t *n_hyp_steps) {
-    if (!m || !hyp_slot || !hyp_last_char || !hyp_cum_cost || !alt_offsets || !alt_chars || !alt_conf || !scratch_slots ||
-        !out_hyp || !out_alt || !out_cum_cost || !out_slot || !n_out)
-        return fail(KLM_EINVAL, "klm_beam_edge: NULL argument");
-    if (n_hyp < 0 || n_alt < 1 || batch_size < 1 || max_out < 0) return fail(KLM_EINVAL, "klm_beam_edge: bad sizes");
-    *n_out = 0;
-    const auto te0 = std::chrono::steady_clock::now();
-    struct EdgeTimer { klm_model *m; std::chrono::steady_clock::time_point t0;
-        ~EdgeTimer() { if (m->timing) { m->t_edges++; m->t_edge_total += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); } } } edge_timer{m, te0};
-    if (n_steps) *n_steps = 0;
-    if (n_hyp_steps) *n_hyp_steps = 0;
-    BeamLists L;
-    std::vector<int> waiting, done, batch, free_slots(scratch_slots, scratch_slots + n_scratch);
+// One edge: candidates = hypotheses x alternatives; `done` receives the finished candidates in beam order (indices into
+// L.c); state slots come from / go back to `free_slots`.
+static int beam_edge_core(klm_model *m, BeamLists &L, int n_hyp, const int32_t *hyp_slot, const int32_t *hyp_last_char,
+                          const double *hyp_cum_cost, int n_alt, const int32_t *alt_offsets, const int32_t *alt_chars,
+                          const double *alt_conf, const int32_t *ctx, double lm_weight, int batch_size,
+                          std::vector<int> &free_slots, std::vector<int> &done, int64_t *n_steps, int64_t *n_hyp_steps) {
+    std::vector<int> waiting, batch;
     const double log2d = std::log(2.0);
     int max_len = 0;
     for (int a = 0; a < n_alt; ++a) max_len = std::max(max_len, alt_offsets[a + 1] - alt_offsets[a]);
+    L.c.clear();
+    done.clear();
     for (int h = 0; h < n_hyp; ++h)
         for (int a = 0; a < n_alt; ++a) {                        // beam-major, not re-sorted (:789-795)
             BeamCand c;
@@ -1513,12 +1512,114 @@ extern "C" int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slo
             waiting.resize(keep);
         }
     }
+    // (candidates still waiting when the rounds are used up keep their slots until the caller drops the edge)
+    for (int i : waiting) release(i);
+    return KLM_OK;
+}
+
+extern "C" int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slot, const int32_t *hyp_last_char,
+                             const double *hyp_cum_cost, int32_t n_alt, const int32_t *alt_offsets,
+                             const int32_t *alt_chars, const double *alt_conf, const int32_t *ctx, double lm_weight,
+                             int32_t batch_size, int32_t n_scratch, const int32_t *scratch_slots, int32_t max_out,
+                             int32_t *out_hyp, int32_t *out_alt, double *out_cum_cost, int32_t *out_slot, int32_t *n_out,
+                             int64_t *n_steps, int64_t *n_hyp_steps) {
+    if (!m || !hyp_slot || !hyp_last_char || !hyp_cum_cost || !alt_offsets || !alt_chars || !alt_conf || !scratch_slots ||
+        !out_hyp || !out_alt || !out_cum_cost || !out_slot || !n_out)
+        return fail(KLM_EINVAL, "klm_beam_edge: NULL argument");
+    if (n_hyp < 0 || n_alt < 1 || batch_size < 1 || max_out < 0) return fail(KLM_EINVAL, "klm_beam_edge: bad sizes");
+    *n_out = 0;
+    const auto te0 = std::chrono::steady_clock::now();
+    struct EdgeTimer { klm_model *m; std::chrono::steady_clock::time_point t0;
+        ~EdgeTimer() { if (m->timing) { m->t_edges++; m->t_edge_total += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); } } } edge_timer{m, te0};
+    if (n_steps) *n_steps = 0;
+    if (n_hyp_steps) *n_hyp_steps = 0;
+    BeamLists L;
+    std::vector<int> done, free_slots(scratch_slots, scratch_slots + n_scratch);
+    int rc = beam_edge_core(m, L, n_hyp, hyp_slot, hyp_last_char, hyp_cum_cost, n_alt, alt_offsets, alt_chars, alt_conf, ctx,
+                            lm_weight, batch_size, free_slots, done, n_steps, n_hyp_steps);
+    if (rc) return rc;
     const int no = std::min<int>(max_out, (int)done.size());
     for (int k = 0; k < no; ++k) {
         const BeamCand &c = L.c[done[k]];
         out_hyp[k] = c.hyp; out_alt[k] = c.alt; out_cum_cost[k] = c.cum; out_slot[k] = c.own ? c.slot : -2;   // -2: the parent's state
     }
     *n_out = no;
+    return KLM_OK;
+}
+
+// A whole LINEAR lattice (a chain of edges: what wrapper/rate.py builds from a PAGE, :343-424) in one call: the
+// per-edge search above for edge after edge, the first `beam_width` finished candidates of an edge being the incoming
+// hypotheses of the next one (rating.py:763-852 for a graph without branches).  The host language gets a table of
+// back-pointers and builds tree nodes only for what it looks at afterwards.
+//
+//   n_edges, edge_alt_first [n_edges+1]          alternatives edge_alt_first[e] .. edge_alt_first[e+1]-1 belong to edge e
+//   alt_offsets [n_alts+1], alt_chars, alt_conf  characters (indices) and confidences of all alternatives
+//   out_first [n_edges+1]                        kept candidates of edge e are rows out_first[e] .. out_first[e+1]-1 of
+//   out_hyp / out_alt / out_cum_cost [max_out]   (index into the kept rows of the previous edge -- or the incoming beam for
+//                                                edge 0 --, alternative index relative to the edge, cumulative cost)
+//   final_slot [beam_width]                      state slots of the last edge's candidates (scratch slots now owned by the
+//                                                caller, or -2 - i: the state of incoming hypothesis i, untouched)
+// scratch_slots: at least (beam_width + batch_size) * (largest number of alternatives of an edge + 2) free slots.
+extern "C" int klm_beam_lattice(klm_model *m, int32_t n_hyp, const int32_t *hyp_slot, const int32_t *hyp_last_char,
+                                const double *hyp_cum_cost, int32_t n_edges, const int32_t *edge_alt_first,
+                                const int32_t *alt_offsets, const int32_t *alt_chars, const double *alt_conf,
+                                const int32_t *ctx, double lm_weight, int32_t batch_size, int32_t beam_width,
+                                int32_t n_scratch, const int32_t *scratch_slots, int32_t max_out, int32_t *out_first,
+                                int32_t *out_hyp, int32_t *out_alt, double *out_cum_cost, int32_t *final_slot,
+                                int64_t *n_steps, int64_t *n_hyp_steps) {
+    if (!m || !hyp_slot || !hyp_last_char || !hyp_cum_cost || !edge_alt_first || !alt_offsets || !alt_chars || !alt_conf ||
+        !scratch_slots || !out_first || !out_hyp || !out_alt || !out_cum_cost || !final_slot)
+        return fail(KLM_EINVAL, "klm_beam_lattice: NULL argument");
+    if (n_hyp < 0 || n_edges < 0 || batch_size < 1 || beam_width < 1 || max_out < 0) return fail(KLM_EINVAL, "klm_beam_lattice: bad sizes");
+    if (n_steps) *n_steps = 0;
+    if (n_hyp_steps) *n_hyp_steps = 0;
+    BeamLists L;
+    std::vector<int> done, free_slots(scratch_slots, scratch_slots + n_scratch);
+    // the current beam: state slot (negative = not ours: -1 zero state, <= -2 incoming hypothesis -2-i), whether the slot is one
+    // of ours, how many rows of the beam share it, last character, cost
+    std::vector<int32_t> b_slot(hyp_slot, hyp_slot + n_hyp), b_last(hyp_last_char, hyp_last_char + n_hyp), b_origin(n_hyp);
+    std::vector<double> b_cum(hyp_cum_cost, hyp_cum_cost + n_hyp);
+    std::vector<char> b_own(n_hyp, 0);
+    for (int i = 0; i < n_hyp; ++i) b_origin[i] = -2 - i;
+    out_first[0] = 0;
+    int nout = 0;
+    for (int e = 0; e < n_edges; ++e) {
+        const int a0 = edge_alt_first[e], n_alt = edge_alt_first[e + 1] - a0;
+        if (n_alt < 1) return fail(KLM_EINVAL, "klm_beam_lattice: edge %d has no alternatives", e);
+        // offsets of this edge's alternatives, relative to alt_chars
+        int rc = beam_edge_core(m, L, (int)b_slot.size(), b_slot.data(), b_last.data(), b_cum.data(), n_alt, alt_offsets + a0,
+                                alt_chars, alt_conf + a0, ctx, lm_weight, batch_size, free_slots, done, n_steps, n_hyp_steps);
+        if (rc) return rc;
+        const int keep = std::min<int>(beam_width, (int)done.size());
+        if (nout + keep > max_out) return fail(KLM_EINVAL, "klm_beam_lattice: output arrays too small");
+        std::vector<int32_t> n_slot(keep), n_last(keep), n_origin(keep);
+        std::vector<double> n_cum(keep);
+        std::vector<char> n_own(keep), parent_kept(b_slot.size(), 0);
+        for (int k = 0; k < keep; ++k) {
+            const BeamCand &c = L.c[done[k]];
+            out_hyp[nout + k] = c.hyp; out_alt[nout + k] = c.alt; out_cum_cost[nout + k] = c.cum;
+            n_cum[k] = c.cum;
+            n_last[k] = c.alt_len ? alt_chars[alt_offsets[a0 + c.alt] + c.alt_len - 1] : b_last[c.hyp];
+            if (c.own) { n_slot[k] = c.slot; n_own[k] = 1; n_origin[k] = c.slot; }
+            else {       // an empty alternative: the candidate lives on with its parent's state
+                n_slot[k] = b_slot[c.hyp]; n_own[k] = b_own[c.hyp]; n_origin[k] = b_origin[c.hyp]; parent_kept[c.hyp] = 1;
+            }
+        }
+        for (size_t k = keep; k < done.size(); ++k)               // finished, but outside the beam
+            if (L.c[done[k]].own) free_slots.push_back(L.c[done[k]].slot);
+        for (size_t i = 0; i < b_slot.size(); ++i)                // the previous beam's states are no longer needed
+            if (b_own[i] && !parent_kept[i]) {
+                bool dup = false;                                  // (rows of a beam may share a slot through empty alternatives)
+                for (size_t j = 0; j < i; ++j) if (b_own[j] && b_slot[j] == b_slot[i] && !parent_kept[j]) dup = true;
+                bool still = false;
+                for (int k = 0; k < keep; ++k) if (n_own[k] && n_slot[k] == b_slot[i]) still = true;
+                if (!dup && !still) free_slots.push_back(b_slot[i]);
+            }
+        b_slot.swap(n_slot); b_last.swap(n_last); b_cum.swap(n_cum); b_own.swap(n_own); b_origin.swap(n_origin);
+        nout += keep;
+        out_first[e + 1] = nout;
+    }
+    for (int k = 0; k < beam_width; ++k) final_slot[k] = k < (int)b_slot.size() ? (b_own[k] ? b_slot[k] : b_origin[k]) : -1;
     return KLM_OK;
 }
 

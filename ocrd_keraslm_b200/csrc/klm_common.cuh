@@ -235,6 +235,8 @@ struct KlmTcParams {
                                   //    hypotheses, tick g advances hypotheses 64 g .. 64 g + 63 (state in / out through the pool)
     int n_hyp;                    // step mode: number of hypotheses
     int n_proj, n_lse_warps;      // PROJ CTAs; LSE warps at work
+    int exp;                      // experiment switches (klm_set_option "tc_exp"): 1 = back-off between flag polls, 2 = a REC CTA fetches
+                                  //   nothing of the next tick before its own publication is through, 4 = IN / PROJ publish at once
     unsigned spin_limit;          // device-side watchdog: polls of one wait before it gives up (klm_set_option "tc_spin_limit")
     int fault;                    // test hook (klm_set_option "tc_fault"): CTA 0 withholds its hand-over signal of tick 2
 };

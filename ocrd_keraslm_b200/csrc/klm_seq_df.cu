@@ -53,6 +53,17 @@ __device__ __forceinline__ void df_st_release(unsigned *p, unsigned v) {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ bool df_reached(unsigned v, unsigned target) { return (int)(v - target) >= 0; }
+// Signals a slice that went out as a bulk async store the calling thread has waited for (cp.async.bulk.wait_group 0).
+// mode 1 (default): gpu-scope release.  A relaxed store (mode 0) is NOT enough: the flag can be seen before the data
+// (scripts/exp/df_race.py); modes 2 / 3 are experiments (proxy fence + relaxed store; delay + relaxed store).
+__device__ __forceinline__ void df_signal(unsigned *flag, unsigned value, int mode) {
+    if (mode == 1) df_st_release(flag, value);
+    else {
+        if (mode == 2) tc::fence_proxy_async();
+        else if (mode == 3) __nanosleep(300);
+        df_st_relaxed(flag, value);
+    }
+}
 
 // one thread waits until *w has reached `target` (wrap-safe); false = watchdog
 __device__ __forceinline__ bool df_wait_word(const KlmTcParams &p, const unsigned *w, unsigned target, int code) {
@@ -149,6 +160,7 @@ __device__ __noinline__ void df_produce(const KlmTcParams &p, const KlmTcRole &r
                             }
                             have |= m;
                             if ((have & need) == need) break;
+                            if (p.exp & 1) __nanosleep(100);
                             int bad = tc_spin_fail(n, p, 1) ? 1 : 0;
                             if (__any_sync(0xffffffffu, bad)) { alive = false; break; }
                         }
@@ -304,7 +316,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         tc_bar_epi();
         if (tid == 64) {
             bulk_out(hx_l + (size_t)1 * hx_slice + (size_t)(role.first_pair / 4) * (128 * 8));     // version 1
-            if (p.pub_release) df_st_release(my_flag, epoch + 1u); else df_st_relaxed(my_flag, epoch + 1u);
+            df_signal(my_flag, epoch + 1u, p.pub_release);
         }
     } else {
         __half *hx0_l = p.hx0 + (size_t)l * KLM_DF_MAXG * hx_slice;
@@ -318,7 +330,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         }
         if (tid == 64) {
             unsigned *f0 = p.sync + KLM_DF_HFLAG0 + l * 64 + role.idx;
-            if (p.pub_release) df_st_release(f0, epoch + 1u); else df_st_relaxed(f0, epoch + 1u);
+            df_signal(f0, epoch + 1u, p.pub_release);
         }
     }
     tc_bar_epi();                                                    // (staging free again before the ring is used)
@@ -523,8 +535,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
             // everything this CTA hands over went through that one bulk store and it has been performed (wait_group 0): a
             // release has nothing left to order (klm_set_option "tc_pub_release" restores it)
             if (p.fault && blockIdx.x == 0 && tick == 2) { }                       // (test hook: the watchdog must end the launch)
-            else if (p.pub_release) df_st_release(my_flag, epoch + version);
-            else df_st_relaxed(my_flag, epoch + version);
+            else df_signal(my_flag, epoch + version, p.pub_release);
             if (l > 0) df_st_relaxed(p.sync + KLM_DF_ZRD + l * 64 + role.idx, tick_base + (unsigned)tick + 1u);   // Z of this tick consumed (all threads: bar.sync above)
             if (x.guard) tc::mbar_arrive(x.bar_epid);
             if (TRACE) tc_trace(p, tick, 7);
@@ -559,6 +570,8 @@ __device__ __noinline__ void df_epi_inproj(const KlmTcParams &p, const KlmTcRole
     unsigned *done_word = p.sync + (is_in ? KLM_DF_ZPROG + l * 64 : KLM_DF_PPROG) + role.idx;
     unsigned *read_word = p.sync + KLM_DF_HRD + role.src_layer * 64 + role.idx;
     const int nslots = is_in ? KLM_DF_NZ : KLM_DF_NL;
+    const bool deferred = x.guard != 0;
+    if (tid == 64 && deferred) tc::mbar_arrive(x.bar_epid);          // (arrival 0: the producer may fetch tick 0)
     bool alive = true;
     for (int tick = 0; tick < T; ++tick) {
         // back-pressure: the slot written now was last read in tick - nslots (IN: by the REC CTAs of the layer, a counter;
@@ -582,6 +595,14 @@ __device__ __noinline__ void df_epi_inproj(const KlmTcParams &p, const KlmTcRole
         if (tid == 64) {
             df_st_relaxed(read_word, tick_base + (unsigned)tick + 1u);   // every MMA of the tick is complete: the operand has been read
             if (TRACE) tc_trace(p, tick, 4);
+            if (deferred) {
+                // the quiet moment of this CTA: every bulk copy of the tick has landed, the producer holds the next ones back.
+                // A gpu-scope release issued while copies are streaming in takes ~4 600 clk instead of ~900 (measured), so
+                // what the previous tick stored is published HERE, one tick late, and only then may the producer go on
+                if (tick > 0) df_st_release(done_word, tick_base + (unsigned)tick);
+                tc::mbar_arrive(x.bar_epid);
+                if (TRACE && tick > 0) tc_trace(p, tick - 1, 7);
+            }
         }
         tc::tc_fence_after();
         float4 *dst;
@@ -610,11 +631,12 @@ __device__ __noinline__ void df_epi_inproj(const KlmTcParams &p, const KlmTcRole
         tc::mbar_arrive(x.bar_tempty);
         if (TRACE && tid == 64) tc_trace(p, tick, 5);
         tc_bar_epi();                                                // all stores of the CTA issued ...
-        if (tid == 64) {
+        if (tid == 64 && !deferred) {
             df_st_release(done_word, tick_base + (unsigned)tick + 1u);   // ... and published (release: cumulative over the bar.sync)
             if (TRACE) tc_trace(p, tick, 7);
         }
     }
+    if (tid == 64 && deferred) df_st_release(done_word, tick_base + (unsigned)T);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -726,19 +748,22 @@ __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *sme
         tc::mbar_init(bar_tfull, 1);
         tc::mbar_init(bar_tempty, 256);
         tc::mbar_init(bar_epid, 1);
+        tc::mbar_init(tc::smem_u32(bars + 13), 1);       // B image landed
         tc::fence_mbar_init();
     }
     if (tid >= 64 && tid < 80) masks[tid - 64] = role.ch_mask[tid - 64];
-    {   // B image: global -> shared, once per launch
-        const uint4 *src = reinterpret_cast<const uint4 *>(p.wimg + role.wofs);
-        uint4 *dst = reinterpret_cast<uint4 *>(wsm);
-        const int n16 = (W / 8) * 2 * N;
-        for (int i = tid; i < n16; i += KLM_TC_THREADS) dst[i] = __ldg(src + i);
-        tc::fence_proxy_async();                     // generic writes -> visible to the MMA's operand reads
-    }
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
+    // B image: global -> shared, once per launch, as bulk async copies on a barrier of their own (the MMA warp waits for it
+    // before its first MMA; everything else of the prologue overlaps the ~130-180 KB transfer)
+    const uint32_t bar_img = tc::smem_u32(bars + 13);
+    if (tid == 32) {
+        const uint32_t img_bytes = (uint32_t)W * 2u * (uint32_t)N * 2u;
+        tc::mbar_arrive_expect_tx(bar_img, img_bytes);
+        for (uint32_t off = 0; off < img_bytes; off += 32768u)
+            tc::bulk_g2s(tc::smem_u32(wsm) + off, p.wimg + role.wofs + off, min(32768u, img_bytes - off), bar_img);
+    }
 
     DfCtx x;
     x.ring_a = tc::smem_u32(smem); x.bar_full = bar_full; x.bar_empty = bar_empty; x.bar_tfull = bar_tfull;
@@ -746,14 +771,18 @@ __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *sme
     x.masks_a = tc::smem_u32(masks);
     x.T = p.step_groups > 0 ? p.step_groups : p.T_max;
     x.N = N; x.NP = NP; x.W = W; x.nch = W / kc;
-    x.guard = (role.kind == KLM_TC_REC && (role.guard || p.step_groups > 0)) ? 1 : 0;
+    // REC: the producer waits for the epilogue where the aliased buffers are not covered by the own-flag rule;
+    // IN / PROJ: the producer waits until the epilogue has published the previous tick (at the quiet moment after the MMAs)
+    // (step mode: IN / PROJ publish at once -- a beam step is about latency, and there is little to stream in)
+    x.guard = role.kind == KLM_TC_REC ? ((role.guard || p.step_groups > 0 || (p.exp & 2)) ? 1 : 0)
+                                      : (((p.exp & 4) || p.step_groups > 0) ? 0 : 1);
     // REC: the chunk with the CTA's own slice goes into ring slot `alias_slot`; the others in rotated order behind / before it
     x.crot = role.kind == KLM_TC_REC ? role.sigma : (int)(blockIdx.x % (unsigned)x.nch);
 
     if (warp == 0) {
         if (!df_run_loops<TRACE>(true, p, role, x) && tid == 0) atomicExch(p.err, 90);
     } else if (warp == 1) {
-        df_run_loops<TRACE>(false, p, role, x);
+        if (__all_sync(0xffffffffu, tc_wait_mbar(bar_img, 0, p, 13) ? 1 : 0)) df_run_loops<TRACE>(false, p, role, x);
     } else if (role.kind == KLM_TC_REC) {
         unsigned char *alias = smem + (size_t)role.alias_slot * kc * 256;
         const int own = ((NP + 1) / 2 + 1) / 2;

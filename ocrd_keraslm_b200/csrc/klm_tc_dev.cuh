@@ -43,7 +43,12 @@ __device__ __forceinline__ void tc_trace(const KlmTcParams &p, int tick, int ev)
     if (p.trace) {
         const int k = tick - p.trace_t0;
         if (k >= 0 && k < KLM_TC_TRACE_TICKS)
-            p.trace[((size_t)blockIdx.x * KLM_TC_TRACE_TICKS + k) * 8 + ev] = (unsigned long long)clock64();
+        {
+            unsigned long long now;
+            if (p.trace_mode == 5) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));     // ns, comparable across SMs
+            else now = (unsigned long long)clock64();
+            p.trace[((size_t)blockIdx.x * KLM_TC_TRACE_TICKS + k) * 8 + ev] = now;
+        }
     }
 }
 __device__ __forceinline__ void tc_bar_epi() { asm volatile("bar.sync 1, 256;" ::: "memory"); }

@@ -217,6 +217,7 @@ class Rater(object):
         self._pin = None
         self._worker = None
         self.native_beam = True            # rate_best: run whole lattice edges through klm_beam_edge where possible
+        self.native_lattice = True         # ... and whole linear lattices (a PAGE) through klm_beam_lattice
         self.device_steps = 0              # klm_step calls / hypotheses advanced so far (bench.py: beam steps/sec)
         self.hypothesis_steps = 0
 
@@ -820,6 +821,12 @@ class Rater(object):
                     reached.append(head)
         out_node = None
         out_attrs = None
+        if self.native_beam and self.native_lattice and not beam_clustering_dist and self._is_chain(graph, order, start_node):
+            # a linear lattice (what a PAGE gives): all edges in ONE native call, tree nodes only for what is looked at later
+            out_node = order[-1][1]
+            out_attrs = graph.nodes[out_node]
+            out_attrs['traceback'] = self._beam_lattice_native(graph, order, start_traceback[0], context, lm_weight, beam_width)
+            order = []
         for in_node, out_node in order:
             edge = graph.edges[in_node, out_node]
             element, alternatives = edge['element'], edge['alternatives']
@@ -928,6 +935,95 @@ class Rater(object):
             state = DeviceState(self._pool, int(sl)) if sl >= 0 else hyp.state
             node = Node(parent=hyp, state=state, value=alt.Unicode, cost=0.0, extras=(element, alt))
             node.cum_cost = float(cost)
+            out.append(node)
+        return out
+
+    @staticmethod
+    def _is_chain(graph, order, start_node):
+        """True if the edges in search order form one path from `start_node` through nodes that carry no beam yet."""
+        if not order or order[0][0] != start_node:
+            return False
+        for k, (tail, head) in enumerate(order):
+            if k and tail != order[k - 1][1]:
+                return False
+            if 'traceback' in graph.nodes[head] or not graph.edges[tail, head]['alternatives']:
+                return False
+        return len(set(head for _, head in order)) == len(order)
+
+    def _beam_lattice_native(self, graph, order, beam, context, lm_weight, beam_width):
+        """All edges of a linear lattice through ``klm_beam_lattice`` (the per-edge loop of reference :789-852, edge after
+        edge, natively).  Returns the beam at the last node; ``Node`` objects are made only for the final beam and its
+        ancestors (everything `next_path` can reach), the rest of the back-pointer table is dropped."""
+        c_i = self.mapping[0]
+        edges = [graph.edges[tail, head] for tail, head in order]
+        edge_first = np.zeros(len(edges) + 1, dtype=np.int32)
+        offsets, chars, conf = [0], [], []
+        max_alts = 1
+        for e, edge in enumerate(edges):
+            element, alternatives = edge['element'], edge['alternatives']
+            max_alts = max(max_alts, len(alternatives))
+            for alt in alternatives:
+                seen = []
+                for ch in alt.Unicode:
+                    if ch not in c_i and ch not in seen:
+                        self.logger.error('unmapped character "%s" at input alternative %d of element %s',
+                                          ch, alt.index or 0, element.id if element else "space")
+                        seen.append(ch)
+                    chars.append(c_i.get(ch, 0))
+                offsets.append(len(chars))
+                conf.append(alt.conf)
+            edge_first[e + 1] = len(conf)
+        n_hyp = len(beam)
+        if n_hyp == 0:
+            return []
+        slots, temps = self._slots_for([hyp.state for hyp in beam])
+        last = np.fromiter((c_i.get(hyp.value[-1], 0) for hyp in beam), dtype=np.int32, count=n_hyp)
+        cum = np.fromiter((hyp.cum_cost for hyp in beam), dtype=np.float64, count=n_hyp)
+        width = max(beam_width, n_hyp)
+        scratch = self._pool.acquire(width * (max_alts + 1) + self.batch_size + width)
+        try:
+            first, oh, oa, oc, fslot, steps, hsteps = self._native.beam_lattice(
+                slots, last, cum, edge_first, np.asarray(offsets, dtype=np.int32), np.asarray(chars, dtype=np.int32),
+                np.asarray(conf, dtype=np.float64), context, lm_weight, self.batch_size, beam_width, scratch)
+        except Exception:
+            self._pool.release_many(scratch)
+            raise
+        self.device_steps += steps
+        self.hypothesis_steps += hsteps
+        n_final = int(first[-1] - first[-2])
+        kept = set(int(s) for s in fslot[:n_final] if s >= 0)
+        self._pool.release_many([sl for sl in scratch if sl not in kept])
+        del temps
+        made = {}
+
+        def node_at(e, row):
+            """Tree node of kept candidate `row` of edge `e` (memoised; ancestors first, iteratively)."""
+            todo = []
+            while e >= 0 and (e, row) not in made:
+                todo.append((e, row))
+                row = int(oh[first[e] + row])
+                e -= 1
+            parent = beam[row] if e < 0 else made[(e, row)]
+            for e2, row2 in reversed(todo):
+                k = int(first[e2]) + row2
+                edge = edges[e2]
+                alt = edge['alternatives'][int(oa[k])]
+                node = Node(parent=parent, state=parent.state if not alt.Unicode else None, value=alt.Unicode, cost=0.0,
+                            extras=(edge['element'], alt))
+                node.cum_cost = float(oc[k])
+                made[(e2, row2)] = node
+                parent = node
+            return parent
+
+        out = []
+        last_edge = len(edges) - 1
+        for row in range(n_final):
+            node = node_at(last_edge, row)
+            sl = int(fslot[row])
+            if sl >= 0:
+                node.state = DeviceState(self._pool, sl)
+            elif sl <= -2:
+                node.state = beam[-2 - sl].state
             out.append(node)
         return out
 

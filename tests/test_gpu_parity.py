@@ -348,9 +348,9 @@ def test_rate_best_native_edge_equals_python_loop(width, beam_width, batch_size)
     wd = synth.weights(21, width=width, depth=2, voc_size=256, style='trained')
     maparr = synth.vocabulary()
     results = []
-    for native in (True, False):
+    for native, lattice in ((True, True), (False, False), (True, False)):   # whole lattice natively / host loop / edge by edge
         r = product(wd, maparr, 8, stateful=False, incremental=True)
-        r.native_beam = native
+        r.native_beam, r.native_lattice = native, lattice
         r.batch_size = batch_size
         tb = None
         pages = []
@@ -364,7 +364,12 @@ def test_rate_best_native_edge_equals_python_loop(width, beam_width, batch_size)
         pages.append(([(el.id if el else None, alt.Unicode, alt.index) for el, alt, _ in path], [s for _, _, s in path],
                       entropy, [], []))
         results.append((pages, r.device_steps, r.hypothesis_steps))
-    (pa, sa, ha), (pb, sb, hb) = results
+    (pa, sa, ha), (pb, sb, hb) = results[:2]
+    for pc, sc, hc in results[2:]:
+        assert (sc, hc) == (sb, hb)
+        for x, y in zip(pc, pb):
+            assert x[0] == y[0] and x[3] == y[3]
+            np.testing.assert_allclose(x[4], y[4], rtol=1e-6, atol=1e-6)
     assert (sa, ha) == (sb, hb)                      # same number of device steps and hypotheses advanced
     for x, y in zip(pa, pb):
         assert x[0] == y[0] and x[3] == y[3]

@@ -275,7 +275,7 @@ def test_dataflow_kernel_matches_barrier_kernel_and_oracle(width, depth, nctx, n
     slots = r._pool.acquire(n)
     results = {}
     for df in (1, 0, 1):                                         # dataflow, barrier, dataflow again (epochs keep running)
-        nat.set_option('tc_df', df)
+        nat.set_option('tc_df', 2 if df else 0)                  # (2: the dataflow kernel for sequences, too)
         nat.state_reset(slots)
         outs = []
         for piece in (slice(0, 120), slice(119, None)):          # second launch continues from the carried state
@@ -296,8 +296,8 @@ def test_dataflow_kernel_matches_barrier_kernel_and_oracle(width, depth, nctx, n
     (o1, s1), (o0, s0) = results[1], results[0]
     for (_, _, a), (_, _, b) in zip(o1, o0):
         assert not np.isnan(a).any()
-        assert np.abs(a.astype(np.float64) - b).max() <= 2e-5
-    assert np.abs(s1 - s0).max() <= 2e-5 * max(np.abs(s0).max(), 1.0)
+        assert np.abs(a.astype(np.float64) - b).max() <= 1e-4     # (two fp32-level evaluation orders)
+    assert np.abs(s1 - s0).max() <= 1e-4 * max(np.abs(s0).max(), 1.0)
     m = util.to_model(wd).astype(np.float64)
     for k in (0, 2, 5, min(n - 1, 11)):
         states = ln.zero_states(m, 1, np.float64)
