@@ -140,6 +140,14 @@ int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx,
              float *out, int mem);
 
 /*
+ * klm_step whose result is reduced on the device: instead of the n x voc_size softmax rows only the k most probable
+ * entries of every row come back, ascending by probability -- what Rater.generate keeps of them
+ * (rating.py:690-704: `argsort(pred)[-10:]`, then a threshold).  out_index / out_prob: [n][k] host arrays.
+ */
+int klm_step_topk(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx, const int32_t *slots_in,
+                  const int32_t *slots_out, int32_t k, int32_t *out_index, float *out_prob);
+
+/*
  * One lattice edge of the beam search.  Replaces the per-edge loop of Rater.rate_best (rating.py:789-852):
  * candidates = incoming hypotheses x alternatives, character-synchronous batched steps (klm_step with
  * targets), worst-first pops, projected-cost ordering with bisect.insort_left semantics, the +15 bit

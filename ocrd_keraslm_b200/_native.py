@@ -113,6 +113,7 @@ SYMBOLS = [
     ('klm_state_l2_distance', ctypes.c_int, [_P, _P, _P, _I, _I, _P]),
     ('klm_rate', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
     ('klm_step', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
+    ('klm_step_topk', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _I, _P, _P]),
     ('klm_get_info', ctypes.c_int, [_P, ctypes.POINTER(KlmInfo)]),
     ('klm_selftest_umma', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
     ('klm_selftest_umma2', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
@@ -365,3 +366,14 @@ class Model(object):
         targets = None if targets is None else _i32(targets)
         self.check(self._lib.klm_step(self._h, len(chars), _ptr(chars), _ptr(ctx), _ptr(si), _ptr(so), _ptr(targets),
                                       _ptr(out), mem))
+
+    def step_topk(self, chars, ctx, slots_in, slots_out, k):
+        """See klm_step_topk.  Returns (indices [n, k] int32, probabilities [n, k] float32), ascending by probability."""
+        chars = _i32(chars)
+        ctx = None if ctx is None else _i32(ctx)
+        si, so = _i32(slots_in), _i32(slots_out)
+        idx = np.empty((len(chars), k), dtype=np.int32)
+        prob = np.empty((len(chars), k), dtype=np.float32)
+        self.check(self._lib.klm_step_topk(self._h, len(chars), _ptr(chars), _ptr(ctx), _ptr(si), _ptr(so), int(k), _ptr(idx),
+                                           _ptr(prob)))
+        return idx, prob

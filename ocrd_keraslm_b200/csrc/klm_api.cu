@@ -164,6 +164,8 @@ struct klm_model {
     int *d_chars = nullptr, *d_targets = nullptr;
     float *d_out = nullptr;
     size_t cap_pos = 0, cap_out = 0;
+    void *d_topk = nullptr;            // klm_step_topk: [n][k] indices, [n][k] probabilities
+    size_t topk_bytes = 0;
     // stats
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
@@ -642,7 +644,7 @@ extern "C" int klm_destroy(klm_model *m) {
         cudaFree(m->d_ring[i]);
         if (m->ring_ev[i]) cudaEventDestroy(m->ring_ev[i]);
     }
-    cudaFree(m->d_chars); cudaFree(m->d_targets); cudaFree(m->d_out);
+    cudaFree(m->d_chars); cudaFree(m->d_targets); cudaFree(m->d_out); cudaFree(m->d_topk);
     if (m->ev0) cudaEventDestroy(m->ev0);
     if (m->ev1) cudaEventDestroy(m->ev1);
     if (m->own_stream) cudaStreamDestroy(m->own_stream);
@@ -1254,11 +1256,41 @@ extern "C" int klm_rate(klm_model *m, int32_t n, const int32_t *slots, const int
     return KLM_OK;
 }
 
-extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx, const int32_t *slots_in,
-                        const int32_t *slots_out, const int32_t *targets, float *out, int mem) {
+// k best entries of every softmax row, ascending by (probability, index) -- the order of np.argsort(p)[-k:] for distinct
+// values (rating.py:690-692); one warp per row, k rounds of a warp-wide arg-max over what is left.
+__global__ void klm_topk_rows(const float *__restrict__ rows, int n, int V, int k, int *__restrict__ out_idx,
+                              float *__restrict__ out_prob) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= n) return;
+    const float *p = rows + (size_t)row * V;
+    float last_p = INFINITY;
+    int last_i = 0x7fffffff;
+    for (int j = 0; j < k; ++j) {
+        float best = -1.f;
+        int bi = -1;
+        for (int v = lane; v < V; v += 32) {
+            const float x = p[v];
+            // still available = strictly below the last pick in (probability, index) order
+            const bool avail = x < last_p || (x == last_p && v < last_i);
+            if (avail && (x > best || (x == best && v > bi))) { best = x; bi = v; }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ob > best || (ob == best && oi > bi)) { best = ob; bi = oi; }
+        }
+        last_p = best; last_i = bi;
+        if (lane == 0) { out_idx[(size_t)row * k + (k - 1 - j)] = bi; out_prob[(size_t)row * k + (k - 1 - j)] = bi >= 0 ? best : 0.f; }
+    }
+}
+
+static int step_impl(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx, const int32_t *slots_in,
+                     const int32_t *slots_out, const int32_t *targets, float *out, int mem, int topk, int32_t *out_index) {
     if (!m) return fail(KLM_EINVAL, "NULL model");
     if (n <= 0) return KLM_OK;
     if (!chars || !out) return fail(KLM_EINVAL, "klm_step: NULL argument");
+    if (topk && (topk < 1 || topk > m->V || mem != KLM_MEM_HOST || !out_index || targets))
+        return fail(KLM_EINVAL, "klm_step_topk: k must be in 1..voc_size, host buffers, no targets");
     if (m->Nc > 0 && !ctx) return fail(KLM_EINVAL, "klm_step: model has %d context variables but ctx is NULL", m->Nc);
     CK(cudaSetDevice(m->device));
     const auto tm0 = std::chrono::steady_clock::now();
@@ -1318,11 +1350,33 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
     m->timed = true;
     if (mem == KLM_MEM_HOST) {
         float *hout = reinterpret_cast<float *>(m->h_step + (size_t)n * 8);
-        CK(cudaMemcpyAsync(hout, m->d_out, nout * 4, cudaMemcpyDeviceToHost, m->stream));
+        size_t ncopy = nout;
+        if (topk) {
+            // the rows stay on the device: k (index, probability) pairs per hypothesis come back instead of voc_size floats
+            if ((size_t)n * topk * 8 > m->topk_bytes) {
+                CK(cudaStreamSynchronize(m->stream));
+                cudaFree(m->d_topk); m->d_topk = nullptr; m->topk_bytes = 0;
+                CK(cudaMalloc(&m->d_topk, (size_t)n * topk * 8 * 2));
+                m->topk_bytes = (size_t)n * topk * 8 * 2;
+            }
+            int *d_idx = reinterpret_cast<int *>(m->d_topk);
+            float *d_prob = reinterpret_cast<float *>(m->d_topk) + (size_t)n * topk;
+            klm_topk_rows<<<(n + 3) / 4, 128, 0, m->stream>>>(m->d_out, n, m->V, topk, d_idx, d_prob);
+            m->launches++;
+            ncopy = (size_t)n * topk * 2;                              // indices, then probabilities
+            CK(cudaMemcpyAsync(hout, m->d_topk, ncopy * 4, cudaMemcpyDeviceToHost, m->stream));
+        } else {
+            CK(cudaMemcpyAsync(hout, m->d_out, nout * 4, cudaMemcpyDeviceToHost, m->stream));
+        }
         rc = fetch_errors_async(m); if (rc) return rc;
         const auto tm1 = std::chrono::steady_clock::now();
         CK(cudaStreamSynchronize(m->stream));
-        memcpy(out, hout, nout * 4);
+        if (topk) {
+            memcpy(out_index, hout, (size_t)n * topk * 4);
+            memcpy(out, hout + (size_t)n * topk, (size_t)n * topk * 4);
+        } else {
+            memcpy(out, hout, nout * 4);
+        }
         if (m->timing) {
             const auto tm2 = std::chrono::steady_clock::now();
             float ms = 0.f;
@@ -1335,6 +1389,16 @@ extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int
         return check_fetched_errors(m);
     }
     return KLM_OK;
+}
+
+extern "C" int klm_step(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx, const int32_t *slots_in,
+                        const int32_t *slots_out, const int32_t *targets, float *out, int mem) {
+    return step_impl(m, n, chars, ctx, slots_in, slots_out, targets, out, mem, 0, nullptr);
+}
+
+extern "C" int klm_step_topk(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx, const int32_t *slots_in,
+                             const int32_t *slots_out, int32_t k, int32_t *out_index, float *out_prob) {
+    return step_impl(m, n, chars, ctx, slots_in, slots_out, nullptr, out_prob, KLM_MEM_HOST, k, out_index);
 }
 
 extern "C" int klm_get_info(klm_model *m, klm_info *out) {

@@ -737,6 +737,20 @@ class Rater(object):
         del temps
         return out, new_states
 
+    def _advance_topk(self, indices, initial_states, context, k):
+        """One timestep for n hypotheses; only the k most probable next characters of each come back
+        (indices [n, k], probabilities [n, k], ascending by probability) + the new states."""
+        n = len(indices)
+        slots_in, temps = self._slots_for(initial_states)
+        out_slots = self._pool.acquire(n)
+        new_states = [DeviceState(self._pool, s) for s in out_slots]
+        ctx = np.tile(np.asarray(context, dtype=np.int32), (n, 1)) if len(context) else None
+        tops, probs = self._native.step_topk(indices, ctx, slots_in, out_slots, k)
+        self.device_steps += 1
+        self.hypothesis_steps += n
+        del temps
+        return tops, probs, new_states
+
     def predict(self, candidates, initial_states, context=None):
         """Next-character distributions and new states for n hypotheses (reference :578-639).
 
@@ -771,16 +785,17 @@ class Rater(object):
         for char in prefix[:-1]:
             _, states = self.predict([char], states, context=context)
         fringe = [Node(state=states[0], value=prefix[-1], cost=0.0)]
-        i_c = self.mapping[1]
+        c_i, i_c = self.mapping
         for _ in range(length):
             current = fringe
-            preds, states = self.predict([n.value for n in current], [n.state for n in current], context=context)
+            # the ten best continuations of every hypothesis are picked on the device (klm_step_topk): 10 (index,
+            # probability) pairs per hypothesis come back instead of a softmax row
+            indices = np.fromiter((c_i.get(n.value, 0) for n in current), dtype=np.int32, count=len(current))
+            tops, probs, states = self._advance_topk(indices, [n.state for n in current], context, min(10, self.voc_size))
             fringe = []
             for j, node in enumerate(current):
-                p = preds[j]
-                top = np.argsort(p)[-10:]                          # ten best ...
-                top = top[np.searchsorted(p[top], 0.004):]         # ... above the absolute threshold
-                for v, cost in zip(top, -np.log(p[top])):
+                first = np.searchsorted(probs[j], 0.004)           # ascending: keep what reaches the absolute threshold
+                for v, cost in zip(tops[j, first:], -np.log(probs[j, first:])):
                     if v not in i_c:
                         continue
                     bisect.insort_left(fringe, Node(parent=node, state=states[j], value=i_c[v], cost=cost))

@@ -410,3 +410,28 @@ def test_remove_from_mapping_shifts_indices_and_rebuilds_model():
     # removal by index
     assert r.remove_from_mapping(idx=1) is True
     assert r.voc_size == voc0 - 2
+
+
+# ------------------------------------------------------------------ device top-k (klm_step_topk; Rater.generate)
+@pytest.mark.parametrize('width,n,k', [(64, 5, 10), (128, 40, 10), (256, 130, 3), (64, 3, 256)])
+def test_step_topk_matches_argsort_of_full_rows(width, n, k):
+    """The k best entries of every softmax row, picked on the device, are what np.argsort(p)[-k:] (reference :690-692)
+    picks from the full rows klm_step returns: same indices in the same (ascending) order, same probabilities; the new
+    states are the same, too."""
+    wd = synth.weights(33, width=width, depth=2, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 8, stateful=False, incremental=True)
+    nat = r._native
+    rng = np.random.default_rng(n)
+    chars = rng.integers(0, 256, n).astype(np.int32)
+    ctx = rng.integers(0, 200, (n, 1)).astype(np.int32)
+    s_in = np.full(n, -1, dtype=np.int32)
+    a, b = r._pool.acquire(n), r._pool.acquire(n)
+    full = np.empty((n, 256), dtype=np.float32)
+    nat.step(chars, ctx, s_in, a, None, full)
+    idx, prob = nat.step_topk(chars, ctx, s_in, b, k)
+    for j in range(n):
+        want = np.argsort(full[j], kind='stable')[-k:]
+        np.testing.assert_array_equal(idx[j], want)
+        np.testing.assert_array_equal(prob[j], full[j][want])
+    np.testing.assert_array_equal(nat.state_to_host(a), nat.state_to_host(b))
