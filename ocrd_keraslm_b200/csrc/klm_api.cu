@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <chrono>
+#include <cstddef>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -103,6 +104,7 @@ struct KlmKnobs {
     int ll_debug = 0;             // KLM_LL_DEBUG
     int cl_debug = 0;             // KLM_CL_DEBUG
     int step_timing = 0;          // KLM_STEP_TIMING
+    int step_mapped = 1;          // KLM_STEP_MAPPED: beam steps read / write mapped host memory (no copies around the kernel)
 };
 static int env_int(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
 static void read_knobs(KlmKnobs &k) {
@@ -120,6 +122,7 @@ static void read_knobs(KlmKnobs &k) {
     k.ll_debug = env_int("KLM_LL_DEBUG", 0);
     k.cl_debug = env_int("KLM_CL_DEBUG", 0);
     k.step_timing = env_int("KLM_STEP_TIMING", 0);
+    k.step_mapped = env_int("KLM_STEP_MAPPED", 1);
 }
 
 #define KLM_RING 4
@@ -150,6 +153,9 @@ struct klm_model {
     // klm_step with host arrays: page-locked staging (a copy from/to pageable memory blocks in the driver for ~10 us)
     char *h_step = nullptr;
     size_t h_step_bytes = 0;
+    char *h_map = nullptr;             // klm_step, beam steps: mapped page-locked memory the kernel reads / writes directly
+    void *d_map = nullptr;
+    size_t h_map_bytes = 0;
     int *h_err = nullptr;              // page-locked copies of the device-side watchdog words, fetched with the results
     int bp_cap = 0;
     // state pool
@@ -573,6 +579,8 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
                     r.guard = 1; r.alias_slot = 0; r.sigma = r.idx % nch;
                     if (alias_bytes > (size_t)r.ring_bytes) ok = false;
                 }
+                // step mode stages the initial hidden values of all hypothesis groups side by side (the ring is idle then)
+                if ((size_t)2 * ((r.npairs + 1) / 2) * 2048 + (size_t)KLM_DF_MAXG * (r.npairs / 4) * 2048 > (size_t)r.ring_bytes) ok = false;
             } else if (r.kind == KLM_TC_IN) {
                 r.n_zcons = (int)rec_of[r.layer].size();
                 r.idx = (int)(std::find(in_of[r.layer].begin(), in_of[r.layer].end(), i) - in_of[r.layer].begin());
@@ -638,6 +646,7 @@ extern "C" int klm_destroy(klm_model *m) {
     cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
     cudaFree(m->hbuf_ll); cudaFree(m->logits_ll); cudaFree(m->progress); cudaFree(m->ll_err);
     if (m->h_step) cudaFreeHost(m->h_step);
+    if (m->h_map) cudaFreeHost(m->h_map);
     if (m->h_err) cudaFreeHost(m->h_err);
     for (int i = 0; i < KLM_RING; ++i) {
         if (m->h_ring[i]) cudaFreeHost(m->h_ring[i]);
@@ -828,6 +837,7 @@ extern "C" int klm_set_option(klm_model *m, const char *name, int64_t value) {
     else if (n == "tc_consumer_fence") k.tc_consumer_fence = (int)value;
     else if (n == "tc_spin_limit") k.tc_spin_limit = (unsigned)value;
     else if (n == "ll_debug") k.ll_debug = (int)value;
+    else if (n == "step_mapped") k.step_mapped = (int)value;
     else if (n == "step_timing") { k.step_timing = (int)value; m->timing = (int)value; }
     else return fail(KLM_EINVAL, "klm_set_option: unknown option '%s'", name);
     return KLM_OK;
@@ -1110,9 +1120,12 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
 
 // Step mode of the dataflow kernel: ONE position for nb <= 64 * KLM_DF_MAXG hypotheses in one launch (tick g advances
 // hypotheses 64g .. 64g+63; states in / out through the pool).
+struct StepHostArgs { const int32_t *chars, *targets, *slots_in, *slots_out, *ctx; };
+static int launch_step_df(klm_model *m, int nb, const int *d_si, const int *d_so, const int *d_cx, const int *d_chars,
+                          const int *d_targets, float *d_out, int full_rows, int *err_host, const StepHostArgs *inl = nullptr);
+
 static int run_step_df(klm_model *m, int nb, const int32_t *slots_in, const int32_t *slots_out, const int32_t *ctx,
                        const int *d_chars, const int *d_targets, float *d_out, int full_rows) {
-    KlmTcPlan &tp = m->tc;
     RingSlot rs;
     int rc = ring_acquire(m, &rs, (size_t)nb * (4 * 2 + 4 * m->Nc) + 128);
     if (rc) return rc;
@@ -1122,8 +1135,23 @@ static int run_step_df(klm_model *m, int nb, const int32_t *slots_in, const int3
     int *hcx = ring_put<int>(&rs, nullptr, (size_t)nb * std::max(1, m->Nc), &d_cx);
     for (int i = 0; i < nb * m->Nc; ++i) hcx[i] = ctx ? ctx[i] : 0;
     rc = ring_commit(m, &rs); if (rc) return rc;
-    KlmTcParams q;
-    memset(&q, 0, sizeof q);
+    return launch_step_df(m, nb, d_si, d_so, d_cx, d_chars, d_targets, d_out, full_rows, nullptr);
+}
+
+// all pointers: visible to the device (device memory, or mapped page-locked host memory)
+static int launch_step_df(klm_model *m, int nb, const int *d_si, const int *d_so, const int *d_cx, const int *d_chars,
+                          const int *d_targets, float *d_out, int full_rows, int *err_host, const StepHostArgs *inl) {
+    KlmTcPlan &tp = m->tc;
+    static thread_local KlmTcParams q;                               // (12 KB: not on the stack of every call)
+    memset(&q, 0, offsetof(KlmTcParams, step));
+    if (inl) {
+        q.step_inline = 1;
+        memcpy(q.step.chars, inl->chars, (size_t)nb * 4);
+        if (inl->targets) memcpy(q.step.targets, inl->targets, (size_t)nb * 4);
+        memcpy(q.step.slots_in, inl->slots_in, (size_t)nb * 4);
+        memcpy(q.step.slots_out, inl->slots_out, (size_t)nb * 4);
+        for (int i = 0; i < nb * m->Nc; ++i) q.step.ctx[i] = inl->ctx ? inl->ctx[i] : 0;
+    }
     q.W = m->W; q.D = m->D; q.V = m->V; q.Vp = tp.Vp; q.Nc = m->Nc;
     q.B = std::min(nb, KLM_TC_STREAMS); q.T_max = 1; q.stages = tp.stages;
     for (int k = 0; k < m->Nc; ++k) { q.ctx_rows[k] = m->cfg.ctx_rows[k]; q.Q[k] = m->Q[k]; }
@@ -1139,6 +1167,7 @@ static int run_step_df(klm_model *m, int nb, const int32_t *slots_in, const int3
     tc_df_params(m, q);
     q.step_groups = (nb + KLM_TC_STREAMS - 1) / KLM_TC_STREAMS;
     q.n_hyp = nb;
+    q.err_host = err_host;
     CK(klm_launch_seq_df(q, tp.grid, tp.df_smem, m->stream));
     tp.tick_base += (unsigned)q.step_groups; tp.epoch += (unsigned)q.step_groups + 1u;
     m->launches++; m->tc_launches++; m->df_launches++;
@@ -1303,6 +1332,50 @@ static int step_impl(klm_model *m, int32_t n, const int32_t *chars, const int32_
                             ctx[s * m->Nc + k], m->cfg.ctx_rows[k]);
     const int full = targets ? 0 : 1;
     const size_t nout = full ? (size_t)n * m->V : (size_t)n;
+    if (mem == KLM_MEM_HOST && !topk && n > KLM_MODEK_MAXB && n <= KLM_TC_STREAMS * KLM_DF_MAXG && m->tc.ok && m->tc.df_ok &&
+        m->knobs.tc_df && m->knobs.step_mapped) {
+        // Beam step, zero copy: the per-hypothesis arrays travel INSIDE the kernel parameters (KlmStepArgs), the scores and
+        // the watchdog word are written by the kernel straight into MAPPED page-locked host memory.  One launch and one
+        // stream synchronisation per step -- no copy-engine transfer in front of or behind the kernel.
+        const size_t need = nout * 4 + 256;
+        if (need > m->h_map_bytes) {
+            CK(cudaStreamSynchronize(m->stream));
+            if (m->h_map) cudaFreeHost(m->h_map);
+            m->h_map = nullptr; m->h_map_bytes = 0;
+            CK(cudaHostAlloc(&m->h_map, need * 2, cudaHostAllocMapped));
+            CK(cudaHostGetDevicePointer(&m->d_map, m->h_map, 0));
+            m->h_map_bytes = need * 2;
+        }
+        int32_t *h_err = reinterpret_cast<int32_t *>(m->h_map);
+        float *h_out = reinterpret_cast<float *>(m->h_map + 64);
+        h_err[0] = 0;
+        char *db = reinterpret_cast<char *>(m->d_map);
+        const StepHostArgs inl = {chars, targets, slots_in, slots_out, ctx};
+        CK(cudaEventRecord(m->ev0, m->stream));
+        rc = launch_step_df(m, n, nullptr, nullptr, nullptr, nullptr, nullptr, reinterpret_cast<float *>(db + 64), full,
+                            reinterpret_cast<int *>(db), &inl);
+        if (rc) return rc;
+        CK(cudaEventRecord(m->ev1, m->stream));
+        m->timed = true;
+        const auto tm1 = std::chrono::steady_clock::now();
+        CK(cudaStreamSynchronize(m->stream));
+        memcpy(out, h_out, nout * 4);
+        if (m->timing) {
+            const auto tm2 = std::chrono::steady_clock::now();
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, m->ev0, m->ev1);
+            m->t_steps++; m->t_step_kernel_ms += ms;
+            m->t_step_submit += std::chrono::duration<double>(tm1 - tm0).count();
+            m->t_step_wait += std::chrono::duration<double>(tm2 - tm1).count();
+            m->t_step_total += std::chrono::duration<double>(std::chrono::steady_clock::now() - tm0).count();
+        }
+        if (h_err[0]) {
+            const int code = h_err[0];
+            tc_df_reset(m);
+            return fail(KLM_ECUDA, "klm_seq_tc: device-side wait timed out (code %d)", code);
+        }
+        return KLM_OK;
+    }
     rc = ensure_pos_cap(m, (size_t)n, mem == KLM_MEM_HOST ? nout : 0); if (rc) return rc;
     // chars/targets are per-hypothesis host arrays: they ride along as position arrays of length n,
     // through page-locked staging

@@ -185,6 +185,14 @@ struct KlmTcRole {
     unsigned long long ch_mask[16];   // per operand chunk (natural order): flags of the source-layer CTAs whose slices lie in it
 };
 
+// Per-hypothesis arguments of a beam step, carried INSIDE the kernel parameters (constant bank: there when the kernel
+// starts -- no copy in front of the launch, no first-touch latency on the step's critical path)
+#define KLM_STEP_MAX (64 * 4)                       // = KLM_TC_STREAMS * KLM_DF_MAXG
+struct KlmStepArgs {
+    int chars[KLM_STEP_MAX], targets[KLM_STEP_MAX], slots_in[KLM_STEP_MAX], slots_out[KLM_STEP_MAX];
+    int ctx[KLM_STEP_MAX * KLM_MAX_CTX];
+};
+
 struct KlmTcParams {
     int W, D, V, Vp, Nc;
     int B, T_max, stages;
@@ -209,6 +217,7 @@ struct KlmTcParams {
     int full_rows;
     unsigned int *barrier;
     int *err;                     // device-side watchdog: non-zero = a wait timed out (code says which)
+    int *err_host;                // dataflow kernel: where a set watchdog word is mirrored at the end of the launch (mapped host memory), or NULL
     unsigned long long *trace;    // optional [grid][KLM_TC_TRACE_TICKS][8] SM-clock timeline (klm_tc_trace)
     int trace_t0;
     int poll_mode;                // grid barrier: 0 = ld.acquire per poll, 1 = relaxed polls + one acquire fence, 2 = relaxed, no fence (experiment)
@@ -234,9 +243,11 @@ struct KlmTcParams {
     int step_groups;              // 0: sequence mode (position = tick); G > 0: step mode -- ONE position for up to 64 * G
                                   //    hypotheses, tick g advances hypotheses 64 g .. 64 g + 63 (state in / out through the pool)
     int n_hyp;                    // step mode: number of hypotheses
+    int step_inline;              // step mode: 1 = chars / targets / slots / ctx are taken from `step` below, not from the pointers
     int n_proj, n_lse_warps;      // PROJ CTAs; LSE warps at work
     int exp;                      // experiment switches (klm_set_option "tc_exp"): 1 = back-off between flag polls, 2 = a REC CTA fetches
                                   //   nothing of the next tick before its own publication is through, 4 = IN / PROJ publish at once
     unsigned spin_limit;          // device-side watchdog: polls of one wait before it gives up (klm_set_option "tc_spin_limit")
     int fault;                    // test hook (klm_set_option "tc_fault"): CTA 0 withholds its hand-over signal of tick 2
+    KlmStepArgs step;             // (last: only the launches of a beam step fill it)
 };

@@ -319,22 +319,54 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
             df_signal(my_flag, epoch + 1u, p.pub_release);
         }
     } else {
+        // the initial hidden values of ALL groups: loads first (they are independent), staged side by side behind the
+        // hand-over buffer, one bulk store per group, ONE wait and one release for all of them
         __half *hx0_l = p.hx0 + (size_t)l * KLM_DF_MAXG * hx_slice;
-        for (int g = 0; g < p.step_groups; ++g) {
+        float h0[KLM_DF_MAXG][OWN][2];
+#pragma unroll
+        for (int g = 0; g < KLM_DF_MAXG; ++g) {
             const int hyp = 64 * g + s;
-            load_state(hyp < p.n_hyp ? p.slots_in[hyp] : -1, true);
-            if (g > 0) tc_bar_epi();                                   // the previous group's bulk store has read the staging
-            stage();
-            tc_bar_epi();
-            if (tid == 64) bulk_out(hx0_l + (size_t)g * hx_slice + (size_t)(role.first_pair / 4) * (128 * 8));
+            const int slot = (g < p.step_groups && hyp < p.n_hyp) ? (p.step_inline ? p.step.slots_in[hyp] : p.slots_in[hyp]) : -1;
+#pragma unroll
+            for (int i = 0; i < OWN; ++i) {
+                h0[g][i][0] = h0[g][i][1] = 0.f;
+                if (i < R.nown && slot >= 0) {
+                    const float2 h2 = *reinterpret_cast<const float2 *>(p.state + ((size_t)slot * p.D + l) * 2 * W + 2 * (pr0 + i));
+                    h0[g][i][0] = h2.x; h0[g][i][1] = h2.y;
+                }
+            }
         }
+#pragma unroll
+        for (int g = 0; g < KLM_DF_MAXG; ++g)
+            if (g < p.step_groups) {
+                __half *pb = pubbuf + (size_t)g * (pub_bytes / 2);
+#pragma unroll
+                for (int i = 0; i < OWN; ++i)
+                    if (i < R.nown) {
+                        const int ul = 2 * (R.own_first + i);
+                        __half hi0, lo0, hi1, lo1;
+                        tc_split(h0[g][i][0], hi0, lo0); tc_split(h0[g][i][1], hi1, lo1);
+                        __half *dst = pb + (ul / 8) * (128 * 8) + (ul & 7);
+                        *reinterpret_cast<__half2 *>(dst + s * 8) = __halves2half2(hi0, hi1);
+                        *reinterpret_cast<__half2 *>(dst + (64 + s) * 8) = __halves2half2(lo0, lo1);
+                    }
+            }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        tc_bar_epi();
         if (tid == 64) {
+            for (int g = 0; g < p.step_groups; ++g)
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                             ::"l"(hx0_l + (size_t)g * hx_slice + (size_t)(role.first_pair / 4) * (128 * 8)),
+                               "r"(tc::smem_u32(pubbuf) + (uint32_t)g * pub_bytes), "r"(pub_bytes) : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
             unsigned *f0 = p.sync + KLM_DF_HFLAG0 + l * 64 + role.idx;
             df_signal(f0, epoch + 1u, p.pub_release);
         }
     }
     tc_bar_epi();                                                    // (staging free again before the ring is used)
     if (tid == 64 && x.guard) tc::mbar_arrive(x.bar_epid);
+    if (TRACE && tid == 64) tc_trace(p, p.trace_t0 + KLM_TC_TRACE_TICKS - 1, 2);
 
     int x_next = 0, nreal_s = 0x7fffffff;
     if (l == 0 && !step && s < p.B) {
@@ -346,7 +378,11 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         const int hyp = step ? 64 * tick + s : s;
         const bool active = step ? hyp < p.n_hyp : (s < p.B && tick < len);
         const long long pos = step ? hyp : o0 + tick;
-        if (step) load_state(active ? p.slots_in[hyp] : -1, false);
+        int slot_out = 0;
+        if (step) {
+            load_state(active ? (p.step_inline ? p.step.slots_in[hyp] : p.slots_in[hyp]) : -1, false);
+            if (active) slot_out = p.step_inline ? p.step.slots_out[hyp] : p.slots_out[hyp];   // (fetched now, needed behind the cell)
+        }
         // back-pressure on the version ring: version tick+2 overwrites version tick+2-R, read by the IN / PROJ CTAs in tick
         // tick-R.  Polled here, needed only at the very end of the tick.
         bool bp_ok = true;
@@ -361,7 +397,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
             if (active) {
                 int xc;
                 bool real = true;
-                if (step) xc = __ldg(p.chars + hyp);
+                if (step) xc = p.step_inline ? p.step.chars[hyp] : __ldg(p.chars + hyp);
                 else {
                     xc = x_next;
                     if (tick + 1 < len) x_next = __ldg(p.chars + o0 + tick + 1);
@@ -378,7 +414,8 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
 #pragma unroll
                             for (int k = 0; k < KLM_MAX_CTX; ++k)
                                 if (k < p.Nc) {
-                                    int z = real ? __ldg(p.ctx + (size_t)hyp * p.Nc + k) : 0;     // padding: context 0 (:1141-1143)
+                                    int z = !real ? 0 : (step && p.step_inline) ? p.step.ctx[hyp * p.Nc + k]
+                                                                                : __ldg(p.ctx + (size_t)hyp * p.Nc + k);   // padding: context 0 (:1141-1143)
                                     z = min(max(z, 0), p.ctx_rows[k] - 1);
                                     const float4 b = __ldg(p.Q[k] + (size_t)z * W + u + e);
                                     a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
@@ -511,7 +548,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         if (step) {
             // step mode: the new state goes straight to the pool (the hypothesis' own output slot)
             if (active) {
-                float *st = p.state + ((size_t)p.slots_out[hyp] * p.D + l) * 2 * W;
+                float *st = p.state + ((size_t)slot_out * p.D + l) * 2 * W;
 #pragma unroll
                 for (int i = 0; i < OWN; ++i)
                     if (i < R.nown) {
@@ -656,9 +693,14 @@ __device__ void df_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
     const int *targets = p.targets;
     // work items: (tick, group) pairs, item k = tick * ngroups + group; warp gw takes the ticks gw, gw + nw, ... and all
     // groups of a tick (so that "tick finished" is one word per warp)
-    for (int tick = gw; tick < T; tick += nw) {
+    // sequence mode: warp gw takes the ticks gw, gw + nw, ... with all their stream groups ("tick finished" is one word per
+    // warp); step mode: the few (tick, group) items are spread over the warps -- a beam step waits for the last of them
+    const int nitems = step ? T * ngroups : T;
+    for (int item = gw; item < nitems; item += nw) {
+        const int tick = step ? item / ngroups : item;
+        const int g_first = step ? item % ngroups : 0, g_end = step ? g_first + 1 : ngroups;
         if (!df_wait_all(p, p.sync + KLM_DF_PPROG, p.n_proj, tick_base + (unsigned)tick + 1u, 10)) return;
-        for (int g = 0; g < ngroups; ++g) {
+        for (int g = g_first; g < g_end; ++g) {
             const int s = 32 * g + lane;
             const int hyp = step ? 64 * tick + s : s;
             long long o0 = 0;
@@ -670,16 +712,16 @@ __device__ void df_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
             const float4 *pb = pa + (size_t)Vq * 64;
             float tl = 0.f;
             if (act && !full_rows) {
-                int tg = __ldg(targets + pos);
+                int tg = (step && p.step_inline) ? p.step.targets[hyp] : __ldg(targets + pos);
                 tg = min(max(tg, 0), V - 1);
                 tl = __ldcg(reinterpret_cast<const float *>(pa + (size_t)(tg >> 2) * 64) + (tg & 3)) +
                      __ldcg(reinterpret_cast<const float *>(pb + (size_t)(tg >> 2) * 64) + (tg & 3));
             }
             float m = -INFINITY, sum = 0.f;
-            for (int v0 = 0; v0 < V4; v0 += 4) {
-                float4 xv[4];
+            for (int v0 = 0; v0 < V4; v0 += 8) {          // 16 loads in flight per lane: the loop is pure L2 latency
+                float4 xv[8];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < 8; ++j) {
                     if (v0 + j < V4) {
                         const float4 a = __ldcg(pa + (size_t)(v0 + j) * 64), b = __ldcg(pb + (size_t)(v0 + j) * 64);
                         xv[j] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
@@ -693,10 +735,10 @@ __device__ void df_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
                 }
                 float mx = m;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) mx = fmaxf(fmaxf(fmaxf(mx, xv[j].x), fmaxf(xv[j].y, xv[j].z)), xv[j].w);
+                for (int j = 0; j < 8; ++j) mx = fmaxf(fmaxf(fmaxf(mx, xv[j].x), fmaxf(xv[j].y, xv[j].z)), xv[j].w);
                 float acc = sum * __expf(m - mx);
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
+                for (int j = 0; j < 8; ++j)
                     acc += __expf(xv[j].x - mx) + __expf(xv[j].y - mx) + __expf(xv[j].z - mx) + __expf(xv[j].w - mx);
                 sum = acc; m = mx;
             }
@@ -718,14 +760,23 @@ __device__ void df_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
             }
         }
         __syncwarp();
-        if (lane == 0) df_st_relaxed(my_prog, tick_base + (unsigned)tick + 1u);    // the logits of this tick have been consumed
+        if (lane == 0 && !step) df_st_relaxed(my_prog, tick_base + (unsigned)tick + 1u);    // the logits of this tick have been consumed
     }
 }
 
 template <bool TRACE>
 __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *smem) {
+    if (TRACE && threadIdx.x == 64) tc_trace(p, p.trace_t0 + KLM_TC_TRACE_TICKS - 1, 0);      // (last trace slot: phases of the launch)
     const KlmTcRole role = p.roles[blockIdx.x];
-    if (role.kind == KLM_TC_LSE) { df_lse_role(p, role); return; }
+    if (role.kind == KLM_TC_LSE) {
+        df_lse_role(p, role);
+        __syncthreads();
+        if (threadIdx.x == 0 && p.err_host) {
+            const int code = *(volatile int *)p.err;
+            if (code) *(volatile int *)p.err_host = code;
+        }
+        return;
+    }
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const int W = p.W, S = role.stages, kc = role.kc;
@@ -765,6 +816,7 @@ __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *sme
             tc::bulk_g2s(tc::smem_u32(wsm) + off, p.wimg + role.wofs + off, min(32768u, img_bytes - off), bar_img);
     }
 
+    if (TRACE && tid == 64) tc_trace(p, p.trace_t0 + KLM_TC_TRACE_TICKS - 1, 1);
     DfCtx x;
     x.ring_a = tc::smem_u32(smem); x.bar_full = bar_full; x.bar_empty = bar_empty; x.bar_tfull = bar_tfull;
     x.bar_tempty = bar_tempty; x.bar_epid = bar_epid; x.tmem_base = *tmem_slot; x.wsm_a = tc::smem_u32(wsm);
@@ -793,11 +845,17 @@ __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *sme
         df_epi_inproj<TRACE>(p, role, x);
     }
 
+    if (TRACE && tid == 64) tc_trace(p, p.trace_t0 + KLM_TC_TRACE_TICKS - 1, 3);
     tc::tc_fence_before();
     __syncthreads();
     if (warp == 0) {
         __syncwarp();
         tc::tmem_dealloc(x.tmem_base, KLM_TC_TMEM_COLS);
+    }
+    if (TRACE && tid == 64) tc_trace(p, p.trace_t0 + KLM_TC_TRACE_TICKS - 1, 4);
+    if (tid == 0 && p.err_host) {
+        const int code = *(volatile int *)p.err;
+        if (code) *(volatile int *)p.err_host = code;
     }
 }
 
@@ -824,6 +882,10 @@ cudaError_t klm_launch_seq_df(const KlmTcParams &p, int grid, size_t smem, cudaS
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) smem_set[which][dev] = smem;
     }
-    // cooperative launch: all CTAs must be co-resident (they wait for one another)
-    return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
+    // All CTAs must be co-resident (they wait for one another).  The grid never exceeds one CTA per SM and the model's
+    // stream runs one kernel at a time, so a plain launch has them resident as well -- and costs ~25 us less per launch than
+    // a cooperative one, which matters for beam steps (a device-side watchdog turns a violation into an error, not a hang).
+    // klm_set_option "tc_exp" bit 8 asks for the cooperative launch.
+    if (p.exp & 8) return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
+    return cudaLaunchKernel(fn, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
 }

@@ -134,8 +134,14 @@ def _pad8(b):
 class _Reader(object):
     def __init__(self, data):
         self.d = data
-        if data[:8] != SIGNATURE:
-            raise H5Error('not an HDF5 file (bad signature)')
+        # the superblock sits at offset 0 or, behind a user block, at 512, 1024, 2048, ... (format spec II.A); file
+        # addresses count from the superblock's base address field
+        sb = 0
+        while data[sb:sb + 8] != SIGNATURE:
+            sb = 512 if sb == 0 else 2 * sb
+            if sb + 8 > len(data):
+                raise H5Error('not an HDF5 file (bad signature)')
+        data = data[sb:] if sb else data
         ver = data[8]
         if ver not in (0, 1):
             raise H5Error('HDF5 superblock version %d is not supported (only the "earliest" format '
@@ -148,6 +154,10 @@ class _Reader(object):
         p += 32
         # root group symbol table entry
         _name, self.root_header, cache, _r = struct.unpack_from('<QQII', data, p)
+        if self.base != sb:
+            # (libhdf5 stores the user block size as the base address; a file whose front was cut off or padded afterwards
+            #  would have to be told the new base -- not guessed here)
+            raise H5Error('superblock at %d but base address %d' % (sb, self.base))
         self._gcol = {}
 
     # ---- object headers ----
@@ -316,11 +326,23 @@ class Dataset(object):
     def __getitem__(self, key):
         body = self._layout
         ver = body[0]
+        shape = self.shape if self.shape is not None else ()
+        nbytes = (int(np.prod(shape)) if shape else 1) * self._itemsize()
+        if ver in (1, 2):
+            # libhdf5 <= 1.6 (format spec IV.A.2.i, versions 1 and 2): dimensionality, class, 5 reserved bytes, then the data
+            # address (not for compact storage) and the dimension sizes
+            ndim, cls = body[1], body[2]
+            if cls == 1:
+                body = bytes([3, 1]) + body[8:16] + struct.pack('<Q', nbytes)
+            elif cls == 0:
+                size = struct.unpack_from('<I', body, 8 + 4 * ndim)[0]
+                body = bytes([3, 0]) + struct.pack('<H', size) + body[12 + 4 * ndim:12 + 4 * ndim + size]
+            else:
+                raise H5Error('chunked datasets are not supported (dataset %s)' % self.name)
+            ver = 3
         if ver != 3:
             raise H5Error('data layout message version %d is not supported' % ver)
         cls = body[1]
-        shape = self.shape if self.shape is not None else ()
-        nbytes = (int(np.prod(shape)) if shape else 1) * self._itemsize()
         if cls == 1:
             addr, size = struct.unpack_from('<QQ', body, 2)
             if addr == UNDEF:

@@ -39,3 +39,9 @@ for tick in range((n + 63) // 64):
             print('tick %d %s l%d: ' % (tick, names[kind], layer) + ' '.join(
                 '%s %d..%d' % (e, (x[:, k][x[:, k] > 0] - t0).min() if (x[:, k] > 0).any() else -1,
                                (x[:, k][x[:, k] > 0] - t0).max() if (x[:, k] > 0).any() else -1) for k, e in enumerate(ev)))
+
+x = tr[:, 15, :5]
+names5 = ['kernel entry', 'setup done (barriers, TMEM, image copies issued)', 'REC prologue done (initial h published)', 'ticks done', 'exit']
+for k, nm in enumerate(names5):
+    v = x[:, k][x[:, k] > 0]
+    if len(v): print('%s: %d..%d ns after the first tick event' % (nm, v.min() - t0, v.max() - t0))
