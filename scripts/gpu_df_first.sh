@@ -1,4 +1,8 @@
-OUT=gpurun_out/r2m; mkdir -p $OUT
-timeout 300 python scripts/exp/df_step_trace.py 117 > $OUT/df_step_trace.txt 2>&1; head -4 $OUT/df_step_trace.txt | cut -c1-250; tail -5 $OUT/df_step_trace.txt
-KLM_STEP_TIMING=1 timeout 600 python bench.py --workload cfg3 --steps 2 --warmup 2 > $OUT/bench_cfg3.json 2> $OUT/bench_cfg3.err; cut -c1-200 $OUT/bench_cfg3.json; tail -3 $OUT/bench_cfg3.err
-timeout 900 python -m pytest tests -m gpu -q -x > $OUT/pytest.log 2>&1; echo "exit $?" >> $OUT/pytest.log; tail -4 $OUT/pytest.log
+OUT=gpurun_out/r2o; mkdir -p $OUT
+for PUB in 2 1; do for REL in 1 0; do
+  echo "=== KLM_TC_PUB=$PUB KLM_TC_PUB_RELEASE=$REL" >> $OUT/pub_modes.txt
+  KLM_TC_PUB=$PUB KLM_TC_PUB_RELEASE=$REL timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu --chars 30000 2>/dev/null | cut -c1-120 >> $OUT/pub_modes.txt
+done; done
+cat $OUT/pub_modes.txt
+timeout 300 python scripts/tc_trace.py cfg2 3000 > $OUT/timeline_tc_release.txt 2>&1; cat $OUT/timeline_tc_release.txt
+KLM_TC_PUB=1 timeout 300 python scripts/tc_trace.py cfg2 3000 > $OUT/timeline_tc_pub1.txt 2>&1; cat $OUT/timeline_tc_pub1.txt

@@ -205,3 +205,56 @@ def test_rate_sharded_world_size_2_gloo(tmp_path):
     for r, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, o
         assert 'rank %d ok' % r in o
+
+
+# ------------------------------------------------------------------ h5lite against a file written by libhdf5
+def test_h5lite_reads_a_libhdf5_written_file():
+    """The only third-party HDF5 file on the box: scipy's MATLAB 7.4 test file -- written by libhdf5 1.6, superblock v0
+    behind a 512-byte user block (base address 512), symbol-table group, v1 object headers, layout message v2.  Not a
+    Keras file (none is available: h5lite's writer -> reader round trip stays the only check of those objects), but it
+    pins the reader's superblock / group / object-header / dataspace / datatype code against the real library."""
+    scipy = pytest.importorskip('scipy')
+    path = os.path.join(os.path.dirname(scipy.__file__), 'io', 'matlab', 'tests', 'data', 'testhdf5_7.4_GLNX86.mat')
+    if not os.path.exists(path):
+        pytest.skip('scipy test data not installed')
+    from ocrd_keraslm_b200 import h5lite
+    with h5lite.File(path, 'r') as f:
+        assert list(f.keys()) == ['testdouble']
+        d = f['testdouble']
+        assert d.shape == (9, 1) and d.dtype == np.float64
+        assert d.attrs['MATLAB_class'] == b'double'
+        np.testing.assert_allclose(d[()].ravel(), np.arange(9) * np.pi / 4, rtol=1e-15)
+    with open(path, 'rb') as fh:
+        data = fh.read()
+    with pytest.raises(h5lite.H5Error):                         # user block cut off: base address no longer matches
+        h5lite._Reader(data[512:])
+    with pytest.raises(h5lite.H5Error):
+        h5lite._Reader(b'MATLAB 7.0 MAT-file' + b'\0' * 2000)
+
+
+# ------------------------------------------------------------------ the golden fixtures are what the reference produces
+@pytest.mark.skipif(not os.path.exists('/root/reference/ocrd_keraslm/lib/rating.py'), reason='needs /root/reference (build container only)')
+def test_golden_fixtures_are_reproduced_by_the_reference(tmp_path):
+    """Re-runs tests/golden/make_golden.py (the reference's own rating.py on the Keras shim) in a scratch copy and checks
+    that the committed fixtures come out again, bit for bit."""
+    import json
+    import shutil
+    work = tmp_path / 'repo'
+    (work / 'tests').mkdir(parents=True)
+    shutil.copytree(os.path.join(ROOT, 'tests', 'golden'), work / 'tests' / 'golden')
+    for pkg in ('oracle', 'ocrd_keraslm_b200'):
+        os.symlink(os.path.join(ROOT, pkg), work / pkg)
+    for name in ('golden.json', 'golden.npz'):
+        os.remove(work / 'tests' / 'golden' / name)
+    res = subprocess.run([sys.executable, str(work / 'tests' / 'golden' / 'make_golden.py')], stdout=subprocess.PIPE,
+                         stderr=subprocess.STDOUT, timeout=600)
+    assert res.returncode == 0, res.stdout.decode()
+    with open(work / 'tests' / 'golden' / 'golden.json', encoding='utf-8') as f:
+        new = json.load(f)
+    with open(os.path.join(ROOT, 'tests', 'golden', 'golden.json'), encoding='utf-8') as f:
+        old = json.load(f)
+    assert new == old
+    a, b = np.load(work / 'tests' / 'golden' / 'golden.npz'), np.load(os.path.join(ROOT, 'tests', 'golden', 'golden.npz'))
+    assert sorted(a.files) == sorted(b.files)
+    for k in a.files:
+        np.testing.assert_array_equal(a[k], b[k], err_msg=k)
