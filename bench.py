@@ -394,6 +394,83 @@ def base_line(args, value, ms_per_step):
     }
 
 
+def run_sharded(args):
+    """`--sharded`: the page-sharded form BASELINE.json words for cfg5 -- every rank holds the SAME list of units (10 000
+    lines), `shard.rate_sharded` gives each rank its longest-processing-time-first share, rates it with `Rater.rate_many`
+    and gathers all scores on every rank (NCCL all_gather) -- all inside the timed region, through the public API, from
+    Python strings.  STRONG scaling: the work is fixed, value = characters of the whole list / wall clock of the slowest
+    rank."""
+    import torch
+    import torch.distributed as dist
+    from ocrd_keraslm_b200 import shard
+    from ocrd_keraslm_b200.lib import Rater
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    args.gpus = world
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    wl = args.workload
+    width, depth, length, contexts, docs, chars, what = WORKLOADS[wl]
+    docs = args.docs or docs
+    chars = args.chars or chars
+    rater = Rater.from_weights(model_weights(wl), synth.vocabulary(), length, logger=quiet, device=local)
+    texts, ctxs = make_docs(wl, docs, chars, 0)                       # the same units on every rank
+    total_chars = sum(max(len(t) - 1, 0) for t in texts)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(args.warmup):
+        res = shard.rate_sharded(rater, texts, ctxs, gather=True)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    l0 = rater._native.info()['kernel_launches']
+    barrier()
+    sampler.start()
+    phases = {'rate_many_s': 0.0, 'total_s': 0.0}
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res = shard.rate_sharded(rater, texts, ctxs, gather=True)
+    torch.cuda.synchronize()
+    dt_local = time.perf_counter() - t0
+    barrier()
+    clocks = sampler.finish()
+    launches = rater._native.info()['kernel_launches'] - l0
+    # how the slowest rank's time splits: its own rating (host tokenisation + launches + copies) vs the rest (gather, unpack)
+    t1 = time.perf_counter()
+    mine = shard.partition([len(t) for t in texts], world)[rank]
+    rater.rate_many([texts[i] for i in mine], [ctxs[i] for i in mine])
+    rate_only = time.perf_counter() - t1
+    dt = dt_local
+    if world > 1:
+        t = torch.tensor([dt_local, rate_only, float(launches)], dtype=torch.float64, device='cuda')
+        tm = t.clone()
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        dt, rate_only, launches = float(tm[0].item()), float(tm[1].item()), int(t[2].item())
+    checksum = float(sum(np.log(np.maximum(r[1:].astype(np.float64), 1e-300)).sum() for r in res))
+    value = total_chars * args.steps / dt
+    line = base_line(args, value, 1000.0 * dt / args.steps)
+    line['scaling'] = 'strong'
+    line['config']['units'] = '%d lines, the same list on every rank; LPT partition over %d rank(s); scores gathered on every rank' % (docs, world)
+    line['config'].pop('docs_per_gpu', None)
+    line.update({
+        'e2e': {'value': value, 'unit': 'chars/s', 'h2d_bytes_per_step': 8 * total_chars, 'd2h_bytes_per_step': 4 * total_chars,
+                'api': 'shard.rate_sharded(rater, texts, contexts, gather=True) -> Rater.rate_many on the rank\'s share + all_gather'},
+        'gpu_launches': launches, 'clocks': clocks, 'checksum_logp': checksum,
+        'per_step_ms': {'whole': 1000.0 * dt / args.steps, 'rating_of_the_largest_share': 1000.0 * rate_only,
+                        'gather_and_unpack': 1000.0 * (dt / args.steps - rate_only)},
+        'note': 'no device-resident leg in this mode: value is the end-to-end number',
+    })
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -602,6 +679,7 @@ def main():
     ap.add_argument('--docs', type=int, default=0, help='documents per GPU (default: the workload\'s)')
     ap.add_argument('--chars', type=int, default=0, help='characters per document (default: the workload\'s)')
     ap.add_argument('--no-cpu', action='store_true', help='skip the CPU baseline leg')
+    ap.add_argument('--sharded', action='store_true', help='strong scaling: the same units on every rank, rate_sharded + gather timed')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     # stdout carries exactly ONE JSON line: libraries that write to file descriptor 1 on their own (NCCL prints its
@@ -615,6 +693,8 @@ def main():
             run_beam(args)
         elif args.impl == 'reference':
             run_reference(args)
+        elif args.sharded:
+            run_sharded(args)
         else:
             run_ours(args)
     finally:
