@@ -17,8 +17,8 @@
 cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_df(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
-cudaError_t klm_launch_seq_cl(const KlmSeqParams &p, const KlmClGeom &g, cudaStream_t stream);
-size_t klm_cl_smem_bytes(const KlmSeqParams &p, const KlmClGeom &g);
+cudaError_t klm_launch_seq_rg(const KlmSeqParams &p, cudaStream_t stream, int *cluster);
+bool klm_rg_eligible(int W, int D, int V);
 cudaError_t klm_launch_umma2_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
 cudaError_t klm_launch_umma_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
 
@@ -773,27 +773,8 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
         TRYC(cudaMalloc(&m->ll_err, 256));
         TRYC(cudaMemset(m->ll_err, 0, 256));
     }
-    // one-cluster kernel: opt-in (KLM_ENABLE_CL=1): correct, but slower than klm_seq_fma_ll in its present form
-    if (m->ll_err && getenv("KLM_ENABLE_CL") && atoi(getenv("KLM_ENABLE_CL")) > 0 && W % 8 == 0) {
-        // the smallest cluster (8 portable, 16 opt-in) whose CTAs can hold their slices for one stream
-        const int c_first = getenv("KLM_CL_MINC") ? std::max(8, atoi(getenv("KLM_CL_MINC"))) : 8;
-        for (int C = c_first; C <= 16 && m->cl.C == 0; C *= 2) {
-            if (W % C != 0) continue;
-            KlmClGeom g;
-            g.C = C; g.U = W / C; g.PU = (m->V4 / 4 + C - 1) / C;       // (V4 = vocabulary rows padded to a multiple of 4)
-            g.ntask = D * g.U + g.PU;
-            g.w4 = g.U * W + (D - 1) * g.U * 2 * W + g.PU * W;
-            if (g.ntask > KLM_WARPS * KLM_CL_MAXT || g.PU > KLM_WARPS / 2) continue;
-            KlmSeqParams q;
-            memset(&q, 0, sizeof q);
-            q.W = W; q.D = D; q.B = 1;
-            if (klm_cl_smem_bytes(q, g) + 1024 <= m->smem_optin) m->cl = g;
-        }
-        if (getenv("KLM_CL_MAXC") && m->cl.C > atoi(getenv("KLM_CL_MAXC"))) m->cl.C = 0;
-        if (getenv("KLM_CL_DEBUG"))
-            fprintf(stderr, "klm cluster plan: W %d D %d V4 %d -> C %d, U %d, PU %d, tasks %d, %d float4 of weights per CTA\n", W, D, m->V4,
-                    m->cl.C, m->cl.U, m->cl.PU, m->cl.ntask, m->cl.w4);
-    }
+    // one text at a time, small model: the register-resident cluster kernel (klm_seq_rg.cu); KLM_DISABLE_RG=1 switches it off
+    m->cl.C = (m->ll_err && klm_rg_eligible(W, D, V) && !getenv("KLM_DISABLE_RG")) ? (getenv("KLM_RG_CLUSTER") && atoi(getenv("KLM_RG_CLUSTER")) == 8 ? 8 : 16) : 0;
     TRYC(cudaMalloc(&m->barrier, 256));
     m->ring_bytes = (size_t)m->bp_cap * (4 * 4 + 8 + 4 * KLM_MAX_CTX) + 64;
     m->ring_bytes = std::max(m->ring_bytes, (size_t)1 << 16);
@@ -1088,14 +1069,11 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     p.chars = d_chars; p.targets = d_targets; p.n_real = d_nr; p.ctx = d_cx;
     p.out = d_out; p.full_rows = full_rows;
     p.hbuf = m->hbuf; p.logits = m->logits; p.barrier = m->barrier;
-    if (nb <= KLM_MODEK_MAXB && m->cl.C > 0 && m->ll_err && klm_cl_smem_bytes(p, m->cl) + 1024 <= m->smem_optin &&
-        (m->D * m->W + 4 * m->cl.PU) * nb <= KLM_CL_PUBS * KLM_THREADS) {
-        // the whole model in one thread-block cluster, recurrence exchanged through distributed shared memory
+    if (nb == 1 && m->cl.C > 0 && m->ll_err) {
+        // ONE stream, small model: weights in the registers of one thread-block cluster, recurrence through distributed shared memory
         p.err = m->ll_err;
         p.debug = m->knobs.ll_debug;
-        cudaError_t e = klm_launch_seq_cl(p, m->cl, m->stream);
-        if (m->knobs.cl_debug)
-            fprintf(stderr, "klm cluster launch: B %d T %d smem %zu -> %s\n", nb, (int)tmax, klm_cl_smem_bytes(p, m->cl), cudaGetErrorString(e));
+        cudaError_t e = klm_launch_seq_rg(p, m->stream, &m->cl.C);
         if (e == cudaSuccess) { m->launches++; m->ll_launches++; m->cl_launches++; return KLM_OK; }
         fprintf(stderr, "klm: cluster kernel cannot be launched (%s), using the grid-wide kernel\n", cudaGetErrorString(e));
         cudaGetLastError();

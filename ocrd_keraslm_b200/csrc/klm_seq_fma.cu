@@ -685,374 +685,6 @@ __global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_fma_ll(const __grid_co
 }
 
 // ---------------------------------------------------------------------------------------------
-// One-cluster kernel for <= 8 streams and models whose FP32 weights fit the shared memory of 8 or 16 SMs
-// (width <= 128 x depth <= 3: the reference's default model; Rater.rate of one text, tiny beams).
-// OPT-IN (KLM_ENABLE_CL=1): parity-green, but at 4.2 us per tick (cfg1 model) slower than klm_seq_fma_ll (2.5 us): with
-// the whole model on 8-16 SMs every warp runs 2-3 units one after the other, and one unit is ~1 700 clk of dependent
-// latency (8 k-steps, 10 shuffles, the cell); the hand-over itself is no longer the cost.  See DESIGN.md 3.1c.
-//
-// Replaces the per-window Session.run of Rater.rate (rating.py:516) like the kernels above; the difference is where
-// the recurrence is exchanged.  A tick of klm_seq_fma_ll costs ~4 900 clk, of which ~2 500 are the trip of the
-// {value, tick} words through L2 (490-1 100 clk one way between two SMs, scripts/ubench/pingpong.cu).  Here the whole
-// model lives in ONE thread-block cluster: CTA c keeps units [c U, (c+1) U) of EVERY layer and its share of the
-// embedding rows in shared memory, and the words travel through distributed shared memory -- every CTA stores its
-// new values straight into the exchange ring of every peer (st.shared::cluster, ~215 clk) and polls only its own
-// shared memory.  All CTAs take part in layer 1's recurrence, so nobody runs more than one tick ahead of anybody:
-// a ring of KLM_CL_RING ticks needs no progress words.  Same wavefront as the other kernels (layer l works on
-// position tick - l, projection on tick - D, log-sum-exp on tick - D - 1 by spare warps of CTA 0).
-__device__ __forceinline__ uint32_t cl_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ uint32_t cl_mapa(uint32_t local, uint32_t rank) {
-    uint32_t r;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
-    return r;
-}
-__device__ __forceinline__ void cl_st_remote(uint32_t addr, unsigned x, unsigned y) {
-    asm volatile("st.shared::cluster.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(x), "r"(y) : "memory");
-}
-__device__ __forceinline__ uint2 cl_ld_word(const uint2 *p) {
-    uint2 v;
-    asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(cl_smem_u32(p)) : "memory");
-    return v;
-}
-__device__ __forceinline__ void cl_sync() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// spins until the word carries `tick`; false (and the launch is flagged) after ~2^22 polls
-__device__ __forceinline__ bool cl_wait(const uint2 *p, unsigned tick, int *err) {
-    unsigned n = 0;
-    while (cl_ld_word(p).y != tick) {
-        if (++n > (1u << 22)) { atomicCAS(err, 0, 30); return false; }
-        if ((n & 0x3FFu) == 0 && *(volatile int *)err != 0) return false;
-    }
-    return true;
-}
-
-template <int BT>
-__global__ void __launch_bounds__(KLM_THREADS, 1) klm_seq_cl(const __grid_constant__ KlmSeqParams p, const KlmClGeom g) {
-    extern __shared__ float4 smem4[];
-    const int W = p.W, B = p.B, D = p.D, VG = p.V4 / 4;      // VG = groups of 4 vocabulary rows
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int C = g.C, U = g.U, PU = g.PU;
-    unsigned rank;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
-    constexpr int R = KLM_CL_RING;
-    const int slot_words = (D * W + 4 * C * PU) * B;          // hidden vectors of all layers, then the logits
-    // shared memory: [weight slices][exchange ring][results of this tick]
-    uint2 *ring = reinterpret_cast<uint2 *>(smem4 + g.w4);
-    float *outbuf = reinterpret_cast<float *>(ring + (size_t)R * slot_words);
-    const int nout = (D * U + 4 * PU) * B;                     // words this CTA publishes per tick
-
-    // ---- weight slices: layer l rows [rank U, rank U + U) x K_l, projection groups [rank PU, ..) x W ----
-    {
-        int ofs = 0;
-        for (int l = 0; l < D; ++l) {
-            const int K = l > 0 ? 2 * W : W;
-            const float4 *src = p.Wl[l] + (size_t)rank * U * K;
-            for (int i = threadIdx.x; i < U * K; i += KLM_THREADS) smem4[ofs + i] = __ldg(src + i);
-            ofs += U * K;
-        }
-        for (int i = threadIdx.x; i < PU * W; i += KLM_THREADS) {
-            const int gq = (int)rank * PU + i / W;
-            smem4[ofs + i] = gq < VG ? __ldg(p.Ep + (size_t)gq * W + (i % W)) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-    }
-    for (int i = threadIdx.x; i < R * slot_words; i += KLM_THREADS) ring[i] = make_uint2(0u, 0xFFFFFFFFu);
-    __syncthreads();
-    cl_sync();                                                 // every ring is initialised before anybody stores into it
-
-    // ---- tasks of this warp: task = warp + 16 j; [0, D U) = (layer, unit), then projection groups ----
-    float c_reg[KLM_CL_MAXT], h_reg[KLM_CL_MAXT];
-    float4 qsum[KLM_CL_MAXT], pre[KLM_CL_MAXT];
-    long long o0 = 0;
-    int len = 0, x_next = 0, nreal = 0x7fffffff;
-    if (lane < B) { o0 = p.offsets[lane]; len = (int)(p.offsets[lane + 1] - o0); }
-    if (lane < B) {
-        if (len > 0) x_next = __ldg(p.chars + o0);
-        if (p.n_real) nreal = __ldg(p.n_real + lane);
-    }
-#pragma unroll
-    for (int j = 0; j < KLM_CL_MAXT; ++j) {
-        c_reg[j] = h_reg[j] = 0.f;
-        qsum[j] = pre[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int task = warp + j * KLM_WARPS;
-        if (task < D * U && lane < B) {
-            const int l = task / U, u = (int)rank * U + task % U;
-            const int slot = p.slots_in[lane];
-            if (slot >= 0) {
-                const float *st = p.state + ((size_t)slot * D + l) * 2 * W;
-                h_reg[j] = st[u]; c_reg[j] = st[W + u];
-            }
-            if (l == 0) {
-                for (int k = 0; k < p.Nc; ++k) {
-                    int z = __ldg(p.ctx + lane * p.Nc + k);
-                    z = min(max(z, 0), p.ctx_rows[k] - 1);
-                    add4(qsum[j], __ldg(p.Q[k] + (size_t)z * W + u));
-                }
-            } else {
-                pre[j] = __ldg(p.bias[l] + u);
-            }
-            // the carried hidden state is the word of tick 0, in every CTA's ring
-            const uint32_t local = cl_smem_u32(ring + (size_t)(l * W + u) * B + lane);
-            for (int c = 0; c < C; ++c) cl_st_remote(cl_mapa(local, (uint32_t)c), __float_as_uint(h_reg[j]), 0u);
-        }
-    }
-
-    // per-task constants (no integer division inside the tick loop)
-    int t_l[KLM_CL_MAXT], t_K[KLM_CL_MAXT], t_src0[KLM_CL_MAXT], t_src1[KLM_CL_MAXT], t_out[KLM_CL_MAXT], t_u[KLM_CL_MAXT];
-    const float4 *t_w[KLM_CL_MAXT];
-#pragma unroll
-    for (int j = 0; j < KLM_CL_MAXT; ++j) {
-        const int task = warp + j * KLM_WARPS;
-        t_l[j] = -1; t_K[j] = 0; t_src0[j] = t_src1[j] = 0; t_out[j] = 0; t_u[j] = 0; t_w[j] = smem4;
-        if (task < D * U) {                              // (layer, unit): inputs h_{l-1} then h_l (layer 1: h_0 only)
-            const int l = task / U, ui = task - l * U;
-            t_l[j] = l; t_K[j] = l > 0 ? 2 * W : W; t_u[j] = (int)rank * U + ui;
-            t_w[j] = smem4 + (l == 0 ? 0 : U * W + (l - 1) * U * 2 * W) + ui * t_K[j];
-            t_src0[j] = (l > 0 ? l - 1 : 0) * W * B; t_src1[j] = l * W * B;
-            t_out[j] = task;
-        } else if (task < g.ntask) {                     // group of 4 vocabulary rows: input h_{D-1}
-            const int pi = task - D * U;
-            t_K[j] = W;
-            t_w[j] = smem4 + U * W + (D - 1) * U * 2 * W + pi * W;
-            t_src0[j] = t_src1[j] = (D - 1) * W * B;
-            t_out[j] = D * U + 4 * pi;
-        }
-    }
-    // publication: thread -> (peer, word) pairs, fixed for the launch; remote addresses of ring slot 0
-    int pub_src[KLM_CL_PUBS];
-    uint32_t pub_dst[KLM_CL_PUBS];
-    {
-        const int nh = D * U * B;
-#pragma unroll
-        for (int q = 0; q < KLM_CL_PUBS; ++q) {
-            const int i = threadIdx.x + q * KLM_THREADS;
-            pub_src[q] = -1; pub_dst[q] = 0;
-            if (i < nh * C) {
-                const int c = i / nh, w = i - c * nh;
-                const int task = w / B, b = w - task * B;
-                const int l = task / U, u = (int)rank * U + task % U;
-                pub_src[q] = w;
-                pub_dst[q] = cl_mapa(cl_smem_u32(ring + (size_t)(l * W + u) * B + b), (uint32_t)c);
-            } else if (i < nh * C + 4 * PU * B) {
-                const int i2 = i - nh * C;
-                const int r4 = i2 / B, b = i2 - r4 * B;
-                const int v = 4 * ((int)rank * PU) + r4;
-                pub_src[q] = nh + i2;
-                pub_dst[q] = cl_mapa(cl_smem_u32(ring + (size_t)(D * W + v) * B + b), 0u);
-            }
-        }
-    }
-    const int nticks = p.T_max + D + 1;
-    int tg_next = 0, tg_next_t = -1;
-    bool ok = true;
-    long long cdbg[6] = {0, 0, 0, 0, 0, 0}, cdbg_t = 0;
-#define CL_DBG(i) if (p.debug) { const long long now_ = clock64(); cdbg[i] += now_ - cdbg_t; cdbg_t = now_; }
-    for (int tick = 0; tick < nticks && ok; ++tick) {
-        const int slot = tick % R, nslot = (tick + 1) % R;
-        const uint2 *cur = ring + (size_t)slot * slot_words;
-        if (p.debug) cdbg_t = clock64();
-        // layer 1's table rows: issued before the polls, consumed in the cell
-        if (lane < B && tick < len) {
-            const int x = min(max(x_next, 0), p.V - 1);
-            if (tick + 1 < len) x_next = __ldg(p.chars + o0 + tick + 1);
-#pragma unroll
-            for (int j = 0; j < KLM_CL_MAXT; ++j) {
-                const int task = warp + j * KLM_WARPS;
-                if (task < U) pre[j] = __ldg(p.P + (size_t)x * W + rank * U + task);
-            }
-        }
-        // ---- this tick's hidden vectors have arrived? (own shared memory only) ----
-        // (ONE warp polls, the others sleep at the barrier: sixteen warps spinning on shared memory starve the
-        //  incoming remote stores of the very port they arrive through -- 8 200 instead of ~2 000 clk per tick)
-        if (warp == 0)
-            for (int i = lane; i < D * W * B; i += 32)
-                if (!cl_wait(cur + i, (unsigned)tick, p.err)) ok = false;
-        CL_DBG(0)                                              // gather issue + own polls
-        ok = __syncthreads_and(ok ? 1 : 0) != 0;
-        if (!ok) break;
-        CL_DBG(1)                                              // everybody's polls
-        // ---- contractions (all tasks of the warp side by side: their loads and FMA chains overlap), then cells ----
-        float4 mine[KLM_CL_MAXT];
-        constexpr int GJ = BT >= 8 ? 1 : (BT >= 4 ? 2 : KLM_CL_MAXT);     // tasks side by side (accumulator registers)
-#pragma unroll
-        for (int j0 = 0; j0 < KLM_CL_MAXT; j0 += GJ) {
-            float4 acc[GJ][BT];
-            int kmax = 0;
-#pragma unroll
-            for (int jj = 0; jj < GJ; ++jj) {
-                kmax = max(kmax, t_K[j0 + jj]);
-#pragma unroll
-                for (int bb = 0; bb < BT; ++bb) acc[jj][bb] = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-            for (int k = lane; k < kmax; k += 32) {
-#pragma unroll
-                for (int jj = 0; jj < GJ; ++jj)
-                    if (k < t_K[j0 + jj]) {
-                        const float4 w = t_w[j0 + jj][k];
-                        const uint2 *src = cur + (k < W ? t_src0[j0 + jj] + k * B : t_src1[j0 + jj] + (k - W) * B);
-#pragma unroll
-                        for (int bb = 0; bb < BT; ++bb)
-                            if (bb < B) fma4(acc[jj][bb], w, __uint_as_float(src[bb].x));
-                    }
-            }
-#pragma unroll
-            for (int jj = 0; jj < GJ; ++jj) {
-                const int j = j0 + jj;
-                mine[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (t_K[j] == 0) continue;
-#pragma unroll
-                for (int bb = 0; bb < BT; ++bb) {
-                    // 4 sums over 32 lanes in 6 shuffles (as in klm_seq_fma_ll)
-                    const bool up16 = lane & 16, up8 = lane & 8;
-                    float s0 = up16 ? acc[jj][bb].x : acc[jj][bb].z, s1 = up16 ? acc[jj][bb].y : acc[jj][bb].w;
-                    float k0 = up16 ? acc[jj][bb].z : acc[jj][bb].x, k1 = up16 ? acc[jj][bb].w : acc[jj][bb].y;
-                    k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
-                    k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
-                    float v = (up8 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, up8 ? k0 : k1, 8);
-                    v += __shfl_xor_sync(0xffffffffu, v, 4);
-                    v += __shfl_xor_sync(0xffffffffu, v, 2);
-                    v += __shfl_xor_sync(0xffffffffu, v, 1);
-                    const float gx = __shfl_sync(0xffffffffu, v, 0), gy = __shfl_sync(0xffffffffu, v, 8),
-                                gz = __shfl_sync(0xffffffffu, v, 16), gw = __shfl_sync(0xffffffffu, v, 24);
-                    if (lane == bb) mine[j] = make_float4(gx, gy, gz, gw);
-                }
-            }
-        }
-        if (lane < B) {
-#pragma unroll
-            for (int j = 0; j < KLM_CL_MAXT; ++j) {
-                if (t_K[j] == 0) continue;
-                if (t_l[j] >= 0) {
-                    const int l = t_l[j], t = tick - l;
-                    if (t >= 0 && t < len) {
-                        add4(mine[j], pre[j]);
-                        if (l == 0) {
-                            if (t < nreal) add4(mine[j], qsum[j]);
-                            else for (int k = 0; k < p.Nc; ++k) add4(mine[j], __ldg(p.Q[k] + t_u[j]));   // padding: context 0
-                        }
-                        lstm_cell_fast(mine[j], c_reg[j], h_reg[j]);
-                    }
-                    outbuf[t_out[j] * B + lane] = h_reg[j];
-                } else {
-                    const int q4 = t_out[j];
-                    outbuf[q4 * B + lane] = mine[j].x; outbuf[(q4 + 1) * B + lane] = mine[j].y;
-                    outbuf[(q4 + 2) * B + lane] = mine[j].z; outbuf[(q4 + 3) * B + lane] = mine[j].w;
-                }
-            }
-        }
-        CL_DBG(2)                                              // contractions + cells
-        __syncthreads();
-        CL_DBG(3)                                              // barrier
-        // ---- publication: hidden values into every CTA's ring, logits into CTA 0's (addresses fixed per thread) ----
-        {
-            const uint32_t slot_ofs = (uint32_t)nslot * (uint32_t)slot_words * 8u;
-#pragma unroll
-            for (int q = 0; q < KLM_CL_PUBS; ++q)
-                if (pub_src[q] >= 0)
-                    cl_st_remote(pub_dst[q] + slot_ofs, __float_as_uint(outbuf[pub_src[q]]), (unsigned)(tick + 1));
-        }
-        CL_DBG(4)                                              // publication
-        // ---- log-sum-exp + target pick: CTA 0, one spare warp per stream (the warps without a projection task) ----
-        if (rank == 0) {
-            const int t = tick - D - 1;
-            const int b = KLM_WARPS - 1 - warp;
-            if (t >= 0 && b < B) {
-                const long long ob = p.offsets[b];
-                const int lb = (int)(p.offsets[b + 1] - ob);
-                if (t < lb) {
-                    const uint2 *lg = cur + (size_t)D * W * B;
-                    int tg = 0;
-                    if (!p.full_rows) {
-                        tg = (tg_next_t == t) ? tg_next : __ldg(p.targets + ob + t);
-                        tg = min(max(tg, 0), p.V - 1);
-                        if (t + 1 < lb) { tg_next = __ldg(p.targets + ob + t + 1); tg_next_t = t + 1; }
-                    }
-                    float m = -INFINITY, sum = 0.f, tl = 0.f;
-                    for (int v0 = 0; v0 < p.V && ok; v0 += 256) {
-                        float x[8];
-#pragma unroll
-                        for (int jj = 0; jj < 8; ++jj) {
-                            const int v = v0 + 32 * jj + lane;
-                            x[jj] = -INFINITY;
-                            if (v < p.V) {
-                                if (!cl_wait(lg + (size_t)v * B + b, (unsigned)tick, p.err)) ok = false;
-                                x[jj] = __uint_as_float(cl_ld_word(lg + (size_t)v * B + b).x);
-                            }
-                            if (v == tg) tl = x[jj];
-                        }
-                        float mx = m;
-#pragma unroll
-                        for (int jj = 0; jj < 8; ++jj) mx = fmaxf(mx, x[jj]);
-                        if (mx > -INFINITY) {
-                            float a = sum * __expf(m - mx);
-#pragma unroll
-                            for (int jj = 0; jj < 8; ++jj) a += __expf(x[jj] - mx);
-                            sum = a; m = mx;
-                        }
-                    }
-                    float mw = m;
-                    for (int s = 16; s > 0; s >>= 1) mw = fmaxf(mw, __shfl_xor_sync(0xffffffffu, mw, s));
-                    sum = (m > -INFINITY) ? sum * __expf(m - mw) : 0.f;
-                    for (int s = 16; s > 0; s >>= 1) {
-                        sum += __shfl_xor_sync(0xffffffffu, sum, s);
-                        tl += __shfl_xor_sync(0xffffffffu, tl, s);       // exactly one lane holds the target's logit
-                    }
-                    if (p.full_rows) {
-                        float *row = p.out + (size_t)(ob + t) * p.V;
-                        const float inv = 1.0f / sum;
-                        for (int v = lane; v < p.V; v += 32)
-                            row[v] = expf(__uint_as_float(cl_ld_word(lg + (size_t)v * B + b).x) - mw) * inv;
-                    } else if (lane == 0) {
-                        p.out[ob + t] = (tl - mw) - logf(sum);
-                    }
-                }
-            }
-        }
-    }
-
-    if (p.debug && (threadIdx.x == 0 || threadIdx.x == KLM_THREADS - 32))
-        printf("klm_seq_cl cta %u thread %d: polls %lld, all polls %lld, tasks %lld, barrier %lld, publication %lld clk per tick\n", rank,
-               threadIdx.x, cdbg[0] / nticks, cdbg[1] / nticks, cdbg[2] / nticks, cdbg[3] / nticks, cdbg[4] / nticks);
-    // ---- final state ----
-#pragma unroll
-    for (int j = 0; j < KLM_CL_MAXT; ++j) {
-        const int task = warp + j * KLM_WARPS;
-        if (task < D * U && lane < B) {
-            const int l = task / U, u = (int)rank * U + task % U;
-            float *st = p.state + ((size_t)p.slots_out[lane] * D + l) * 2 * W;
-            st[u] = h_reg[j]; st[W + u] = c_reg[j];
-        }
-    }
-    __syncthreads();
-    cl_sync();                                                 // nobody leaves while a peer may still store into its ring
-}
-
-size_t klm_cl_smem_bytes(const KlmSeqParams &p, const KlmClGeom &g) {
-    const size_t slot_words = (size_t)(p.D * p.W + 4 * g.C * g.PU) * p.B;
-    return (size_t)g.w4 * 16 + (size_t)KLM_CL_RING * slot_words * 8 + (size_t)(p.D * g.U + 4 * g.PU) * p.B * 4 + 16;
-}
-
-cudaError_t klm_launch_seq_cl(const KlmSeqParams &p, const KlmClGeom &g, cudaStream_t stream) {
-    typedef void (*Fn)(const KlmSeqParams, const KlmClGeom);
-    Fn fn = p.B > 4 ? klm_seq_cl<8> : p.B > 2 ? klm_seq_cl<4> : p.B > 1 ? klm_seq_cl<2> : klm_seq_cl<1>;
-    const size_t smem = klm_cl_smem_bytes(p, g);
-    cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    if (g.C > 8) {
-        e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-        if (e != cudaSuccess) return e;
-    }
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof cfg);
-    cfg.gridDim = dim3(g.C); cfg.blockDim = dim3(KLM_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = g.C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, fn, p, g);
-}
-
-// ---------------------------------------------------------------------------------------------
 // Launch helper used by klm_api.cu
 cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cudaStream_t stream) {
     void *args[] = { const_cast<KlmSeqParams *>(&p) };

@@ -449,6 +449,11 @@ class Rater(object):
         """
         assert self.status > 1
         assert self.incremental is False
+        if not self.stateful:
+            # The reference's stateless mode scores every position from a zero state over a sliding window of at most
+            # `length` characters (:1060-1094) -- a different quantity from the stateful recurrence, used only by models
+            # trained stateless, and outside the B200 path: refuse rather than return other numbers.
+            raise NotImplementedError('stateless (windowed) rating is not part of the B200 rating path; load the model stateful')
         context = self._context_row(context)
         text = unicodedata.normalize('NFC', text)
         size = len(text)

@@ -1,8 +1,3 @@
-OUT=gpurun_out/r2o; mkdir -p $OUT
-for PUB in 2 1; do for REL in 1 0; do
-  echo "=== KLM_TC_PUB=$PUB KLM_TC_PUB_RELEASE=$REL" >> $OUT/pub_modes.txt
-  KLM_TC_PUB=$PUB KLM_TC_PUB_RELEASE=$REL timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu --chars 30000 2>/dev/null | cut -c1-120 >> $OUT/pub_modes.txt
-done; done
-cat $OUT/pub_modes.txt
-timeout 300 python scripts/tc_trace.py cfg2 3000 > $OUT/timeline_tc_release.txt 2>&1; cat $OUT/timeline_tc_release.txt
-KLM_TC_PUB=1 timeout 300 python scripts/tc_trace.py cfg2 3000 > $OUT/timeline_tc_pub1.txt 2>&1; cat $OUT/timeline_tc_pub1.txt
+OUT=gpurun_out/r2s; mkdir -p $OUT
+timeout 300 python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "register_resident or golden or degenerate" > $OUT/pytest_rg.log 2>&1; echo "exit $?" >> $OUT/pytest_rg.log; tail -5 $OUT/pytest_rg.log
+KLM_LL_DEBUG=1 timeout 600 python bench.py --workload cfg1 --steps 1 --warmup 3 --no-cpu > $OUT/bench_cfg1_dbg.json 2> $OUT/bench_cfg1_dbg.err; cut -c1-120 $OUT/bench_cfg1_dbg.json; grep "klm_seq_rg" $OUT/bench_cfg1_dbg.err | tail -7

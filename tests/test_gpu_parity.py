@@ -257,33 +257,39 @@ def test_value_tick_exchange_kernel_over_many_ring_turns(n_docs):
         assert_logp_close(first[i], [p for _, p in ref])
 
 
-@pytest.mark.parametrize('width,depth,n_docs', [(128, 2, 1), (128, 3, 2), (64, 2, 5), (128, 1, 3)])
-def test_one_cluster_kernel_matches_oracle(monkeypatch, width, depth, n_docs):
-    """klm_seq_cl (opt-in): the model in one thread-block cluster, recurrence exchanged through distributed shared
-    memory; ragged streams, carried state out of the launch, twice in a row."""
-    monkeypatch.setenv('KLM_ENABLE_CL', '1')
-    wd = synth.weights(41 + width, width=width, depth=depth, voc_size=256, style='trained')
-    maparr = synth.vocabulary()
+@pytest.mark.parametrize('depth,voc', [(2, 256), (1, 256), (3, 256), (2, 100), (2, 400)])
+def test_register_resident_cluster_kernel_matches_oracle(depth, voc):
+    """klm_seq_rg: ONE text, width 128 -- the model in the registers of one 8-CTA cluster, recurrence through distributed
+    shared memory (the reference's default use: Rater.rate / rate2 of a string).  Texts of several lengths incl. one and
+    two positions, state carried from call to call (padded tail included), twice in a row bit-identical."""
+    wd = synth.weights(141 + depth, width=128, depth=depth, voc_size=voc, style='trained')
+    maparr = synth.vocabulary()[:voc] if voc <= 256 else np.concatenate(
+        [synth.vocabulary(), np.arange(0x400, 0x400 + voc - 256, dtype=np.uint32)])
     r = product(wd, maparr, 32)
     assert r._native.info()['cl_cluster'] in (8, 16)
     o = oracle_for(wd, maparr, 32)
-    sizes = [150, 2, 40, 33, 90][:n_docs]
-    texts = [synth.text(3300 + i, s) for i, s in enumerate(sizes)]
-    ctxs = [[i * 11] for i in range(n_docs)]
-    first = r.rate_many(texts, ctxs)
-    assert r._native.info()['cl_launches'] >= 1
-    again = r.rate_many(texts, ctxs)
-    for i, (t, c) in enumerate(zip(texts, ctxs)):
-        np.testing.assert_array_equal(first[i], again[i])
-        ref, _ = o.rate2(t, c)
-        assert_logp_close(first[i], [p for _, p in ref])
-    # stateful single-text rating with carry (Rater.rate), against the oracle
+    for size, ctx in ((150, [7]), (2, [0]), (3, [199]), (40, [33]), (333, [5])):
+        text = synth.text(3300 + size, size, mapping_arr=maparr)
+        launches = r._native.info()['cl_launches']
+        got, ppl = r.rate2(text, ctx)
+        assert r._native.info()['cl_launches'] == launches + 1
+        again, _ = r.rate2(text, ctx)
+        assert got == again
+        ref, ppl_o = o.rate2(text, ctx)
+        assert_logp_close([q for _, q in got], [q for _, q in ref])
+        assert ppl == pytest.approx(ppl_o, rel=1e-3)
+    # stateful rating with carry (Rater.rate: windows of `length`, padded tail), against the oracle, incl. the final state
     r.reset_states()
     o.reset_states()
-    a = r.rate(texts[0], ctxs[0])
-    b = r.rate(texts[0], ctxs[0])
-    assert_logp_close(a, o.rate(texts[0], ctxs[0]))
-    assert_logp_close(b, o.rate(texts[0], ctxs[0]))
+    text = synth.text(3399, 150, mapping_arr=maparr)
+    for piece in (text[:70], text[70:], text):
+        assert_logp_close(r.rate(piece, [11]), o.rate(piece, [11]))
+    assert_state_close(r._native.state_to_host([0])[0], np.concatenate([s for s in o.states], axis=0))
+    # a single hypothesis through klm_step (predict) takes the same kernel: full softmax row
+    ri = product(wd, maparr, 32, stateful=False, incremental=True)
+    probs, states = ri.predict(['a'], [None], context=[3])
+    pr, st = o.predict(['a'], [None], context=[3])
+    assert_logp_close(probs[0], pr[0], tol=2e-3)
 
 
 def test_rate_many_degenerate_inputs():
