@@ -296,10 +296,14 @@ def run_beam(args):
                  'gpu_launches': r._native.info()['kernel_launches'] - l0,
                  'e2e': {'value': steps / dt, 'unit': 'steps/s', 'h2d_bytes_per_step': int(12 * hyps / args.steps),
                          'd2h_bytes_per_step': int(4 * hyps / args.steps), 'api': 'Rater.rate_best(graph, ...)'},
-                 'roofline': {'bound': 'tensor', 'kernel': 'klm_seq_tc (one tick per klm_step)', 'achieved': hyps / dt * F / 1e12,
-                              'peak': float(pk.get('bf16_tflops', 1590.0)), 'unit': 'TFLOP/s',
-                              'frac': hyps / dt * F / 1e12 / float(pk.get('bf16_tflops', 1590.0)), 'traffic': None,
-                              'note': 'wall-clock of the whole search incl. the host-side beam logic, not kernel time'}})
+                 'roofline': {'bound': 'tensor', 'kernel': 'klm_seq_df (step mode: one launch per beam step)',
+                              'achieved': hyps / dt * F / 1e12,
+                              'peak': float(pk.get('bf16_tflops_sustained', FALLBACK_PEAKS['bf16_tflops_sustained'])), 'unit': 'TFLOP/s',
+                              'frac': hyps / dt * F / 1e12 / float(pk.get('bf16_tflops_sustained', FALLBACK_PEAKS['bf16_tflops_sustained'])),
+                              'traffic': None, 'peak_source': pk_src + ', bf16 sustained',
+                              'note': 'achieved = algorithmic FLOPs of all hypothesis steps / WALL CLOCK of the whole search (host-side '
+                                      'beam logic included); a beam step is a latency chain (REC -> IN -> REC -> ... -> PROJ -> LSE for one '
+                                      'position), not a throughput problem: KLM_STEP_TIMING=1 prints the device share per step'}})
     print(json.dumps(line))
 
 
@@ -629,6 +633,24 @@ def run_ours(args):
         'smem_bytes': info['tc_smem_bytes'] if info.get('tc_launches', 0) > 0 else info['smem_bytes'],
         'weights_in_smem': (0 if info.get('tc_enabled') == 3 else 1) if info.get('tc_launches', 0) > 0 else info['weights_in_smem'],
     }
+
+    if info.get('tc_launches', 0) == 0:
+        # <= 8 streams: the FP32 kernels (klm_seq_rg: one cluster, weights in registers; klm_seq_fma_ll) -- the roofline is the
+        # measured FP32 FMA peak, and what actually bounds them is the hand-over latency of the recurrence
+        fma_peak = _native.measure_fma_peak(local)
+        ticks = chars + depth + 1
+        roofline.update({
+            'bound': 'fp32-fma', 'kernel': 'klm_seq_rg' if info.get('cl_launches', 0) > 0 else 'klm_seq_fma_ll',
+            'peak': fma_peak, 'frac': achieved / fma_peak, 'peak_source': 'measured here (klm_measure_fma_peak: FFMA chains on all SMs)',
+            'grid': info['cl_cluster'] if info.get('cl_launches', 0) > 0 else info['grid'],
+            'latency_floor': {
+                'us_per_char_measured': 1e3 * k_ms / max(chars_per_step // max(docs, 1), 1),
+                'us_per_char_floor': (215 + 250) / 1965.0,
+                'note': 'one stream: every character is one trip of the hidden vector between the SMs that hold the model -- '
+                        'distributed shared memory ~215 clk (B300_MICROARCH.md) + the dependent chain of one LSTM cell (~250 clk '
+                        'of MUFU latency) at %d MHz; the kernel does not touch the FMA roofline (%d FLOP per character)' % (1965, F)},
+        })
+        del ticks
 
     line = base_line(args, value, total_ms / args.steps)
     line.update({

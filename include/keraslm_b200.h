@@ -215,6 +215,10 @@ typedef struct klm_info {
 } klm_info;
 int klm_get_info(klm_model *m, klm_info *out);
 
+/* Measured FP32 FMA throughput of the device in TFLOP/s (a ~2 ms micro-benchmark: independent FFMA chains on every SM):
+ * the roofline denominator of the small-batch kernels (<= 8 streams), which run on the FP32 pipes, not the tensor cores. */
+int klm_measure_fma_peak(int device, double *tflops);
+
 /* Self-test of the tcgen05 / TMEM / bulk-copy building blocks: D[128 x N] = A[128 x K] . B[N x K]^T for
  * fp16 operand images in the kernel's shared-memory layout ([K/8][rows][8] halves); host pointers. */
 int klm_selftest_umma(int device, int32_t N, int32_t K, const uint16_t *A_img, const uint16_t *B_img, float *D);

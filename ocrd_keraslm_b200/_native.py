@@ -115,6 +115,7 @@ SYMBOLS = [
     ('klm_step', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
     ('klm_step_topk', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _I, _P, _P]),
     ('klm_get_info', ctypes.c_int, [_P, ctypes.POINTER(KlmInfo)]),
+    ('klm_measure_fma_peak', ctypes.c_int, [ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
     ('klm_selftest_umma', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
     ('klm_selftest_umma2', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
     ('klm_tc_trace', ctypes.c_int, [_P, _I, _P, _P]),
@@ -169,6 +170,16 @@ def operand_image(mat):
     rows, K = mat.shape
     assert K % 8 == 0
     return np.ascontiguousarray(mat.astype(np.float16).reshape(rows, K // 8, 8).transpose(1, 0, 2)).view(np.uint16)
+
+
+def measure_fma_peak(device=0):
+    """Measured FP32 FMA throughput of the device in TFLOP/s (klm_measure_fma_peak)."""
+    lib = load()
+    v = ctypes.c_double(0)
+    rc = lib.klm_measure_fma_peak(device, ctypes.byref(v))
+    if rc != 0:
+        raise NativeError('libkeraslm_b200 error %d: %s' % (rc, lib.klm_last_error().decode('utf-8', 'replace')))
+    return v.value
 
 
 def selftest_umma(A, B, device=0):

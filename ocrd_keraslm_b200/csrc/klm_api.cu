@@ -595,6 +595,7 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
             pl.n_proj = (int)proj.size();
         }
     }
+    for (size_t i = 0; i < pl.roles.size(); ++i) pl.roles[i].rot = (int)i;
     CK(cudaMalloc(&pl.d_roles, pl.roles.size() * sizeof(KlmTcRole)));
     CK(cudaMemcpy(pl.d_roles, pl.roles.data(), pl.roles.size() * sizeof(KlmTcRole), cudaMemcpyHostToDevice));
     CK(cudaMalloc(&pl.d_wimg, img.size() * sizeof(__half)));
@@ -1735,6 +1736,47 @@ extern "C" int klm_beam_lattice(klm_model *m, int32_t n_hyp, const int32_t *hyp_
         out_first[e + 1] = nout;
     }
     for (int k = 0; k < beam_width; ++k) final_slot[k] = k < (int)b_slot.size() ? (b_own[k] ? b_slot[k] : b_origin[k]) : -1;
+    return KLM_OK;
+}
+
+// Micro-benchmark behind the roofline of the small-batch (FP32 FMA) kernels: 8 independent FFMA chains per thread, 4 CTAs of
+// 256 threads per SM, ~0.5 ms; returns the measured FP32 FMA throughput of the device in TFLOP/s (2 flops per FMA).
+__global__ void klm_fma_peak_kernel(float *out, int iters) {
+    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
+    const float b = 1.0000001f, c = 1e-7f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            a0 = fmaf(a0, b, c); a1 = fmaf(a1, b, c); a2 = fmaf(a2, b, c); a3 = fmaf(a3, b, c);
+            a4 = fmaf(a4, b, c); a5 = fmaf(a5, b, c); a6 = fmaf(a6, b, c); a7 = fmaf(a7, b, c);
+        }
+    }
+    const float r = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (r == 123.456f) out[0] = r;                           // (never true: keeps the chains alive)
+}
+extern "C" int klm_measure_fma_peak(int device, double *tflops) {
+    if (!tflops) return fail(KLM_EINVAL, "klm_measure_fma_peak: NULL argument");
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    float *d = nullptr;
+    CK(cudaMalloc(&d, 4));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    const int grid = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep) {
+        CK(cudaEventRecord(e0, 0));
+        klm_fma_peak_kernel<<<grid, threads>>>(d, iters);
+        CK(cudaEventRecord(e1, 0));
+        CK(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        const double fl = 2.0 * 8 * 16 * (double)iters * threads * grid;
+        if (rep > 0) best = std::max(best, fl / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    *tflops = best;
     return KLM_OK;
 }
 

@@ -174,6 +174,8 @@ struct KlmTcRole {
                        // publication staging of this CTA's slice)
     float scale;       // accumulator -> pre-activation: 1 / (KLM_TC_HSCALE * weight scale of this CTA's matrix), a power of two
     // dataflow kernel (klm_seq_df.cu): who this CTA waits for and who waits for it
+    int rot;           // index of the role in plan order (NOT the block it runs in: roles are placed on blocks by measured SM speed);
+                       // decides the order in which the CTA walks the operand chunks, so results do not depend on the placement
     int idx;           // index of this CTA within its stage (REC: index of its hand-over flag)
     int n_src;         // REC CTAs of the source layer (flags watched by the producer warp)
     int n_readers;     // REC: CTAs of other stages that read this layer's hidden vector (IN l+1 or PROJ)

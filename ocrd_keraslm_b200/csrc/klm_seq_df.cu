@@ -571,7 +571,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
             bulk_out(hx_l + (size_t)(version & (KLM_DF_R - 1)) * hx_slice + (size_t)(role.first_pair / 4) * (128 * 8));
             // everything this CTA hands over went through that one bulk store and it has been performed (wait_group 0): a
             // release has nothing left to order (klm_set_option "tc_pub_release" restores it)
-            if (p.fault && blockIdx.x == 0 && tick == 2) { }                       // (test hook: the watchdog must end the launch)
+            if (p.fault && role.rot == 0 && tick == 2) { }                       // (test hook: the watchdog must end the launch)
             else df_signal(my_flag, epoch + version, p.pub_release);
             if (l > 0) df_st_relaxed(p.sync + KLM_DF_ZRD + l * 64 + role.idx, tick_base + (unsigned)tick + 1u);   // Z of this tick consumed (all threads: bar.sync above)
             if (x.guard) tc::mbar_arrive(x.bar_epid);
@@ -829,7 +829,7 @@ __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *sme
     x.guard = role.kind == KLM_TC_REC ? ((role.guard || p.step_groups > 0 || (p.exp & 2)) ? 1 : 0)
                                       : (((p.exp & 4) || p.step_groups > 0) ? 0 : 1);
     // REC: the chunk with the CTA's own slice goes into ring slot `alias_slot`; the others in rotated order behind / before it
-    x.crot = role.kind == KLM_TC_REC ? role.sigma : (int)(blockIdx.x % (unsigned)x.nch);
+    x.crot = role.kind == KLM_TC_REC ? role.sigma : role.rot % x.nch;
 
     if (warp == 0) {
         if (!df_run_loops<TRACE>(true, p, role, x) && tid == 0) atomicExch(p.err, 90);

@@ -349,7 +349,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
     TcLoopCtx lx;
     lx.ring_a = tc::smem_u32(ring); lx.bar_full = bar_full; lx.bar_empty = bar_empty; lx.bar_tfull = bar_tfull;
     lx.bar_tempty = bar_tempty; lx.bar_go = bar_go; lx.tmem_base = tmem_base; lx.wsm_a = tc::smem_u32(wsm);
-    lx.nticks = nticks; lx.N = N; lx.crot = (int)(blockIdx.x % (unsigned)nchunks); lx.src_layer = role.src_layer; lx.W = W;
+    lx.nticks = nticks; lx.N = N; lx.crot = role.rot % nchunks; lx.src_layer = role.src_layer; lx.W = W;
     lx.G = G; lx.guard = guard ? 1 : 0; lx.bar_epid = bar_epid;
     lx.cbb = (uint32_t)kc * 32u * (uint32_t)NP;            // kc/8 k groups x 2N rows x 16 bytes
     lx.slot_bytes = chunk_bytes + lx.cbb;
@@ -363,7 +363,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
         if (!tc_run_fixed<STREAM, TRACE>(true, p, lx, kc, nchunks, S) && lane == 0) {
             if (STREAM) { atomicExch(p.err, 90); return; }   // the streamed form has compile-time geometries only
             uint32_t st = 0, ph = 0, ring_ofs = 0;
-            const int crot = (int)(blockIdx.x % (unsigned)nchunks);    // spread the CTAs over the chunks
+            const int crot = role.rot % nchunks;                       // spread the CTAs over the chunks
             const uint32_t ring_a = tc::smem_u32(ring);
             bool ok = true;
             for (int tick = 0; tick < nticks && ok; ++tick) {
@@ -401,7 +401,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
             const uint64_t b_base = tc::smem_desc(tc::smem_u32(wsm), lbo_b, 128);
             const uint32_t a_chunk = chunk_bytes >> 4, a_k16 = (2 * lbo_a) >> 4;
             const uint32_t b_chunk = ((uint32_t)(kc / 8) * lbo_b) >> 4, b_k16 = (2 * lbo_b) >> 4;
-            const int crot = (int)(blockIdx.x % (unsigned)nchunks);
+            const int crot = role.rot % nchunks;
             const int nk32 = kc / 32;
             uint32_t st = 0, ph = 0, a_ofs = 0;
             bool ok = true;
@@ -756,7 +756,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                             // everything this CTA hands over in a tick went through that one bulk store, and it has been
                             // performed: a release (a gpu-scope fence in front of the add, ~900 clk on the recurrence:
                             // scripts/ubench/pingpong.cu) has nothing left to order
-                            if (p.fault && blockIdx.x == 0 && tick == 2) { }          // (test hook: the watchdog must end the launch)
+                            if (p.fault && role.rot == 0 && tick == 2) { }          // (test hook: the watchdog must end the launch)
                             else if (p.pub_release) tc::red_release_add(p.barrier, 1u);
                             else tc::red_relaxed_add(p.barrier, 1u);
                             if (TRACE && (p.trace_mode == 0 || p.trace_mode == 4)) tc_trace(p, tick, 7);

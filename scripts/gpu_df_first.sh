@@ -1,3 +1,8 @@
-OUT=gpurun_out/r2s; mkdir -p $OUT
-timeout 300 python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "register_resident or golden or degenerate" > $OUT/pytest_rg.log 2>&1; echo "exit $?" >> $OUT/pytest_rg.log; tail -5 $OUT/pytest_rg.log
-KLM_LL_DEBUG=1 timeout 600 python bench.py --workload cfg1 --steps 1 --warmup 3 --no-cpu > $OUT/bench_cfg1_dbg.json 2> $OUT/bench_cfg1_dbg.err; cut -c1-120 $OUT/bench_cfg1_dbg.json; grep "klm_seq_rg" $OUT/bench_cfg1_dbg.err | tail -7
+OUT=gpurun_out/r2u; mkdir -p $OUT
+for SB in none 128-147; do
+  echo "=== KLM_TC_SLOW_BLOCKS=$SB" >> $OUT/place.txt
+  if [ $SB = none ]; then timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu --chars 30000 2>/dev/null | cut -c1-120 >> $OUT/place.txt
+  else KLM_TC_SLOW_BLOCKS=$SB timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu --chars 30000 2>/dev/null | cut -c1-120 >> $OUT/place.txt; fi
+done
+cat $OUT/place.txt
+KLM_TC_SLOW_BLOCKS=128-147 timeout 300 python scripts/tc_trace.py cfg2 3000 > $OUT/timeline_placed.txt 2>&1; cat $OUT/timeline_placed.txt
