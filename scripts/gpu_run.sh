@@ -4,6 +4,8 @@
 #   smoke      __graft_entry__.smoke()           bench      bench.py (cfg2, default steps) + the reference arm
 #   cfgs       bench lines of cfg1/3/4/5         launches   ncu launch list of a short bench
 #   ncu        ncu --set full of the sequence kernel (one launch)        trace   in-kernel timeline (scripts/tc_trace.py)
+#   drift      16 x 99 999 positions against the fp64 windows (scripts/drift_1e5.py)
+#   relaxed    cfg2 with the round-1 relaxed hand-over signal (KLM_TC_PUB_RELEASE=0; measures what the release costs)
 #   memcheck | synccheck | racecheck   compute-sanitizer over the reduced selection of scripts/sanitize_select.txt (ONE tool per call)
 TAG=$1; shift
 OUT=gpurun_out/$TAG
@@ -25,6 +27,8 @@ for STEP in "$@"; do
               timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file $OUT/launches.csv $SMALL > $OUT/ncu_launches.log 2>&1; tail -3 $OUT/ncu_launches.log ;;
     ncu) timeout 300 $SMALL > $OUT/plain2.log 2>&1 &&
          timeout 900 ncu --set full --clock-control none --import-source on -k regex:klm_seq -s 3 -c 1 -o $OUT/prof $SMALL > $OUT/ncu_full.log 2>&1; tail -3 $OUT/ncu_full.log ;;
+    drift) timeout 900 python scripts/drift_1e5.py > $OUT/drift_1e5.json 2> $OUT/drift_1e5.err; echo "drift exit $?" >> $OUT/drift_1e5.err; cat $OUT/drift_1e5.json | tr -d '\n' | cut -c1-900; echo ;;
+    relaxed) KLM_TC_PUB_RELEASE=0 timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu > $OUT/bench_relaxed.json 2> $OUT/bench_relaxed.err; cat $OUT/bench_relaxed.json ;;
     trace) timeout 600 python scripts/tc_trace.py > $OUT/timeline.txt 2>&1; tail -30 $OUT/timeline.txt ;;
     memcheck|synccheck|racecheck)
          timeout 2400 compute-sanitizer --tool $STEP --error-exitcode 9 --log-file $OUT/sanitizer_$STEP.log python -m pytest $SEL -m gpu -x -q > $OUT/sanitizer_${STEP}_pytest.log 2>&1
