@@ -98,6 +98,19 @@ int klm_state_from_host(klm_model *m, const int32_t *slots, int32_t n, const flo
  * list (rating.py:887-916 compares range(depth) of them); out [n][n_arrays] host floats. */
 int klm_state_l2_distance(klm_model *m, const int32_t *a, const int32_t *b, int32_t n,
                           int32_t n_arrays, float *out);
+/* klm_state_l2_distance that allocates NOTHING (no cudaMalloc / cudaFree, no allocating library
+ * call): for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  It has no counterpart in the reference.
+ * Same arguments, same kernel, same results; the scratch (the
+ * device copies of the two slot lists and the distances) lives in ONE static device array of
+ * KLM_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until exit.
+ * Limit: 256-byte-rounded 8*n + 4*n*n_arrays <= KLM_NOALLOC_SCRATCH_BYTES (e.g. 2048 pairs x 6
+ * arrays); beyond it the call returns KLM_EINVAL and the message names the size.
+ * All calls share the array (and it keeps the last call's contents; the part a call reads back
+ * is cleared first): calls that overlap on one GPU -- two models, two host threads -- race. */
+#define KLM_NOALLOC_SCRATCH_BYTES 65536
+int klm_state_l2_distance_noalloc(klm_model *m, const int32_t *a, const int32_t *b, int32_t n,
+                                  int32_t n_arrays, float *out);
 
 /*
  * Teacher-forced rating of n_streams independent character streams in ONE launch.

@@ -19,6 +19,7 @@ NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', 
 
 KLM_MAX_CTX = 4
 MEM_HOST, MEM_DEVICE = 0, 1
+NOALLOC_SCRATCH_BYTES = 65536      # KLM_NOALLOC_SCRATCH_BYTES (include/keraslm_b200.h)
 
 
 class NativeError(RuntimeError):
@@ -111,6 +112,7 @@ SYMBOLS = [
     ('klm_state_to_host', ctypes.c_int, [_P, _P, _I, _P]),
     ('klm_state_from_host', ctypes.c_int, [_P, _P, _I, _P]),
     ('klm_state_l2_distance', ctypes.c_int, [_P, _P, _P, _I, _I, _P]),
+    ('klm_state_l2_distance_noalloc', ctypes.c_int, [_P, _P, _P, _I, _I, _P]),
     ('klm_rate', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
     ('klm_step', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
     ('klm_step_topk', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _I, _P, _P]),
@@ -358,6 +360,15 @@ class Model(object):
         a, b = _i32(a), _i32(b)
         out = np.empty((len(a), n_arrays), dtype=np.float32)
         self.check(self._lib.klm_state_l2_distance(self._h, _ptr(a), _ptr(b), len(a), n_arrays, _ptr(out)))
+        return out
+
+    def state_l2_distance_noalloc(self, a, b, n_arrays, out=None):
+        """klm_state_l2_distance_noalloc: the same distances through the static device scratch (no device allocation;
+        at most NOALLOC_SCRATCH_BYTES; calls that overlap on one GPU race)."""
+        a, b = _i32(a), _i32(b)
+        if out is None:
+            out = np.empty((len(a), n_arrays), dtype=np.float32)
+        self.check(self._lib.klm_state_l2_distance_noalloc(self._h, _ptr(a), _ptr(b), len(a), n_arrays, _ptr(out)))
         return out
 
     # ---- the path ----

@@ -953,6 +953,60 @@ extern "C" int klm_state_l2_distance(klm_model *m, const int32_t *a, const int32
     return KLM_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// klm_state_l2_distance without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: graph capture, tight serving loops).  Same kernel, the scratch
+// (device copies of the two slot lists + the distances) in a file-scope device array of KLM_NOALLOC_SCRATCH_BYTES
+// that every GPU which loads the library holds until exit.  In host code the array's name is only a stand-in; its
+// device address comes from cudaGetSymbolAddress, once per device, with that device current.
+// ALL calls share the array (and it keeps the last call's contents): calls that overlap on one GPU race.
+static __device__ __align__(256) unsigned char klm_noalloc_scratch[KLM_NOALLOC_SCRATCH_BYTES];
+#define KLM_NOALLOC_MAX_DEVICES 64
+static void *g_noalloc_ptr[KLM_NOALLOC_MAX_DEVICES];          // device address of klm_noalloc_scratch per device, 0 = not asked yet
+
+static int noalloc_scratch(int device, unsigned char **ptr) {
+    if (device < 0 || device >= KLM_NOALLOC_MAX_DEVICES) return fail(KLM_EINVAL, "no-alloc scratch: device %d", device);
+    void *p = __atomic_load_n(&g_noalloc_ptr[device], __ATOMIC_ACQUIRE);
+    if (!p) {                                                 // set-up, once per device (the device is current: caller)
+        const cudaError_t e = cudaGetSymbolAddress(&p, klm_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(KLM_ECUDA, "cudaGetSymbolAddress(klm_noalloc_scratch) on device %d: %s", device, cudaGetErrorString(e));
+        __atomic_store_n(&g_noalloc_ptr[device], p, __ATOMIC_RELEASE);   // (two threads racing here store the same address)
+    }
+    *ptr = static_cast<unsigned char *>(p);
+    return KLM_OK;
+}
+
+extern "C" int klm_state_l2_distance_noalloc(klm_model *m, const int32_t *a, const int32_t *b, int32_t n, int32_t n_arrays,
+                                             float *out) {
+    if (!m || !a || !b || !out) return fail(KLM_EINVAL, "klm_state_l2_distance_noalloc: NULL argument");
+    if (n <= 0) return KLM_OK;
+    if (n_arrays < 1 || n_arrays > 2 * m->D) return fail(KLM_EINVAL, "klm_state_l2_distance_noalloc: n_arrays %d", n_arrays);
+    // layout of the scratch: [a: n ints][b: n ints] padded to 256 bytes, then [n][n_arrays] floats
+    const size_t slots_bytes = (((size_t)n * 8) + 255) & ~(size_t)255;
+    const size_t need = slots_bytes + (size_t)n * n_arrays * 4;
+    if (need > (size_t)KLM_NOALLOC_SCRATCH_BYTES)
+        return fail(KLM_EINVAL, "klm_state_l2_distance_noalloc: %d pairs x %d arrays need %zu bytes of scratch, the static "
+                    "array has %d (use klm_state_l2_distance)", n, n_arrays, need, KLM_NOALLOC_SCRATCH_BYTES);
+    CK(cudaSetDevice(m->device));
+    int rc = check_slots(m, a, n, false, "klm_state_l2_distance_noalloc"); if (rc) return rc;
+    rc = check_slots(m, b, n, false, "klm_state_l2_distance_noalloc"); if (rc) return rc;
+    unsigned char *scratch = nullptr;
+    rc = noalloc_scratch(m->device, &scratch); if (rc) return rc;
+    int *da = reinterpret_cast<int *>(scratch);
+    float *dout = reinterpret_cast<float *>(scratch + slots_bytes);
+    CK(cudaMemcpyAsync(da, a, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    CK(cudaMemcpyAsync(da + n, b, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    // the kernel writes every distance it is asked for; the clear keeps a short launch from handing out the last call's
+    CK(cudaMemsetAsync(dout, 0, (size_t)n * n_arrays * 4, m->stream));
+    klm_state_dist<<<n * n_arrays, 128, 0, m->stream>>>(m->state, da, da + n, n, n_arrays, m->W, m->D * 2 * m->W, dout);
+    CK(cudaGetLastError());
+    m->launches++;
+    CK(cudaMemcpyAsync(out, dout, (size_t)n * n_arrays * 4, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    return KLM_OK;
+}
+
 // Fields of the dataflow kernel (klm_seq_df.cu) that do not depend on the batch.
 static void tc_df_params(klm_model *m, KlmTcParams &q) {
     KlmTcPlan &tp = m->tc;
