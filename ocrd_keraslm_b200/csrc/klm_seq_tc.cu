@@ -238,10 +238,12 @@ static __device__ __forceinline__ TcRound tc_round(int NP, int r, int half, int 
 // NR = epilogue rounds (pairs per CTA <= NR * KLM_TC1_MAX_PAIRS), STREAM = streamed-weights form.
 // TRACE = timeline instrumentation compiled in (klm_tc_trace armed): the production instantiations carry none of it --
 // a handful of run-time-disabled checks in the epilogue cost the resident kernel 3 % on cfg2.
-template <int NR, bool STREAM, bool TRACE>
-static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigned char *smem) {
-    const KlmTcRole role = p.roles[blockIdx.x];
-    if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }
+// OWN = pairs of units one epilogue thread finishes per round (2 covers slices of <= 8 pairs), REC = the CTA is a
+// recurrence stage.  Compile-time so that a REC CTA carries no IN / PROJ state and vice versa: the kernel runs at its
+// register limit (10 warps: 168 registers), and a spilled value costs an L2 round trip in the tick loop -- the acquire
+// polls of the grid barrier invalidate L1 every time (12 spilled floats were 5 % on cfg2).
+template <int NR, bool STREAM, bool TRACE, int OWN, bool REC>
+static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const KlmTcRole &role, unsigned char *smem) {
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int W = p.W, S = role.stages, kc = role.kc;
@@ -295,7 +297,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
 #pragma unroll
     for (int r = 0; r < NR; ++r) rd[r] = tc_round(NP, r, half, ch);
     const bool is_epi = warp >= 2;
-    const bool is_rec = role.kind == KLM_TC_REC;
+    constexpr bool is_rec = REC;
     const int l = role.layer;
     // wavefront stage of this CTA (see KlmTcParams::skew)
     const int sigma = is_rec ? p.skew * l : role.kind == KLM_TC_IN ? p.skew * l - (p.skew - 1) : p.skew * p.D - (p.skew - 1);
@@ -311,7 +313,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
     // critical path and plain coalesced stores are as good or better (14.37 M against 14.23 M)
     const bool zpub = !is_rec && role.pub == 2 && (!early || p.zpub_early);
 
-    float c_reg[NR][KLM_TC_OWN][2], h_reg[NR][KLM_TC_OWN][2];
+    float c_reg[NR][OWN][2], h_reg[NR][OWN][2];
     long long o0 = 0;
     int len = 0;
     if (is_epi) {
@@ -319,7 +321,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
 #pragma unroll
         for (int r = 0; r < NR; ++r)
 #pragma unroll
-            for (int i = 0; i < KLM_TC_OWN; ++i) {
+            for (int i = 0; i < OWN; ++i) {
                 c_reg[r][i][0] = c_reg[r][i][1] = h_reg[r][i][0] = h_reg[r][i][1] = 0.f;
                 if (is_rec && i < rd[r].nown) {
                     const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
@@ -440,28 +442,29 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
         // (the same few lines each time: L1 hits)
         constexpr bool KEEP = NR == 1;
         constexpr int NRK = KEEP ? NR : 1;
-        float4 bias4[NRK][KLM_TC_OWN][2];
+        // tick-invariant addends, ONE array for both uses (registers are what this kernel is short of): the bias of an IN
+        // CTA, the context part sum_k Q_k[z_k][u] of layer 1's input contraction of a REC CTA of layer 1
+        float4 inv4[NRK][OWN][2];
+#pragma unroll
+        for (int r = 0; r < NRK; ++r)
+#pragma unroll
+            for (int i = 0; i < OWN; ++i) inv4[r][i][0] = inv4[r][i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (KEEP && role.kind == KLM_TC_IN) {
 #pragma unroll
             for (int r = 0; r < NRK; ++r)
 #pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
+                for (int i = 0; i < OWN; ++i)
                     if (i < rd[r].nown) {
                         const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
-                        bias4[r][i][0] = __ldg(p.bias[l] + u); bias4[r][i][1] = __ldg(p.bias[l] + u + 1);
+                        inv4[r][i][0] = __ldg(p.bias[l] + u); inv4[r][i][1] = __ldg(p.bias[l] + u + 1);
                     }
         }
         // REC layer 1: first character index, number of real (non-padding) positions, and the context part of the
         // input contraction sum_k Q_k[z_k][u], which does not change over the ticks
         int x_next = 0, nreal_s = 0x7fffffff;
-        float4 qsum[NRK][KLM_TC_OWN][2];
         int zk[KLM_MAX_CTX];
 #pragma unroll
         for (int k = 0; k < KLM_MAX_CTX; ++k) zk[k] = 0;
-#pragma unroll
-        for (int r = 0; r < NRK; ++r)
-#pragma unroll
-            for (int i = 0; i < KLM_TC_OWN; ++i) qsum[r][i][0] = qsum[r][i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (is_rec && l == 0 && s < p.B) {
             if (len > 0) x_next = __ldg(p.chars + o0);
             if (p.n_real) nreal_s = __ldg(p.n_real + s);
@@ -474,13 +477,13 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
 #pragma unroll
                     for (int r = 0; r < (KEEP ? NRK : 0); ++r)
 #pragma unroll
-                        for (int i = 0; i < KLM_TC_OWN; ++i)
+                        for (int i = 0; i < OWN; ++i)
                             if (i < rd[r].nown) {
                                 const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
 #pragma unroll
                                 for (int e = 0; e < 2; ++e) {
                                     const float4 b = __ldg(p.Q[k] + (size_t)z * W + u + e);
-                                    qsum[r][i][e].x += b.x; qsum[r][i][e].y += b.y; qsum[r][i][e].z += b.z; qsum[r][i][e].w += b.w;
+                                    inv4[r][i][e].x += b.x; inv4[r][i][e].y += b.y; inv4[r][i][e].z += b.z; inv4[r][i][e].w += b.w;
                                 }
                             }
                 }
@@ -505,23 +508,23 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 real = t < nreal_s;
             }
             // ---- addends of one round (fetched while the MMAs run / while the previous round is finished) ----
-            auto load_add = [&](const int r, float4 (&add4)[KLM_TC_OWN][2]) {
+            auto load_add = [&](const int r, float4 (&add4)[OWN][2]) {
 #pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i) add4[i][0] = add4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int i = 0; i < OWN; ++i) add4[i][0] = add4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (!(is_rec && active)) return;
                 const int pr0 = role.first_pair + rd[r].pb + rd[r].own_first;
                 if (l == 0) {
                     // fused char + context embedding gather / concat / input contraction (rating.py:103-115,125);
                     // the context part is tick-invariant (qsum)
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                    for (int i = 0; i < OWN; ++i)
                         if (i < rd[r].nown) {
                             const int u = 2 * (pr0 + i);
 #pragma unroll
                             for (int e = 0; e < 2; ++e) {
                                 float4 a = __ldg(p.P + (size_t)x * W + u + e);
                                 if (real && KEEP) {
-                                    const float4 b = qsum[KEEP ? r : 0][i][e];
+                                    const float4 b = inv4[KEEP ? r : 0][i][e];
                                     a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
                                 } else {                     // padding position: context 0 (:1141-1143)
 #pragma unroll
@@ -539,14 +542,14 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     // contiguous bytes per unit, on the IN side (stores) as well as here
                     const float4 *zrow = reinterpret_cast<const float4 *>(p.Z) + (size_t)(l * nz + zs_in) * W * 64 + s;
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                    for (int i = 0; i < OWN; ++i)
                         if (i < rd[r].nown) {
                             const int u = 2 * (pr0 + i);
                             add4[i][0] = __ldcg(zrow + (size_t)u * 64); add4[i][1] = __ldcg(zrow + (size_t)(u + 1) * 64);
                         }
                 }
             };
-            float4 add4[KLM_TC_OWN][2];
+            float4 add4[OWN][2];
             load_add(0, add4);
 
             // ---- accumulators ----
@@ -566,14 +569,58 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
             for (int r = 0; r < NR; ++r) {
                 const TcRound R = rd[r];
                 if (r > 0) tc_bar_epi();                      // the hand-over buffer is reused: round r-1 has been read
-                float acc[KLM_TC_OWN][8];
+                float acc[OWN][8];
 #pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
+                for (int i = 0; i < OWN; ++i)
 #pragma unroll
                     for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+                if constexpr (OWN <= 2) {
+                // The TMEM loads of a round go out in two batches with ONE wait each (a wait per pair serialised four
+                // TMEM round trips): first the pairs that the other half finishes -- this row's part of them travels
+                // through shared memory (both directions at once) --, then the own pairs (hi rows: hi.hi + hi.lo columns;
+                // lo rows: lo.hi columns).  Nothing may touch the destination registers between a load and its wait.
+                {
+                    float v[OWN][8], b[OWN][8];
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i)
+                        if (i < R.nsend) {
+                            const int pr = R.pb + R.send_first + i;
+                            tc::tmem_ld8(trow + 8 * pr, v[i]);
+                            if (half == 0) tc::tmem_ld8(trow + N + 8 * pr, b[i]);
+                        }
+                    tc::tmem_ld_wait();
+                    float *xs = xchg + (half ? 0 : KLM_TC1_MAX_PAIRS / 2 * 8 * 64);
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i)
+                        if (i < R.nsend) {
+                            const int xi = R.send_first + i - R.oth_first;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) xs[(xi * 8 + j) * 64 + s] = half == 0 ? v[i][j] + b[i][j] : v[i][j];
+                        }
+                }
+                {
+                    float b[OWN][8];
+#pragma unroll
+                    for (int i = 0; i < OWN; ++i)
+                        if (i < R.nown) {
+                            const int pr = R.pb + R.own_first + i;
+                            tc::tmem_ld8(trow + 8 * pr, acc[i]);
+                            if (half == 0) tc::tmem_ld8(trow + N + 8 * pr, b[i]);
+                        }
+                    tc::tmem_ld_wait();
+                    if (half == 0) {
+#pragma unroll
+                        for (int i = 0; i < OWN; ++i)
+                            if (i < R.nown) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) acc[i][j] += b[i][j];
+                            }
+                    }
+                }
+                } else {
                 // own pairs: this row's part (hi rows: hi.hi + hi.lo columns; lo rows: lo.hi columns)
 #pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
+                for (int i = 0; i < OWN; ++i)
                     if (i < R.nown) {
                         const int pr = R.pb + R.own_first + i;
                         tc::tmem_ld8(trow + 8 * pr, acc[i]);
@@ -591,7 +638,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 {
                     float *xs = xchg + (half ? 0 : KLM_TC1_MAX_PAIRS / 2 * 8 * 64);
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                    for (int i = 0; i < OWN; ++i)
                         if (i < R.nsend) {
                             const int pr = R.pb + R.send_first + i, xi = R.send_first + i - R.oth_first;
                             float v[8];
@@ -609,6 +656,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                             for (int j = 0; j < 8; ++j) xs[(xi * 8 + j) * 64 + s] = v[j];
                         }
                 }
+                }
                 if (r == NR - 1) {
                     tc::tc_fence_before();
                     tc::mbar_arrive(bar_tempty);                  // this thread is done reading TMEM
@@ -618,7 +666,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 {
                     const float *xr = xchg + (half ? KLM_TC1_MAX_PAIRS / 2 * 8 * 64 : 0);
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                    for (int i = 0; i < OWN; ++i)
                         if (i < R.nown) {
                             const int xi = R.own_first + i - R.my_first;
 #pragma unroll
@@ -630,7 +678,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 }
                 if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 2 + 3 * r);      // ... hand-over read
                 // addends of the next round: in flight while this round is finished
-                float4 add_nxt[KLM_TC_OWN][2];
+                float4 add_nxt[OWN][2];
                 if (r + 1 < NR) load_add(r + 1, add_nxt);
 
                 // ---- finish the round ----
@@ -638,9 +686,9 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 const int pr0 = role.first_pair + R.pb + R.own_first;        // first own pair of the round (layer-wide index)
                 if (is_rec) {
                     // LSTM cell for all owned units, staged so that the MUFU chains of different units overlap
-                    float e1[KLM_TC_OWN][2], e2[KLM_TC_OWN][2], e3[KLM_TC_OWN][2], e4[KLM_TC_OWN][2], ag[KLM_TC_OWN][2];
+                    float e1[OWN][2], e2[OWN][2], e3[OWN][2], e4[OWN][2], ag[OWN][2];
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                    for (int i = 0; i < OWN; ++i)
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             if (i >= R.nown) continue;             // (warp-uniform)
@@ -652,7 +700,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                             e4[i][e] = tc_exp(-tc_clamp(acc[i][4 * e + 3] + a.w));
                         }
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                    for (int i = 0; i < OWN; ++i)
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             if (i >= R.nown) continue;
@@ -664,7 +712,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                             e2[i][e] = tc_exp(-2.f * tc_clamp(e1[i][e]));
                         }
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                    for (int i = 0; i < OWN; ++i)
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             if (i >= R.nown) continue;
@@ -677,7 +725,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     if (role.pub) {
                         // slice = whole groups of 8 units: stage [group][128 rows][8]; whole 2 KB blocks are written below
 #pragma unroll
-                        for (int i = 0; i < KLM_TC_OWN; ++i)
+                        for (int i = 0; i < OWN; ++i)
                             if (i < R.nown) {
                                 const int ul = 2 * (R.pb + R.own_first + i);
                                 __half hi0, lo0, hi1, lo1;
@@ -689,7 +737,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     } else {
                         __half *hx_out = p.hx + ((size_t)(l * 2 + par_out) * (W / 8)) * (128 * 8);
 #pragma unroll
-                        for (int i = 0; i < KLM_TC_OWN; ++i)
+                        for (int i = 0; i < OWN; ++i)
                             if (i < R.nown) {
                                 const int u = 2 * (pr0 + i);
                                 __half hi0, lo0, hi1, lo1;
@@ -706,12 +754,12 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     float4 *zrow = zpub ? zstage - (ptrdiff_t)(2 * role.first_pair) * 64 + s
                                                  : reinterpret_cast<float4 *>(p.Z) + (size_t)(l * nz + zs_out) * W * 64 + s;
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                    for (int i = 0; i < OWN; ++i)
                         if (i < R.nown) {
                             const int u = 2 * (pr0 + i);
 #pragma unroll
                             for (int e = 0; e < 2; ++e) {
-                                const float4 b = KEEP ? bias4[KEEP ? r : 0][i][e] : __ldg(p.bias[l] + u + e);
+                                const float4 b = KEEP ? inv4[KEEP ? r : 0][i][e] : __ldg(p.bias[l] + u + e);
                                 const float4 v = make_float4(acc[i][4 * e] + b.x, acc[i][4 * e + 1] + b.y,
                                                              acc[i][4 * e + 2] + b.z, acc[i][4 * e + 3] + b.w);
                                 if (zpub) zrow[(size_t)(u + e) * 64] = v;
@@ -723,7 +771,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                     float4 *lrow = zpub ? zstage - (ptrdiff_t)(2 * role.first_pair) * 64 + s
                                                  : reinterpret_cast<float4 *>(p.logits) + (size_t)zs_out * (p.Vp / 4) * 64 + s;
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i)
+                    for (int i = 0; i < OWN; ++i)
                         if (i < R.nown) {
                             const int g8 = pr0 + i;
                             const float4 v0 = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
@@ -735,7 +783,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
                 if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 3 + 3 * r);      // ... round finished
                 if (r + 1 < NR) {
 #pragma unroll
-                    for (int i = 0; i < KLM_TC_OWN; ++i) { add4[i][0] = add_nxt[i][0]; add4[i][1] = add_nxt[i][1]; }
+                    for (int i = 0; i < OWN; ++i) { add4[i][0] = add_nxt[i][0]; add4[i][1] = add_nxt[i][1]; }
                 }
             }
 
@@ -808,7 +856,7 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
 #pragma unroll
             for (int r = 0; r < NR; ++r)
 #pragma unroll
-                for (int i = 0; i < KLM_TC_OWN; ++i)
+                for (int i = 0; i < OWN; ++i)
                     if (i < rd[r].nown) {
                         const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
                         st[u] = h_reg[r][i][0]; st[u + 1] = h_reg[r][i][1];
@@ -822,6 +870,18 @@ static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigne
     if (warp == 0) {
         __syncwarp();
         tc::tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+template <int NR, bool STREAM, bool TRACE>
+static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigned char *smem) {
+    const KlmTcRole role = p.roles[blockIdx.x];
+    if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }
+    if (role.kind == KLM_TC_REC) {
+        if (NR == 1 && role.npairs <= 8) tc_seq_role<NR, STREAM, TRACE, 2, true>(p, role, smem);
+        else tc_seq_role<NR, STREAM, TRACE, KLM_TC_OWN, true>(p, role, smem);
+    } else {
+        tc_seq_role<NR, STREAM, TRACE, KLM_TC_OWN, false>(p, role, smem);
     }
 }
 

@@ -1,5 +1,5 @@
 """Race hunt for klm_seq_df: repeat launches on the same input, count positions that differ from the grid-barrier kernel
-(tolerance 2e-5) under combinations of the memory-ordering switches."""
+(tolerance 1e-4: two fp32 evaluation orders) under combinations of the memory-ordering switches."""
 import os, sys, logging, itertools
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
@@ -7,7 +7,11 @@ from ocrd_keraslm_b200 import synth
 from ocrd_keraslm_b200.lib import Rater
 log = logging.getLogger('x'); log.setLevel(logging.CRITICAL)
 
-def run(width, depth, n, T, opts, reps=6):
+TOL = 1e-4
+REPS = int(os.environ.get('DF_RACE_REPS', '6'))
+
+def run(width, depth, n, T, opts, reps=None):
+    reps = reps or REPS
     wd = synth.weights(5 + width, width=width, depth=depth, voc_size=256, style='trained')
     r = Rater.from_weights(wd, synth.vocabulary(), 64, logger=log)
     nat = r._native
@@ -28,16 +32,16 @@ def run(width, depth, n, T, opts, reps=6):
     for _ in range(reps):
         o = once()
         d = np.abs(o.astype(np.float64) - ref)
-        bad.append(int((d > 2e-5).sum()) + int(np.isnan(o).sum()))
+        bad.append(int((d > TOL).sum()) + int(np.isnan(o).sum()))
         if first is None: first = o
     # where is the first bad position (tick) of the last run?
-    d = np.abs(o.astype(np.float64) - ref) > 2e-5
+    d = np.abs(o.astype(np.float64) - ref) > TOL
     t_first = [int(np.argmax(d[offsets[s]:offsets[s+1]])) if d[offsets[s]:offsets[s+1]].any() else -1 for s in range(n)]
     tf = [t for t in t_first if t >= 0]
     print('W%d D%d n%d T%d %s: bad positions per run %s of %d; first bad tick min %s, streams hit %d' % (
         width, depth, n, T, opts, bad, len(chars), min(tf) if tf else None, len(tf)), flush=True)
 
-cases = [(512, 3, 64, 400), (128, 2, 37, 400), (256, 3, 64, 300)]
+cases = [(512, 3, 64, int(os.environ.get('DF_RACE_T', '400'))), (128, 2, 37, 400), (256, 3, 64, 300)]
 modes = [{}] + [dict(kv.split('=') for kv in arg.split(',')) for arg in sys.argv[1:]]
 for w, d, n, T in cases:
     for opts in modes:

@@ -1,8 +1,18 @@
-OUT=gpurun_out/r2u; mkdir -p $OUT
-for SB in none 128-147; do
-  echo "=== KLM_TC_SLOW_BLOCKS=$SB" >> $OUT/place.txt
-  if [ $SB = none ]; then timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu --chars 30000 2>/dev/null | cut -c1-120 >> $OUT/place.txt
-  else KLM_TC_SLOW_BLOCKS=$SB timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu --chars 30000 2>/dev/null | cut -c1-120 >> $OUT/place.txt; fi
+#!/bin/bash
+# scratch: cfg2 under combinations of environment switches (one bench line each)
+OUT=gpurun_out/$1; shift
+mkdir -p $OUT
+B="python bench.py --steps 2 --warmup 3 --no-cpu"
+i=0
+for V in "$@"; do
+  i=$((i+1))
+  env $V timeout 300 $B > $OUT/v$i.json 2> $OUT/v$i.err
+  python - "$V" $OUT/v$i.json <<'PY'
+import json,sys
+try:
+    j=json.loads(open(sys.argv[2]).read().strip().splitlines()[-1])
+    print('%-60s %.3f M chars/s  e2e %.3f  ms %.1f  checksum %.3f' % (sys.argv[1], j['value']/1e6, j['e2e']['value']/1e6, j['ms_per_step'], j['checksum_logp']))
+except Exception as e:
+    print(sys.argv[1], 'FAILED', e)
+PY
 done
-cat $OUT/place.txt
-KLM_TC_SLOW_BLOCKS=128-147 timeout 300 python scripts/tc_trace.py cfg2 3000 > $OUT/timeline_placed.txt 2>&1; cat $OUT/timeline_placed.txt
