@@ -215,14 +215,15 @@ static __device__ __forceinline__ bool tc_run_fixed(bool producer, const KlmTcPa
     return false;
 }
 
-// One epilogue round = up to KLM_TC1_MAX_PAIRS pairs of the CTA's slice.  The pairs of a round are split between the
-// hi-row and the lo-row threads, and between the two warps that share a TMEM lane quarter; all indices below are
-// relative to the round's first pair `pb`.
+// One epilogue round = up to RP = 4 * OWN pairs of the CTA's slice.  The pairs of a round are split between the hi-row
+// and the lo-row threads, and between the two warps that share a TMEM lane quarter; all indices below are relative
+// to the round's first pair `pb`.  (Recomputed where it is needed: an array of these per thread cost 7 registers a round.)
 struct TcRound { int pb, my_first, oth_first, own_first, nown, send_first, nsend; };
+template <int RP>
 static __device__ __forceinline__ TcRound tc_round(int NP, int r, int half, int ch) {
     TcRound o;
-    o.pb = r * KLM_TC1_MAX_PAIRS;
-    const int npr = min(max(NP - o.pb, 0), KLM_TC1_MAX_PAIRS);
+    o.pb = r * RP;
+    const int npr = min(max(NP - o.pb, 0), RP);
     const int Ph = (npr + 1) / 2;                    // pairs [0,Ph) are finished by hi-row threads, the rest by lo-row threads
     const int my_n = half ? npr - Ph : Ph, oth_n = half ? Ph : npr - Ph;
     o.my_first = half ? Ph : 0;
@@ -235,7 +236,7 @@ static __device__ __forceinline__ TcRound tc_round(int NP, int r, int half, int 
 }
 
 // ---------------------------------------------------------------------------------------------
-// NR = epilogue rounds (pairs per CTA <= NR * KLM_TC1_MAX_PAIRS), STREAM = streamed-weights form.
+// NR = epilogue rounds (pairs per CTA <= NR * 4 * OWN), STREAM = streamed-weights form.
 // TRACE = timeline instrumentation compiled in (klm_tc_trace armed): the production instantiations carry none of it --
 // a handful of run-time-disabled checks in the epilogue cost the resident kernel 3 % on cfg2.
 // OWN = pairs of units one epilogue thread finishes per round (2 covers slices of <= 8 pairs), REC = the CTA is a
@@ -293,9 +294,9 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
     const int row = 32 * q + lane;                   // accumulator row: 0..63 hi part, 64..127 lo part
     const int half = row >> 6, s = row & 63;
     const int ch = (warp - 2) >> 2;                  // two warps share a lane quarter and split its pairs
-    TcRound rd[NR];
-#pragma unroll
-    for (int r = 0; r < NR; ++r) rd[r] = tc_round(NP, r, half, ch);
+    constexpr int RP = 4 * OWN;                      // pairs per epilogue round
+    const TcRound rd0 = tc_round<RP>(NP, 0, half, ch);
+    auto rd = [&](const int r) { return r == 0 ? rd0 : tc_round<RP>(NP, r, half, ch); };      // (later rounds: recomputed)
     const bool is_epi = warp >= 2;
     constexpr bool is_rec = REC;
     const int l = role.layer;
@@ -323,8 +324,8 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
 #pragma unroll
             for (int i = 0; i < OWN; ++i) {
                 c_reg[r][i][0] = c_reg[r][i][1] = h_reg[r][i][0] = h_reg[r][i][1] = 0.f;
-                if (is_rec && i < rd[r].nown) {
-                    const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
+                if (is_rec && i < rd(r).nown) {
+                    const int u = 2 * (role.first_pair + rd(r).pb + rd(r).own_first + i);
                     if (s < p.B) {
                         const int slot = p.slots_in[s];
                         if (slot >= 0) {
@@ -454,8 +455,8 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
             for (int r = 0; r < NRK; ++r)
 #pragma unroll
                 for (int i = 0; i < OWN; ++i)
-                    if (i < rd[r].nown) {
-                        const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
+                    if (i < rd(r).nown) {
+                        const int u = 2 * (role.first_pair + rd(r).pb + rd(r).own_first + i);
                         inv4[r][i][0] = __ldg(p.bias[l] + u); inv4[r][i][1] = __ldg(p.bias[l] + u + 1);
                     }
         }
@@ -478,8 +479,8 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
                     for (int r = 0; r < (KEEP ? NRK : 0); ++r)
 #pragma unroll
                         for (int i = 0; i < OWN; ++i)
-                            if (i < rd[r].nown) {
-                                const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
+                            if (i < rd(r).nown) {
+                                const int u = 2 * (role.first_pair + rd(r).pb + rd(r).own_first + i);
 #pragma unroll
                                 for (int e = 0; e < 2; ++e) {
                                     const float4 b = __ldg(p.Q[k] + (size_t)z * W + u + e);
@@ -512,13 +513,13 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
 #pragma unroll
                 for (int i = 0; i < OWN; ++i) add4[i][0] = add4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (!(is_rec && active)) return;
-                const int pr0 = role.first_pair + rd[r].pb + rd[r].own_first;
+                const int pr0 = role.first_pair + rd(r).pb + rd(r).own_first;
                 if (l == 0) {
                     // fused char + context embedding gather / concat / input contraction (rating.py:103-115,125);
                     // the context part is tick-invariant (qsum)
 #pragma unroll
                     for (int i = 0; i < OWN; ++i)
-                        if (i < rd[r].nown) {
+                        if (i < rd(r).nown) {
                             const int u = 2 * (pr0 + i);
 #pragma unroll
                             for (int e = 0; e < 2; ++e) {
@@ -543,7 +544,7 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
                     const float4 *zrow = reinterpret_cast<const float4 *>(p.Z) + (size_t)(l * nz + zs_in) * W * 64 + s;
 #pragma unroll
                     for (int i = 0; i < OWN; ++i)
-                        if (i < rd[r].nown) {
+                        if (i < rd(r).nown) {
                             const int u = 2 * (pr0 + i);
                             add4[i][0] = __ldcg(zrow + (size_t)u * 64); add4[i][1] = __ldcg(zrow + (size_t)(u + 1) * 64);
                         }
@@ -567,14 +568,15 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
             tc::tc_fence_after();
 #pragma unroll
             for (int r = 0; r < NR; ++r) {
-                const TcRound R = rd[r];
+                const TcRound R = rd(r);
+                const bool last_round = r == NR - 1 || (r + 1) * RP >= NP;      // (CTA-uniform: slices shorter than NR rounds)
                 if (r > 0) tc_bar_epi();                      // the hand-over buffer is reused: round r-1 has been read
                 float acc[OWN][8];
 #pragma unroll
                 for (int i = 0; i < OWN; ++i)
 #pragma unroll
                     for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-                if constexpr (OWN <= 2) {
+                if constexpr (OWN <= 2 && !STREAM) {
                 // The TMEM loads of a round go out in two batches with ONE wait each (a wait per pair serialised four
                 // TMEM round trips): first the pairs that the other half finishes -- this row's part of them travels
                 // through shared memory (both directions at once) --, then the own pairs (hi rows: hi.hi + hi.lo columns;
@@ -657,7 +659,7 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
                         }
                 }
                 }
-                if (r == NR - 1) {
+                if (last_round) {
                     tc::tc_fence_before();
                     tc::mbar_arrive(bar_tempty);                  // this thread is done reading TMEM
                 }
@@ -679,10 +681,10 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
                 if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 2 + 3 * r);      // ... hand-over read
                 // addends of the next round: in flight while this round is finished
                 float4 add_nxt[OWN][2];
-                if (r + 1 < NR) load_add(r + 1, add_nxt);
+                if (r + 1 < NR && !last_round) load_add(r + 1, add_nxt);
 
                 // ---- finish the round ----
-                if (TRACE && r == NR - 1 && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 5);
+                if (TRACE && last_round && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 5);
                 const int pr0 = role.first_pair + R.pb + R.own_first;        // first own pair of the round (layer-wide index)
                 if (is_rec) {
                     // LSTM cell for all owned units, staged so that the MUFU chains of different units overlap
@@ -781,6 +783,7 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
                         }
                 }
                 if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 3 + 3 * r);      // ... round finished
+                if (last_round) break;
                 if (r + 1 < NR) {
 #pragma unroll
                     for (int i = 0; i < OWN; ++i) { add4[i][0] = add_nxt[i][0]; add4[i][1] = add_nxt[i][1]; }
@@ -857,8 +860,8 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
             for (int r = 0; r < NR; ++r)
 #pragma unroll
                 for (int i = 0; i < OWN; ++i)
-                    if (i < rd[r].nown) {
-                        const int u = 2 * (role.first_pair + rd[r].pb + rd[r].own_first + i);
+                    if (i < rd(r).nown) {
+                        const int u = 2 * (role.first_pair + rd(r).pb + rd(r).own_first + i);
                         st[u] = h_reg[r][i][0]; st[u + 1] = h_reg[r][i][1];
                         st[W + u] = c_reg[r][i][0]; st[W + u + 1] = c_reg[r][i][1];
                     }
@@ -873,35 +876,39 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
     }
 }
 
-template <int NR, bool STREAM, bool TRACE>
+template <bool STREAM, bool TRACE>
 static __device__ __forceinline__ void tc_seq_body(const KlmTcParams &p, unsigned char *smem) {
     const KlmTcRole role = p.roles[blockIdx.x];
     if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }
-    if (role.kind == KLM_TC_REC) {
-        if (NR == 1 && role.npairs <= 8) tc_seq_role<NR, STREAM, TRACE, 2, true>(p, role, smem);
-        else tc_seq_role<NR, STREAM, TRACE, KLM_TC_OWN, true>(p, role, smem);
+    if (STREAM) {
+        // streamed-weights form: slices of up to 24 pairs in up to three rounds of 8 (2 pairs per thread and round)
+        if (role.kind == KLM_TC_REC) tc_seq_role<3, STREAM, TRACE, 2, true>(p, role, smem);
+        else tc_seq_role<3, STREAM, TRACE, 2, false>(p, role, smem);
+    } else if (role.kind == KLM_TC_REC) {
+        if (role.npairs <= 8) tc_seq_role<1, STREAM, TRACE, 2, true>(p, role, smem);
+        else tc_seq_role<1, STREAM, TRACE, KLM_TC_OWN, true>(p, role, smem);
     } else {
-        tc_seq_role<NR, STREAM, TRACE, KLM_TC_OWN, false>(p, role, smem);
+        tc_seq_role<1, STREAM, TRACE, KLM_TC_OWN, false>(p, role, smem);
     }
 }
 
 __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    tc_seq_body<1, false, false>(p, smem);
+    tc_seq_body<false, false>(p, smem);
 }
 __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tc_traced(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    tc_seq_body<1, false, true>(p, smem);
+    tc_seq_body<false, true>(p, smem);
 }
 
 // Streamed-weights form: the B images stay in global memory (L2) and travel through the ring with the A chunks.
 __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tcs(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    tc_seq_body<2, true, false>(p, smem);
+    tc_seq_body<true, false>(p, smem);
 }
 __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tcs_traced(const __grid_constant__ KlmTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    tc_seq_body<2, true, true>(p, smem);
+    tc_seq_body<true, true>(p, smem);
 }
 
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream) {

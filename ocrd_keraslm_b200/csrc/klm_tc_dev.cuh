@@ -42,7 +42,7 @@ __device__ __forceinline__ bool tc_wait_mbar(uint32_t bar, uint32_t parity, cons
 __device__ __forceinline__ void tc_trace(const KlmTcParams &p, int tick, int ev) {
     if (p.trace) {
         const int k = tick - p.trace_t0;
-        if (k >= 0 && k < KLM_TC_TRACE_TICKS)
+        if (k >= 0 && k < KLM_TC_TRACE_TICKS && ev < 8)
         {
             unsigned long long now;
             if (p.trace_mode == 5) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));     // ns, comparable across SMs
