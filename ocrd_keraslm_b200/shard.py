@@ -15,14 +15,16 @@ def partition(lengths, world_size):
     Returns a list of ``world_size`` index lists; deterministic (ties broken by index), so every
     rank computes the same partition without communicating.
     """
+    import heapq
     lengths = np.asarray(lengths, dtype=np.int64)
-    order = sorted(range(len(lengths)), key=lambda i: (-int(lengths[i]), i))
-    loads = [0] * world_size
+    order = np.lexsort((np.arange(len(lengths)), -lengths))       # longest first, ties by index
+    heap = [(0, r) for r in range(world_size)]                    # (load, rank): least loaded first, ties by rank
     parts = [[] for _ in range(world_size)]
-    for i in order:
-        r = min(range(world_size), key=lambda k: (loads[k], k))
+    costs = (lengths + 1).tolist()                                # +1: an empty unit still costs a slot
+    for i in order.tolist():
+        load, r = heap[0]
         parts[r].append(i)
-        loads[r] += int(lengths[i]) + 1            # +1: an empty unit still costs a slot
+        heapq.heapreplace(heap, (load + costs[i], r))
     for p in parts:
         p.sort()
     return parts
@@ -88,11 +90,12 @@ def rate_sharded(rater, texts, contexts=None, gather=True, group=None):
     recv = torch.empty(world * cap, dtype=torch.float32, device=dev)
     dist.all_gather_into_tensor(recv, send, group=group)
     everything = recv.cpu().numpy().reshape(world, cap)
+    lens = np.asarray(lengths, dtype=np.int64)
     for r, p in enumerate(parts):
-        if r == rank:
+        if r == rank or not p:
             continue
-        pos = 0
-        for i in p:
-            out[i] = everything[r, pos:pos + lengths[i]].copy()
-            pos += lengths[i]
+        # views into the gathered row, cut at the cumulative lengths of that rank's units (no copy per text)
+        pieces = np.split(everything[r, :sizes[r]], np.cumsum(lens[p])[:-1])
+        for i, piece in zip(p, pieces):
+            out[i] = piece
     return out
