@@ -453,6 +453,48 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         for (int i = 0; i < OWN; ++i)
 #pragma unroll
             for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+        if constexpr (OWN <= 2) {
+        // two batches of TMEM loads with one wait each: the pairs the other half finishes (this row's part goes over through
+        // shared memory, both directions at once), then the own pairs (hi rows: hi.hi + hi.lo columns; lo rows: lo.hi columns)
+        {
+            float v[OWN][8], b[OWN][8];
+#pragma unroll
+            for (int i = 0; i < OWN; ++i)
+                if (i < R.nsend) {
+                    const int pr = R.send_first + i;
+                    tc::tmem_ld8(trow + 8 * pr, v[i]);
+                    if (half == 0) tc::tmem_ld8(trow + N + 8 * pr, b[i]);
+                }
+            tc::tmem_ld_wait();
+            float *xs = xchg + (half ? 0 : xh * 8 * 64);
+#pragma unroll
+            for (int i = 0; i < OWN; ++i)
+                if (i < R.nsend) {
+                    const int xi = R.send_first + i - R.oth_first;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) xs[(xi * 8 + j) * 64 + s] = half == 0 ? v[i][j] + b[i][j] : v[i][j];
+                }
+        }
+        {
+            float b[OWN][8];
+#pragma unroll
+            for (int i = 0; i < OWN; ++i)
+                if (i < R.nown) {
+                    const int pr = R.own_first + i;
+                    tc::tmem_ld8(trow + 8 * pr, acc[i]);
+                    if (half == 0) tc::tmem_ld8(trow + N + 8 * pr, b[i]);
+                }
+            tc::tmem_ld_wait();
+            if (half == 0) {
+#pragma unroll
+                for (int i = 0; i < OWN; ++i)
+                    if (i < R.nown) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc[i][j] += b[i][j];
+                    }
+            }
+        }
+        } else {
         // own pairs: this row's part (hi rows: hi.hi + hi.lo columns; lo rows: lo.hi columns)
 #pragma unroll
         for (int i = 0; i < OWN; ++i)
@@ -490,6 +532,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
 #pragma unroll
                     for (int j = 0; j < 8; ++j) xs[(xi * 8 + j) * 64 + s] = v[j];
                 }
+        }
         }
         tc::tc_fence_before();
         tc::mbar_arrive(x.bar_tempty);                               // this thread is done reading TMEM
@@ -545,21 +588,9 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
                     if (active) { c_reg[i][e] = e1[i][e]; h_reg[i][e] = hn; }
                 }
         }
-        if (step) {
-            // step mode: the new state goes straight to the pool (the hypothesis' own output slot)
-            if (active) {
-                float *st = p.state + ((size_t)slot_out * p.D + l) * 2 * W;
+        if (step && !active) {
 #pragma unroll
-                for (int i = 0; i < OWN; ++i)
-                    if (i < R.nown) {
-                        const int u = 2 * (pr0 + i);
-                        *reinterpret_cast<float2 *>(st + u) = make_float2(h_reg[i][0], h_reg[i][1]);
-                        *reinterpret_cast<float2 *>(st + W + u) = make_float2(c_reg[i][0], c_reg[i][1]);
-                    }
-            } else {
-#pragma unroll
-                for (int i = 0; i < OWN; ++i) h_reg[i][0] = h_reg[i][1] = 0.f;
-            }
+            for (int i = 0; i < OWN; ++i) h_reg[i][0] = h_reg[i][1] = 0.f;
         }
         stage();
         if (TRACE && tid == 64) tc_trace(p, tick, 6);
@@ -576,6 +607,19 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
             if (l > 0) df_st_relaxed(p.sync + KLM_DF_ZRD + l * 64 + role.idx, tick_base + (unsigned)tick + 1u);   // Z of this tick consumed (all threads: bar.sync above)
             if (x.guard) tc::mbar_arrive(x.bar_epid);
             if (TRACE) tc_trace(p, tick, 7);
+        }
+        if (step && active) {
+            // step mode: the new state goes straight to the pool (the hypothesis' own output slot) -- BEHIND the publication:
+            // nobody reads it in this launch, and in front of it the 32-sector stores sat in the memory pipeline before the
+            // staging stores and under the release of the hand-over (~1 us per hop of the beam step's chain)
+            float *st = p.state + ((size_t)slot_out * p.D + l) * 2 * W;
+#pragma unroll
+            for (int i = 0; i < OWN; ++i)
+                if (i < R.nown) {
+                    const int u = 2 * (pr0 + i);
+                    *reinterpret_cast<float2 *>(st + u) = make_float2(h_reg[i][0], h_reg[i][1]);
+                    *reinterpret_cast<float2 *>(st + W + u) = make_float2(c_reg[i][0], c_reg[i][1]);
+                }
         }
         alive = __all_sync(0xffffffffu, alive ? 1 : 0) != 0;
     }
