@@ -679,9 +679,6 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
                     if (!STREAM) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 }
                 if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 2 + 3 * r);      // ... hand-over read
-                // addends of the next round: in flight while this round is finished
-                float4 add_nxt[OWN][2];
-                if (r + 1 < NR && !last_round) load_add(r + 1, add_nxt);
 
                 // ---- finish the round ----
                 if (TRACE && last_round && tid == 64 && p.trace_mode == 0) tc_trace(p, tick, 5);
@@ -784,10 +781,10 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
                 }
                 if (TRACE && tid == 64 && p.trace_mode == 4) tc_trace(p, tick, 3 + 3 * r);      // ... round finished
                 if (last_round) break;
-                if (r + 1 < NR) {
-#pragma unroll
-                    for (int i = 0; i < OWN; ++i) { add4[i][0] = add_nxt[i][0]; add4[i][1] = add_nxt[i][1]; }
-                }
+                // addends of the next round, fetched BEHIND this round's cell and staging (in front of them the issue of the
+                // scattered table-row loads of layer 1 alone was ~1 800 clk on the recurrence); they are in flight while the
+                // next round drains its accumulators and exchanges the hi / lo parts
+                if (r + 1 < NR) load_add(r + 1, add4);
             }
 
             // ---- hand over ----
