@@ -13,7 +13,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB_PATH = os.path.join(HERE, 'libkeraslm_b200.so')
-SOURCES = ['klm_api.cu', 'klm_seq_fma.cu', 'klm_seq_tc.cu', 'klm_seq_df.cu', 'klm_seq_rg.cu']
+SOURCES = ['klm_api.cu', 'klm_seq_fma.cu', 'klm_seq_tc.cu', 'klm_seq_df.cu', 'klm_seq_rg.cu', 'klm_seq_tw.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-shared', '-Xcompiler', '-fPIC']
 

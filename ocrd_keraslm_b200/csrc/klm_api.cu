@@ -17,6 +17,7 @@
 cudaError_t klm_launch_seq_fma(const KlmSeqParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_tc(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_df(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
+cudaError_t klm_launch_seq_tw(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream);
 cudaError_t klm_launch_seq_rg(const KlmSeqParams &p, cudaStream_t stream, int *cluster);
 bool klm_rg_eligible(int W, int D, int V);
 cudaError_t klm_launch_umma2_selftest(const __half *A, const __half *B, float *D, int N, int K, int *err, cudaStream_t stream);
@@ -81,6 +82,12 @@ struct KlmTcPlan {
     __half *hx_df = nullptr, *hx0 = nullptr;
     float *Z_df = nullptr, *logits_df = nullptr;
     int n_proj = 0;
+    // wide streamed form (klm_seq_tw.cu): 128 streams per launch, its own exchange buffers
+    bool wide_ok = false;
+    size_t wide_smem = 0;
+    __half *hx_w = nullptr;
+    float *Z_w = nullptr, *logits_w = nullptr;
+    long long wide_launches = 0;
 };
 
 // Run-time switches: read from the environment ONCE (klm_create), changed afterwards with klm_set_option -- no getenv on
@@ -89,6 +96,7 @@ struct KlmKnobs {
     int tc_trace_mode = 0;        // KLM_TC_TRACE_MODE
     int tc_debug_skip = 0;        // KLM_TC_DEBUG_SKIP (timing experiments, traced instantiations only)
     int tc_poll = 0;              // KLM_TC_POLL
+    int tc_wide = 1;              // KLM_TC_WIDE: 0 = never the 128-stream kernel (streamed-weights plans)
     int tc_skew = 0;              // KLM_TC_SKEW: 0 = by launch length, 2 / 3 = forced
     int tc_zpub = -1;             // KLM_TC_ZPUB: 2 = IN / PROJ stage + bulk-store their slice also with the early signal
     int tc_pub_release = 1;       // KLM_TC_PUB_RELEASE: 1 = a published slice is signalled with a gpu-scope RELEASE.  0 (a relaxed
@@ -112,6 +120,7 @@ static void read_knobs(KlmKnobs &k) {
     k.tc_debug_skip = env_int("KLM_TC_DEBUG_SKIP", 0);
     k.tc_poll = env_int("KLM_TC_POLL", 0);
     k.tc_skew = env_int("KLM_TC_SKEW", 0);
+    k.tc_wide = env_int("KLM_TC_WIDE", 1);
     k.tc_zpub = env_int("KLM_TC_ZPUB", -1);
     k.tc_pub_release = env_int("KLM_TC_PUB_RELEASE", 1);
     k.tc_df = env_int("KLM_TC_DF", 1);
@@ -595,6 +604,21 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
             pl.n_proj = (int)proj.size();
         }
     }
+    // ---- wide streamed form (klm_seq_tw.cu): the same roles and images, 128 streams per launch ----
+    if (pl.stream_b && pl.pub == 2 && W % 64 == 0) {
+        bool ok = true;
+        size_t need = 0;
+        const size_t avail = m->smem_optin - 1024;                   // (1 KB of static shared memory: the LSE role)
+        for (auto &r : pl.roles) {
+            if (r.kind == KLM_TC_LSE) continue;
+            const size_t pub = r.kind == KLM_TC_REC ? (size_t)(r.npairs / 4) * 4096 : 0;
+            const size_t slot = (size_t)2 * 64 * 256 + (size_t)64 * 32 * r.npairs;
+            if (r.npairs < 2 || (r.npairs & 1) || r.npairs > 24 || (r.kind == KLM_TC_REC && (r.npairs & 3))) ok = false;
+            if (1024 + pub + 2 * slot > avail) ok = false;           // at least two ring slots
+            need = std::max(need, std::min(avail, 1024 + pub + 3 * slot));
+        }
+        if (ok) { pl.wide_ok = true; pl.wide_smem = need; }
+    }
     for (size_t i = 0; i < pl.roles.size(); ++i) pl.roles[i].rot = (int)i;
     CK(cudaMalloc(&pl.d_roles, pl.roles.size() * sizeof(KlmTcRole)));
     CK(cudaMemcpy(pl.d_roles, pl.roles.data(), pl.roles.size() * sizeof(KlmTcRole), cudaMemcpyHostToDevice));
@@ -616,6 +640,14 @@ static int make_tc1_plan(klm_model *m, const float *E, const float *const *L, Kl
         CK(cudaMalloc(&pl.hx0, (size_t)D * KLM_DF_MAXG * hxv)); CK(cudaMemset(pl.hx0, 0, (size_t)D * KLM_DF_MAXG * hxv));
         CK(cudaMalloc(&pl.Z_df, zdf)); CK(cudaMemset(pl.Z_df, 0, zdf));
         CK(cudaMalloc(&pl.logits_df, ldf)); CK(cudaMemset(pl.logits_df, 0, ldf));
+    }
+    if (pl.wide_ok) {
+        const size_t hxw = (size_t)D * 2 * 2 * W * 128 * sizeof(__half);
+        const size_t zw = (size_t)D * 2 * W * 128 * sizeof(float4);
+        const size_t lw = (size_t)2 * (pl.Vp / 4) * 128 * sizeof(float4);
+        CK(cudaMalloc(&pl.hx_w, hxw)); CK(cudaMemset(pl.hx_w, 0, hxw));
+        CK(cudaMalloc(&pl.Z_w, zw)); CK(cudaMemset(pl.Z_w, 0, zw));
+        CK(cudaMalloc(&pl.logits_w, lw)); CK(cudaMemset(pl.logits_w, 0, lw));
     }
     pl.ok = true;                                            // launched cooperatively: all CTAs are co-resident
     return KLM_OK;
@@ -643,6 +675,7 @@ extern "C" int klm_destroy(klm_model *m) {
     cudaFree(m->plan_k.d_roles); cudaFree(m->plan_b.d_roles);
     cudaFree(m->tc.d_roles); cudaFree(m->tc.d_wimg); cudaFree(m->tc.hx); cudaFree(m->tc.Z); cudaFree(m->tc.logits);
     cudaFree(m->tc.err); cudaFree(m->tc.trace);
+    cudaFree(m->tc.hx_w); cudaFree(m->tc.Z_w); cudaFree(m->tc.logits_w);
     cudaFree(m->tc.sync); cudaFree(m->tc.hx_df); cudaFree(m->tc.hx0); cudaFree(m->tc.Z_df); cudaFree(m->tc.logits_df);
     cudaFree(m->hbuf); cudaFree(m->logits); cudaFree(m->barrier); cudaFree(m->state);
     cudaFree(m->hbuf_ll); cudaFree(m->logits_ll); cudaFree(m->progress); cudaFree(m->ll_err);
@@ -811,6 +844,7 @@ extern "C" int klm_set_option(klm_model *m, const char *name, int64_t value) {
     else if (n == "tc_debug_skip") k.tc_debug_skip = (int)value;
     else if (n == "tc_poll") k.tc_poll = (int)value;
     else if (n == "tc_skew") k.tc_skew = (int)value;
+    else if (n == "tc_wide") k.tc_wide = (int)value;
     else if (n == "tc_zpub") k.tc_zpub = (int)value;
     else if (n == "tc_pub_release") k.tc_pub_release = (int)value;
     else if (n == "tc_fault") k.tc_fault = (int)value;
@@ -1033,7 +1067,8 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
                      const int32_t *n_real, const int32_t *ctx, const int *d_chars, const int *d_targets, float *d_out,
                      int full_rows) {
     KlmPlan &pl = (nb <= KLM_MODEK_MAXB) ? m->plan_k : m->plan_b;
-    if (nb > pl.max_streams) return fail(KLM_EINVAL, "internal: batch of %d streams exceeds plan (%d)", nb, pl.max_streams);
+    const bool wide = m->tc.ok && m->tc.wide_ok && nb > KLM_TC_STREAMS && nb <= 2 * KLM_TC_STREAMS;
+    if (nb > pl.max_streams && !wide) return fail(KLM_EINVAL, "internal: batch of %d streams exceeds plan (%d)", nb, pl.max_streams);
     long long tmax = 0;
     for (int s = 0; s < nb; ++s) {
         const long long len = offsets0[s + 1] - offsets0[s];
@@ -1044,7 +1079,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     RingSlot rs;
     int rc = ring_acquire(m, &rs, (size_t)nb * (4 * 3 + 4 * m->Nc) + (nb + 1) * 8 + 128);
     if (rc) return rc;
-    if (m->tc.ok && nb > KLM_MODEK_MAXB && nb <= KLM_TC_STREAMS) {
+    if (m->tc.ok && nb > KLM_MODEK_MAXB && (nb <= KLM_TC_STREAMS || wide)) {
         KlmTcPlan &tp = m->tc;
         if ((double)(tmax + 3 * m->D + 2) * tp.grid >= 4.0e9)
             return fail(KLM_EINVAL, "stream of %lld positions is too long for one launch", tmax);
@@ -1099,6 +1134,15 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
             return KLM_OK;
         }
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
+        if (wide) {
+            // 65..128 streams of a streamed-weights plan: one launch of klm_seq_tw (skew 2, two slots of Z / logits)
+            q.wide = 1; q.hx = tp.hx_w; q.Z = tp.Z_w; q.logits = tp.logits_w;
+            q.skew = 2; q.zmask = 1; q.zlag = 1; q.trace = nullptr;
+            q.ring_bytes = (int)tp.wide_smem;
+            CK(klm_launch_seq_tw(q, tp.grid, tp.wide_smem, m->stream));
+            m->launches++; m->tc_launches++; tp.wide_launches++;
+            return KLM_OK;
+        }
         CK(klm_launch_seq_tc(q, tp.grid, tp.smem, m->stream));
         m->launches++; m->tc_launches++;
         return KLM_OK;
@@ -1210,7 +1254,7 @@ static int launch_step_df(klm_model *m, int nb, const int *d_si, const int *d_so
 // Largest number of streams one launch takes for a call of n streams.
 static int batch_max(klm_model *m, int n) {
     if (n <= KLM_MODEK_MAXB) return KLM_MODEK_MAXB;
-    if (m->tc.ok) return KLM_TC_STREAMS;
+    if (m->tc.ok) return (m->tc.wide_ok && m->knobs.tc_wide && n > KLM_TC_STREAMS) ? 2 * KLM_TC_STREAMS : KLM_TC_STREAMS;
     return m->plan_b.max_streams;
 }
 

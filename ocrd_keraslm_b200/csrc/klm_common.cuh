@@ -251,5 +251,6 @@ struct KlmTcParams {
                                   //   nothing of the next tick before its own publication is through, 4 = IN / PROJ publish at once
     unsigned spin_limit;          // device-side watchdog: polls of one wait before it gives up (klm_set_option "tc_spin_limit")
     int fault;                    // test hook (klm_set_option "tc_fault"): CTA 0 withholds its hand-over signal of tick 2
+    int wide;                     // 1: klm_seq_tw -- 128 streams per launch (exchange buffers and LSE rows of 128 streams)
     KlmStepArgs step;             // (last: only the launches of a beam step fill it)
 };

@@ -1,0 +1,457 @@
+// "Wide" streamed-weights form of the tensor-core sequence kernel: up to 128 concurrent streams per launch for models
+// whose fp16 hi/lo weight images do not fit shared memory (width 1024: cfg5 of BASELINE.json, 10 000 lines).
+// Replaces the per-window Session.run of Rater.rate (rating.py:516) for 65..128 streams per launch.
+//
+// klm_seq_tcs (klm_seq_tc.cu) multiplies A = [64 streams hi ; 64 streams lo] (M = 128) with B = [N columns hi ; N lo]:
+// four products per stream of which three are wanted, 2N accumulator columns, and every streamed B chunk serves 64
+// streams.  Here a row of the accumulator is a STREAM and the three wanted products are accumulated into the SAME N
+// columns by three MMAs per k-step:
+//     D[128 x N] += h_hi . W_hi^T  +  h_hi . W_lo^T  +  h_lo . W_hi^T        (A tiles h_hi, h_lo: [W/8][128 rows][8] halves)
+// -> 3 units of tensor work per 128 streams instead of 4 per 64, half the weight bytes per stream through the SM's
+//    ingest port (the bound of the streamed form), N <= 192 TMEM columns, and NO hi/lo hand-over in the epilogue: a
+//    thread owns a stream and half of the CTA's unit pairs, the pre-activation arrives complete.
+//
+// Same plan (roles, B images, scales) as klm_seq_tcs; same wavefront with skew 2 (REC l at 2l, IN l at 2l-1, PROJ at
+// 2D-1, LSE at 2D), one grid barrier per tick.  Exchange buffers of its own (KlmTcParams::hx / Z / logits point at them):
+//     hx     [D][2 parities][2 tiles: hi, lo][W/8][128][8] halves
+//     Z      [D][2 slots][W units][128 streams] float4          logits [2 slots][Vp/4][128 streams] float4
+// Shared memory: [1 KB barriers + bias of the slice][publication staging (REC): (pairs/4) x (2 KB hi + 2 KB lo)]
+//                [ring of S <= 3 slots: A_hi chunk 16 KB | A_lo chunk 16 KB | B chunk 2 KB x pairs]
+// Warp roles as in klm_seq_tc: warp 0 producer, warp 1 MMA issuer, warps 2..9 epilogue (row = 32 (warp & 3) + lane,
+// the two warps of a TMEM lane quarter split the CTA's pairs).
+#include <cstdio>
+#include "klm_tc_dev.cuh"
+
+#define TW_KC        64
+#define TW_ACH       (TW_KC * 256)          // bytes of one chunk of one A tile (64 k x 128 rows x 2 B)
+#define TW_MAXR      6                      // epilogue rounds of 2 pairs per thread (<= 12 pairs per thread, 24 per CTA)
+#define TW_HEAD      1024                   // barriers (first 128 bytes) + bias of the slice (from byte 256)
+
+namespace {
+
+struct TwCtx {
+    uint32_t ring_a, bar_full, bar_empty, bar_tfull, bar_tempty, bar_go, tmem_base;
+    uint32_t slot_bytes, cbb;
+    int S, NCH, N, nticks, crot, src_layer, W;
+    unsigned G;
+    const unsigned char *bsrc;
+};
+
+// Producer warp (converged; the elected lane issues): per tick the B parts of the first ring round go out before the
+// grid barrier (they do not depend on the tick), the A tiles follow behind it.
+__device__ __noinline__ void tw_produce(const KlmTcParams &p, const TwCtx &x) {
+    const uint32_t ring_a = x.ring_a, bar_full = x.bar_full, bar_empty = x.bar_empty, bar_go = x.bar_go;
+    const uint32_t slot_bytes = x.slot_bytes, cbb = x.cbb;
+    const int S = x.S, NCH = x.NCH, nticks = x.nticks, crot = x.crot;
+    const unsigned G = x.G;
+    const unsigned char *bsrc = x.bsrc;
+    const size_t tile_bytes = (size_t)x.W * 128 * sizeof(__half);                 // one tile of one parity of one layer
+    const unsigned char *hx0 = reinterpret_cast<const unsigned char *>(p.hx) + (size_t)x.src_layer * 4 * tile_bytes;
+    const bool lane0 = (threadIdx.x & 31) == 0;
+    const int npre = S < NCH ? S : NCH;
+    uint32_t phbits = 0;                                   // bit st: uses of slot st so far, mod 2
+    for (int tick = 0; tick < nticks; ++tick) {
+        for (int c0 = 0; c0 < npre; ++c0) {
+            const int okw = tc_wait_mbar(bar_empty + 8 * c0, ((phbits >> c0) & 1u) ^ 1u, p, 2) ? 1 : 0;
+            if (!__all_sync(0xffffffffu, okw)) return;
+            if (tc::elect_one()) {
+                const int cb = crot + c0 >= NCH ? crot + c0 - NCH : crot + c0;
+                tc::mbar_arrive_expect_tx(bar_full + 8 * c0, 2 * TW_ACH + cbb);
+                tc::bulk_g2s(ring_a + c0 * slot_bytes + 2 * TW_ACH, bsrc + (size_t)cb * cbb, cbb, bar_full + 8 * c0);
+            }
+            __syncwarp();
+        }
+        int okg = 1;
+        if (lane0) {
+            okg = tc_wait_grid(p, (unsigned)(tick + 1) * G, 1) ? 1 : 0;
+            if (okg) tc::mbar_arrive(bar_go);
+        }
+        if (!__shfl_sync(0xffffffffu, okg, 0)) return;
+        const unsigned char *src_hi = hx0 + (size_t)((tick & 1) * 2) * tile_bytes, *src_lo = src_hi + tile_bytes;
+        int c = crot, st = 0;
+        for (int c0 = 0; c0 < NCH; ++c0) {
+            if (c0 >= npre) {
+                const int okw = tc_wait_mbar(bar_empty + 8 * st, ((phbits >> st) & 1u) ^ 1u, p, 2) ? 1 : 0;
+                if (!__all_sync(0xffffffffu, okw)) return;
+            }
+            if (tc::elect_one()) {
+                const uint32_t dst = ring_a + st * slot_bytes, bar = bar_full + 8 * st;
+                if (c0 >= npre) {
+                    tc::mbar_arrive_expect_tx(bar, 2 * TW_ACH + cbb);
+                    tc::bulk_g2s(dst + 2 * TW_ACH, bsrc + (size_t)c * cbb, cbb, bar);
+                }
+                tc::bulk_g2s(dst, src_hi + (size_t)c * TW_ACH, TW_ACH, bar);
+                tc::bulk_g2s(dst + TW_ACH, src_lo + (size_t)c * TW_ACH, TW_ACH, bar);
+            }
+            __syncwarp();
+            phbits ^= 1u << st;
+            st = st + 1 == S ? 0 : st + 1;
+            c = c + 1 == NCH ? 0 : c + 1;
+        }
+    }
+}
+
+// MMA warp: per k-step of 16 three MMAs into the same N accumulator columns (hi.hi, hi.lo, lo.hi).
+__device__ __noinline__ void tw_mma(const KlmTcParams &p, const TwCtx &x) {
+    const uint32_t idesc = tc::idesc_f16(128, x.N);
+    const uint32_t lbo_a = 128 * 16, lbo_b = 2 * x.N * 16;
+    const uint64_t a_base = tc::smem_desc(x.ring_a, lbo_a, 128);
+    const uint64_t b_base = tc::smem_desc(x.ring_a + 2 * TW_ACH, lbo_b, 128);
+    constexpr uint32_t a_k16 = (2 * 128 * 16) >> 4, a_lo = TW_ACH >> 4;
+    const uint32_t b_k16 = (2 * lbo_b) >> 4, b_lo = (uint32_t)x.N;           // lo rows start N * 16 bytes into a k group
+    const uint32_t slot16 = x.slot_bytes >> 4;
+    const uint32_t bar_full = x.bar_full, bar_empty = x.bar_empty, bar_tfull = x.bar_tfull, bar_tempty = x.bar_tempty;
+    const uint32_t tmem_base = x.tmem_base;
+    const int S = x.S, NCH = x.NCH, nticks = x.nticks;
+    uint32_t phbits = 0;
+    for (int tick = 0; tick < nticks; ++tick) {
+        int okw = tc_wait_mbar(bar_tempty, (tick & 1) ^ 1, p, 3) ? 1 : 0;
+        if (!__all_sync(0xffffffffu, okw)) return;
+        tc::tc_fence_after();
+        int st = 0;
+        for (int c0 = 0; c0 < NCH; ++c0) {
+            okw = tc_wait_mbar(bar_full + 8 * st, (phbits >> st) & 1u, p, 4) ? 1 : 0;
+            if (!__all_sync(0xffffffffu, okw)) return;
+            const uint64_t ad = a_base + (uint32_t)st * slot16, bd = b_base + (uint32_t)st * slot16;
+            if (tc::elect_one()) {
+#pragma unroll
+                for (int kk = 0; kk < TW_KC / 16; ++kk) {
+                    const uint64_t a = ad + kk * a_k16, b = bd + kk * b_k16;
+                    tc::mma_f16(tmem_base, a, b, idesc, (c0 | kk) != 0 ? 1u : 0u);        // h_hi . W_hi
+                    tc::mma_f16(tmem_base, a, b + b_lo, idesc, 1u);                        // h_hi . W_lo
+                    tc::mma_f16(tmem_base, a + a_lo, b, idesc, 1u);                        // h_lo . W_hi
+                }
+                tc::mma_commit(bar_empty + 8 * st);          // ring slot free once these MMAs have read it
+                if (c0 == NCH - 1) tc::mma_commit(bar_tfull);   // accumulators of this tick complete
+            }
+            __syncwarp();
+            phbits ^= 1u << st;
+            st = st + 1 == S ? 0 : st + 1;
+        }
+    }
+}
+
+}  // namespace
+
+namespace {
+
+// Epilogue of one GEMM CTA.  KIND = KLM_TC_REC / KLM_TC_IN / KLM_TC_PROJ (compile-time: a REC CTA carries no IN state
+// and vice versa -- the kernel runs at 168 registers per thread).  A thread owns stream s = 32 (warp & 3) + lane and NP / 2
+// of the CTA's unit pairs, finished in rounds of two pairs (16 accumulator columns).
+template <int KIND>
+__device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRole &role, const TwCtx &x, unsigned char *smem) {
+    constexpr bool REC = KIND == KLM_TC_REC;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int W = p.W, l = role.layer, NP = role.npairs;
+    const int q = warp & 3, s = 32 * q + lane, ch = (warp - 2) >> 2;
+    const int NPT = NP / 2, pfirst = ch * NPT, nrounds = (NPT + 1) / 2;
+    const uint32_t trow = x.tmem_base + ((uint32_t)(32 * q) << 16);
+    const int sigma = REC ? 2 * l : KIND == KLM_TC_IN ? 2 * l - 1 : 2 * p.D - 1;
+    const int nticks = x.nticks;
+    const float scale = role.scale;
+    const int ngrp = NP / 4;                                     // REC: groups of 8 units in the slice
+    __half *pub = reinterpret_cast<__half *>(smem + TW_HEAD);    // [tile hi, lo][group][128 rows][8]
+    float4 *bias_sm = reinterpret_cast<float4 *>(smem + 256);
+    const size_t tile_halves = (size_t)W * 128;
+
+    float c_reg[REC ? TW_MAXR : 1][2][2], h_reg[REC ? TW_MAXR : 1][2][2];
+    long long o0 = 0;
+    int len = 0;
+    if (s < p.B) { o0 = p.offsets[s]; len = (int)(p.offsets[s + 1] - o0); }
+    int x_next = 0, nreal_s = 0x7fffffff;
+    int zk[KLM_MAX_CTX];
+#pragma unroll
+    for (int k = 0; k < KLM_MAX_CTX; ++k) zk[k] = 0;
+    if constexpr (REC) {
+        // ---- carried state in, initial hidden vector published for tick 0 (parity 0) ----
+        const int slot = s < p.B ? p.slots_in[s] : -1;
+#pragma unroll
+        for (int r = 0; r < TW_MAXR; ++r)
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                c_reg[r][i][0] = c_reg[r][i][1] = h_reg[r][i][0] = h_reg[r][i][1] = 0.f;
+                if (2 * r + i < NPT) {
+                    const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
+                    if (slot >= 0) {
+                        const float *st = p.state + ((size_t)slot * p.D + l) * 2 * W;
+                        h_reg[r][i][0] = st[u]; h_reg[r][i][1] = st[u + 1];
+                        c_reg[r][i][0] = st[W + u]; c_reg[r][i][1] = st[W + u + 1];
+                    }
+                    __half hi0, lo0, hi1, lo1;
+                    tc_split(h_reg[r][i][0], hi0, lo0); tc_split(h_reg[r][i][1], hi1, lo1);
+                    __half *dst = p.hx + (size_t)(l * 4) * tile_halves + (size_t)(u / 8) * (128 * 8) + (size_t)s * 8 + (u & 7);
+                    *reinterpret_cast<__half2 *>(dst) = __halves2half2(hi0, hi1);
+                    *reinterpret_cast<__half2 *>(dst + tile_halves) = __halves2half2(lo0, lo1);
+                }
+            }
+        tc::fence_proxy_async();                    // generic global writes -> later bulk (async proxy) reads
+        if (l == 0 && s < p.B) {
+            if (len > 0) x_next = __ldg(p.chars + o0);
+            if (p.n_real) nreal_s = __ldg(p.n_real + s);
+#pragma unroll
+            for (int k = 0; k < KLM_MAX_CTX; ++k)
+                if (k < p.Nc) zk[k] = min(max(__ldg(p.ctx + s * p.Nc + k), 0), p.ctx_rows[k] - 1);
+        }
+    }
+    if (KIND == KLM_TC_IN)
+        for (int j = tid - 64; j < 2 * NP; j += 256) bias_sm[j] = __ldg(p.bias[l] + 2 * role.first_pair + j);
+    // everything this CTA must have written before anybody's first fetch is out: first arrival at the grid barrier
+    asm volatile("bar.sync 2, 320;" ::: "memory");
+    if (tid == 64) tc::red_release_add(p.barrier, 1u);
+
+    for (int tick = 0; tick < nticks; ++tick) {
+        int ok = tc_wait_mbar(x.bar_go, tick & 1, p, 5) ? 1 : 0;
+        if (!__all_sync(0xffffffffu, ok)) break;
+        const int t = tick - sigma;
+        const bool active = s < p.B && t >= 0 && t < len;
+        const int par_out = (tick + 1) & 1, zs_in = tick & 1, zs_out = (tick + 1) & 1;
+        int xc = 0;
+        bool real = true;
+        if (REC && l == 0 && active) {
+            xc = min(max(x_next, 0), p.V - 1);
+            if (t + 1 < len) x_next = __ldg(p.chars + o0 + t + 1);
+            real = t < nreal_s;
+        }
+        // addends of round r (REC): layer 1 = fused char + context embedding gather (tables P, Q: rating.py:103-115,125;
+        // padding positions take context 0, :1141-1143); layers above = Z of the IN stage
+        auto load_add = [&](const int r, float4 (&a4)[2][2]) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) a4[i][0] = a4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (!REC || !active) return;
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+                if (2 * r + i < NPT) {
+                    const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
+                    if (l == 0) {
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            float4 a = __ldg(p.P + (size_t)xc * W + u + e);
+#pragma unroll
+                            for (int k = 0; k < KLM_MAX_CTX; ++k)
+                                if (k < p.Nc) {
+                                    const float4 b = __ldg(p.Q[k] + (real ? (size_t)zk[k] * W : (size_t)0) + u + e);
+                                    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+                                }
+                            a4[i][e] = a;
+                        }
+                    } else {
+                        const float4 *zrow = reinterpret_cast<const float4 *>(p.Z) + ((size_t)(l * 2 + zs_in) * W) * 128 + s;
+                        a4[i][0] = __ldcg(zrow + (size_t)u * 128); a4[i][1] = __ldcg(zrow + (size_t)(u + 1) * 128);
+                    }
+                }
+        };
+        float4 add4[2][2];
+        load_add(0, add4);
+
+        ok = tc_wait_mbar(x.bar_tfull, tick & 1, p, 6) ? 1 : 0;
+        if (!__all_sync(0xffffffffu, ok)) break;
+        tc::tc_fence_after();
+#pragma unroll
+        for (int r = 0; r < TW_MAXR; ++r) {
+            if (r >= nrounds) break;                            // (CTA-uniform)
+            float acc[2][8];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+                if (2 * r + i < NPT) tc::tmem_ld8(trow + 8 * (pfirst + 2 * r + i), acc[i]);
+            }
+            tc::tmem_ld_wait();
+            if (r == nrounds - 1) {
+                tc::tc_fence_before();
+                tc::mbar_arrive(x.bar_tempty);                  // this thread is done reading TMEM
+            }
+            float4 add_nxt[2][2];
+            if (REC && l > 0 && r + 1 < nrounds) load_add(r + 1, add_nxt);      // (coalesced: cheap to issue, in flight under the cell)
+            if constexpr (REC) {
+                // LSTM cell (Keras LSTMCell, gate order i|f|c|o, exact logistic: rating.py:133-134); 8 MUFU per unit, staged
+                float e1[2][2], e2[2][2], e3[2][2], e4[2][2], ag[2][2];
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float4 a = add4[i][e];
+                        ag[i][e] = fmaf(acc[i][4 * e + 2], scale, a.z);
+                        e1[i][e] = tc_exp(-tc_clamp(fmaf(acc[i][4 * e], scale, a.x)));
+                        e2[i][e] = tc_exp(-tc_clamp(fmaf(acc[i][4 * e + 1], scale, a.y)));
+                        e3[i][e] = tc_exp(-2.f * tc_clamp(ag[i][e]));
+                        e4[i][e] = tc_exp(-tc_clamp(fmaf(acc[i][4 * e + 3], scale, a.w)));
+                    }
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        float num, den;
+                        klm_tanh_parts(ag[i][e], e3[i][e], num, den);
+                        const float ig = __fdividef(num, (1.f + e1[i][e]) * den);
+                        const float f = __fdividef(1.f, 1.f + e2[i][e]);
+                        e1[i][e] = fmaf(f, c_reg[r][i][e], ig);                    // new cell state
+                        e2[i][e] = tc_exp(-2.f * tc_clamp(e1[i][e]));
+                    }
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        float num, den;
+                        klm_tanh_parts(e1[i][e], e2[i][e], num, den);
+                        const float hn = __fdividef(num, (1.f + e4[i][e]) * den);
+                        if (active) { c_reg[r][i][e] = e1[i][e]; h_reg[r][i][e] = hn; }
+                    }
+                    if (2 * r + i < NPT) {
+                        // the new hidden values as fp16 hi / lo in the readers' operand layout
+                        const int ul = 2 * (pfirst + 2 * r + i);
+                        __half hi0, lo0, hi1, lo1;
+                        tc_split(h_reg[r][i][0], hi0, lo0); tc_split(h_reg[r][i][1], hi1, lo1);
+                        __half *dst = pub + ((size_t)(ul / 8) * 128 + s) * 8 + (ul & 7);
+                        *reinterpret_cast<__half2 *>(dst) = __halves2half2(hi0, hi1);
+                        *reinterpret_cast<__half2 *>(dst + (size_t)ngrp * 128 * 8) = __halves2half2(lo0, lo1);
+                    }
+                }
+                if (r + 1 < nrounds) {
+                    if (l > 0) {
+#pragma unroll
+                        for (int i = 0; i < 2; ++i) { add4[i][0] = add_nxt[i][0]; add4[i][1] = add_nxt[i][1]; }
+                    } else {
+                        load_add(r + 1, add4);      // (scattered table rows: issued behind the cell, see klm_seq_tc.cu)
+                    }
+                }
+            } else if constexpr (KIND == KLM_TC_IN) {
+                float4 *zrow = reinterpret_cast<float4 *>(p.Z) + ((size_t)(l * 2 + zs_out) * W) * 128 + s;
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+                    if (2 * r + i < NPT) {
+                        const int pl = pfirst + 2 * r + i, u = 2 * (role.first_pair + pl);
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const float4 b = bias_sm[2 * pl + e];
+                            __stcg(zrow + (size_t)(u + e) * 128,
+                                   make_float4(fmaf(acc[i][4 * e], scale, b.x), fmaf(acc[i][4 * e + 1], scale, b.y),
+                                               fmaf(acc[i][4 * e + 2], scale, b.z), fmaf(acc[i][4 * e + 3], scale, b.w)));
+                        }
+                    }
+            } else {   // PROJ: logits of vocabulary rows 8 * (first_pair + pair) ..
+                float4 *lrow = reinterpret_cast<float4 *>(p.logits) + ((size_t)zs_out * (p.Vp / 4)) * 128 + s;
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+                    if (2 * r + i < NPT) {
+                        const int g8 = role.first_pair + pfirst + 2 * r + i;
+                        __stcg(lrow + (size_t)(2 * g8) * 128, make_float4(acc[i][0] * scale, acc[i][1] * scale, acc[i][2] * scale, acc[i][3] * scale));
+                        __stcg(lrow + (size_t)(2 * g8 + 1) * 128, make_float4(acc[i][4] * scale, acc[i][5] * scale, acc[i][6] * scale, acc[i][7] * scale));
+                    }
+            }
+        }
+        // ---- hand over ----
+        if (REC) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // staging writes -> bulk store reads
+        tc_bar_epi();
+        if (tid == 64) {
+            if (REC) {
+                __half *ghi = p.hx + (size_t)((l * 2 + par_out) * 2) * tile_halves + (size_t)(role.first_pair / 4) * (128 * 8);
+                const uint32_t bytes = (uint32_t)ngrp * 2048u;
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                             ::"l"(ghi), "r"(tc::smem_u32(pub)), "r"(bytes) : "memory");
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                             ::"l"(ghi + tile_halves), "r"(tc::smem_u32(pub) + bytes), "r"(bytes) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");       // writes complete (not just read)
+            }
+            tc::red_release_add(p.barrier, 1u);
+        }
+        // (the staging is rewritten only behind the next tick's grid barrier, which this CTA's arrival -- behind the completed
+        //  bulk store -- is part of)
+    }
+    // ---- write the final state back ----
+    if constexpr (REC) if (s < p.B) {
+        float *st = p.state + ((size_t)p.slots_out[s] * p.D + l) * 2 * W;
+#pragma unroll
+        for (int r = 0; r < TW_MAXR; ++r)
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+                if (2 * r + i < NPT) {
+                    const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
+                    st[u] = h_reg[r][i][0]; st[u + 1] = h_reg[r][i][1];
+                    st[W + u] = c_reg[r][i][0]; st[W + u + 1] = c_reg[r][i][1];
+                }
+    }
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tw(const __grid_constant__ KlmTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const KlmTcRole role = p.roles[blockIdx.x];
+    if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int NP = role.npairs, N = 8 * NP, W = p.W;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem);
+    const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + 4);
+    const uint32_t bar_tfull = tc::smem_u32(bars + 8), bar_tempty = tc::smem_u32(bars + 9), bar_go = tc::smem_u32(bars + 10);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 11);
+    // ring geometry: everything behind the head and (REC) the publication staging, at most 3 slots
+    const uint32_t pub_bytes = role.kind == KLM_TC_REC ? (uint32_t)(NP / 4) * 4096u : 0u;
+    const uint32_t cbb = (uint32_t)TW_KC * 32u * (uint32_t)NP;            // 8 k groups x 2N rows x 16 bytes
+    const uint32_t slot_bytes = 2u * TW_ACH + cbb;
+    const int S = min(3, (int)(((uint32_t)p.ring_bytes - TW_HEAD - pub_bytes) / slot_bytes));
+    if (S < 2 || NP < 2 || (NP & 1) || NP > 4 * TW_MAXR || (role.kind == KLM_TC_REC && (NP & 3))) {
+        if (tid == 0) atomicCAS(p.err, 0, 91);               // (the host checks the plan before it launches this kernel)
+        return;
+    }
+    if (warp == 0) {
+        tc::tmem_alloc(tc::smem_u32(tmem_slot), 256);
+        tc::tmem_relinquish();
+    }
+    if (tid == 32) {
+        for (int i = 0; i < S; ++i) { tc::mbar_init(bar_full + 8 * i, 1); tc::mbar_init(bar_empty + 8 * i, 1); }
+        tc::mbar_init(bar_tfull, 1);
+        tc::mbar_init(bar_tempty, 256);
+        tc::mbar_init(bar_go, 1);
+        tc::fence_mbar_init();
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+
+    TwCtx x;
+    x.ring_a = tc::smem_u32(smem + TW_HEAD + pub_bytes);
+    x.bar_full = bar_full; x.bar_empty = bar_empty; x.bar_tfull = bar_tfull; x.bar_tempty = bar_tempty; x.bar_go = bar_go;
+    x.tmem_base = *tmem_slot;
+    x.slot_bytes = slot_bytes; x.cbb = cbb;
+    x.S = S; x.NCH = W / TW_KC; x.N = N; x.nticks = p.T_max + 2 * p.D;
+    x.crot = role.rot % (W / TW_KC); x.src_layer = role.src_layer; x.W = W;
+    x.G = gridDim.x;
+    x.bsrc = p.wimg + role.wofs;
+
+    if (warp == 0) {
+        asm volatile("bar.sync 2, 320;" ::: "memory");       // (the epilogue warps' prologue: carried state in, bias staged)
+        tw_produce(p, x);
+    } else if (warp == 1) {
+        asm volatile("bar.sync 2, 320;" ::: "memory");
+        tw_mma(p, x);
+    } else if (role.kind == KLM_TC_REC) {
+        tw_epilogue<KLM_TC_REC>(p, role, x, smem);
+    } else if (role.kind == KLM_TC_IN) {
+        tw_epilogue<KLM_TC_IN>(p, role, x, smem);
+    } else {
+        tw_epilogue<KLM_TC_PROJ>(p, role, x, smem);
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        __syncwarp();
+        tc::tmem_dealloc(x.tmem_base, 256);
+    }
+}
+
+// ring_bytes of the parameters = dynamic shared memory of the launch (the kernel derives the ring geometry from it)
+cudaError_t klm_launch_seq_tw(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream) {
+    void *args[] = { const_cast<KlmTcParams *>(&p) };
+    static size_t smem_set[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || smem_set[dev] != smem) {
+        cudaError_t e = cudaFuncSetAttribute((const void *)klm_seq_tw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        if (dev >= 0 && dev < 64) smem_set[dev] = smem;
+    }
+    return cudaLaunchCooperativeKernel((const void *)klm_seq_tw, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
+}

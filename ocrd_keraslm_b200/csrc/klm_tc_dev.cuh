@@ -97,6 +97,7 @@ static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role, 
     const unsigned G = gridDim.x;
     const int nticks = p.T_max + p.skew * p.D;
     const int V = p.V, Vq = p.Vp / 4, V4 = (V + 3) / 4, B = p.B, sigma = p.skew * p.D, full_rows = p.full_rows;
+    const int SB = p.wide ? 128 : 64;                      // streams per row of the logits buffer
     const float4 *logits4 = reinterpret_cast<const float4 *>(p.logits);
     const int *targets = p.targets;
     float *out = p.out;
@@ -125,12 +126,12 @@ static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role, 
         if (p.trace && p.trace_mode == 0 && tid == 0) tc_trace(p, tick, 0);
         const int t = tick - sigma;
         const bool act = warp_on && s < B && t >= 0 && t < len;
-        const float4 *base = logits4 + (size_t)((tick + 1 - p.zlag) & p.zmask) * Vq * 64 + s;
+        const float4 *base = logits4 + (size_t)((tick + 1 - p.zlag) & p.zmask) * Vq * SB + s;
         float tl = 0.f;
         if (act && sl == 0 && !full_rows) {
             int tg = __ldg(targets + o0 + t);
             tg = min(max(tg, 0), V - 1);
-            tl = __ldcg(reinterpret_cast<const float *>(base + (size_t)(tg >> 2) * 64) + (tg & 3));
+            tl = __ldcg(reinterpret_cast<const float *>(base + (size_t)(tg >> 2) * SB) + (tg & 3));
         }
         float m = -INFINITY, sum = 0.f;
         if (warp_on && t >= 0) {
@@ -138,7 +139,7 @@ static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role, 
                 float4 x[8];
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
-                    x[j] = (v0 + j < v4_hi) ? __ldcg(base + (size_t)(v0 + j) * 64) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+                    x[j] = (v0 + j < v4_hi) ? __ldcg(base + (size_t)(v0 + j) * SB) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
                 if (4 * (v0 + 8) > V) {                      // mask the padding entries of the last float4
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
@@ -179,7 +180,7 @@ static __device__ void tc_lse_role(const KlmTcParams &p, const KlmTcRole &role, 
                 float *dst = out + (size_t)(o0 + t) * V;
                 const float inv = 1.0f / S;
                 for (int v4 = v4_lo; v4 < v4_hi; ++v4) {
-                    const float4 x = __ldcg(base + (size_t)v4 * 64);
+                    const float4 x = __ldcg(base + (size_t)v4 * SB);
                     const int v = 4 * v4;
                     dst[v] = expf(x.x - M) * inv;
                     if (v + 1 < V) dst[v + 1] = expf(x.y - M) * inv;
