@@ -357,3 +357,68 @@ def test_dataflow_step_mode_matches_fma_step(n):
         np.testing.assert_array_equal(sa, sb)
         assert np.abs(sa - sc).max() <= 1e-4 * np.abs(sc).max()
         prev = out_a
+
+
+@pytest.mark.parametrize('width,depth,n_docs,nctx', [(1024, 3, 128, 1), (1024, 2, 97, 2), (512, 4, 65, 1), (768, 2, 100, 1)])
+def test_tw_wide_streamed_kernel_matches_narrow_kernel_and_oracle(width, depth, n_docs, nctx):
+    """klm_seq_tw (65..128 streams per launch of a streamed-weights plan: a row of the accumulator is a stream, three MMAs
+    per k-step into the same columns) against klm_seq_tcs on the same input and against the oracle: ragged lengths incl.
+    one-character texts, several context variables, ONE launch where the narrow kernel needs two."""
+    wd = synth.weights(31 + width + depth, width=width, depth=depth, voc_size=256, contexts=((200, 10),) * nctx, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 32)
+    nat = r._native
+    assert nat.info()['tc_enabled'] == 3
+    rng = np.random.default_rng(width + n_docs)
+    sizes = rng.integers(2, 40, n_docs)
+    sizes[1] = 1
+    sizes[n_docs - 1] = 57
+    texts = [synth.text(4100 + i, int(s)) for i, s in enumerate(sizes)]
+    ctxs = [[int(x) for x in rng.integers(0, 200, nctx)] for _ in texts]
+    l0 = nat.info()['tc_launches']
+    wide = r.rate_many(texts, ctxs)
+    l1 = nat.info()['tc_launches']
+    nat.set_option('tc_wide', 0)
+    narrow = r.rate_many(texts, ctxs)
+    l2 = nat.info()['tc_launches']
+    nat.set_option('tc_wide', 1)
+    assert l1 - l0 == 1 and l2 - l1 in (1, 2)          # (a remainder of <= 8 streams goes to the FMA kernel)
+    assert max(logp_err(a, b) for a, b in zip(wide, narrow)) <= 1e-4
+    o = OracleRater(util.to_model(wd), synth.mapping_from_array(maparr), 32, logger=quiet)
+    worst = 0.0
+    for i in sorted({0, 1, 63, 64, n_docs // 2, n_docs - 1}):
+        ref, _ = o.rate2(texts[i], ctxs[i])
+        worst = max(worst, logp_err(wide[i], [p for _, p in ref]))
+    assert worst <= 1e-3, worst
+
+
+def test_tw_states_carry_over_launches_like_the_narrow_kernel():
+    """Carried state in, final state out of klm_seq_tw: two launches over 100 streams continue from the pool slots; scores
+    and states equal those of klm_seq_tcs (which the oracle tests above pin) within the state tolerance."""
+    width, depth, n = 1024, 2, 100
+    wd = synth.weights(8, width=width, depth=depth, voc_size=256, contexts=((200, 10),), style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 16)
+    nat = r._native
+    texts = [synth.text(900 + i, 20 + i % 23) for i in range(n)]
+    results = {}
+    for mode in (1, 0):
+        nat.set_option('tc_wide', mode)
+        slots = r._pool.acquire(n)
+        nat.state_reset(slots)
+        logps = []
+        for piece in (slice(0, 9), slice(8, None)):          # second piece continues from the carried state
+            idx = [r._indices(t[piece])[0] for t in texts]
+            lens = np.array([len(i) - 1 for i in idx])
+            offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+            chars = np.concatenate([i[:-1] for i in idx]).astype(np.int32)
+            targets = np.concatenate([i[1:] for i in idx]).astype(np.int32)
+            logp = np.full(len(chars), np.nan, dtype=np.float32)
+            nat.rate(slots, offsets, chars, targets, None, [[(3 * k) % 200] for k in range(n)], logp)
+            logps.append(logp)
+        results[mode] = (np.concatenate(logps), nat.state_to_host(slots))
+        r._pool.release_many(slots)
+    nat.set_option('tc_wide', 1)
+    assert not np.isnan(results[1][0]).any()
+    assert np.abs(results[1][0].astype(np.float64) - results[0][0]).max() <= 1e-4
+    assert np.abs(results[1][1] - results[0][1]).max() <= 1e-4 * np.abs(results[0][1]).max()
