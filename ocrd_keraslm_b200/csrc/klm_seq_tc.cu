@@ -521,22 +521,24 @@ static __device__ __forceinline__ void tc_seq_role(const KlmTcParams &p, const K
                     for (int i = 0; i < OWN; ++i)
                         if (i < rd(r).nown) {
                             const int u = 2 * (pr0 + i);
+                            // (one 256-bit load per pair and table: tc_ldg_pair)
+                            float4 a0, a1;
+                            tc_ldg_pair(p.P + (size_t)x * W + u, a0, a1);
+                            if (real && KEEP) {
+                                const float4 b0 = inv4[KEEP ? r : 0][i][0], b1 = inv4[KEEP ? r : 0][i][1];
+                                a0.x += b0.x; a0.y += b0.y; a0.z += b0.z; a0.w += b0.w;
+                                a1.x += b1.x; a1.y += b1.y; a1.z += b1.z; a1.w += b1.w;
+                            } else {                         // padding position: context 0 (:1141-1143)
 #pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                float4 a = __ldg(p.P + (size_t)x * W + u + e);
-                                if (real && KEEP) {
-                                    const float4 b = inv4[KEEP ? r : 0][i][e];
-                                    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-                                } else {                     // padding position: context 0 (:1141-1143)
-#pragma unroll
-                                    for (int k = 0; k < KLM_MAX_CTX; ++k)
-                                        if (k < p.Nc) {
-                                            const float4 b = __ldg(p.Q[k] + (real ? (size_t)zk[k] * W : (size_t)0) + u + e);
-                                            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-                                        }
-                                }
-                                add4[i][e] = a;
+                                for (int k = 0; k < KLM_MAX_CTX; ++k)
+                                    if (k < p.Nc) {
+                                        float4 b0, b1;
+                                        tc_ldg_pair(p.Q[k] + (real ? (size_t)zk[k] * W : (size_t)0) + u, b0, b1);
+                                        a0.x += b0.x; a0.y += b0.y; a0.z += b0.z; a0.w += b0.w;
+                                        a1.x += b1.x; a1.y += b1.y; a1.z += b1.z; a1.w += b1.w;
+                                    }
                             }
+                            add4[i][0] = a0; add4[i][1] = a1;
                         }
                 } else {
                     // Z is [layer][parity][unit][64 streams] float4: the lanes of a warp (consecutive streams) touch 512

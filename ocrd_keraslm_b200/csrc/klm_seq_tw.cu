@@ -39,6 +39,7 @@ struct TwCtx {
 
 // Producer warp (converged; the elected lane issues): per tick the B parts of the first ring round go out before the
 // grid barrier (they do not depend on the tick), the A tiles follow behind it.
+template <bool TRACE>
 __device__ __noinline__ void tw_produce(const KlmTcParams &p, const TwCtx &x) {
     const uint32_t ring_a = x.ring_a, bar_full = x.bar_full, bar_empty = x.bar_empty, bar_go = x.bar_go;
     const uint32_t slot_bytes = x.slot_bytes, cbb = x.cbb;
@@ -65,6 +66,7 @@ __device__ __noinline__ void tw_produce(const KlmTcParams &p, const TwCtx &x) {
         if (lane0) {
             okg = tc_wait_grid(p, (unsigned)(tick + 1) * G, 1) ? 1 : 0;
             if (okg) tc::mbar_arrive(bar_go);
+            if (TRACE && okg) tc_trace(p, tick, 0);
         }
         if (!__shfl_sync(0xffffffffu, okg, 0)) return;
         const unsigned char *src_hi = hx0 + (size_t)((tick & 1) * 2) * tile_bytes, *src_lo = src_hi + tile_bytes;
@@ -82,6 +84,7 @@ __device__ __noinline__ void tw_produce(const KlmTcParams &p, const TwCtx &x) {
                 }
                 tc::bulk_g2s(dst, src_hi + (size_t)c * TW_ACH, TW_ACH, bar);
                 tc::bulk_g2s(dst + TW_ACH, src_lo + (size_t)c * TW_ACH, TW_ACH, bar);
+                if (TRACE && c0 == 0) tc_trace(p, tick, 1);
             }
             __syncwarp();
             phbits ^= 1u << st;
@@ -92,6 +95,7 @@ __device__ __noinline__ void tw_produce(const KlmTcParams &p, const TwCtx &x) {
 }
 
 // MMA warp: per k-step of 16 three MMAs into the same N accumulator columns (hi.hi, hi.lo, lo.hi).
+template <bool TRACE>
 __device__ __noinline__ void tw_mma(const KlmTcParams &p, const TwCtx &x) {
     const uint32_t idesc = tc::idesc_f16(128, x.N);
     const uint32_t lbo_a = 128 * 16, lbo_b = 2 * x.N * 16;
@@ -114,6 +118,7 @@ __device__ __noinline__ void tw_mma(const KlmTcParams &p, const TwCtx &x) {
             if (!__all_sync(0xffffffffu, okw)) return;
             const uint64_t ad = a_base + (uint32_t)st * slot16, bd = b_base + (uint32_t)st * slot16;
             if (tc::elect_one()) {
+                if (TRACE && (c0 == 0 || c0 == NCH - 1)) tc_trace(p, tick, c0 == 0 ? 2 : 3);
 #pragma unroll
                 for (int kk = 0; kk < TW_KC / 16; ++kk) {
                     const uint64_t a = ad + kk * a_k16, b = bd + kk * b_k16;
@@ -138,7 +143,7 @@ namespace {
 // Epilogue of one GEMM CTA.  KIND = KLM_TC_REC / KLM_TC_IN / KLM_TC_PROJ (compile-time: a REC CTA carries no IN state
 // and vice versa -- the kernel runs at 168 registers per thread).  A thread owns stream s = 32 (warp & 3) + lane and NP / 2
 // of the CTA's unit pairs, finished in rounds of two pairs (16 accumulator columns).
-template <int KIND>
+template <int KIND, bool TRACE>
 __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRole &role, const TwCtx &x, unsigned char *smem) {
     constexpr bool REC = KIND == KLM_TC_REC;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -223,17 +228,17 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
                 if (2 * r + i < NPT) {
                     const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
                     if (l == 0) {
+                        float4 a0, a1;
+                        tc_ldg_pair(p.P + (size_t)xc * W + u, a0, a1);
 #pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            float4 a = __ldg(p.P + (size_t)xc * W + u + e);
-#pragma unroll
-                            for (int k = 0; k < KLM_MAX_CTX; ++k)
-                                if (k < p.Nc) {
-                                    const float4 b = __ldg(p.Q[k] + (real ? (size_t)zk[k] * W : (size_t)0) + u + e);
-                                    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-                                }
-                            a4[i][e] = a;
-                        }
+                        for (int k = 0; k < KLM_MAX_CTX; ++k)
+                            if (k < p.Nc) {
+                                float4 b0, b1;
+                                tc_ldg_pair(p.Q[k] + (real ? (size_t)zk[k] * W : (size_t)0) + u, b0, b1);
+                                a0.x += b0.x; a0.y += b0.y; a0.z += b0.z; a0.w += b0.w;
+                                a1.x += b1.x; a1.y += b1.y; a1.z += b1.z; a1.w += b1.w;
+                            }
+                        a4[i][0] = a0; a4[i][1] = a1;
                     } else {
                         const float4 *zrow = reinterpret_cast<const float4 *>(p.Z) + ((size_t)(l * 2 + zs_in) * W) * 128 + s;
                         a4[i][0] = __ldcg(zrow + (size_t)u * 128); a4[i][1] = __ldcg(zrow + (size_t)(u + 1) * 128);
@@ -245,6 +250,7 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
 
         ok = tc_wait_mbar(x.bar_tfull, tick & 1, p, 6) ? 1 : 0;
         if (!__all_sync(0xffffffffu, ok)) break;
+        if (TRACE && tid == 64) tc_trace(p, tick, 4);
         tc::tc_fence_after();
 #pragma unroll
         for (int r = 0; r < TW_MAXR; ++r) {
@@ -260,6 +266,7 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
             if (r == nrounds - 1) {
                 tc::tc_fence_before();
                 tc::mbar_arrive(x.bar_tempty);                  // this thread is done reading TMEM
+                if (TRACE && tid == 64) tc_trace(p, tick, 5);
             }
             float4 add_nxt[2][2];
             if (REC && l > 0 && r + 1 < nrounds) load_add(r + 1, add_nxt);      // (coalesced: cheap to issue, in flight under the cell)
@@ -342,6 +349,7 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
         }
         // ---- hand over ----
         if (REC) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // staging writes -> bulk store reads
+        if (TRACE && tid == 64) tc_trace(p, tick, 6);
         tc_bar_epi();
         if (tid == 64) {
             if (REC) {
@@ -355,6 +363,7 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
                 asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");       // writes complete (not just read)
             }
             tc::red_release_add(p.barrier, 1u);
+            if (TRACE) tc_trace(p, tick, 7);
         }
         // (the staging is rewritten only behind the next tick's grid barrier, which this CTA's arrival -- behind the completed
         //  bulk store -- is part of)
@@ -376,8 +385,8 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
 
 }  // namespace
 
-__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tw(const __grid_constant__ KlmTcParams p) {
-    extern __shared__ __align__(1024) unsigned char smem[];
+template <bool TRACE>
+static __device__ __forceinline__ void tw_body(const KlmTcParams &p, unsigned char *smem) {
     const KlmTcRole role = p.roles[blockIdx.x];
     if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }
 
@@ -423,16 +432,16 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tw(const __grid_con
 
     if (warp == 0) {
         asm volatile("bar.sync 2, 320;" ::: "memory");       // (the epilogue warps' prologue: carried state in, bias staged)
-        tw_produce(p, x);
+        tw_produce<TRACE>(p, x);
     } else if (warp == 1) {
         asm volatile("bar.sync 2, 320;" ::: "memory");
-        tw_mma(p, x);
+        tw_mma<TRACE>(p, x);
     } else if (role.kind == KLM_TC_REC) {
-        tw_epilogue<KLM_TC_REC>(p, role, x, smem);
+        tw_epilogue<KLM_TC_REC, TRACE>(p, role, x, smem);
     } else if (role.kind == KLM_TC_IN) {
-        tw_epilogue<KLM_TC_IN>(p, role, x, smem);
+        tw_epilogue<KLM_TC_IN, TRACE>(p, role, x, smem);
     } else {
-        tw_epilogue<KLM_TC_PROJ>(p, role, x, smem);
+        tw_epilogue<KLM_TC_PROJ, TRACE>(p, role, x, smem);
     }
     tc::tc_fence_before();
     __syncthreads();
@@ -442,16 +451,28 @@ __global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tw(const __grid_con
     }
 }
 
+__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tw(const __grid_constant__ KlmTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    tw_body<false>(p, smem);
+}
+// timeline instrumentation compiled in: launched only while klm_tc_trace is armed
+__global__ void __launch_bounds__(KLM_TC_THREADS, 1) klm_seq_tw_traced(const __grid_constant__ KlmTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    tw_body<true>(p, smem);
+}
+
 // ring_bytes of the parameters = dynamic shared memory of the launch (the kernel derives the ring geometry from it)
 cudaError_t klm_launch_seq_tw(const KlmTcParams &p, int grid, size_t smem, cudaStream_t stream) {
     void *args[] = { const_cast<KlmTcParams *>(&p) };
-    static size_t smem_set[64] = {0};
+    static size_t smem_set[2][64] = {{0}};
+    const int which = p.trace ? 1 : 0;
+    const void *fn = which ? (const void *)klm_seq_tw_traced : (const void *)klm_seq_tw;
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64 || smem_set[dev] != smem) {
-        cudaError_t e = cudaFuncSetAttribute((const void *)klm_seq_tw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (dev < 0 || dev >= 64 || smem_set[which][dev] != smem) {
+        cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64) smem_set[dev] = smem;
+        if (dev >= 0 && dev < 64) smem_set[which][dev] = smem;
     }
-    return cudaLaunchCooperativeKernel((const void *)klm_seq_tw, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
+    return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(KLM_TC_THREADS), args, smem, stream);
 }

@@ -78,6 +78,14 @@ __device__ __forceinline__ void tc_cell(float ai, float af, float ag, float ao, 
     h = __fdividef(num, (1.f + eo) * den);
 }
 
+// Two adjacent float4 (32 bytes, 32-byte aligned) of a read-only table with ONE 256-bit load (LDG.E.256): the table-row
+// gathers of layer 1 are scattered over the lanes (every stream has its own character), so an instruction costs a sector
+// per lane whatever it fetches from it -- a pair of units per instruction halves the sectors touched per value.
+__device__ __forceinline__ void tc_ldg_pair(const float4 *p, float4 &a, float4 &b) {
+    asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
+
 // hidden value -> fp16 hi/lo operand pair, scaled by KLM_TC_HSCALE so that the lo part stays a normal fp16 number
 __device__ __forceinline__ void tc_split(float v, __half &hi, __half &lo) {
     v *= KLM_TC_HSCALE;

@@ -18,8 +18,9 @@ else:
     length = 512
     wd = synth.weights(3, width=width, depth=depth, style='keras')
 r = Rater.from_weights(wd, synth.vocabulary(), length, logger=log)
-texts = [synth.text(100 + i, T) for i in range(64)]
-ctxs = [[179]] * 64 if len(r.context_shapes) == 1 else [[1] * len(r.context_shapes)] * 64
+NS = int(os.environ.get('TC_TRACE_STREAMS', '64'))          # 128: the wide streamed kernel (klm_seq_tw)
+texts = [synth.text(100 + i, T) for i in range(NS)]
+ctxs = [[179]] * NS if len(r.context_shapes) == 1 else [[1] * len(r.context_shapes)] * NS
 r.rate_many(texts, ctxs)
 r._native.tc_trace_arm(1000)
 r.rate_many(texts, ctxs)
