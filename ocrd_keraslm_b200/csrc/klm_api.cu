@@ -1136,7 +1136,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         CK(cudaMemsetAsync(m->barrier, 0, 4, m->stream));
         if (wide) {
             // 65..128 streams of a streamed-weights plan: one launch of klm_seq_tw (skew 2, two slots of Z / logits)
-            q.wide = 1; q.hx = tp.hx_w; q.Z = tp.Z_w; q.logits = tp.logits_w;
+            q.wide = 1; q.hx = tp.hx_w; q.Z = tp.Z_w; q.logits = tp.logits_w; q.exp = m->knobs.tc_exp;
             q.skew = 2; q.zmask = 1; q.zlag = 1;
             q.ring_bytes = (int)tp.wide_smem;
             CK(klm_launch_seq_tw(q, tp.grid, tp.wide_smem, m->stream));

@@ -22,8 +22,7 @@
 #include <cstdio>
 #include "klm_tc_dev.cuh"
 
-#define TW_KC        64
-#define TW_ACH       (TW_KC * 256)          // bytes of one chunk of one A tile (64 k x 128 rows x 2 B)
+// k per ring chunk: 64 (A tile chunk 16 KB) when three slots fit, else 32 with up to six slots (slices of 22 pairs)
 #define TW_MAXR      6                      // epilogue rounds of 2 pairs per thread (<= 12 pairs per thread, 24 per CTA)
 #define TW_HEAD      1024                   // barriers (first 128 bytes) + bias of the slice (from byte 256)
 
@@ -31,8 +30,8 @@ namespace {
 
 struct TwCtx {
     uint32_t ring_a, bar_full, bar_empty, bar_tfull, bar_tempty, bar_go, tmem_base;
-    uint32_t slot_bytes, cbb;
-    int S, NCH, N, nticks, crot, src_layer, W;
+    uint32_t slot_bytes, cbb, ach;         // bytes of a ring slot, of its B part, of one A tile chunk
+    int S, NCH, N, nticks, crot, src_layer, W, kc;
     unsigned G;
     const unsigned char *bsrc;
 };
@@ -42,7 +41,7 @@ struct TwCtx {
 template <bool TRACE>
 __device__ __noinline__ void tw_produce(const KlmTcParams &p, const TwCtx &x) {
     const uint32_t ring_a = x.ring_a, bar_full = x.bar_full, bar_empty = x.bar_empty, bar_go = x.bar_go;
-    const uint32_t slot_bytes = x.slot_bytes, cbb = x.cbb;
+    const uint32_t slot_bytes = x.slot_bytes, cbb = x.cbb, ach = x.ach;
     const int S = x.S, NCH = x.NCH, nticks = x.nticks, crot = x.crot;
     const unsigned G = x.G;
     const unsigned char *bsrc = x.bsrc;
@@ -57,8 +56,8 @@ __device__ __noinline__ void tw_produce(const KlmTcParams &p, const TwCtx &x) {
             if (!__all_sync(0xffffffffu, okw)) return;
             if (tc::elect_one()) {
                 const int cb = crot + c0 >= NCH ? crot + c0 - NCH : crot + c0;
-                tc::mbar_arrive_expect_tx(bar_full + 8 * c0, 2 * TW_ACH + cbb);
-                tc::bulk_g2s(ring_a + c0 * slot_bytes + 2 * TW_ACH, bsrc + (size_t)cb * cbb, cbb, bar_full + 8 * c0);
+                tc::mbar_arrive_expect_tx(bar_full + 8 * c0, 2 * ach + cbb);
+                tc::bulk_g2s(ring_a + c0 * slot_bytes + 2 * ach, bsrc + (size_t)cb * cbb, cbb, bar_full + 8 * c0);
             }
             __syncwarp();
         }
@@ -79,11 +78,11 @@ __device__ __noinline__ void tw_produce(const KlmTcParams &p, const TwCtx &x) {
             if (tc::elect_one()) {
                 const uint32_t dst = ring_a + st * slot_bytes, bar = bar_full + 8 * st;
                 if (c0 >= npre) {
-                    tc::mbar_arrive_expect_tx(bar, 2 * TW_ACH + cbb);
-                    tc::bulk_g2s(dst + 2 * TW_ACH, bsrc + (size_t)c * cbb, cbb, bar);
+                    tc::mbar_arrive_expect_tx(bar, 2 * ach + cbb);
+                    tc::bulk_g2s(dst + 2 * ach, bsrc + (size_t)c * cbb, cbb, bar);
                 }
-                tc::bulk_g2s(dst, src_hi + (size_t)c * TW_ACH, TW_ACH, bar);
-                tc::bulk_g2s(dst + TW_ACH, src_lo + (size_t)c * TW_ACH, TW_ACH, bar);
+                tc::bulk_g2s(dst, src_hi + (size_t)c * ach, ach, bar);
+                tc::bulk_g2s(dst + ach, src_lo + (size_t)c * ach, ach, bar);
                 if (TRACE && c0 == 0) tc_trace(p, tick, 1);
             }
             __syncwarp();
@@ -100,8 +99,10 @@ __device__ __noinline__ void tw_mma(const KlmTcParams &p, const TwCtx &x) {
     const uint32_t idesc = tc::idesc_f16(128, x.N);
     const uint32_t lbo_a = 128 * 16, lbo_b = 2 * x.N * 16;
     const uint64_t a_base = tc::smem_desc(x.ring_a, lbo_a, 128);
-    const uint64_t b_base = tc::smem_desc(x.ring_a + 2 * TW_ACH, lbo_b, 128);
-    constexpr uint32_t a_k16 = (2 * 128 * 16) >> 4, a_lo = TW_ACH >> 4;
+    const uint64_t b_base = tc::smem_desc(x.ring_a + 2 * x.ach, lbo_b, 128);
+    constexpr uint32_t a_k16 = (2 * 128 * 16) >> 4;
+    const uint32_t a_lo = x.ach >> 4;
+    const int nk16 = x.kc / 16;
     const uint32_t b_k16 = (2 * lbo_b) >> 4, b_lo = (uint32_t)x.N;           // lo rows start N * 16 bytes into a k group
     const uint32_t slot16 = x.slot_bytes >> 4;
     const uint32_t bar_full = x.bar_full, bar_empty = x.bar_empty, bar_tfull = x.bar_tfull, bar_tempty = x.bar_tempty;
@@ -120,7 +121,8 @@ __device__ __noinline__ void tw_mma(const KlmTcParams &p, const TwCtx &x) {
             if (tc::elect_one()) {
                 if (TRACE && (c0 == 0 || c0 == NCH - 1)) tc_trace(p, tick, c0 == 0 ? 2 : 3);
 #pragma unroll
-                for (int kk = 0; kk < TW_KC / 16; ++kk) {
+                for (int kk = 0; kk < 4; ++kk) {
+                    if (kk >= nk16) break;
                     const uint64_t a = ad + kk * a_k16, b = bd + kk * b_k16;
                     tc::mma_f16(tmem_base, a, b, idesc, (c0 | kk) != 0 ? 1u : 0u);        // h_hi . W_hi
                     tc::mma_f16(tmem_base, a, b + b_lo, idesc, 1u);                        // h_hi . W_lo
@@ -158,6 +160,7 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
     __half *pub = reinterpret_cast<__half *>(smem + TW_HEAD);    // [tile hi, lo][group][128 rows][8]
     float4 *bias_sm = reinterpret_cast<float4 *>(smem + 256);
     const size_t tile_halves = (size_t)W * 128;
+    const bool pre0 = !(p.exp & 32);                             // (experiment switch: layer 1's table rows gathered per round)
 
     float c_reg[REC ? TW_MAXR : 1][2][2], h_reg[REC ? TW_MAXR : 1][2][2];
     long long o0 = 0;
@@ -227,7 +230,7 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
             for (int i = 0; i < 2; ++i)
                 if (2 * r + i < NPT) {
                     const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
-                    if (l == 0) {
+                    if (l == 0 && (r == 0 || !pre0)) {
                         float4 a0, a1;
                         tc_ldg_pair(p.P + (size_t)xc * W + u, a0, a1);
 #pragma unroll
@@ -240,6 +243,7 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
                             }
                         a4[i][0] = a0; a4[i][1] = a1;
                     } else {
+                        // layers above: Z of the IN stage; layer 1, rounds >= 1: what this thread gathered at the top of the tick
                         const float4 *zrow = reinterpret_cast<const float4 *>(p.Z) + ((size_t)(l * 2 + zs_in) * W) * 128 + s;
                         a4[i][0] = __ldcg(zrow + (size_t)u * 128); a4[i][1] = __ldcg(zrow + (size_t)(u + 1) * 128);
                     }
@@ -247,6 +251,31 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
         };
         float4 add4[2][2];
         load_add(0, add4);
+        if (REC && pre0 && l == 0 && active) {
+            // Layer 1, rounds >= 1: the table rows are gathered NOW, while the operand streams in and this warp has nothing
+            // to do, and parked in the layer's own (otherwise unused) Z slot in the coalesced [unit][128 streams] layout; the
+            // rounds then fetch them a round ahead like the layers above fetch Z.  Gathered just in time they cost an exposed
+            // L2 round trip per round (~3 000 clk of the tick: REC l0 was the last stage to reach the grid barrier).
+            float4 *zrow = reinterpret_cast<float4 *>(p.Z) + ((size_t)zs_in * W) * 128 + s;
+            for (int r = 1; r < nrounds; ++r) {
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+                    if (2 * r + i < NPT) {
+                        const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
+                        float4 a0, a1;
+                        tc_ldg_pair(p.P + (size_t)xc * W + u, a0, a1);
+#pragma unroll
+                        for (int k = 0; k < KLM_MAX_CTX; ++k)
+                            if (k < p.Nc) {
+                                float4 b0, b1;
+                                tc_ldg_pair(p.Q[k] + (real ? (size_t)zk[k] * W : (size_t)0) + u, b0, b1);
+                                a0.x += b0.x; a0.y += b0.y; a0.z += b0.z; a0.w += b0.w;
+                                a1.x += b1.x; a1.y += b1.y; a1.z += b1.z; a1.w += b1.w;
+                            }
+                        __stcg(zrow + (size_t)u * 128, a0); __stcg(zrow + (size_t)(u + 1) * 128, a1);
+                    }
+            }
+        }
 
         ok = tc_wait_mbar(x.bar_tfull, tick & 1, p, 6) ? 1 : 0;
         if (!__all_sync(0xffffffffu, ok)) break;
@@ -269,7 +298,7 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
                 if (TRACE && tid == 64) tc_trace(p, tick, 5);
             }
             float4 add_nxt[2][2];
-            if (REC && l > 0 && r + 1 < nrounds) load_add(r + 1, add_nxt);      // (coalesced: cheap to issue, in flight under the cell)
+            if (REC && (l > 0 || pre0) && r + 1 < nrounds) load_add(r + 1, add_nxt);      // (coalesced: cheap to issue, in flight under the cell)
             if constexpr (REC) {
                 // LSTM cell (Keras LSTMCell, gate order i|f|c|o, exact logistic: rating.py:133-134); 8 MUFU per unit, staged
                 float e1[2][2], e2[2][2], e3[2][2], e4[2][2], ag[2][2];
@@ -315,7 +344,7 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
                     }
                 }
                 if (r + 1 < nrounds) {
-                    if (l > 0) {
+                    if (l > 0 || pre0) {
 #pragma unroll
                         for (int i = 0; i < 2; ++i) { add4[i][0] = add_nxt[i][0]; add4[i][1] = add_nxt[i][1]; }
                     } else {
@@ -393,14 +422,18 @@ static __device__ __forceinline__ void tw_body(const KlmTcParams &p, unsigned ch
     const int tid = threadIdx.x, warp = tid >> 5;
     const int NP = role.npairs, N = 8 * NP, W = p.W;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem);
-    const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + 4);
-    const uint32_t bar_tfull = tc::smem_u32(bars + 8), bar_tempty = tc::smem_u32(bars + 9), bar_go = tc::smem_u32(bars + 10);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 11);
+    const uint32_t bar_full = tc::smem_u32(bars), bar_empty = tc::smem_u32(bars + 6);            // up to 6 ring slots
+    const uint32_t bar_tfull = tc::smem_u32(bars + 12), bar_tempty = tc::smem_u32(bars + 13), bar_go = tc::smem_u32(bars + 14);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 15);
     // ring geometry: everything behind the head and (REC) the publication staging, at most 3 slots
     const uint32_t pub_bytes = role.kind == KLM_TC_REC ? (uint32_t)(NP / 4) * 4096u : 0u;
-    const uint32_t cbb = (uint32_t)TW_KC * 32u * (uint32_t)NP;            // 8 k groups x 2N rows x 16 bytes
-    const uint32_t slot_bytes = 2u * TW_ACH + cbb;
-    const int S = min(3, (int)(((uint32_t)p.ring_bytes - TW_HEAD - pub_bytes) / slot_bytes));
+    const uint32_t room = (uint32_t)p.ring_bytes - TW_HEAD - pub_bytes;
+    int kc = 64;
+    if (3u * (2u * 64u * 256u + 64u * 32u * (uint32_t)NP) > room && !(p.exp & 64)) kc = 32;      // three slots of 64 k do not fit: finer chunks (+3 % on cfg5 over two slots of 64 k)
+    const uint32_t ach = (uint32_t)kc * 256u;                             // one chunk of one A tile: kc k x 128 rows x 2 B
+    const uint32_t cbb = (uint32_t)kc * 32u * (uint32_t)NP;               // kc / 8 k groups x 2N rows x 16 bytes
+    const uint32_t slot_bytes = 2u * ach + cbb;
+    const int S = min(kc == 64 ? 3 : 6, (int)(room / slot_bytes));
     if (S < 2 || NP < 2 || (NP & 1) || NP > 4 * TW_MAXR || (role.kind == KLM_TC_REC && (NP & 3))) {
         if (tid == 0) atomicCAS(p.err, 0, 91);               // (the host checks the plan before it launches this kernel)
         return;
@@ -424,9 +457,9 @@ static __device__ __forceinline__ void tw_body(const KlmTcParams &p, unsigned ch
     x.ring_a = tc::smem_u32(smem + TW_HEAD + pub_bytes);
     x.bar_full = bar_full; x.bar_empty = bar_empty; x.bar_tfull = bar_tfull; x.bar_tempty = bar_tempty; x.bar_go = bar_go;
     x.tmem_base = *tmem_slot;
-    x.slot_bytes = slot_bytes; x.cbb = cbb;
-    x.S = S; x.NCH = W / TW_KC; x.N = N; x.nticks = p.T_max + 2 * p.D;
-    x.crot = role.rot % (W / TW_KC); x.src_layer = role.src_layer; x.W = W;
+    x.slot_bytes = slot_bytes; x.cbb = cbb; x.ach = ach; x.kc = kc;
+    x.S = S; x.NCH = W / kc; x.N = N; x.nticks = p.T_max + 2 * p.D;
+    x.crot = role.rot % (W / kc); x.src_layer = role.src_layer; x.W = W;
     x.G = gridDim.x;
     x.bsrc = p.wimg + role.wofs;
 
