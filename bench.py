@@ -624,7 +624,7 @@ def run_ours(args):
     except Exception:
         pass
     roofline = {
-        'bound': 'tensor', 'kernel': ('klm_seq_tcs' if info.get('tc_enabled') == 3 else 'klm_seq_tc') if info.get('tc_launches', 0) > 0 else 'klm_seq_fma', 'achieved': achieved, 'peak': peak,
+        'bound': 'tensor', 'kernel': (('klm_seq_tw' if info.get('tc_wide_launches', 0) > 0 else 'klm_seq_tcs') if info.get('tc_enabled') == 3 else 'klm_seq_tc') if info.get('tc_launches', 0) > 0 else 'klm_seq_fma', 'achieved': achieved, 'peak': peak,
         'unit': 'TFLOP/s', 'frac': achieved / peak, 'traffic': traffic, 'peak_source': pk_src + ', bf16 sustained',
         'kernel_ms': k_ms, 'algorithmic_flops_per_launch': chars_per_step * F,
         'algorithmic_hbm_bytes_per_launch': 8 * chars_per_step,

@@ -81,7 +81,8 @@ int klm_sync(klm_model *m);
 /* Run-time switches of the library (diagnostics and timing experiments; the defaults are the product configuration).
  * Initial values come from the environment variables of the same name in upper case with the prefix KLM_
  * (e.g. KLM_TC_SKEW), read once in klm_create.  Names: tc_skew, tc_trace_mode, tc_debug_skip, tc_poll, tc_zpub,
- * tc_pub_release, tc_spin_limit, tc_fault, tc_df, tc_consumer_fence, ll_debug, step_timing. */
+ * tc_pub_release, tc_spin_limit, tc_fault, tc_df, tc_wide, tc_exp, tc_consumer_fence, ll_debug, step_mapped,
+ * step_timing. */
 int klm_set_option(klm_model *m, const char *name, int64_t value);
 
 /*
@@ -215,7 +216,7 @@ typedef struct klm_info {
     int32_t smem_bytes;         /* dynamic shared memory per CTA */
     int64_t kernel_launches;    /* kernels of this library launched so far on this model */
     double  last_kernel_ms;     /* device time of the last klm_rate/klm_step main kernel (CUDA events) */
-    int32_t max_streams;        /* largest n one launch takes; larger calls are split */
+    int32_t max_streams;        /* largest n one launch takes (128 with tc_wide); larger calls are split */
     int32_t tc_enabled;         /* tcgen05 sequence kernel serving 9..64 streams: 0 none (FMA kernels), 1 weights resident in
                                  * shared memory, 2 CTA-pair variant, 3 weights streamed through the operand ring */
     int32_t tc_grid;            /* CTAs of the tcgen05 kernel */
@@ -225,6 +226,8 @@ typedef struct klm_info {
     int32_t cl_cluster;         /* CTAs of that cluster (8 or 16); 0 = the model does not fit one cluster */
     int32_t tc_dataflow;        /* 1: the tcgen05 kernel in use is the dataflow form (a flag per hand-over, no grid barrier;
                                  * also serves klm_step for up to 256 hypotheses per launch), 0: the grid-barrier form */
+    int32_t tc_wide;            /* 1: calls of more than 64 streams run in launches of 128 (klm_seq_tw, streamed-weights plans) */
+    int64_t tc_wide_launches;   /* launches of klm_seq_tw so far (counted in tc_launches as well) */
 } klm_info;
 int klm_get_info(klm_model *m, klm_info *out);
 

@@ -92,7 +92,8 @@ class KlmInfo(ctypes.Structure):
                 ('smem_bytes', ctypes.c_int32), ('kernel_launches', ctypes.c_int64),
                 ('last_kernel_ms', ctypes.c_double), ('max_streams', ctypes.c_int32), ('tc_enabled', ctypes.c_int32),
                 ('tc_grid', ctypes.c_int32), ('tc_smem_bytes', ctypes.c_int32), ('tc_launches', ctypes.c_int64),
-                ('cl_launches', ctypes.c_int64), ('cl_cluster', ctypes.c_int32), ('tc_dataflow', ctypes.c_int32)]
+                ('cl_launches', ctypes.c_int64), ('cl_cluster', ctypes.c_int32), ('tc_dataflow', ctypes.c_int32),
+                ('tc_wide', ctypes.c_int32), ('tc_wide_launches', ctypes.c_int64)]
 
 
 # every symbol include/keraslm_b200.h declares: (name, restype, argtypes)

@@ -1559,13 +1559,15 @@ extern "C" int klm_get_info(klm_model *m, klm_info *out) {
     out->weights_in_smem = m->plan_b.wsmem;
     out->smem_bytes = (int32_t)m->plan_b.smem;
     out->kernel_launches = m->launches;
-    out->max_streams = m->tc.ok ? KLM_TC_STREAMS : m->plan_b.max_streams;
+    out->max_streams = m->tc.ok ? ((m->tc.wide_ok && m->knobs.tc_wide) ? 2 * KLM_TC_STREAMS : KLM_TC_STREAMS) : m->plan_b.max_streams;
     out->tc_enabled = m->tc.ok ? (m->tc.stream_b ? 3 : 1) : 0; // 3: streamed-weights form (images stay in global memory / L2)
     out->tc_grid = m->tc.grid;
     out->tc_smem_bytes = (int32_t)m->tc.smem;
     out->tc_launches = m->tc_launches;
     out->cl_launches = m->cl_launches; out->cl_cluster = m->cl.C;
     out->tc_dataflow = (m->tc.ok && m->tc.df_ok && m->knobs.tc_df) ? 1 : 0;
+    out->tc_wide = (m->tc.ok && m->tc.wide_ok && m->knobs.tc_wide) ? 1 : 0;
+    out->tc_wide_launches = m->tc.wide_launches;
     if (m->timed) {
         CK(cudaSetDevice(m->device));
         CK(cudaEventSynchronize(m->ev1));
