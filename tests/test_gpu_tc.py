@@ -422,3 +422,33 @@ def test_tw_states_carry_over_launches_like_the_narrow_kernel():
     assert not np.isnan(results[1][0]).any()
     assert np.abs(results[1][0].astype(np.float64) - results[0][0]).max() <= 1e-4
     assert np.abs(results[1][1] - results[0][1]).max() <= 1e-4 * np.abs(results[0][1]).max()
+
+
+def test_tw_padding_positions_take_context_zero_like_the_narrow_kernel():
+    """n_real (window padding of Rater.rate, rating.py:1141-1143: positions >= n_real[s] see context 0) through klm_seq_tw:
+    90 streams with padded tails, scores equal to klm_seq_tcs on the same call."""
+    width, depth, n = 1024, 2, 90
+    wd = synth.weights(19, width=width, depth=depth, voc_size=256, contexts=((200, 10),), style='trained')
+    r = product(wd, synth.vocabulary(), 16)
+    nat = r._native
+    rng = np.random.default_rng(90)
+    lens = rng.integers(3, 30, n)
+    n_real = np.maximum(lens - rng.integers(0, 4, n), 1).astype(np.int32)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    chars = rng.integers(1, 200, int(lens.sum())).astype(np.int32)
+    targets = rng.integers(1, 200, int(lens.sum())).astype(np.int32)
+    ctx = [[int(c)] for c in rng.integers(1, 200, n)]
+    out = {}
+    for mode in (1, 0):
+        nat.set_option('tc_wide', mode)
+        slots = r._pool.acquire(n)
+        nat.state_reset(slots)
+        logp = np.full(len(chars), np.nan, dtype=np.float32)
+        before = nat.info()['tc_wide_launches']
+        nat.rate(slots, offsets, chars, targets, n_real, ctx, logp)
+        assert nat.info()['tc_wide_launches'] - before == (1 if mode else 0)
+        out[mode] = logp
+        r._pool.release_many(slots)
+    nat.set_option('tc_wide', 1)
+    assert not np.isnan(out[1]).any()
+    assert np.abs(out[1].astype(np.float64) - out[0]).max() <= 1e-4
