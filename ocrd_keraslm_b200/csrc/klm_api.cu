@@ -11,6 +11,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <queue>
 
 #include "klm_common.cuh"
 
@@ -812,6 +813,7 @@ extern "C" int klm_create(const klm_config *cfg, const float *const *weights, in
     TRYC(cudaMalloc(&m->barrier, 256));
     m->ring_bytes = (size_t)m->bp_cap * (4 * 4 + 8 + 4 * KLM_MAX_CTX) + 64;
     m->ring_bytes = std::max(m->ring_bytes, (size_t)1 << 16);
+    if (m->tc.wide_ok) m->ring_bytes = std::max(m->ring_bytes, (size_t)KLM_TW_MAX_STREAMS * (4 * 4 + 8 + 4 * KLM_MAX_CTX) + 1024);
     for (int i = 0; i < KLM_RING; ++i) {
         TRYC(cudaMallocHost(&m->h_ring[i], m->ring_bytes));
         TRYC(cudaMalloc(&m->d_ring[i], m->ring_bytes));
@@ -1067,7 +1069,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
                      const int32_t *n_real, const int32_t *ctx, const int *d_chars, const int *d_targets, float *d_out,
                      int full_rows) {
     KlmPlan &pl = (nb <= KLM_MODEK_MAXB) ? m->plan_k : m->plan_b;
-    const bool wide = m->tc.ok && m->tc.wide_ok && nb > KLM_TC_STREAMS && nb <= 2 * KLM_TC_STREAMS;
+    const bool wide = m->tc.ok && m->tc.wide_ok && nb > KLM_TC_STREAMS && nb <= KLM_TW_MAX_STREAMS;
     if (nb > pl.max_streams && !wide) return fail(KLM_EINVAL, "internal: batch of %d streams exceeds plan (%d)", nb, pl.max_streams);
     long long tmax = 0;
     for (int s = 0; s < nb; ++s) {
@@ -1077,8 +1079,35 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
     }
     if (tmax == 0) return KLM_OK;
     RingSlot rs;
-    int rc = ring_acquire(m, &rs, (size_t)nb * (4 * 3 + 4 * m->Nc) + (nb + 1) * 8 + 128);
+    int rc = ring_acquire(m, &rs, (size_t)nb * (4 * 4 + 4 * m->Nc) + (nb + 1) * 8 + 130 * 4 + 192);
     if (rc) return rc;
+    // wide form: the streams are queued on the 128 rows of the accumulator (longest-processing-time first; a text costs its
+    // positions + one gap tick), a row rates its texts one after the other in ONE launch
+    std::vector<int> lane_ptr, lane_streams;
+    if (wide) {
+        const int R = 2 * KLM_TC_STREAMS;
+        std::vector<int> order(nb);
+        for (int i = 0; i < nb; ++i) order[i] = i;
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+            return offsets0[a + 1] - offsets0[a] > offsets0[b + 1] - offsets0[b]; });
+        typedef std::pair<long long, int> LR;                                   // (load, row): least loaded first, ties by row
+        std::priority_queue<LR, std::vector<LR>, std::greater<LR>> heap;
+        for (int r = 0; r < R; ++r) heap.push(LR(0, r));
+        std::vector<std::vector<int>> rows(R);
+        for (int i : order) {
+            LR top = heap.top(); heap.pop();
+            rows[top.second].push_back(i);
+            heap.push(LR(top.first + (offsets0[i + 1] - offsets0[i]) + 1, top.second));
+        }
+        lane_ptr.assign(R + 1, 0);
+        tmax = 0;
+        for (int r = 0; r < R; ++r) {
+            long long load = 0;
+            for (int i : rows[r]) { lane_streams.push_back(i); load += (offsets0[i + 1] - offsets0[i]) + 1; }
+            lane_ptr[r + 1] = (int)lane_streams.size();
+            tmax = std::max(tmax, load);
+        }
+    }
     if (m->tc.ok && nb > KLM_MODEK_MAXB && (nb <= KLM_TC_STREAMS || wide)) {
         KlmTcPlan &tp = m->tc;
         if ((double)(tmax + 3 * m->D + 2) * tp.grid >= 4.0e9)
@@ -1093,7 +1122,13 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         if (n_real) ring_put(&rs, n_real, nb, &d_nr);
         int *hcx = ring_put<int>(&rs, nullptr, (size_t)nb * std::max(1, m->Nc), &d_cx);
         for (int i = 0; i < nb * m->Nc; ++i) hcx[i] = ctx ? ctx[i] : 0;
+        int *d_lp = nullptr, *d_ls = nullptr;
+        if (wide) {
+            ring_put(&rs, lane_ptr.data(), lane_ptr.size(), &d_lp);
+            ring_put(&rs, lane_streams.data(), lane_streams.size(), &d_ls);
+        }
         rc = ring_commit(m, &rs); if (rc) return rc;
+        q.lane_ptr = d_lp; q.lane_streams = d_ls;
         q.W = m->W; q.D = m->D; q.V = m->V; q.Vp = tp.Vp; q.Nc = m->Nc;
         q.B = nb; q.T_max = (int)tmax; q.stages = tp.stages;
         for (int k = 0; k < m->Nc; ++k) { q.ctx_rows[k] = m->cfg.ctx_rows[k]; q.Q[k] = m->Q[k]; }
@@ -1137,6 +1172,7 @@ static int run_batch(klm_model *m, int nb, const int32_t *slots_in, const int32_
         if (wide) {
             // 65..128 streams of a streamed-weights plan: one launch of klm_seq_tw (skew 2, two slots of Z / logits)
             q.wide = 1; q.hx = tp.hx_w; q.Z = tp.Z_w; q.logits = tp.logits_w; q.exp = m->knobs.tc_exp;
+            q.B = std::min(nb, 2 * KLM_TC_STREAMS);                          // rows in use
             q.skew = 2; q.zmask = 1; q.zlag = 1;
             q.ring_bytes = (int)tp.wide_smem;
             CK(klm_launch_seq_tw(q, tp.grid, tp.wide_smem, m->stream));
@@ -1254,7 +1290,7 @@ static int launch_step_df(klm_model *m, int nb, const int *d_si, const int *d_so
 // Largest number of streams one launch takes for a call of n streams.
 static int batch_max(klm_model *m, int n) {
     if (n <= KLM_MODEK_MAXB) return KLM_MODEK_MAXB;
-    if (m->tc.ok) return (m->tc.wide_ok && m->knobs.tc_wide && n > KLM_TC_STREAMS) ? 2 * KLM_TC_STREAMS : KLM_TC_STREAMS;
+    if (m->tc.ok) return (m->tc.wide_ok && m->knobs.tc_wide && n > KLM_TC_STREAMS) ? KLM_TW_MAX_STREAMS : KLM_TC_STREAMS;
     return m->plan_b.max_streams;
 }
 
@@ -1559,7 +1595,7 @@ extern "C" int klm_get_info(klm_model *m, klm_info *out) {
     out->weights_in_smem = m->plan_b.wsmem;
     out->smem_bytes = (int32_t)m->plan_b.smem;
     out->kernel_launches = m->launches;
-    out->max_streams = m->tc.ok ? ((m->tc.wide_ok && m->knobs.tc_wide) ? 2 * KLM_TC_STREAMS : KLM_TC_STREAMS) : m->plan_b.max_streams;
+    out->max_streams = m->tc.ok ? ((m->tc.wide_ok && m->knobs.tc_wide) ? KLM_TW_MAX_STREAMS : KLM_TC_STREAMS) : m->plan_b.max_streams;
     out->tc_enabled = m->tc.ok ? (m->tc.stream_b ? 3 : 1) : 0; // 3: streamed-weights form (images stay in global memory / L2)
     out->tc_grid = m->tc.grid;
     out->tc_smem_bytes = (int32_t)m->tc.smem;

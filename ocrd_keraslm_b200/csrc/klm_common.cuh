@@ -125,6 +125,7 @@ struct KlmClGeom {
 // aliased), so that the B parts of the next tick's first chunks can be fetched while the epilogue still runs
 // (KlmTcRole::ring_ofs = KLM_TC1_PUB_OFS + 2 KB per group of 8 units of a REC slice)
 #define KLM_TCS_MAX_PAIRS   24
+#define KLM_TW_MAX_STREAMS  4096                   // wide form (klm_seq_tw): streams of one launch, queued on its 128 rows
 #define KLM_TC_TRACE_TICKS  16
 // fp16 has 5 exponent bits: the lo part of a hi/lo split (|lo| <= 2^-11 |x|) falls into the subnormal range (below
 // 6.1e-5) for |x| < 0.125, and with Keras-default initialisation hidden values are ~1e-3 and weights ~0.05 -- the split
@@ -252,5 +253,7 @@ struct KlmTcParams {
     unsigned spin_limit;          // device-side watchdog: polls of one wait before it gives up (klm_set_option "tc_spin_limit")
     int fault;                    // test hook (klm_set_option "tc_fault"): CTA 0 withholds its hand-over signal of tick 2
     int wide;                     // 1: klm_seq_tw -- 128 streams per launch (exchange buffers and LSE rows of 128 streams)
+    const int *lane_ptr;          // klm_seq_tw: row r of the accumulator rates the streams lane_streams[lane_ptr[r] .. lane_ptr[r+1]) one
+    const int *lane_streams;      //   after the other, a gap tick between two texts (129 / n ints)
     KlmStepArgs step;             // (last: only the launches of a beam step fill it)
 };

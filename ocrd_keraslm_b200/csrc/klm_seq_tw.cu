@@ -163,28 +163,69 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
     const bool pre0 = !(p.exp & 32);                             // (experiment switch: layer 1's table rows gathered per round)
 
     float c_reg[REC ? TW_MAXR : 1][2][2], h_reg[REC ? TW_MAXR : 1][2][2];
+    // The row's queue of texts (continuous batching: KlmTcParams::lane_ptr): text `cur` occupies positions g0 .. g0 + len - 1
+    // of the row's time line, position g0 + len is a gap tick in which the recurrence stages swap the state (final state of
+    // the text to its slot, initial state of the next text in, and THAT is what they publish), then the next text starts.
+    int cur = 0, qend = 0, sid = -1, len = 0, g0 = 0;
     long long o0 = 0;
-    int len = 0;
-    if (s < p.B) { o0 = p.offsets[s]; len = (int)(p.offsets[s + 1] - o0); }
     int x_next = 0, nreal_s = 0x7fffffff;
     int zk[KLM_MAX_CTX];
 #pragma unroll
     for (int k = 0; k < KLM_MAX_CTX; ++k) zk[k] = 0;
+    auto open_text = [&]() {
+        sid = -1; len = 0; o0 = 0;
+        if (cur < qend) { sid = __ldg(p.lane_streams + cur); o0 = p.offsets[sid]; len = (int)(p.offsets[sid + 1] - o0); }
+    };
+    // state of the open text in (zeros if the row has run out of texts); layer 1 also fetches what its input needs
+    auto load_text_state = [&]() {
+        const int slot = sid >= 0 ? p.slots_in[sid] : -1;
+#pragma unroll
+        for (int r = 0; r < (REC ? TW_MAXR : 0); ++r)
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                c_reg[r][i][0] = c_reg[r][i][1] = h_reg[r][i][0] = h_reg[r][i][1] = 0.f;
+                if (2 * r + i < NPT && slot >= 0) {
+                    const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
+                    const float *st = p.state + ((size_t)slot * p.D + l) * 2 * W;
+                    const float2 h2 = *reinterpret_cast<const float2 *>(st + u), c2 = *reinterpret_cast<const float2 *>(st + W + u);
+                    h_reg[r][i][0] = h2.x; h_reg[r][i][1] = h2.y; c_reg[r][i][0] = c2.x; c_reg[r][i][1] = c2.y;
+                }
+            }
+        if (l == 0) {
+            x_next = 0; nreal_s = 0x7fffffff;
+            if (sid >= 0) {
+                if (len > 0) x_next = __ldg(p.chars + o0);
+                if (p.n_real) nreal_s = __ldg(p.n_real + sid);
+#pragma unroll
+                for (int k = 0; k < KLM_MAX_CTX; ++k)
+                    if (k < p.Nc) zk[k] = min(max(__ldg(p.ctx + sid * p.Nc + k), 0), p.ctx_rows[k] - 1);
+            }
+        }
+    };
+    auto store_text_state = [&]() {
+        if (sid < 0) return;
+        float *st = p.state + ((size_t)p.slots_out[sid] * p.D + l) * 2 * W;
+#pragma unroll
+        for (int r = 0; r < (REC ? TW_MAXR : 0); ++r)
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+                if (2 * r + i < NPT) {
+                    const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
+                    *reinterpret_cast<float2 *>(st + u) = make_float2(h_reg[r][i][0], h_reg[r][i][1]);
+                    *reinterpret_cast<float2 *>(st + W + u) = make_float2(c_reg[r][i][0], c_reg[r][i][1]);
+                }
+    };
     if constexpr (REC) {
-        // ---- carried state in, initial hidden vector published for tick 0 (parity 0) ----
-        const int slot = s < p.B ? p.slots_in[s] : -1;
+        // ---- first text of the row: carried state in, initial hidden vector published for tick 0 (parity 0) ----
+        cur = __ldg(p.lane_ptr + s); qend = __ldg(p.lane_ptr + s + 1);
+        open_text();
+        load_text_state();
 #pragma unroll
         for (int r = 0; r < TW_MAXR; ++r)
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
-                c_reg[r][i][0] = c_reg[r][i][1] = h_reg[r][i][0] = h_reg[r][i][1] = 0.f;
                 if (2 * r + i < NPT) {
                     const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
-                    if (slot >= 0) {
-                        const float *st = p.state + ((size_t)slot * p.D + l) * 2 * W;
-                        h_reg[r][i][0] = st[u]; h_reg[r][i][1] = st[u + 1];
-                        c_reg[r][i][0] = st[W + u]; c_reg[r][i][1] = st[W + u + 1];
-                    }
                     __half hi0, lo0, hi1, lo1;
                     tc_split(h_reg[r][i][0], hi0, lo0); tc_split(h_reg[r][i][1], hi1, lo1);
                     __half *dst = p.hx + (size_t)(l * 4) * tile_halves + (size_t)(u / 8) * (128 * 8) + (size_t)s * 8 + (u & 7);
@@ -193,13 +234,6 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
                 }
             }
         tc::fence_proxy_async();                    // generic global writes -> later bulk (async proxy) reads
-        if (l == 0 && s < p.B) {
-            if (len > 0) x_next = __ldg(p.chars + o0);
-            if (p.n_real) nreal_s = __ldg(p.n_real + s);
-#pragma unroll
-            for (int k = 0; k < KLM_MAX_CTX; ++k)
-                if (k < p.Nc) zk[k] = min(max(__ldg(p.ctx + s * p.Nc + k), 0), p.ctx_rows[k] - 1);
-        }
     }
     if (KIND == KLM_TC_IN)
         for (int j = tid - 64; j < 2 * NP; j += 256) bias_sm[j] = __ldg(p.bias[l] + 2 * role.first_pair + j);
@@ -210,8 +244,17 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
     for (int tick = 0; tick < nticks; ++tick) {
         int ok = tc_wait_mbar(x.bar_go, tick & 1, p, 5) ? 1 : 0;
         if (!__all_sync(0xffffffffu, ok)) break;
-        const int t = tick - sigma;
-        const bool active = s < p.B && t >= 0 && t < len;
+        int t = tick - sigma - g0;
+        if (REC && sid >= 0 && t == len) {
+            // gap tick behind text `cur`: its final state out, the next text's initial state in (its loads are in flight while
+            // the operand streams in; the rounds below stage and publish the new hidden values unchanged: nothing is active)
+            store_text_state();
+            ++cur; g0 += len + 1;
+            open_text();
+            load_text_state();
+            t = -1;
+        }
+        const bool active = REC && sid >= 0 && t >= 0 && t < len;
         const int par_out = (tick + 1) & 1, zs_in = tick & 1, zs_out = (tick + 1) & 1;
         int xc = 0;
         bool real = true;
@@ -397,27 +440,121 @@ __device__ __forceinline__ void tw_epilogue(const KlmTcParams &p, const KlmTcRol
         // (the staging is rewritten only behind the next tick's grid barrier, which this CTA's arrival -- behind the completed
         //  bulk store -- is part of)
     }
-    // ---- write the final state back ----
-    if constexpr (REC) if (s < p.B) {
-        float *st = p.state + ((size_t)p.slots_out[s] * p.D + l) * 2 * W;
-#pragma unroll
-        for (int r = 0; r < TW_MAXR; ++r)
-#pragma unroll
-            for (int i = 0; i < 2; ++i)
-                if (2 * r + i < NPT) {
-                    const int u = 2 * (role.first_pair + pfirst + 2 * r + i);
-                    st[u] = h_reg[r][i][0]; st[u + 1] = h_reg[r][i][1];
-                    st[W + u] = c_reg[r][i][0]; st[W + u + 1] = c_reg[r][i][1];
-                }
-    }
+    // (the final state of a row's last text went out in its gap tick: the launch covers it; a text still open here means the
+    //  host sized the launch too short)
+    if constexpr (REC) store_text_state();
 }
 
 }  // namespace
 
+
+// LSE stage of the wide form: tc_lse_role (klm_tc_dev.cuh) with rows of 128 streams and the per-row text queues -- lane =
+// row, a warp covers 32 rows and one slice of the vocabulary; the row's text and position follow from the tick as in the
+// epilogue of the recurrence stages (a gap tick between two texts).
+static __device__ void tw_lse_role(const KlmTcParams &p, const KlmTcRole &role, unsigned char *dyn_smem) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const unsigned G = gridDim.x;
+    const int nticks = p.T_max + 2 * p.D;
+    const int V = p.V, Vq = p.Vp / 4, V4 = (V + 3) / 4, sigma = 2 * p.D, full_rows = p.full_rows;
+    const float4 *logits4 = reinterpret_cast<const float4 *>(p.logits);
+    const int *targets = p.targets;
+    float *out = p.out;
+    __shared__ int ok_s;
+    float (*part_m)[32] = reinterpret_cast<float (*)[32]>(dyn_smem);
+    float (*part_s)[32] = reinterpret_cast<float (*)[32]>(dyn_smem + TC_LSE_WARPS * 32 * sizeof(float));
+    const int ngroups = (p.B + 31) / 32;                                     // p.B = rows in use
+    const int gmine = role.first_pair < ngroups ? (ngroups - role.first_pair + role.npairs - 1) / role.npairs : 0;
+    const int nslices = gmine > 0 ? TC_LSE_WARPS / gmine : 1;
+    const int gl = warp / nslices, sl = warp - gl * nslices;
+    const bool warp_on = gmine > 0 && gl < gmine;
+    const int s = warp_on ? 32 * (role.first_pair + gl * role.npairs) + lane : 0;
+    int cur = 0, qend = 0, sid = -1, len = 0, g0 = 0;
+    long long o0 = 0;
+    auto open_text = [&]() {
+        sid = -1; len = 0; o0 = 0;
+        if (cur < qend) { sid = __ldg(p.lane_streams + cur); o0 = p.offsets[sid]; len = (int)(p.offsets[sid + 1] - o0); }
+    };
+    if (warp_on && s < 128) { cur = __ldg(p.lane_ptr + s); qend = __ldg(p.lane_ptr + s + 1); open_text(); }
+    const int v4_lo = (int)((long long)V4 * sl / nslices), v4_hi = (int)((long long)V4 * (sl + 1) / nslices);
+    if (tid == 0) tc::red_release_add(p.barrier, 1u);
+    for (int tick = 0; tick < nticks; ++tick) {
+        if (tid == 0) ok_s = tc_wait_grid(p, (unsigned)(tick + 1) * G, 10) ? 1 : 0;
+        __syncthreads();
+        if (!ok_s) return;
+        int t = tick - sigma - g0;
+        if (sid >= 0 && t == len) { ++cur; g0 += len + 1; open_text(); t = -1; }      // gap tick: next text of the row
+        const bool act = warp_on && sid >= 0 && t >= 0 && t < len;
+        const float4 *base = logits4 + (size_t)(tick & 1) * Vq * 128 + s;           // (slot written by PROJ one tick ago)
+        float tl = 0.f;
+        if (act && sl == 0 && !full_rows) {
+            int tg = __ldg(targets + o0 + t);
+            tg = min(max(tg, 0), V - 1);
+            tl = __ldcg(reinterpret_cast<const float *>(base + (size_t)(tg >> 2) * 128) + (tg & 3));
+        }
+        float m = -INFINITY, sum = 0.f;
+        if (warp_on && tick >= sigma) {
+            for (int v0 = v4_lo; v0 < v4_hi; v0 += 8) {
+                float4 x[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    x[j] = (v0 + j < v4_hi) ? __ldcg(base + (size_t)(v0 + j) * 128) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+                if (4 * (v0 + 8) > V) {                      // mask the padding entries of the last float4
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int v = 4 * (v0 + j);
+                        if (v + 1 >= V) x[j].y = -INFINITY;
+                        if (v + 2 >= V) x[j].z = -INFINITY;
+                        if (v + 3 >= V) x[j].w = -INFINITY;
+                        if (v >= V) x[j].x = -INFINITY;
+                    }
+                }
+                float mx = m;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) mx = fmaxf(fmaxf(fmaxf(mx, x[j].x), fmaxf(x[j].y, x[j].z)), x[j].w);
+                if (mx > -INFINITY) {
+                    float acc = sum * __expf(m - mx);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        acc += __expf(x[j].x - mx) + __expf(x[j].y - mx) + __expf(x[j].z - mx) + __expf(x[j].w - mx);
+                    sum = acc; m = mx;
+                }
+            }
+        }
+        part_m[warp][lane] = m; part_s[warp][lane] = sum;
+        __syncthreads();
+        float M = -INFINITY, S = 0.f;
+        if (warp_on) {
+            for (int i = 0; i < nslices; ++i) M = fmaxf(M, part_m[gl * nslices + i][lane]);
+            for (int i = 0; i < nslices; ++i) {
+                const float mi = part_m[gl * nslices + i][lane];
+                if (mi > -INFINITY) S += part_s[gl * nslices + i][lane] * __expf(mi - M);
+            }
+        }
+        if (act) {
+            if (!full_rows) {
+                if (sl == 0) out[o0 + t] = (tl - M) - logf(S);
+            } else {
+                float *dst = out + (size_t)(o0 + t) * V;
+                const float inv = 1.0f / S;
+                for (int v4 = v4_lo; v4 < v4_hi; ++v4) {
+                    const float4 x = __ldcg(base + (size_t)v4 * 128);
+                    const int v = 4 * v4;
+                    dst[v] = expf(x.x - M) * inv;
+                    if (v + 1 < V) dst[v + 1] = expf(x.y - M) * inv;
+                    if (v + 2 < V) dst[v + 2] = expf(x.z - M) * inv;
+                    if (v + 3 < V) dst[v + 3] = expf(x.w - M) * inv;
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) tc::red_release_add(p.barrier, 1u);
+    }
+}
+
 template <bool TRACE>
 static __device__ __forceinline__ void tw_body(const KlmTcParams &p, unsigned char *smem) {
     const KlmTcRole role = p.roles[blockIdx.x];
-    if (role.kind == KLM_TC_LSE) { tc_lse_role(p, role, smem); return; }
+    if (role.kind == KLM_TC_LSE) { tw_lse_role(p, role, smem); return; }
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const int NP = role.npairs, N = 8 * NP, W = p.W;

@@ -452,3 +452,48 @@ def test_tw_padding_positions_take_context_zero_like_the_narrow_kernel():
     nat.set_option('tc_wide', 1)
     assert not np.isnan(out[1]).any()
     assert np.abs(out[1].astype(np.float64) - out[0]).max() <= 1e-4
+
+
+def test_tw_rows_rate_queues_of_texts_in_one_launch():
+    """Continuous batching of klm_seq_tw: 700 texts (some empty, some of one character) queued on the 128 rows of ONE launch
+    -- a gap tick between two texts of a row swaps the state -- against klm_seq_tcs in 11 launches: scores and the final
+    state of every text (each in its own pool slot), plus the oracle on a sample."""
+    width, depth, n = 1024, 2, 700
+    wd = synth.weights(23, width=width, depth=depth, voc_size=256, contexts=((200, 10),), style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 16)
+    nat = r._native
+    rng = np.random.default_rng(700)
+    lens = rng.integers(0, 25, n)
+    lens[[3, 77, 130]] = 0
+    lens[[4, 500]] = 1
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    chars = rng.integers(1, 200, int(lens.sum())).astype(np.int32)
+    targets = rng.integers(1, 200, int(lens.sum())).astype(np.int32)
+    ctx = [[int(c)] for c in rng.integers(0, 200, n)]
+    res = {}
+    for mode in (1, 0):
+        nat.set_option('tc_wide', mode)
+        slots = r._pool.acquire(n)
+        nat.state_reset(slots)
+        logp = np.full(len(chars), np.nan, dtype=np.float32)
+        w0, t0 = nat.info()['tc_wide_launches'], nat.info()['tc_launches']
+        nat.rate(slots, offsets, chars, targets, None, ctx, logp)
+        if mode:
+            assert nat.info()['tc_wide_launches'] - w0 == 1 and nat.info()['tc_launches'] - t0 == 1
+        res[mode] = (logp, nat.state_to_host(slots))
+        r._pool.release_many(slots)
+    nat.set_option('tc_wide', 1)
+    assert not np.isnan(res[1][0]).any()
+    assert np.abs(res[1][0].astype(np.float64) - res[0][0]).max() <= 1e-4
+    assert np.abs(res[1][1] - res[0][1]).max() <= 1e-4 * np.abs(res[0][1]).max()
+    assert (res[1][1][[3, 77, 130]] == 0).all()                      # empty texts leave their (zero) state alone
+    from oracle import lstm_numpy as ln
+    w = util.to_model(wd)
+    for k in (0, 4, 129, 699):
+        if lens[k] == 0:
+            continue
+        x = chars[offsets[k]:offsets[k + 1]][None, :].astype(np.int64)
+        out, _ = ln.run_sequence(w, x, [np.full_like(x, ctx[k][0])], ln.zero_states(w, 1), want='target',
+                                 targets=targets[offsets[k]:offsets[k + 1]][None, :].astype(np.int64))
+        assert np.abs(res[1][0][offsets[k]:offsets[k + 1]] - np.log(out[0].astype(np.float64))).max() <= 1e-3
