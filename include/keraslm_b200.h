@@ -216,7 +216,7 @@ typedef struct klm_info {
     int32_t smem_bytes;         /* dynamic shared memory per CTA */
     int64_t kernel_launches;    /* kernels of this library launched so far on this model */
     double  last_kernel_ms;     /* device time of the last klm_rate/klm_step main kernel (CUDA events) */
-    int32_t max_streams;        /* largest n one launch takes (128 with tc_wide); larger calls are split */
+    int32_t max_streams;        /* largest n one launch takes (4096 with tc_wide: queued on 128 rows); larger calls are split */
     int32_t tc_enabled;         /* tcgen05 sequence kernel serving 9..64 streams: 0 none (FMA kernels), 1 weights resident in
                                  * shared memory, 2 CTA-pair variant, 3 weights streamed through the operand ring */
     int32_t tc_grid;            /* CTAs of the tcgen05 kernel */
@@ -226,7 +226,7 @@ typedef struct klm_info {
     int32_t cl_cluster;         /* CTAs of that cluster (8 or 16); 0 = the model does not fit one cluster */
     int32_t tc_dataflow;        /* 1: the tcgen05 kernel in use is the dataflow form (a flag per hand-over, no grid barrier;
                                  * also serves klm_step for up to 256 hypotheses per launch), 0: the grid-barrier form */
-    int32_t tc_wide;            /* 1: calls of more than 64 streams run in launches of 128 (klm_seq_tw, streamed-weights plans) */
+    int32_t tc_wide;            /* 1: calls of more than 64 streams run in launches of up to 4096 queued on 128 rows (klm_seq_tw, streamed-weights plans) */
     int64_t tc_wide_launches;   /* launches of klm_seq_tw so far (counted in tc_launches as well) */
 } klm_info;
 int klm_get_info(klm_model *m, klm_info *out);
