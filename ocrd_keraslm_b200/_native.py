@@ -48,6 +48,22 @@ def build(force=False, verbose=False):
     than the object), then linked."""
     if not force and not needs_build():
         return LIB_PATH
+    # one builder at a time: the ranks of a torchrun job that all find the library stale would otherwise compile into
+    # the same object files and link over each other (seen on an 8-GPU box: "file too short" / undefined symbols);
+    # the others wait for the lock, find the library fresh and return
+    import fcntl
+    os.makedirs(os.path.join(HERE, 'build'), exist_ok=True)
+    with open(os.path.join(HERE, 'build', '.lock'), 'w') as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not needs_build():
+                return LIB_PATH
+            return _build_locked(force, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(force, verbose):
     from concurrent.futures import ThreadPoolExecutor
     nvcc = os.environ.get('NVCC') or '/usr/local/cuda/bin/nvcc'
     if not os.path.exists(nvcc):
@@ -72,12 +88,14 @@ def build(force=False, verbose=False):
     for obj, rc, out in results:
         if rc != 0:
             raise NativeError('nvcc failed:\n' + out)
-    cmd = [nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-o', LIB_PATH] + [r[0] for r in results]
+    tmp = LIB_PATH + '.tmp%d' % os.getpid()          # linked beside the library and renamed: a reader never sees half a file
+    cmd = [nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-o', tmp] + [r[0] for r in results]
     if verbose:
         print(' '.join(cmd), file=sys.stderr)
     res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, universal_newlines=True)
     if res.returncode != 0:
         raise NativeError('nvcc (link) failed:\n' + res.stdout)
+    os.replace(tmp, LIB_PATH)
     return LIB_PATH
 
 
