@@ -497,3 +497,29 @@ def test_tw_rows_rate_queues_of_texts_in_one_launch():
         out, _ = ln.run_sequence(w, x, [np.full_like(x, ctx[k][0])], ln.zero_states(w, 1), want='target',
                                  targets=targets[offsets[k]:offsets[k + 1]][None, :].astype(np.int64))
         assert np.abs(res[1][0][offsets[k]:offsets[k + 1]] - np.log(out[0].astype(np.float64))).max() <= 1e-3
+
+
+@pytest.mark.parametrize('n', [100, 300])
+def test_tw_step_full_rows_and_states_match_fma(n):
+    """klm_step (Rater.predict: one position, full softmax rows, states handed back through other pool slots) for more
+    than 64 hypotheses on a streamed-weights model: one launch of klm_seq_tw (300 hypotheses queue up on its 128 rows)
+    against the FMA K-parallel kernel (groups of 8) on the same inputs, two steps deep."""
+    wd = synth.weights(83, width=1024, depth=2, voc_size=256, style='trained')
+    maparr = synth.vocabulary()
+    r = product(wd, maparr, 8, stateful=False, incremental=True)
+    nat = r._native
+    assert nat.info()['tc_enabled'] == 3 and nat.info()['tc_wide'] == 1
+    cands = [chr(97 + (i * 7) % 26) for i in range(n)]
+    w0 = nat.info()['tc_wide_launches']
+    p1, s1 = r.predict(list(cands), [None] * n, [3])
+    p2, s2 = r.predict(list(cands[::-1]), list(s1), [3])
+    assert nat.info()['tc_wide_launches'] - w0 == 2
+    np.testing.assert_allclose(np.stack(p2).sum(axis=1), 1.0, rtol=1e-5)
+    for lo in (0, 64, n - 8):
+        q1, t1 = r.predict(cands[lo:lo + 8], [None] * 8, [3])
+        q2, t2 = r.predict(cands[::-1][lo:lo + 8], list(t1), [3])
+        assert logp_err(np.stack(p1[lo:lo + 8]), np.stack(q1)) <= 1e-3
+        assert logp_err(np.stack(p2[lo:lo + 8]), np.stack(q2)) <= 1e-3
+        a = np.stack([np.concatenate(list(s), 0) for s in s2[lo:lo + 8]])
+        b = np.stack([np.concatenate(list(s), 0) for s in t2])
+        assert np.abs(a - b).max() <= 1e-4 * np.abs(b).max()
