@@ -600,6 +600,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         if (tid == 64) {
             const unsigned version = (unsigned)tick + 2u;
             bulk_out(hx_l + (size_t)(version & (KLM_DF_R - 1)) * hx_slice + (size_t)(role.first_pair / 4) * (128 * 8));
+            if (TRACE && (p.exp & 128)) tc_trace(p, tick, 6);          // (tc_exp bit 128: 'staged' = bulk store performed)
             // everything this CTA hands over went through that one bulk store and it has been performed (wait_group 0): a
             // release has nothing left to order (klm_set_option "tc_pub_release" restores it)
             if (p.fault && role.rot == 0 && tick == 2) { }                       // (test hook: the watchdog must end the launch)
