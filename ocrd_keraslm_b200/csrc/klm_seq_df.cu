@@ -58,7 +58,10 @@ __device__ __forceinline__ bool df_reached(unsigned v, unsigned target) { return
 // (scripts/exp/df_race.py); modes 2 / 3 are experiments (proxy fence + relaxed store; delay + relaxed store).
 __device__ __forceinline__ void df_signal(unsigned *flag, unsigned value, int mode) {
     if (mode == 1) df_st_release(flag, value);
-    else {
+    else if (mode == 4) {           // (experiment: the release as an atomic performed at the home L2 partition)
+        unsigned old;
+        asm volatile("atom.release.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old) : "l"(flag), "r"(value) : "memory");
+    } else {
         if (mode == 2) tc::fence_proxy_async();
         else if (mode == 3) __nanosleep(300);
         df_st_relaxed(flag, value);
