@@ -113,6 +113,7 @@ struct KlmKnobs {
     int ll_debug = 0;             // KLM_LL_DEBUG
     int cl_debug = 0;             // KLM_CL_DEBUG
     int step_timing = 0;          // KLM_STEP_TIMING
+    int step_server = 1;          // KLM_STEP_SERVER: klm_beam_edge / klm_beam_lattice keep ONE resident instance of klm_seq_df for all their steps
     int step_mapped = 1;          // KLM_STEP_MAPPED: beam steps read / write mapped host memory (no copies around the kernel)
 };
 static int env_int(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
@@ -133,6 +134,7 @@ static void read_knobs(KlmKnobs &k) {
     k.cl_debug = env_int("KLM_CL_DEBUG", 0);
     k.step_timing = env_int("KLM_STEP_TIMING", 0);
     k.step_mapped = env_int("KLM_STEP_MAPPED", 1);
+    k.step_server = env_int("KLM_STEP_SERVER", 1);
 }
 
 #define KLM_RING 4
@@ -163,6 +165,16 @@ struct klm_model {
     // klm_step with host arrays: page-locked staging (a copy from/to pageable memory blocks in the driver for ~10 us)
     char *h_step = nullptr;
     size_t h_step_bytes = 0;
+    // step server (klm_seq_df resident over the steps of one klm_beam_edge / klm_beam_lattice call)
+    struct StepServer {
+        bool active = false;
+        bool wanted = false;           // a native beam search is running: steps of 9..256 hypotheses go to the resident instance
+        unsigned seq = 0;
+        KlmStepCmd *cmd_host = nullptr, *cmd_host_dev = nullptr, *cmd_dev = nullptr;   // mapped host block (+ its device address), device copy
+        unsigned *done_host = nullptr, *done_host_dev = nullptr;                        // mapped completion words, one per LSE CTA
+        long long steps = 0, starts = 0;
+        double t_relay = 0, t_device = 0, t_start = 0, t_stop = 0;
+    } srv;
     char *h_map = nullptr;             // klm_step, beam steps: mapped page-locked memory the kernel reads / writes directly
     void *d_map = nullptr;
     size_t h_map_bytes = 0;
@@ -669,6 +681,11 @@ extern "C" int klm_destroy(klm_model *m) {
                 1e6 * m->t_step_total / m->t_steps, 1e6 * m->t_step_submit / m->t_steps, 1e6 * m->t_step_wait / m->t_steps,
                 1e3 * m->t_step_kernel_ms / m->t_steps, m->t_edges, m->t_edges ? 1e6 * m->t_edge_total / m->t_edges : 0.0,
                 m->t_edge_total > 0 ? 100.0 * m->t_step_total / m->t_edge_total : 0.0);
+    if (m->timing && m->srv.steps)
+        fprintf(stderr, "klm timing: step server: %lld steps in %lld resident instances; per step on the device: doorbell seen -> "
+                "device bell %.1f us, -> scores out %.1f us; start %.1f us, stop %.1f us per instance\n", m->srv.steps, m->srv.starts,
+                1e6 * m->srv.t_relay / m->srv.steps, 1e6 * m->srv.t_device / m->srv.steps,
+                1e6 * m->srv.t_start / std::max(1LL, m->srv.starts), 1e6 * m->srv.t_stop / std::max(1LL, m->srv.starts));
     if (m->stream) cudaStreamSynchronize(m->stream);
     cudaFree(m->P); cudaFree(m->Ep);
     for (int i = 0; i < KLM_MAX_CTX; ++i) cudaFree(m->Q[i]);
@@ -682,6 +699,9 @@ extern "C" int klm_destroy(klm_model *m) {
     cudaFree(m->hbuf_ll); cudaFree(m->logits_ll); cudaFree(m->progress); cudaFree(m->ll_err);
     if (m->h_step) cudaFreeHost(m->h_step);
     if (m->h_map) cudaFreeHost(m->h_map);
+    if (m->srv.cmd_host) cudaFreeHost(m->srv.cmd_host);
+    if (m->srv.done_host) cudaFreeHost(m->srv.done_host);
+    cudaFree(m->srv.cmd_dev);
     if (m->h_err) cudaFreeHost(m->h_err);
     for (int i = 0; i < KLM_RING; ++i) {
         if (m->h_ring[i]) cudaFreeHost(m->h_ring[i]);
@@ -856,6 +876,7 @@ extern "C" int klm_set_option(klm_model *m, const char *name, int64_t value) {
     else if (n == "tc_spin_limit") k.tc_spin_limit = (unsigned)value;
     else if (n == "ll_debug") k.ll_debug = (int)value;
     else if (n == "step_mapped") k.step_mapped = (int)value;
+    else if (n == "step_server") k.step_server = (int)value;
     else if (n == "step_timing") { k.step_timing = (int)value; m->timing = (int)value; }
     else return fail(KLM_EINVAL, "klm_set_option: unknown option '%s'", name);
     return KLM_OK;
@@ -1426,6 +1447,146 @@ __global__ void klm_topk_rows(const float *__restrict__ rows, int n, int V, int 
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Step server: one resident instance of klm_seq_df serves all beam steps of a klm_beam_edge / klm_beam_lattice call.  A step
+// is a KlmStepCmd written into mapped host memory (sequence number last); the scores come back through mapped memory as
+// before, completion is a word per LSE CTA.  Nothing else may use the model's stream while the instance is resident (the
+// model is not re-entrant, and the two callers do nothing on the device but steps).
+static int server_ensure_map(klm_model *m, size_t need) {
+    if (need <= m->h_map_bytes) return KLM_OK;
+    CK(cudaStreamSynchronize(m->stream));
+    if (m->h_map) cudaFreeHost(m->h_map);
+    m->h_map = nullptr; m->h_map_bytes = 0;
+    CK(cudaHostAlloc(&m->h_map, need * 2, cudaHostAllocMapped));
+    CK(cudaHostGetDevicePointer(&m->d_map, m->h_map, 0));
+    m->h_map_bytes = need * 2;
+    return KLM_OK;
+}
+
+static int server_stop(klm_model *m) {
+    klm_model::StepServer &sv = m->srv;
+    if (!sv.active) return KLM_OK;
+    sv.active = false;
+    const auto t0 = std::chrono::steady_clock::now();
+    sv.cmd_host->n_hyp = -1; sv.cmd_host->groups = 0;
+    __atomic_store_n(&sv.cmd_host->seq, ++sv.seq, __ATOMIC_RELEASE);
+    CK(cudaStreamSynchronize(m->stream));
+    sv.t_stop += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    const int32_t code = *reinterpret_cast<volatile int32_t *>(m->h_map);
+    if (code) {
+        tc_df_reset(m);
+        return fail(KLM_ECUDA, "klm_seq_df (step server): device-side wait timed out (code %d)", code);
+    }
+    return KLM_OK;
+}
+
+// (steps with targets only: the callers are the native beam searches)
+static int server_start(klm_model *m) {
+    klm_model::StepServer &sv = m->srv;
+    KlmTcPlan &tp = m->tc;
+    if (sv.active) return KLM_OK;
+    const auto t_s0 = std::chrono::steady_clock::now();
+    if (!(tp.ok && tp.df_ok && m->knobs.tc_df && m->knobs.step_mapped && m->knobs.step_server) || tp.n_lse > 8) return KLM_OK;
+    int rc = server_ensure_map(m, (size_t)KLM_STEP_MAX * 4 + 256); if (rc) return rc;
+    if (!sv.cmd_host) {
+        CK(cudaHostAlloc(&sv.cmd_host, sizeof(KlmStepCmd), cudaHostAllocMapped));
+        CK(cudaHostGetDevicePointer(reinterpret_cast<void **>(&sv.cmd_host_dev), sv.cmd_host, 0));
+        CK(cudaHostAlloc(&sv.done_host, 64, cudaHostAllocMapped));
+        CK(cudaHostGetDevicePointer(reinterpret_cast<void **>(&sv.done_host_dev), sv.done_host, 0));
+        CK(cudaMalloc(&sv.cmd_dev, sizeof(KlmStepCmd)));
+    }
+    memset(sv.cmd_host, 0, offsetof(KlmStepCmd, args));
+    for (int i = 0; i < 16; ++i) sv.done_host[i] = 0;
+    sv.seq = 0;
+    *reinterpret_cast<volatile int32_t *>(m->h_map) = 0;
+    CK(cudaMemsetAsync(sv.cmd_dev, 0, offsetof(KlmStepCmd, args), m->stream));
+    static thread_local KlmTcParams q;
+    memset(&q, 0, offsetof(KlmTcParams, step));
+    q.W = m->W; q.D = m->D; q.V = m->V; q.Vp = tp.Vp; q.Nc = m->Nc;
+    q.B = KLM_TC_STREAMS; q.T_max = 1; q.stages = tp.stages;
+    for (int k = 0; k < m->Nc; ++k) { q.ctx_rows[k] = m->cfg.ctx_rows[k]; q.Q[k] = m->Q[k]; }
+    q.P = m->P;
+    for (int l = 0; l < m->D; ++l) q.bias[l] = m->bias[l];
+    q.wimg = tp.d_wimg; q.roles = tp.d_roles;
+    q.state = m->state;
+    q.slots_in = sv.cmd_dev->args.slots_in; q.slots_out = sv.cmd_dev->args.slots_out;
+    q.chars = sv.cmd_dev->args.chars; q.targets = sv.cmd_dev->args.targets; q.ctx = sv.cmd_dev->args.ctx;
+    char *db = reinterpret_cast<char *>(m->d_map);
+    q.out = reinterpret_cast<float *>(db + 64); q.full_rows = 0;
+    q.barrier = m->barrier; q.err = tp.err;
+    q.pub_release = m->knobs.tc_pub_release; q.spin_limit = m->knobs.tc_spin_limit; q.fault = m->knobs.tc_fault;
+    tc_df_params(m, q);
+    q.step_groups = 0; q.n_hyp = 0; q.step_inline = 0;
+    q.err_host = reinterpret_cast<int *>(db);
+    q.server = 1; q.cmd_host = sv.cmd_host_dev; q.cmd_dev = sv.cmd_dev; q.srv_done = sv.done_host_dev;
+    CK(klm_launch_seq_df(q, tp.grid, tp.df_smem, m->stream));
+    m->launches++; m->tc_launches++; m->df_launches++;
+    sv.active = true; sv.starts++;
+    sv.t_start += std::chrono::duration<double>(std::chrono::steady_clock::now() - t_s0).count();
+    return KLM_OK;
+}
+
+static int server_step(klm_model *m, int n, const int32_t *chars, const int32_t *ctx, const int32_t *slots_in,
+                       const int32_t *slots_out, const int32_t *targets, float *out) {
+    klm_model::StepServer &sv = m->srv;
+    KlmTcPlan &tp = m->tc;
+    const volatile float *h_out = reinterpret_cast<const volatile float *>(m->h_map + 64);
+    const volatile int32_t *h_err = reinterpret_cast<const volatile int32_t *>(m->h_map);
+    for (int s0 = 0; s0 < n; s0 += KLM_STEP_MAX) {
+        const auto tm0 = std::chrono::steady_clock::now();
+        const int nb = std::min(KLM_STEP_MAX, n - s0);
+        KlmStepCmd *c = sv.cmd_host;
+        memcpy(c->args.chars, chars + s0, (size_t)nb * 4);
+        memcpy(c->args.targets, targets + s0, (size_t)nb * 4);
+        memcpy(c->args.slots_in, slots_in + s0, (size_t)nb * 4);
+        memcpy(c->args.slots_out, slots_out + s0, (size_t)nb * 4);
+        for (int i = 0; i < nb * m->Nc; ++i) c->args.ctx[i] = ctx ? ctx[(size_t)s0 * m->Nc + i] : 0;
+        c->n_hyp = nb; c->groups = (nb + KLM_TC_STREAMS - 1) / KLM_TC_STREAMS;
+        c->epoch = tp.epoch; c->tick_base = tp.tick_base;
+        __atomic_store_n(&c->seq, ++sv.seq, __ATOMIC_RELEASE);
+        tp.tick_base += (unsigned)c->groups; tp.epoch += (unsigned)c->groups + 1u;
+        const auto tm1 = std::chrono::steady_clock::now();
+        // completion: every LSE CTA reports the step number
+        unsigned long long spins = 0;
+        for (;;) {
+            bool all = true;
+            for (int i = 0; i < tp.n_lse; ++i)
+                if (__atomic_load_n(&sv.done_host[i], __ATOMIC_ACQUIRE) != sv.seq) { all = false; break; }
+            if (all) break;
+            if ((++spins & 0xFFF) == 0) {
+                if (*h_err) break;
+                if (std::chrono::duration<double>(std::chrono::steady_clock::now() - tm1).count() > 20.0) {
+                    sv.active = false;                        // (the instance leaves by its own watchdog)
+                    cudaStreamSynchronize(m->stream);
+                    tc_df_reset(m);
+                    return fail(KLM_ECUDA, "klm_seq_df (step server): step %u did not complete within 20 s", sv.seq);
+                }
+            }
+        }
+        if (*h_err) {
+            const int code = *h_err;
+            sv.active = false;
+            cudaStreamSynchronize(m->stream);
+            tc_df_reset(m);
+            return fail(KLM_ECUDA, "klm_seq_df (step server): device-side wait timed out (code %d)", code);
+        }
+        for (int i = 0; i < nb; ++i) out[s0 + i] = h_out[i];
+        sv.steps++;
+        if (m->timing) {       // device-side stamps of the step (globaltimer, ns): doorbell seen -> device bell rung -> scores out
+            const volatile unsigned long long *ts = reinterpret_cast<const volatile unsigned long long *>(sv.done_host + 8);
+            sv.t_relay += (double)(ts[1] - ts[0]) * 1e-9; sv.t_device += (double)(ts[2] - ts[1]) * 1e-9;
+        }
+        if (m->timing) {
+            const auto tm2 = std::chrono::steady_clock::now();
+            m->t_steps++;
+            m->t_step_submit += std::chrono::duration<double>(tm1 - tm0).count();
+            m->t_step_wait += std::chrono::duration<double>(tm2 - tm1).count();
+            m->t_step_total += std::chrono::duration<double>(tm2 - tm0).count();
+        }
+    }
+    return KLM_OK;
+}
+
 static int step_impl(klm_model *m, int32_t n, const int32_t *chars, const int32_t *ctx, const int32_t *slots_in,
                      const int32_t *slots_out, const int32_t *targets, float *out, int mem, int topk, int32_t *out_index) {
     if (!m) return fail(KLM_EINVAL, "NULL model");
@@ -1445,6 +1606,15 @@ static int step_impl(klm_model *m, int32_t n, const int32_t *chars, const int32_
                             ctx[s * m->Nc + k], m->cfg.ctx_rows[k]);
     const int full = targets ? 0 : 1;
     const size_t nout = full ? (size_t)n * m->V : (size_t)n;
+    if (m->srv.wanted || m->srv.active) {
+        // (steps of <= 8 hypotheses keep the FMA kernel -- the same kernel per step size as without the instance, so that all
+        //  forms of the beam search see the same numbers; the instance leaves for them and comes back with the next wide step)
+        if (m->srv.wanted && mem == KLM_MEM_HOST && !topk && targets && n > KLM_MODEK_MAXB) {
+            if (!m->srv.active) { rc = server_start(m); if (rc) return rc; }
+            if (m->srv.active) return server_step(m, n, chars, ctx, slots_in, slots_out, targets, out);
+        }
+        rc = server_stop(m); if (rc) return rc;
+    }
     if (mem == KLM_MEM_HOST && !topk && n > KLM_MODEK_MAXB && n <= KLM_TC_STREAMS * KLM_DF_MAXG && m->tc.ok && m->tc.df_ok &&
         m->knobs.tc_df && m->knobs.step_mapped) {
         // Beam step, zero copy: the per-hypothesis arrays travel INSIDE the kernel parameters (KlmStepArgs), the scores and
@@ -1769,6 +1939,15 @@ static int beam_edge_core(klm_model *m, BeamLists &L, int n_hyp, const int32_t *
     return KLM_OK;
 }
 
+// the resident step instance lives exactly as long as one native beam-search call
+struct ServerGuard {
+    klm_model *m;
+    int rc;
+    explicit ServerGuard(klm_model *m_) : m(m_), rc(KLM_OK) { m->srv.wanted = true; }      // (started by the first wide step)
+    int stop() { m->srv.wanted = false; return server_stop(m); }
+    ~ServerGuard() { m->srv.wanted = false; server_stop(m); }
+};
+
 extern "C" int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slot, const int32_t *hyp_last_char,
                              const double *hyp_cum_cost, int32_t n_alt, const int32_t *alt_offsets,
                              const int32_t *alt_chars, const double *alt_conf, const int32_t *ctx, double lm_weight,
@@ -1787,9 +1966,13 @@ extern "C" int klm_beam_edge(klm_model *m, int32_t n_hyp, const int32_t *hyp_slo
     if (n_hyp_steps) *n_hyp_steps = 0;
     BeamLists L;
     std::vector<int> done, free_slots(scratch_slots, scratch_slots + n_scratch);
+    CK(cudaSetDevice(m->device));
+    ServerGuard server(m);
+    if (server.rc) return server.rc;
     int rc = beam_edge_core(m, L, n_hyp, hyp_slot, hyp_last_char, hyp_cum_cost, n_alt, alt_offsets, alt_chars, alt_conf, ctx,
                             lm_weight, batch_size, free_slots, done, n_steps, n_hyp_steps);
     if (rc) return rc;
+    rc = server.stop(); if (rc) return rc;
     const int no = std::min<int>(max_out, (int)done.size());
     for (int k = 0; k < no; ++k) {
         const BeamCand &c = L.c[done[k]];
@@ -1835,6 +2018,9 @@ extern "C" int klm_beam_lattice(klm_model *m, int32_t n_hyp, const int32_t *hyp_
     for (int i = 0; i < n_hyp; ++i) b_origin[i] = -2 - i;
     out_first[0] = 0;
     int nout = 0;
+    CK(cudaSetDevice(m->device));
+    ServerGuard server(m);
+    if (server.rc) return server.rc;
     for (int e = 0; e < n_edges; ++e) {
         const int a0 = edge_alt_first[e], n_alt = edge_alt_first[e + 1] - a0;
         if (n_alt < 1) return fail(KLM_EINVAL, "klm_beam_lattice: edge %d has no alternatives", e);
@@ -1872,7 +2058,7 @@ extern "C" int klm_beam_lattice(klm_model *m, int32_t n_hyp, const int32_t *hyp_
         out_first[e + 1] = nout;
     }
     for (int k = 0; k < beam_width; ++k) final_slot[k] = k < (int)b_slot.size() ? (b_own[k] ? b_slot[k] : b_origin[k]) : -1;
-    return KLM_OK;
+    return server.stop();
 }
 
 // Micro-benchmark behind the roofline of the small-batch (FP32 FMA) kernels: 8 independent FFMA chains per thread, 4 CTAs of

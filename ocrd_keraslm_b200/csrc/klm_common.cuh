@@ -196,6 +196,19 @@ struct KlmStepArgs {
     int ctx[KLM_STEP_MAX * KLM_MAX_CTX];
 };
 
+// One beam step posted to a RESIDENT instance of klm_seq_df (step server: the kernel stays on the device for all steps of a
+// lattice edge / page; weights, TMEM and instruction caches stay warm, a step costs no launch).  The host fills the block in
+// mapped page-locked memory and writes `seq` last; the first LSE CTA copies it to device memory and rings the device-side
+// doorbell (`seq` of the device copy) for the other CTAs.
+struct KlmStepCmd {
+    unsigned seq;                 // 1, 2, ...: command number (written last)
+    int n_hyp;                    // hypotheses of the step (1 .. KLM_STEP_MAX); < 0: leave the kernel
+    int groups;                   // ceil(n_hyp / 64)
+    unsigned epoch, tick_base;    // as KlmTcParams::epoch / tick_base of a launch
+    int pad_[3];
+    KlmStepArgs args;
+};
+
 struct KlmTcParams {
     int W, D, V, Vp, Nc;
     int B, T_max, stages;
@@ -253,6 +266,10 @@ struct KlmTcParams {
     unsigned spin_limit;          // device-side watchdog: polls of one wait before it gives up (klm_set_option "tc_spin_limit")
     int fault;                    // test hook (klm_set_option "tc_fault"): CTA 0 withholds its hand-over signal of tick 2
     int wide;                     // 1: klm_seq_tw -- 128 streams per launch (exchange buffers and LSE rows of 128 streams)
+    int server;                   // klm_seq_df, step mode: 1 = resident instance, steps arrive as KlmStepCmd
+    const KlmStepCmd *cmd_host;   //   mapped page-locked host memory (read by the first LSE CTA only)
+    KlmStepCmd *cmd_dev;          //   device copy; chars / targets / slots_in / slots_out / ctx point into its args
+    unsigned *srv_done;           //   mapped host memory: word i = number of the last step LSE CTA i has finished
     const int *lane_ptr;          // klm_seq_tw: row r of the accumulator rates the streams lane_streams[lane_ptr[r] .. lane_ptr[r+1]) one
     const int *lane_streams;      //   after the other, a gap tick between two texts (129 / n ints)
     KlmStepArgs step;             // (last: only the launches of a beam step fill it)

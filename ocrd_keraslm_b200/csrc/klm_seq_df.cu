@@ -99,6 +99,9 @@ __device__ __forceinline__ bool df_check_all(const unsigned *w, int n, unsigned 
 struct DfCtx {
     uint32_t ring_a, bar_full, bar_empty, bar_tfull, bar_tempty, bar_epid, tmem_base, wsm_a, masks_a;
     int T, N, NP, crot, W, guard, nch;
+    // what changes from step to step of a resident instance (else: copies of the kernel parameters)
+    unsigned epoch, tick_base;
+    int n_hyp, groups;
 };
 
 // Split of a CTA's NP pairs between the hi-row and the lo-row threads, and between the two warps that share a TMEM
@@ -124,13 +127,13 @@ __device__ __noinline__ void df_produce(const KlmTcParams &p, const KlmTcRole &r
     constexpr uint32_t CB = KC * 256;
     const uint32_t ring_a = x.ring_a, bar_full = x.bar_full, bar_empty = x.bar_empty, bar_epid = x.bar_epid, masks_a = x.masks_a;
     const int T = x.T, crot = x.crot, NCH = x.nch, guard = x.guard, nsrc = role.n_src;
-    const bool is_rec = role.kind == KLM_TC_REC, step_rec = is_rec && p.step_groups > 0;
+    const bool is_rec = role.kind == KLM_TC_REC, step_rec = is_rec && x.groups > 0;
     const int lane = threadIdx.x & 31;
     const size_t hx_bytes = (size_t)x.W * 128 * sizeof(__half);
     const unsigned char *hx = reinterpret_cast<const unsigned char *>(p.hx) + (size_t)role.src_layer * KLM_DF_R * hx_bytes;
     const unsigned char *hx0 = reinterpret_cast<const unsigned char *>(p.hx0) + (size_t)role.src_layer * KLM_DF_MAXG * hx_bytes;
     const unsigned *flags = p.sync + (step_rec ? KLM_DF_HFLAG0 : KLM_DF_HFLAG) + role.src_layer * 64;
-    const unsigned epoch = p.epoch;
+    const unsigned epoch = x.epoch;
     const int cfence = p.consumer_fence;
     uint32_t phbits = 0;
     bool alive = true;
@@ -260,13 +263,13 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
     float *xchg = reinterpret_cast<float *>(alias);
     __half *pubbuf = reinterpret_cast<__half *>(alias + 2 * xh * 2048);
     const uint32_t trow = x.tmem_base + ((uint32_t)(32 * q) << 16);
-    const bool step = p.step_groups > 0;
+    const bool step = x.groups > 0;
     const float scale = role.scale;
     const int pr0 = role.first_pair + R.own_first;                 // first own pair (layer-wide index)
     const size_t hx_slice = (size_t)W * 128;                       // halves of one version of one layer
     __half *hx_l = p.hx + (size_t)l * KLM_DF_R * hx_slice;
     unsigned *my_flag = p.sync + KLM_DF_HFLAG + l * 64 + role.idx;
-    const unsigned epoch = p.epoch, tick_base = p.tick_base;
+    const unsigned epoch = x.epoch, tick_base = x.tick_base;
     const uint32_t pub_bytes = (uint32_t)(NP / 4) * 2048u;
 
     float c_reg[OWN][2], h_reg[OWN][2];
@@ -329,7 +332,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
 #pragma unroll
         for (int g = 0; g < KLM_DF_MAXG; ++g) {
             const int hyp = 64 * g + s;
-            const int slot = (g < p.step_groups && hyp < p.n_hyp) ? (p.step_inline ? p.step.slots_in[hyp] : p.slots_in[hyp]) : -1;
+            const int slot = (g < x.groups && hyp < x.n_hyp) ? (p.step_inline ? p.step.slots_in[hyp] : p.slots_in[hyp]) : -1;
 #pragma unroll
             for (int i = 0; i < OWN; ++i) {
                 h0[g][i][0] = h0[g][i][1] = 0.f;
@@ -341,7 +344,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         }
 #pragma unroll
         for (int g = 0; g < KLM_DF_MAXG; ++g)
-            if (g < p.step_groups) {
+            if (g < x.groups) {
                 __half *pb = pubbuf + (size_t)g * (pub_bytes / 2);
 #pragma unroll
                 for (int i = 0; i < OWN; ++i)
@@ -357,7 +360,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         tc_bar_epi();
         if (tid == 64) {
-            for (int g = 0; g < p.step_groups; ++g)
+            for (int g = 0; g < x.groups; ++g)
                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                              ::"l"(hx0_l + (size_t)g * hx_slice + (size_t)(role.first_pair / 4) * (128 * 8)),
                                "r"(tc::smem_u32(pubbuf) + (uint32_t)g * pub_bytes), "r"(pub_bytes) : "memory");
@@ -379,7 +382,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
     bool alive = true;
     for (int tick = 0; tick < T; ++tick) {
         const int hyp = step ? 64 * tick + s : s;
-        const bool active = step ? hyp < p.n_hyp : (s < p.B && tick < len);
+        const bool active = step ? hyp < x.n_hyp : (s < p.B && tick < len);
         const long long pos = step ? hyp : o0 + tick;
         int slot_out = 0;
         if (step) {
@@ -456,7 +459,7 @@ __device__ __noinline__ void df_epi_rec(const KlmTcParams &p, const KlmTcRole &r
         for (int i = 0; i < OWN; ++i)
 #pragma unroll
             for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-        if constexpr (OWN <= 2) {
+        if constexpr (OWN <= 0) {        // (batched form as in klm_seq_tc: no gain on a beam step, and it costs the registers the step server needs)
         // two batches of TMEM loads with one wait each: the pairs the other half finishes (this row's part goes over through
         // shared memory, both directions at once), then the own pairs (hi rows: hi.hi + hi.lo columns; lo rows: lo.hi columns)
         {
@@ -651,7 +654,7 @@ __device__ __noinline__ void df_epi_inproj(const KlmTcParams &p, const KlmTcRole
     const int k_first = ch ? (NP + 1) / 2 : 0, k_end = ch ? NP : (NP + 1) / 2;      // pairs of this warp
     const uint32_t trow = x.tmem_base + ((uint32_t)(32 * q) << 16);
     const float scale = role.scale;
-    const unsigned tick_base = p.tick_base;
+    const unsigned tick_base = x.tick_base;
     unsigned *done_word = p.sync + (is_in ? KLM_DF_ZPROG + l * 64 : KLM_DF_PPROG) + role.idx;
     unsigned *read_word = p.sync + KLM_DF_HRD + role.src_layer * 64 + role.idx;
     const int nslots = is_in ? KLM_DF_NZ : KLM_DF_NL;
@@ -727,17 +730,17 @@ __device__ __noinline__ void df_epi_inproj(const KlmTcParams &p, const KlmTcRole
 // ---------------------------------------------------------------------------------------------
 // LSE stage: every warp on its own -- lane = stream (32 streams), the whole vocabulary, ticks w, w + n, w + 2n, ...
 // Adds the two parts of the logits, log-sum-exp in one pass, picks the target's logit (or writes the softmax row).
-__device__ void df_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
+__device__ void df_lse_role(const KlmTcParams &p, const KlmTcRole &role, const DfCtx &x) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int V = p.V, Vq = p.Vp / 4, V4 = (V + 3) / 4, full_rows = p.full_rows;
-    const int T = p.step_groups > 0 ? p.step_groups : p.T_max;
-    const bool step = p.step_groups > 0;
+    const int T = x.groups > 0 ? x.groups : p.T_max;
+    const bool step = x.groups > 0;
     const int ngroups = (step ? 64 : p.B) > 32 ? 2 : 1;            // stream groups of 32 per tick
     const int gw = warp + (KLM_TC_THREADS / 32) * role.first_pair;  // global LSE warp index (several LSE CTAs: interleaved)
     const int nw = p.n_lse_warps;
     if (gw >= nw) return;
     unsigned *my_prog = p.sync + KLM_DF_LPROG + gw;
-    const unsigned tick_base = p.tick_base;
+    const unsigned tick_base = x.tick_base;
     const int *targets = p.targets;
     // work items: (tick, group) pairs, item k = tick * ngroups + group; warp gw takes the ticks gw, gw + nw, ... and all
     // groups of a tick (so that "tick finished" is one word per warp)
@@ -754,7 +757,7 @@ __device__ void df_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
             long long o0 = 0;
             int len = 0;
             if (!step && s < p.B) { o0 = p.offsets[s]; len = (int)(p.offsets[s + 1] - o0); }
-            const bool act = step ? hyp < p.n_hyp : (s < p.B && tick < len);
+            const bool act = step ? hyp < x.n_hyp : (s < p.B && tick < len);
             const long long pos = step ? hyp : o0 + tick;
             const float4 *pa = reinterpret_cast<const float4 *>(p.logits) + ((size_t)(tick & (KLM_DF_NL - 1)) * 2) * Vq * 64 + s;
             const float4 *pb = pa + (size_t)Vq * 64;
@@ -812,21 +815,112 @@ __device__ void df_lse_role(const KlmTcParams &p, const KlmTcRole &role) {
     }
 }
 
+__device__ __forceinline__ unsigned df_ld_acquire_sys(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Resident instance (KlmTcParams::server): waits for step `seq`.  The first LSE CTA polls the host's command block in
+// mapped memory, copies what the step needs (header, the arrays of its n_hyp hypotheses) to the device block and rings the
+// device-side doorbell; every other CTA polls that.  Fills the per-step fields of x; false = leave the kernel (exit
+// command, or the watchdog: nobody rang for spin_limit polls).
+__device__ __forceinline__ bool df_next_step(const KlmTcParams &p, const KlmTcRole &role, unsigned seq, DfCtx &x) {
+    __shared__ int s_go;
+    const int tid = threadIdx.x;
+    KlmStepCmd *cd = p.cmd_dev;
+    if (role.kind == KLM_TC_LSE && role.first_pair == 0) {
+        const KlmStepCmd *ch = p.cmd_host;
+        if (tid == 0) {
+            unsigned n = 0;
+            int ok = 1;
+            while (df_ld_acquire_sys(&ch->seq) != seq)
+                if (tc_spin_fail(n, p, 14)) { ok = 0; break; }
+            s_go = ok;
+        }
+        __syncthreads();
+        if (!s_go) return false;
+        unsigned long long t_seen = 0;
+        if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_seen));
+        // ONE pass of 16-byte loads over the bus (everything in flight at once: one round trip): the header by thread 0, the
+        // four per-hypothesis arrays (4 KB) and the context indices by everybody; entries beyond n_hyp are stale and unused
+        {
+            const uint4 *src = reinterpret_cast<const uint4 *>(&ch->args);
+            uint4 *dst = reinterpret_cast<uint4 *>(&cd->args);
+            const int n16 = KLM_STEP_MAX + (KLM_STEP_MAX * p.Nc + 3) / 4;          // uint4 pieces: 4 arrays of 256 ints, then ctx
+            uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0, h0 = v0, h1 = v0;
+            if (tid < n16) v0 = src[tid];
+            if (tid + KLM_TC_THREADS < n16) v1 = src[tid + KLM_TC_THREADS];
+            if (tid == 0) { h0 = reinterpret_cast<const uint4 *>(ch)[0]; h1 = reinterpret_cast<const uint4 *>(ch)[1]; }
+            if (tid < n16) dst[tid] = v0;
+            if (tid + KLM_TC_THREADS < n16) dst[tid + KLM_TC_THREADS] = v1;
+            if (tid == 0) { cd->n_hyp = (int)h0.y; cd->groups = (int)h0.z; cd->epoch = h0.w; cd->tick_base = h1.x; }
+        }
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            df_st_release(&cd->seq, seq);
+            // (diagnostics, words 8..11 of the completion block: when the doorbell was seen / the device-side bell rung, ns)
+            unsigned long long t_rung;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_rung));
+            *(volatile unsigned long long *)(p.srv_done + 8) = t_seen;
+            *(volatile unsigned long long *)(p.srv_done + 10) = t_rung;
+        }
+    } else {
+        if (tid == 0) {
+            unsigned n = 0;
+            int ok = 1;
+            while (!df_reached(df_ld_acquire(&cd->seq), seq)) {
+                if (tc_spin_fail(n, p, 15)) { ok = 0; break; }
+                __nanosleep(100);
+            }
+            s_go = ok;
+        }
+        __syncthreads();
+        if (!s_go) return false;
+    }
+    x.n_hyp = *(volatile int *)&cd->n_hyp; x.groups = *(volatile int *)&cd->groups;
+    x.epoch = *(volatile unsigned *)&cd->epoch; x.tick_base = *(volatile unsigned *)&cd->tick_base;
+    x.T = x.groups;
+    __syncthreads();                                    // (s_go is reused by the next step)
+    return x.n_hyp > 0;
+}
+
 template <bool TRACE>
 __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *smem) {
     if (TRACE && threadIdx.x == 64) tc_trace(p, p.trace_t0 + KLM_TC_TRACE_TICKS - 1, 0);      // (last trace slot: phases of the launch)
     const KlmTcRole role = p.roles[blockIdx.x];
+    const int tid = threadIdx.x, warp = tid >> 5;
+    DfCtx x;
+    x.epoch = p.epoch; x.tick_base = p.tick_base; x.n_hyp = p.n_hyp; x.groups = p.step_groups;
+    x.T = p.step_groups > 0 ? p.step_groups : p.T_max;
     if (role.kind == KLM_TC_LSE) {
-        df_lse_role(p, role);
+        x.ring_a = x.bar_full = x.bar_empty = x.bar_tfull = x.bar_tempty = x.bar_epid = x.tmem_base = x.wsm_a = x.masks_a = 0;
+        x.N = x.NP = x.crot = x.guard = x.nch = 0; x.W = p.W;
+        for (unsigned seq = 1;; ++seq) {
+            if (p.server && !df_next_step(p, role, seq, x)) break;
+            df_lse_role(p, role, x);
+            __syncthreads();
+            if (!p.server) break;
+            // the scores of this CTA's share are in the host's buffer: completion word (mapped host memory)
+            if (tid == 0) {
+                if (role.first_pair == 0) {
+                    unsigned long long t_done;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_done));
+                    *(volatile unsigned long long *)(p.srv_done + 12) = t_done;
+                }
+                __threadfence_system();
+                *(volatile unsigned *)(p.srv_done + role.first_pair) = seq;
+            }
+        }
         __syncthreads();
-        if (threadIdx.x == 0 && p.err_host) {
+        if (tid == 0 && p.err_host) {
             const int code = *(volatile int *)p.err;
             if (code) *(volatile int *)p.err_host = code;
         }
         return;
     }
 
-    const int tid = threadIdx.x, warp = tid >> 5;
     const int W = p.W, S = role.stages, kc = role.kc;
     const int NP = role.npairs, N = 8 * NP;
 
@@ -842,11 +936,14 @@ __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *sme
         tc::tmem_alloc(tc::smem_u32(tmem_slot), KLM_TC_TMEM_COLS);
         tc::tmem_relinquish();
     }
-    if (tid == 32) {
+    auto init_bars = [&]() {         // (thread 32)
         for (int i = 0; i < S; ++i) { tc::mbar_init(bar_full + 8 * i, 1); tc::mbar_init(bar_empty + 8 * i, 1); }
         tc::mbar_init(bar_tfull, 1);
         tc::mbar_init(bar_tempty, 256);
         tc::mbar_init(bar_epid, 1);
+    };
+    if (tid == 32) {
+        init_bars();
         tc::mbar_init(tc::smem_u32(bars + 13), 1);       // B image landed
         tc::fence_mbar_init();
     }
@@ -865,32 +962,57 @@ __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *sme
     }
 
     if (TRACE && tid == 64) tc_trace(p, p.trace_t0 + KLM_TC_TRACE_TICKS - 1, 1);
-    DfCtx x;
     x.ring_a = tc::smem_u32(smem); x.bar_full = bar_full; x.bar_empty = bar_empty; x.bar_tfull = bar_tfull;
     x.bar_tempty = bar_tempty; x.bar_epid = bar_epid; x.tmem_base = *tmem_slot; x.wsm_a = tc::smem_u32(wsm);
     x.masks_a = tc::smem_u32(masks);
-    x.T = p.step_groups > 0 ? p.step_groups : p.T_max;
     x.N = N; x.NP = NP; x.W = W; x.nch = W / kc;
+    const bool stepm = p.step_groups > 0 || p.server;
     // REC: the producer waits for the epilogue where the aliased buffers are not covered by the own-flag rule;
     // IN / PROJ: the producer waits until the epilogue has published the previous tick (at the quiet moment after the MMAs)
     // (step mode: IN / PROJ publish at once -- a beam step is about latency, and there is little to stream in)
-    x.guard = role.kind == KLM_TC_REC ? ((role.guard || p.step_groups > 0 || (p.exp & 2)) ? 1 : 0)
-                                      : (((p.exp & 4) || p.step_groups > 0) ? 0 : 1);
+    x.guard = role.kind == KLM_TC_REC ? ((role.guard || stepm || (p.exp & 2)) ? 1 : 0)
+                                      : (((p.exp & 4) || stepm) ? 0 : 1);
     // REC: the chunk with the CTA's own slice goes into ring slot `alias_slot`; the others in rotated order behind / before it
     x.crot = role.kind == KLM_TC_REC ? role.sigma : role.rot % x.nch;
 
-    if (warp == 0) {
-        if (!df_run_loops<TRACE>(true, p, role, x) && tid == 0) atomicExch(p.err, 90);
-    } else if (warp == 1) {
-        if (__all_sync(0xffffffffu, tc_wait_mbar(bar_img, 0, p, 13) ? 1 : 0)) df_run_loops<TRACE>(false, p, role, x);
-    } else if (role.kind == KLM_TC_REC) {
-        unsigned char *alias = smem + (size_t)role.alias_slot * kc * 256;
-        const int own = ((NP + 1) / 2 + 1) / 2;
-        if (own <= 1) df_epi_rec<1, TRACE>(p, role, x, alias);
-        else if (own == 2) df_epi_rec<2, TRACE>(p, role, x, alias);
-        else df_epi_rec<3, TRACE>(p, role, x, alias);
-    } else {
-        df_epi_inproj<TRACE>(p, role, x);
+    for (unsigned seq = 1;; ++seq) {
+        if (p.server) {
+            if (!df_next_step(p, role, seq, x)) break;
+            if (seq > 1) {
+                // the ring / accumulator barriers start every step in their initial phase (the role loops count from 0)
+                if (tid == 32) {
+                    for (int i = 0; i < S; ++i) {
+                        asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar_full + 8 * i) : "memory");
+                        asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar_empty + 8 * i) : "memory");
+                    }
+                    asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar_tfull) : "memory");
+                    asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar_tempty) : "memory");
+                    asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar_epid) : "memory");
+                    init_bars();
+                    tc::fence_mbar_init();
+                }
+                tc::tc_fence_before();
+                __syncthreads();
+                tc::tc_fence_after();
+            }
+        }
+        if (warp == 0) {
+            if (!df_run_loops<TRACE>(true, p, role, x) && tid == 0) atomicExch(p.err, 90);
+        } else if (warp == 1) {
+            if (__all_sync(0xffffffffu, tc_wait_mbar(bar_img, 0, p, 13) ? 1 : 0)) df_run_loops<TRACE>(false, p, role, x);
+        } else if (role.kind == KLM_TC_REC) {
+            unsigned char *alias = smem + (size_t)role.alias_slot * kc * 256;
+            const int own = ((NP + 1) / 2 + 1) / 2;
+            if (own <= 1) df_epi_rec<1, TRACE>(p, role, x, alias);
+            else if (own == 2) df_epi_rec<2, TRACE>(p, role, x, alias);
+            else df_epi_rec<3, TRACE>(p, role, x, alias);
+        } else {
+            df_epi_inproj<TRACE>(p, role, x);
+        }
+        tc::tc_fence_before();
+        __syncthreads();
+        tc::tc_fence_after();
+        if (!p.server) break;
     }
 
     if (TRACE && tid == 64) tc_trace(p, p.trace_t0 + KLM_TC_TRACE_TICKS - 1, 3);
