@@ -82,7 +82,7 @@ int klm_sync(klm_model *m);
  * Initial values come from the environment variables of the same name in upper case with the prefix KLM_
  * (e.g. KLM_TC_SKEW), read once in klm_create.  Names: tc_skew, tc_trace_mode, tc_debug_skip, tc_poll, tc_zpub,
  * tc_pub_release, tc_spin_limit, tc_fault, tc_df, tc_wide, tc_exp, tc_consumer_fence, ll_debug, step_mapped,
- * step_timing. */
+ * step_server, step_timing. */
 int klm_set_option(klm_model *m, const char *name, int64_t value);
 
 /*
