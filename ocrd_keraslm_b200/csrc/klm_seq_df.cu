@@ -909,6 +909,9 @@ __device__ __forceinline__ void df_body(const KlmTcParams &p, unsigned char *sme
                     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_done));
                     *(volatile unsigned long long *)(p.srv_done + 12) = t_done;
                 }
+                // a wait of this step that timed out anywhere (this CTA's own included) is reported with the completion
+                const int code = *(volatile int *)p.err;
+                if (code && p.err_host) *(volatile int *)p.err_host = code;
                 __threadfence_system();
                 *(volatile unsigned *)(p.srv_done + role.first_pair) = seq;
             }
