@@ -303,7 +303,7 @@ def run_beam(args):
                  'gpu_launches': r._native.info()['kernel_launches'] - l0,
                  'e2e': {'value': steps / dt, 'unit': 'steps/s', 'h2d_bytes_per_step': int(12 * hyps / args.steps),
                          'd2h_bytes_per_step': int(4 * hyps / args.steps), 'api': 'Rater.rate_best(graph, ...)'},
-                 'roofline': {'bound': 'tensor', 'kernel': 'klm_seq_df (step mode: one launch per beam step)',
+                 'roofline': {'bound': 'tensor', 'kernel': 'klm_seq_df (step mode: a resident instance per rate_best call, steps posted through mapped memory)',
                               'achieved': hyps / dt * F / 1e12,
                               'peak': float(pk.get('bf16_tflops_sustained', FALLBACK_PEAKS['bf16_tflops_sustained'])), 'unit': 'TFLOP/s',
                               'frac': hyps / dt * F / 1e12 / float(pk.get('bf16_tflops_sustained', FALLBACK_PEAKS['bf16_tflops_sustained'])),
