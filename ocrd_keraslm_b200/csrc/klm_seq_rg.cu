@@ -7,17 +7,22 @@
 // L2) needs ~4 900 clk per tick, of which ~2 500 are the L2 round trips and most of the rest is one warp walking a
 // whole row of weights (8 k-steps of two shared-memory loads, 10 shuffles); the first cluster kernel (klm_seq_cl,
 // round 1, now scripts/ubench/) removed the L2 trips but kept the walk: 4.2 us.  Here
-//   * CTA c of a cluster of C = 8 owns units [16 c, 16 c + 16) of EVERY layer and V / C rows of the tied output
-//     projection; warp w owns unit 16 c + w of every layer: a warp IS one LSTM unit, lane = (gate g = lane / 8,
-//     k-segment ks = lane % 8), and the lane keeps its W/8 (layer 1) resp. 2 W/8 weights of column (unit, g) in
-//     registers for the whole launch (width 128, depth 2, 256 characters: 16 + 32 + 8 = 56 registers);
-//   * per tick and layer a lane does W/8 (2 W/8) FMAs in four independent chains on 128-bit broadcast loads of the
-//     hidden vector, three xor-shuffles finish the four gate sums, three more bring them to lane 0, lane 0 runs the
-//     cell (8 MUFU operations) and lanes 0..C-1 store the new value as ONE 8-byte {value, tick} word into the ring of
-//     every CTA of the cluster (st.shared::cluster, ~215 clk) -- no fence, no flag, no barrier across CTAs;
-//   * a 17th warp per CTA polls the CTA's own ring, copies a complete hidden vector into a dense, conflict-free
-//     array and releases the 16 unit warps through a named barrier (sixteen warps spinning on shared memory starve
-//     the port the remote stores arrive through); in CTA 0 the same warp does the log-sum-exp + target pick of the
+//   * CTA c of a cluster of C = 16 (8) owns units [8 c, 8 c + 8) of EVERY layer and V / C rows of the tied output
+//     projection; warp w owns unit 8 c + w of every layer: a warp IS one LSTM unit, lane = k-segment (values
+//     4 lane .. 4 lane + 3 of every input vector), and the lane keeps the weights of ALL FOUR gates for its four values
+//     in registers for the whole launch (width 128, depth 2, 256 characters: 16 + 32 + 8 = 56 registers);
+//   * per tick a lane loads ONE float4 per hidden vector (a warp reads every value once: 3 x 512 B per tick; with
+//     lane = (gate, k-segment) the four gate groups each loaded the whole vector and the eight unit warps together kept
+//     the shared-memory pipe busy for ~350 clk of every tick), does 4 (8) FMAs per gate, and the 4 D gate sums are
+//     reduced over the 32 lanes by recursive halving (a lane sends half of its values and keeps the other half:
+//     4 + 2 + 1 + 1 + 1 shuffles for depth 2), four indexed shuffles bring the gates of layer l to lane l, lanes
+//     0..D-1 run the cells side by side (8 MUFU operations) and lanes 0..C-1 store the new values of ALL layers as
+//     adjacent 8-byte {value, tick} words with ONE vector store into the ring of every CTA of the cluster
+//     (st.shared::cluster, ~215 clk) -- no fence, no flag, no barrier across CTAs.  (One store per layer cost 380 clk
+//     of every tick: the 16-destination stores are what the publication pays for.);
+//   * one more warp per CTA polls the CTA's own ring, copies a complete hidden vector into a dense array and
+//     releases the unit warps through a named barrier (sixteen warps spinning on shared memory starve
+//     the port the remote stores arrive through); in CTA 0 another warp does the log-sum-exp + target pick of the
 //     position that left the projection a tick earlier.
 // Wavefront as in the other kernels: layer l works on position tick - l, the projection on tick - D, the
 // log-sum-exp on tick - D - 1; every CTA takes part in layer 1's recurrence, so nobody is more than a tick ahead of
@@ -71,14 +76,6 @@ __device__ __forceinline__ void rg_cell(float ai, float af, float ag, float ao, 
     h = __fdividef(num, (1.f + eo) * den);
 }
 
-// Dense copy of a hidden vector for the unit warps: lane (g, ks) reads values k = 16 ks + 4 q + e as float4 number q:
-// index = q * 32 + 4 * ks + e, so the eight k-segments of one load are 128 contiguous bytes (no bank conflict, the four
-// gate groups read the same addresses: broadcast).
-__device__ __forceinline__ int rg_dense_index(int k, int WS) {      // WS = W / 8 values per k-segment
-    const int ks = k / WS, j = k - ks * WS;
-    return (j >> 2) * 32 + 4 * ks + (j & 3);
-}
-
 }  // namespace
 
 // WS = W / 8 (values per k-segment), D = depth, PR = rows of the output projection per warp (V <= 128 * PR)
@@ -91,7 +88,12 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
     constexpr int LPR = 32 / PR;                 // lanes per projection row
     constexpr int PS = W / LPR;                  // values of the hidden vector per lane in the projection
     constexpr int VP = W * PR;                   // projection rows of the cluster (>= V)
-    constexpr int SLOT = D * W + VP;             // words of one ring slot
+    constexpr int DP = D == 1 ? 1 : (D + 1) / 2 * 2;   // words per unit in a ring slot: the D layers side by side, padded to 16 bytes
+    constexpr int HW = W * DP;                   // hidden words of one ring slot
+    constexpr int SLOT = HW + VP;                // words of one ring slot
+    constexpr int NVP = D == 1 ? 4 : D == 2 ? 8 : 16;  // gate sums per lane (4 D), padded to a power of two for the halving
+    constexpr int LPV = 32 / NVP;                // lanes that end up with the same gate sum
+    static_assert(W == 128, "a lane owns four values of a 128-wide vector");
     extern __shared__ __align__(16) unsigned char rg_smem[];
     uint2 *ring = reinterpret_cast<uint2 *>(rg_smem);
     float *dense = reinterpret_cast<float *>(ring + (size_t)R * SLOT);          // [2][D][W]
@@ -113,24 +115,27 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
     if (warp < UPC) {
         // =========================== unit warp: unit u of every layer, PR rows of the projection ===========================
         const int u = (int)rank * UPC + warp;
-        const int g = lane >> 3, ks = lane & 7;
-        // ---- weights -> registers (column (u, g), k-segment ks) ----
-        float wr[D][WS], wi[D > 1 ? D - 1 : 1][WS], wp[PS];
+        // ---- weights -> registers: values k = 4 lane + e of every input vector, the four gates of unit u as one float4 ----
+        float4 wr[D][4], wi[D > 1 ? D - 1 : 1][4];
+        float wp[PS];
 #pragma unroll
         for (int l = 0; l < D; ++l) {
             const int K = l > 0 ? 2 * W : W;
-            const float *src = reinterpret_cast<const float *>(p.Wl[l] + (size_t)u * K) + g;       // float4 per k: (i, f, g, o)
+            const float4 *src = p.Wl[l] + (size_t)u * K + 4 * lane;                                  // float4 per k: (i, f, g, o)
 #pragma unroll
-            for (int j = 0; j < WS; ++j) {
-                if (l > 0) wi[l > 0 ? l - 1 : 0][j] = __ldg(src + 4 * (ks * WS + j));             // K_l rows (input h_{l-1})
-                wr[l][j] = __ldg(src + 4 * ((l > 0 ? W : 0) + ks * WS + j));                      // R_l rows (input h_l)
+            for (int e = 0; e < 4; ++e) {
+                if (l > 0) wi[l > 0 ? l - 1 : 0][e] = __ldg(src + e);                                 // K_l rows (input h_{l-1})
+                wr[l][e] = __ldg(src + (l > 0 ? W : 0) + e);                                          // R_l rows (input h_l)
             }
         }
+        // projection row v = u PR + prow: lane (prow, pseg) takes the float4s pseg + LPR e of the last hidden vector
         const int prow = lane / LPR, pseg = lane % LPR;
         const int v = u * PR + prow;
 #pragma unroll
-        for (int j = 0; j < PS; ++j)
-            wp[j] = v < p.V ? __ldg(reinterpret_cast<const float *>(p.Ep + (size_t)(v >> 2) * W + pseg * PS + j) + (v & 3)) : 0.f;
+        for (int j = 0; j < PS; ++j) {
+            const int k = 4 * (pseg + LPR * (j >> 2)) + (j & 3);
+            wp[j] = v < p.V ? __ldg(reinterpret_cast<const float *>(p.Ep + (size_t)(v >> 2) * W + k) + (v & 3)) : 0.f;
+        }
         // ---- state, tick-invariant addends (lane 0 runs the cells) ----
         float c_own = 0.f, h_own = 0.f;                    // lane l < D: cell and hidden state of layer l
         float4 *mytab = tab + warp * (D + 1);              // [0] context part (real positions), [l] bias of layer l, [D] context 0
@@ -155,8 +160,8 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
         __syncwarp();
         const int nreal = p.n_real ? __ldg(p.n_real) : 0x7fffffff;
         // remote addresses of this warp's words in ring slot 0 of CTA `lane` (lanes 0..C-1), and of its logits in CTA 0
-        const uint32_t dst_h0 = rg_mapa(rg_smem_u32(ring + u), (uint32_t)(lane & (C - 1)));
-        const uint32_t dst_p = rg_mapa(rg_smem_u32(ring + D * W + v), 0u);
+        const uint32_t dst_h0 = rg_mapa(rg_smem_u32(ring + u * DP), (uint32_t)(lane & (C - 1)));
+        const uint32_t dst_p = rg_mapa(rg_smem_u32(ring + HW + v), 0u);
         // the carried hidden state is the word of tick 0
         {
             float h0[D];
@@ -164,7 +169,7 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
             for (int l = 0; l < D; ++l) h0[l] = __shfl_sync(0xffffffffu, h_own, l);
             if (lane < C) {
 #pragma unroll
-                for (int l = 0; l < D; ++l) rg_st_remote(dst_h0 + (uint32_t)l * W * 8u, h0[l], 0u);
+                for (int l = 0; l < D; ++l) rg_st_remote(dst_h0 + 8u * l, h0[l], 0u);
             }
         }
         // layer 1's table rows travel a tick ahead of their use (the text is known): row of position 0 now
@@ -186,51 +191,57 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
             RG_DBG(1)
             const float4 *hv = reinterpret_cast<const float4 *>(dense + (size_t)(tick & 1) * D * W);
             // ---- contractions of all layers and of the projection (independent: their chains overlap) ----
-            float acc[D];
+            float4 h4[D];
+#pragma unroll
+            for (int l = 0; l < D; ++l) h4[l] = hv[l * (W / 4) + lane];
+            float sv[NVP];                                               // [4 l + gate]
 #pragma unroll
             for (int l = 0; l < D; ++l) {
-                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll
-                for (int q = 0; q < WS / 4; ++q) {
-                    const float4 hr = hv[l * (W / 4) + q * 8 + ks];
-                    a0 = fmaf(wr[l][4 * q], hr.x, a0); a1 = fmaf(wr[l][4 * q + 1], hr.y, a1);
-                    a2 = fmaf(wr[l][4 * q + 2], hr.z, a2); a3 = fmaf(wr[l][4 * q + 3], hr.w, a3);
-                    if (l > 0) {
-                        const float4 hi = hv[(l - 1) * (W / 4) + q * 8 + ks];
-                        a0 = fmaf(wi[l > 0 ? l - 1 : 0][4 * q], hi.x, a0); a1 = fmaf(wi[l > 0 ? l - 1 : 0][4 * q + 1], hi.y, a1);
-                        a2 = fmaf(wi[l > 0 ? l - 1 : 0][4 * q + 2], hi.z, a2); a3 = fmaf(wi[l > 0 ? l - 1 : 0][4 * q + 3], hi.w, a3);
-                    }
+                float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#define RG_FMA4(w_, h_) a.x = fmaf((w_).x, (h_), a.x); a.y = fmaf((w_).y, (h_), a.y); a.z = fmaf((w_).z, (h_), a.z); a.w = fmaf((w_).w, (h_), a.w);
+                RG_FMA4(wr[l][0], h4[l].x) RG_FMA4(wr[l][1], h4[l].y) RG_FMA4(wr[l][2], h4[l].z) RG_FMA4(wr[l][3], h4[l].w)
+                if (l > 0) {
+                    const float4 hi = h4[l > 0 ? l - 1 : 0];
+                    const float4 *w = wi[l > 0 ? l - 1 : 0];
+                    RG_FMA4(w[0], hi.x) RG_FMA4(w[1], hi.y) RG_FMA4(w[2], hi.z) RG_FMA4(w[3], hi.w)
                 }
-                acc[l] = (a0 + a1) + (a2 + a3);
+#undef RG_FMA4
+                sv[4 * l] = a.x; sv[4 * l + 1] = a.y; sv[4 * l + 2] = a.z; sv[4 * l + 3] = a.w;
             }
+#pragma unroll
+            for (int j = 4 * D; j < NVP; ++j) sv[j] = 0.f;
             float accp;
             {
                 float a0 = 0.f, a1 = 0.f;
-                const float *hp = dense + (size_t)(tick & 1) * D * W + (D - 1) * W;
 #pragma unroll
-                for (int j = 0; j < PS; j += 2) {
-                    a0 = fmaf(wp[j], hp[rg_dense_index(pseg * PS + j, WS)], a0);
-                    a1 = fmaf(wp[j + 1], hp[rg_dense_index(pseg * PS + j + 1, WS)], a1);
+                for (int e = 0; e < PR; ++e) {
+                    const float4 hp = hv[(D - 1) * (W / 4) + pseg + LPR * e];
+                    a0 = fmaf(wp[4 * e], hp.x, a0); a1 = fmaf(wp[4 * e + 1], hp.y, a1);
+                    a0 = fmaf(wp[4 * e + 2], hp.z, a0); a1 = fmaf(wp[4 * e + 3], hp.w, a1);
                 }
                 accp = a0 + a1;
             }
             RG_DBG(2)
-            // ---- sums over the k-segments (lanes of one gate: xor 1, 2, 4), gates to lane 0 ----
+            // ---- sums over the 32 k-segments by recursive halving: with mask m a lane hands the half of its values that its
+            //      partner keeps to lane ^ m; afterwards gate sum j lives (complete) in the lanes j LPV .. j LPV + LPV - 1 ----
 #pragma unroll
-            for (int o = 1; o < 8; o <<= 1) {
+            for (int half = NVP / 2, m = 16; half >= 1; half >>= 1, m >>= 1) {
+                const bool up = (lane & m) != 0;
 #pragma unroll
-                for (int l = 0; l < D; ++l) acc[l] += __shfl_xor_sync(0xffffffffu, acc[l], o);
+                for (int q = 0; q < half; ++q) {
+                    const float send = up ? sv[q] : sv[q + half];
+                    const float keep = up ? sv[q + half] : sv[q];
+                    sv[q] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+                }
             }
+#pragma unroll
+            for (int m = LPV / 2; m >= 1; m >>= 1) sv[0] += __shfl_xor_sync(0xffffffffu, sv[0], m);
 #pragma unroll
             for (int o = 1; o < LPR; o <<= 1) accp += __shfl_xor_sync(0xffffffffu, accp, o);
             // the four gate sums of layer l meet in lane l: the cells of all layers run side by side (lanes 0 .. D-1)
-            float gi = 0.f, gf = 0.f, gg = 0.f, go = 0.f;
-#pragma unroll
-            for (int l = 0; l < D; ++l) {
-                const float ai = __shfl_sync(0xffffffffu, acc[l], 0), af = __shfl_sync(0xffffffffu, acc[l], 8),
-                            ag = __shfl_sync(0xffffffffu, acc[l], 16), ao = __shfl_sync(0xffffffffu, acc[l], 24);
-                if (lane == l) { gi = ai; gf = af; gg = ag; go = ao; }
-            }
+            const int lsrc = (lane < D ? 4 * lane : 0) * LPV;
+            const float gi = __shfl_sync(0xffffffffu, sv[0], lsrc), gf = __shfl_sync(0xffffffffu, sv[0], lsrc + LPV),
+                        gg = __shfl_sync(0xffffffffu, sv[0], lsrc + 2 * LPV), go = __shfl_sync(0xffffffffu, sv[0], lsrc + 3 * LPV);
             {
                 const int t = tick - lane;                                   // lane l: layer l, position tick - l
                 if (lane < D && t >= 0 && t < len) {
@@ -246,8 +257,10 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
             // ---- publication: the word of tick + 1 into the ring of every CTA (lanes 0..C-1), logits into CTA 0's ----
             const uint32_t sofs = (uint32_t)((tick + 1) % R) * (uint32_t)SLOT * 8u;
             if (lane < C) {
-#pragma unroll
-                for (int l = 0; l < D; ++l) rg_st_remote(dst_h0 + (uint32_t)l * W * 8u + sofs, hn[l], (unsigned)(tick + 1));
+                if (D >= 2)
+                    asm volatile("st.shared::cluster.v4.u32 [%0], {%1, %2, %3, %2};" ::"r"(dst_h0 + sofs), "r"(__float_as_uint(hn[0])), "r"((unsigned)(tick + 1)),
+                                 "r"(__float_as_uint(hn[D > 1 ? 1 : 0])) : "memory");
+                if (D != 2) rg_st_remote(dst_h0 + (D == 3 ? 16u : 0u) + sofs, hn[D - 1], (unsigned)(tick + 1));
             }
             if (pseg == 0) rg_st_remote(dst_p + sofs, accp, (unsigned)(tick + 1));
             // behind the publication (the warp idles until the next barrier anyway): the table row of the next position and the
@@ -271,13 +284,9 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
     } else if (warp == UPC) {
         // =========================== poll warp ===========================
         bool alive = true;
-        constexpr int NPW = D * W / 32;                     // ring words per lane and tick
-        int didx[NPW];
-#pragma unroll
-        for (int j = 0; j < NPW; ++j) {
-            const int i = lane + 32 * j, l = i / W, k = i - l * W;
-            didx[j] = l * W + rg_dense_index(k, WS);
-        }
+        constexpr int NPW = HW / 32;                        // ring words per lane and tick (word i: unit i / DP, layer i % DP)
+        const bool pad = lane % DP >= D;                    // (32 % DP == 0: a lane sees words of ONE layer, or only padding words)
+        const int dofs = (lane % DP) * W + lane / DP;       // word lane + 32 j -> dense[layer][unit]: dofs + j * (32 / DP)
         long long pdbg[3] = {0, 0, 0}, pdbg_t = clock64();
 #define RG_PDBG(i) if (p.debug) { const long long now_ = clock64(); pdbg[i] += now_ - pdbg_t; pdbg_t = now_; }
         for (int tick = 0; tick < nticks; ++tick) {
@@ -293,9 +302,11 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
                     for (int j = 0; j < NPW; ++j) wv[j] = rg_ld_word(cur + lane + 32 * j);
 #pragma unroll
                     for (int j = 0; j < NPW; ++j) all = all && wv[j].y == (unsigned)tick;
-                    if (__all_sync(0xffffffffu, all ? 1 : 0)) {
+                    if (__all_sync(0xffffffffu, (all || pad) ? 1 : 0)) {
+                        if (!pad) {
 #pragma unroll
-                        for (int j = 0; j < NPW; ++j) dn[didx[j]] = __uint_as_float(wv[j].x);
+                            for (int j = 0; j < NPW; ++j) dn[dofs + j * (32 / DP)] = __uint_as_float(wv[j].x);
+                        }
                         break;
                     }
                     if (++n > RG_SPIN || ((n & 0x3FFu) == 0 && *(volatile int *)p.err != 0)) { atomicCAS(p.err, 0, 31); alive = false; }
@@ -330,7 +341,7 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
         for (int tick = D + 1; tick < nticks && alive; ++tick) {
             const int t = tick - D - 1;
             if (t >= len) break;
-            const uint2 *lg = ring + (size_t)(tick % R) * SLOT + D * W;
+            const uint2 *lg = ring + (size_t)(tick % R) * SLOT + HW;
             int tg = 0;
             if (!p.full_rows) {
                 tg = min(max(tg_next, 0), p.V - 1);
@@ -392,7 +403,7 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
 
 namespace {
 template <int WS, int D, int PR, int C> size_t rg_smem_bytes() {
-    return (size_t)RG_RING * (D * 8 * WS + 8 * WS * PR) * 8 + (size_t)2 * D * 8 * WS * 4 + (size_t)(8 * WS / C) * (D + 1) * 16 + 64;
+    return (size_t)RG_RING * ((D == 1 ? 1 : (D + 1) / 2 * 2) * 8 * WS + 8 * WS * PR) * 8 + (size_t)2 * D * 8 * WS * 4 + (size_t)(8 * WS / C) * (D + 1) * 16 + 64;
 }
 template <int WS, int D, int PR, int C> cudaError_t rg_launch(const KlmSeqParams &p, cudaStream_t stream) {
     auto fn = klm_seq_rg<WS, D, PR, C>;
