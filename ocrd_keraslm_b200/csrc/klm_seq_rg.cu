@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
             if (len > 3) x_n2 = __ldg(p.chars + o0 + 3);
         }
 
-        long long dbg[5] = {0, 0, 0, 0, 0}, dbg_t = clock64();
+        long long dbg[5] = {0, 0, 0, 0, 0}, dbg5 = 0, dbg_t = clock64();
 #define RG_DBG(i) if (p.debug) { const long long now_ = clock64(); dbg[i] += now_ - dbg_t; dbg_t = now_; }
         for (int tick = 0; tick < nticks; ++tick) {
             RG_DBG(0)
@@ -194,6 +194,7 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
             float4 h4[D];
 #pragma unroll
             for (int l = 0; l < D; ++l) h4[l] = hv[l * (W / 4) + lane];
+            if (p.debug && __float_as_uint(h4[0].x) != 0x7fc54321u) dbg5 += clock64() - dbg_t;      // (a clock read that cannot precede the first load's data)
             float sv[NVP];                                               // [4 l + gate]
 #pragma unroll
             for (int l = 0; l < D; ++l) {
@@ -274,8 +275,8 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
             RG_DBG(4)
         }
         if (p.debug && lane == 0 && (warp == 0 || warp == UPC - 1) && (rank == 0 || rank == C - 1))
-            printf("klm_seq_rg cta %u warp %d: per tick: prefetch issue %lld, wait for the poll warp %lld, loads + FMAs %lld, shuffles + cells %lld, publication %lld clk\n",
-                   rank, warp, dbg[0] / nticks, dbg[1] / nticks, dbg[2] / nticks, dbg[3] / nticks, dbg[4] / nticks);
+            printf("klm_seq_rg cta %u warp %d: per tick: prefetch issue %lld, wait for the poll warp %lld, loads + FMAs %lld (first load's data after %lld), shuffles + cells %lld, publication %lld clk\n",
+                   rank, warp, dbg[0] / nticks, dbg[1] / nticks, dbg[2] / nticks, dbg5 / nticks, dbg[3] / nticks, dbg[4] / nticks);
         // ---- final state ----
         if (lane < D) {
             float *st = p.state + ((size_t)p.slots_out[0] * D + lane) * 2 * W;
@@ -287,7 +288,7 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
         constexpr int NPW = HW / 32;                        // ring words per lane and tick (word i: unit i / DP, layer i % DP)
         const bool pad = lane % DP >= D;                    // (32 % DP == 0: a lane sees words of ONE layer, or only padding words)
         const int dofs = (lane % DP) * W + lane / DP;       // word lane + 32 j -> dense[layer][unit]: dofs + j * (32 / DP)
-        long long pdbg[3] = {0, 0, 0}, pdbg_t = clock64();
+        long long pdbg[3] = {0, 0, 0}, pfirst = 0, pdbg_t = clock64();
 #define RG_PDBG(i) if (p.debug) { const long long now_ = clock64(); pdbg[i] += now_ - pdbg_t; pdbg_t = now_; }
         for (int tick = 0; tick < nticks; ++tick) {
             const uint2 *cur = ring + (size_t)(tick % R) * SLOT;
@@ -295,6 +296,7 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
             if (alive) {
                 // one pass = all words of this lane loaded side by side; repeated until every one carries this tick's number
                 unsigned n = 0;
+                bool seen = false;
                 for (;;) {
                     uint2 wv[NPW];
                     bool all = true;
@@ -302,6 +304,12 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
                     for (int j = 0; j < NPW; ++j) wv[j] = rg_ld_word(cur + lane + 32 * j);
 #pragma unroll
                     for (int j = 0; j < NPW; ++j) all = all && wv[j].y == (unsigned)tick;
+                    if (p.debug && !seen) {
+                        bool anyc = false;
+#pragma unroll
+                        for (int j = 0; j < NPW; ++j) anyc = anyc || (wv[j].y == (unsigned)tick && !pad);
+                        if (__any_sync(0xffffffffu, anyc ? 1 : 0)) { seen = true; pfirst += clock64() - pdbg_t; }
+                    }
                     if (__all_sync(0xffffffffu, (all || pad) ? 1 : 0)) {
                         if (!pad) {
 #pragma unroll
@@ -330,8 +338,8 @@ __global__ void __launch_bounds__(32 * (8 * WS / C + 2), 1) klm_seq_rg(const __g
             RG_PDBG(2)
         }
         if (p.debug && lane == 0 && (rank == 0 || rank == C - 1))
-            printf("klm_seq_rg cta %u poll warp: per tick: polling + dense copy %lld, wait for the log-sum-exp warp %lld, barrier %lld clk\n", rank,
-                   pdbg[0] / nticks, pdbg[1] / nticks, pdbg[2] / nticks);
+            printf("klm_seq_rg cta %u poll warp: per tick: polling + dense copy %lld (first word of the tick after %lld), wait for the log-sum-exp warp %lld, barrier %lld clk\n", rank,
+                   pdbg[0] / nticks, pfirst / nticks, pdbg[1] / nticks, pdbg[2] / nticks);
     } else if (rank == 0) {
         // =========================== log-sum-exp warp (CTA 0): position tick - D - 1, whose logits carry this tick's number ===========================
         int tg_next = 0;
