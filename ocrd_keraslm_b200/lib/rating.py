@@ -420,13 +420,15 @@ class Rater(object):
             raise ValueError('%d texts but %d contexts' % (n, len(contexts)))
         default = None
         try:
-            rows = []
-            for c in contexts:
-                if not c:
-                    if default is None:
-                        default = [int(x) for x in self.underspecify_contexts()]
-                    c = default
-                rows.append(c)
+            rows = contexts
+            if not all(contexts):                   # None or [] for a text: every variable unknown (:181-185)
+                rows = []
+                for c in contexts:
+                    if not c:
+                        if default is None:
+                            default = [int(x) for x in self.underspecify_contexts()]
+                        c = default
+                    rows.append(c)
             arr = np.asarray(rows, dtype=np.int64)
             ok = arr.shape == (n, len(self.context_shapes))
             if ok and n:
@@ -519,8 +521,9 @@ class Rater(object):
         assert self.incremental is False
         n = len(texts)
         ctx_rows = self._context_rows(contexts, n)
-        norm = [unicodedata.normalize('NFC', t) for t in texts]
-        nchar = np.fromiter((len(t) for t in norm), dtype=np.int64, count=n)
+        norm = [t if t.isascii() else unicodedata.normalize('NFC', t) for t in texts]
+        nchar = np.fromiter(map(len, norm), dtype=np.int64, count=n)
+        report = self.logger.isEnabledFor(logging.ERROR)    # unmapped characters are reported like the reference does (:1116)
         lens = np.maximum(nchar - 1, 0)
         order = np.argsort(-lens, kind='stable')            # longest first: batches of similar length
         total = int(lens.sum())
@@ -534,14 +537,15 @@ class Rater(object):
         if gather:
             # text i occupies [cstart[i], cstart[i+1]) of idx_all / out_all
             idx_all, known_all = self._indices(''.join(norm))
-            if not known_all.all():
-                for g in np.flatnonzero(~known_all):
-                    i = int(np.searchsorted(cstart, g, side='right')) - 1
-                    self.logger.error('unmapped character "%s" at input position %d', norm[i][int(g - cstart[i])],
-                                      int(g - cstart[i]))
+            if report and not known_all.all():
+                bad = np.flatnonzero(~known_all)
+                own = np.searchsorted(cstart, bad, side='right') - 1
+                for i, pos in zip(own.tolist(), (bad - cstart[own]).tolist()):
+                    self.logger.error('unmapped character "%s" at input position %d', norm[i][pos], pos)
             out_all = np.empty(int(cstart[-1]), dtype=np.float32)
             out_all[cstart[:-1][nchar > 0]] = 0.0 if return_logp else 1.0
-            out = [out_all[cstart[i]:cstart[i + 1]] for i in range(n)]
+            edges = cstart.tolist()
+            out = [out_all[a:b] for a, b in zip(edges, edges[1:])]
         else:
             out = [np.empty(len(t), dtype=np.float32) for t in norm]
             for o in out:
@@ -601,8 +605,9 @@ class Rater(object):
                     base = lo + 1
                 else:
                     base = lo
-                for t in np.flatnonzero(~known):
-                    self.logger.error('unmapped character "%s" at input position %d', norm[i][base + int(t)], base + int(t))
+                if report:
+                    for t in np.flatnonzero(~known).tolist():
+                        self.logger.error('unmapped character "%s" at input position %d', norm[i][base + t], base + t)
                 chars[offsets[j]:offsets[j + 1]] = idx[:-1]
                 targets[offsets[j]:offsets[j + 1]] = idx[1:]
             return slots, offsets, ctx_rows, logp, None
@@ -652,8 +657,7 @@ class Rater(object):
                         except Exception:           # pylint: disable=broad-except
                             pass
         finally:
-            for sl in slots:
-                self._pool.release(sl)
+            self._pool.release_many(slots)
         return out
 
     GATHER_MAX_MEAN_LENGTH = 4096         # rate_many: one lookup + index arithmetic below this mean text length

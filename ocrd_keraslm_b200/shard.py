@@ -95,7 +95,8 @@ def rate_sharded(rater, texts, contexts=None, gather=True, group=None):
         if r == rank or not p:
             continue
         # views into the gathered row, cut at the cumulative lengths of that rank's units (no copy per text)
-        pieces = np.split(everything[r, :sizes[r]], np.cumsum(lens[p])[:-1])
-        for i, piece in zip(p, pieces):
-            out[i] = piece
+        row = everything[r]
+        edges = [0] + np.cumsum(lens[p]).tolist()
+        for i, a, b in zip(p, edges, edges[1:]):
+            out[i] = row[a:b]
     return out
