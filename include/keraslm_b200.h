@@ -113,6 +113,13 @@ int klm_state_l2_distance(klm_model *m, const int32_t *a, const int32_t *b, int3
 int klm_state_l2_distance_noalloc(klm_model *m, const int32_t *a, const int32_t *b, int32_t n,
                                   int32_t n_arrays, float *out);
 
+/* Host-only helper of the sharded form (the reference has no multi-GPU code): longest-processing-time-first
+ * assignment of n independent units (documents, pages, lines) to `world` ranks.  Units are taken by decreasing length
+ * (ties: lower index first) and given to the least loaded rank (ties: lower rank); a unit costs its length + 1.
+ * rank_of[i] receives the rank of unit i.  Deterministic, so every rank computes the same partition without
+ * communicating (ocrd_keraslm_b200/shard.py: partition).  No device work, no model handle. */
+int klm_lpt_partition(const int64_t *lengths, int64_t n, int32_t world, int32_t *rank_of);
+
 /*
  * Teacher-forced rating of n_streams independent character streams in ONE launch.
  * Replaces model.predict_generator over the windows of Rater._gen_data (rating.py:516,

@@ -136,6 +136,7 @@ SYMBOLS = [
     ('klm_step', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _P, _P, ctypes.c_int]),
     ('klm_step_topk', ctypes.c_int, [_P, _I, _P, _P, _P, _P, _I, _P, _P]),
     ('klm_get_info', ctypes.c_int, [_P, ctypes.POINTER(KlmInfo)]),
+    ('klm_lpt_partition', ctypes.c_int, [_P, ctypes.c_int64, _I, _P]),
     ('klm_measure_fma_peak', ctypes.c_int, [ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
     ('klm_selftest_umma', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
     ('klm_selftest_umma2', ctypes.c_int, [ctypes.c_int, _I, _I, _P, _P, _P]),
@@ -191,6 +192,17 @@ def operand_image(mat):
     rows, K = mat.shape
     assert K % 8 == 0
     return np.ascontiguousarray(mat.astype(np.float16).reshape(rows, K // 8, 8).transpose(1, 0, 2)).view(np.uint16)
+
+
+def lpt_partition(lengths, world):
+    """rank of every unit under longest-processing-time-first assignment (klm_lpt_partition; host only)."""
+    lib = load()
+    lengths = np.ascontiguousarray(lengths, dtype=np.int64)
+    rank_of = np.empty(len(lengths), dtype=np.int32)
+    rc = lib.klm_lpt_partition(_ptr(lengths), len(lengths), world, _ptr(rank_of))
+    if rc != 0:
+        raise NativeError('libkeraslm_b200 error %d: %s' % (rc, lib.klm_last_error().decode('utf-8', 'replace')))
+    return rank_of
 
 
 def measure_fma_peak(device=0):

@@ -2076,6 +2076,25 @@ __global__ void klm_fma_peak_kernel(float *out, int iters) {
     const float r = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
     if (r == 123.456f) out[0] = r;                           // (never true: keeps the chains alive)
 }
+extern "C" int klm_lpt_partition(const int64_t *lengths, int64_t n, int32_t world, int32_t *rank_of) {
+    if (n < 0 || world < 1 || (n > 0 && (!lengths || !rank_of))) return fail(KLM_EINVAL, "klm_lpt_partition: bad argument");
+    std::vector<int64_t> order((size_t)n);
+    for (int64_t i = 0; i < n; ++i) order[(size_t)i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int64_t a, int64_t b) { return lengths[a] > lengths[b]; });
+    typedef std::pair<int64_t, int32_t> Load;                              // (load, rank): least loaded first, ties by rank
+    std::priority_queue<Load, std::vector<Load>, std::greater<Load>> heap;
+    for (int32_t r = 0; r < world; ++r) heap.push(Load(0, r));
+    for (int64_t k = 0; k < n; ++k) {
+        const int64_t i = order[(size_t)k];
+        Load top = heap.top();
+        heap.pop();
+        rank_of[i] = top.second;
+        top.first += lengths[i] + 1;
+        heap.push(top);
+    }
+    return KLM_OK;
+}
+
 extern "C" int klm_measure_fma_peak(int device, double *tflops) {
     if (!tflops) return fail(KLM_EINVAL, "klm_measure_fma_peak: NULL argument");
     CK(cudaSetDevice(device));

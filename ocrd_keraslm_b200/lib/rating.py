@@ -167,6 +167,11 @@ class _StatePool(object):
         self.free.extend(slots)
 
 
+class _Scores(list):
+    """The list `rate_many` returns; `flat` (if not None) is the concatenation of its arrays, which are views of it."""
+    flat = None
+
+
 class _DeviceModelView(object):
     """What sits in ``Rater.model``: the handful of Keras-model methods callers may touch."""
 
@@ -545,7 +550,8 @@ class Rater(object):
             out_all = np.empty(int(cstart[-1]), dtype=np.float32)
             out_all[cstart[:-1][nchar > 0]] = 0.0 if return_logp else 1.0
             edges = cstart.tolist()
-            out = [out_all[a:b] for a, b in zip(edges, edges[1:])]
+            out = _Scores(out_all[a:b] for a, b in zip(edges, edges[1:]))
+            out.flat = out_all                      # the same scores as ONE array in input order (rate_sharded sends it as is)
         else:
             out = [np.empty(len(t), dtype=np.float32) for t in norm]
             for o in out:

@@ -258,3 +258,14 @@ def test_golden_fixtures_are_reproduced_by_the_reference(tmp_path):
     assert sorted(a.files) == sorted(b.files)
     for k in a.files:
         np.testing.assert_array_equal(a[k], b[k], err_msg=k)
+
+
+def test_native_partition_follows_the_python_rule():
+    """shard.partition hands large inputs to klm_lpt_partition (host helper of the library): the same lists as the
+    Python statement of the rule, incl. ties, empty units and more ranks than units."""
+    rng = np.random.default_rng(11)
+    for n, world in ((shard.NATIVE_PARTITION_MIN, 2), (3000, 8), (10000, 3), (777, 1), (600, 16)):
+        lengths = rng.integers(0, 121, n)
+        assert shard.partition(lengths, world) == shard._partition_py(np.asarray(lengths, dtype=np.int64), world)
+    few = np.concatenate([np.full(600, 7), np.zeros(5, dtype=np.int64)])
+    assert shard.partition(few, 700) == shard._partition_py(few.astype(np.int64), 700)
