@@ -604,6 +604,8 @@ class Rater(object):
             for j, i in enumerate(order):
                 lo, hi = int(bounds[k][j]), int(bounds[k + 1][j])
                 if hi == lo:
+                    if report and k == 0 and len(norm[i]) == 1 and not self._indices(norm[i])[1][0]:
+                        self.logger.error('unmapped character "%s" at input position %d', norm[i], 0)
                     continue
                 idx, known = self._indices(norm[i][lo:hi + 1])
                 if k > 0:

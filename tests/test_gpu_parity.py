@@ -312,6 +312,36 @@ def test_rate_many_degenerate_inputs():
         np.testing.assert_array_equal(a, b)
 
 
+def test_rate_many_reports_unmapped_characters_like_the_reference(caplog):
+    """Unmapped characters are rated as index 0 and reported one by one with their position in the text (reference
+    :1116-1118) -- from both host paths of rate_many (one lookup over all texts / per-text slices), and not at all
+    when the logger does not take errors; the list of many short texts carries its scores as ONE array, too."""
+    import logging
+    wd, maparr, _ = util.small_model()
+    r = product(wd, maparr, 8)
+    r.logger = logging.getLogger('test_unmapped')
+    texts = ['ab\u2603cd', 'xyz', '', '\u2603', 'q\u2603\u2603']
+    want = [('\u2603', 2), ('\u2603', 0), ('\u2603', 1), ('\u2603', 2)]
+    for limit in (4096, 0):                                 # gather path, per-text path
+        r.GATHER_MAX_MEAN_LENGTH = limit
+        caplog.clear()
+        with caplog.at_level(logging.ERROR, logger='test_unmapped'):
+            got = r.rate_many(texts)
+        seen = [(rec.args[0], rec.args[1]) for rec in caplog.records if 'unmapped character' in rec.msg]
+        assert sorted(seen) == sorted(want), (limit, seen)
+        flat = getattr(got, 'flat', None)
+        if limit:
+            assert flat is not None
+            np.testing.assert_array_equal(flat, np.concatenate(got))
+        caplog.clear()
+        r.logger.setLevel(logging.CRITICAL)
+        again = r.rate_many(texts)
+        r.logger.setLevel(logging.NOTSET)
+        assert not [rec for rec in caplog.records if 'unmapped character' in rec.msg]
+        for a, b in zip(got, again):
+            np.testing.assert_array_equal(a, b)
+
+
 def test_states_after_rate_match_oracle():
     wd = synth.weights(3, width=128, depth=3, voc_size=256, style='trained')
     maparr = synth.vocabulary()
